@@ -1,0 +1,359 @@
+// KV-cache multi-head attention for decode.
+//
+// (1) The reference's three stages (scores / softmax / weighted V sum,
+//     src/thaDNN/thaDNN_mha.cpp) as three generic kernels, for both KV layouts
+//     (v1 batch-major [B][L][S][kvd], v2 time-major [t][B][kvd]).  They keep the
+//     reference entry points alive and serve head sizes the fused kernel rejects.
+// (2) One fused kernel: QK^T, online softmax and PV in a single pass over the KV
+//     rows, split over the time axis (flash-decoding) so a single long sequence
+//     still fills the GPU; the last CTA of a (slot, segment) merges the splits.
+//     K/V rows are read once, fully coalesced (a warp reads whole contiguous row
+//     segments with 128-bit loads); scores never touch HBM.
+#include "common.cuh"
+#include "workspace.h"
+
+namespace tha {
+
+// ------------------------------------------------------------------ three stages ----
+// att[b,h,t] = q[b,h,:] . K[b,t,h/kv_mul,:] / sqrt(hs)   for t <= pos[b]
+__global__ void mha_scores_kernel(const int* __restrict__ pos, const float* __restrict__ q, float* __restrict__ att,
+                                  const float* __restrict__ kbase, long long k_batch_stride, long long k_t_stride,
+                                  int head_size, int att_row, int n_heads, int dim, int kv_mul) {
+  const int h = blockIdx.x, b = blockIdx.y;
+  const int pb = pos[b];
+  if (pb < 0) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const float* qh = q + (size_t)b * dim + h * head_size;
+  const float* kh = kbase + (size_t)b * k_batch_stride + (h / kv_mul) * head_size;
+  float* a = att + ((size_t)b * n_heads + h) * att_row;
+  const float inv = sqrtf((float)head_size);
+  for (int t = warp; t <= pb; t += nw) {
+    const float* k = kh + (size_t)t * k_t_stride;
+    float s = 0.0f;
+    for (int i = lane; i < head_size; i += 32) s = fmaf(qh[i], k[i], s);
+    s = warp_sum(s);
+    if (lane == 0) a[t] = s / inv;
+  }
+}
+
+// softmax over t in [0, pos[b]] in place (thaDNN_mha.cpp:306-352)
+__global__ void mha_softmax_kernel(const int* __restrict__ pos, float* __restrict__ att, int att_row, int n_heads) {
+  __shared__ float red[33];
+  const int h = blockIdx.x, b = blockIdx.y;
+  const int pb = pos[b];
+  if (pb < 0) return;
+  float* x = att + ((size_t)b * n_heads + h) * att_row;
+  const int n = pb + 1;
+  float m = -INFINITY;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) m = fmaxf(m, x[i]);
+  m = block_max(m, red);
+  float s = 0.0f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) { float e = expf(x[i] - m); x[i] = e; s += e; }
+  s = block_sum(s, red);
+  for (int i = threadIdx.x; i < n; i += blockDim.x) x[i] /= s;
+}
+
+// xb[b,h,i] = sum_t att[b,h,t] * V[b,t,h/kv_mul,i]   (thaDNN_mha.cpp:376-406)
+__global__ void mha_weighted_kernel(const int* __restrict__ pos, float* __restrict__ xb, const float* __restrict__ att,
+                                    const float* __restrict__ vbase, long long v_batch_stride, long long v_t_stride,
+                                    int head_size, int att_row, int n_heads, int dim, int kv_mul) {
+  extern __shared__ float part[];  // [8][head_size]
+  const int h = blockIdx.x, b = blockIdx.y;
+  const int pb = pos[b];
+  if (pb < 0) return;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5, ny = blockDim.x >> 5;
+  const float* a = att + ((size_t)b * n_heads + h) * att_row;
+  const float* vh = vbase + (size_t)b * v_batch_stride + (h / kv_mul) * head_size;
+  for (int i = tx; i < head_size; i += 32) {
+    float s = 0.0f;
+    for (int t = ty; t <= pb; t += ny) s = fmaf(a[t], vh[(size_t)t * v_t_stride + i], s);
+    part[ty * head_size + i] = s;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < head_size; i += blockDim.x) {
+    float s = 0.0f;
+    for (int y = 0; y < ny; y++) s += part[y * head_size + i];
+    xb[(size_t)b * dim + h * head_size + i] = s;
+  }
+}
+
+// ------------------------------------------------------------------ fused ----------
+struct AttnP {
+  const int* pos; const float* q; float* out;
+  const float* kc; const float* vc;         // already offset by loff
+  long long kv_batch_stride; int kv_dim, head_size, kv_mul, dim;
+  int nseg, nsplit;
+  float4* part_acc; float2* part_ml; int* counters;
+};
+
+// J = float4 slots per lane; a CTA covers a segment of 128*J query floats (whole heads).
+template <int J>
+__global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
+  constexpr int F = 32 * J;  // slots per segment
+  extern __shared__ float4 sm_acc[];                 // [8][F]
+  float2* sm_ml = reinterpret_cast<float2*>(sm_acc + 8 * F);  // [8][F]
+  __shared__ int is_last;
+
+  pdl_wait();
+  pdl_trigger();
+  const int b = blockIdx.x, seg = blockIdx.y, split = blockIdx.z;
+  const int pb = p.pos[b];
+  if (pb < 0) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int hs = p.head_size, LH = hs >> 2;  // lanes per head
+  const float sqrt_hs = sqrtf((float)hs);
+
+  const int n = pb + 1;
+  const int chunk = (n + p.nsplit - 1) / p.nsplit;
+  const int t0 = split * chunk;
+  const int t1 = (t0 + chunk < n) ? (t0 + chunk) : n;
+
+  float4 qv[J];
+  int koff[J];
+#pragma unroll
+  for (int j = 0; j < J; j++) {
+    const int qo = seg * (128 * J) + 4 * (lane + 32 * j);
+    qv[j] = *reinterpret_cast<const float4*>(p.q + (size_t)b * p.dim + qo);
+    koff[j] = ((qo / hs) / p.kv_mul) * hs + (qo % hs);
+  }
+  float m[J], l[J];
+  float4 acc[J];
+#pragma unroll
+  for (int j = 0; j < J; j++) { m[j] = -INFINITY; l[j] = 0.0f; acc[j] = make_float4(0.f, 0.f, 0.f, 0.f); }
+
+  const float* kb = p.kc + (size_t)b * p.kv_batch_stride;
+  const float* vb = p.vc + (size_t)b * p.kv_batch_stride;
+  for (int t = t0 + warp; t < t1; t += 16) {
+    const bool two = (t + 8) < t1;
+    const float* ka = kb + (size_t)t * p.kv_dim;
+    const float* va = vb + (size_t)t * p.kv_dim;
+    const float* kb2 = two ? ka + (size_t)8 * p.kv_dim : ka;
+    const float* vb2 = two ? va + (size_t)8 * p.kv_dim : va;
+    float4 k_a[J], v_a[J], k_b[J], v_b[J];
+#pragma unroll
+    for (int j = 0; j < J; j++) {
+      k_a[j] = ldg_stream(reinterpret_cast<const float4*>(ka + koff[j]));
+      k_b[j] = ldg_stream(reinterpret_cast<const float4*>(kb2 + koff[j]));
+    }
+#pragma unroll
+    for (int j = 0; j < J; j++) {
+      v_a[j] = ldg_stream(reinterpret_cast<const float4*>(va + koff[j]));
+      v_b[j] = ldg_stream(reinterpret_cast<const float4*>(vb2 + koff[j]));
+    }
+#pragma unroll
+    for (int j = 0; j < J; j++) {
+      float sa = dot4(qv[j], k_a[j], 0.0f);
+      float sb = dot4(qv[j], k_b[j], 0.0f);
+      for (int o = LH >> 1; o > 0; o >>= 1) {
+        sa += __shfl_xor_sync(THA_FULL_MASK, sa, o);
+        sb += __shfl_xor_sync(THA_FULL_MASK, sb, o);
+      }
+      sa /= sqrt_hs;
+      sb = two ? sb / sqrt_hs : -INFINITY;
+      const float mn = fmaxf(m[j], fmaxf(sa, sb));
+      const float corr = expf(m[j] - mn);   // exp(-inf) = 0 on the first step
+      const float pa = expf(sa - mn);
+      const float pb2 = two ? expf(sb - mn) : 0.0f;
+      l[j] = l[j] * corr + pa + pb2;
+      acc[j].x = acc[j].x * corr + pa * v_a[j].x + pb2 * v_b[j].x;
+      acc[j].y = acc[j].y * corr + pa * v_a[j].y + pb2 * v_b[j].y;
+      acc[j].z = acc[j].z * corr + pa * v_a[j].z + pb2 * v_b[j].z;
+      acc[j].w = acc[j].w * corr + pa * v_a[j].w + pb2 * v_b[j].w;
+      m[j] = mn;
+    }
+  }
+
+  // ---- merge the 8 warps of this CTA ----
+#pragma unroll
+  for (int j = 0; j < J; j++) {
+    const int f = lane + 32 * j;
+    sm_acc[warp * F + f] = acc[j];
+    sm_ml[warp * F + f] = make_float2(m[j], l[j]);
+  }
+  __syncthreads();
+  const int f = threadIdx.x;
+  float M = -INFINITY, L = 0.0f;
+  float4 A = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (f < F) {
+#pragma unroll
+    for (int w = 0; w < 8; w++) M = fmaxf(M, sm_ml[w * F + f].x);
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+      const float2 ml = sm_ml[w * F + f];
+      const float e = (ml.x == -INFINITY) ? 0.0f : expf(ml.x - M);
+      const float4 a = sm_acc[w * F + f];
+      L += ml.y * e;
+      A.x += a.x * e; A.y += a.y * e; A.z += a.z * e; A.w += a.w * e;
+    }
+  }
+  float* outp = p.out + (size_t)b * p.dim + seg * (128 * J) + 4 * f;
+  if (p.nsplit == 1) {
+    if (f < F) *reinterpret_cast<float4*>(outp) = make_float4(A.x / L, A.y / L, A.z / L, A.w / L);
+    return;
+  }
+
+  // ---- publish this split's partial; the last CTA of (slot, segment) merges all ----
+  const size_t pbase = ((size_t)(b * p.nseg + seg) * p.nsplit) * F;
+  if (f < F) {
+    p.part_acc[pbase + (size_t)split * F + f] = A;
+    p.part_ml[pbase + (size_t)split * F + f] = make_float2(M, L);
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int old = atomicAdd(&p.counters[b * p.nseg + seg], 1);
+    is_last = (old == p.nsplit - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  if (f < F) {
+    float GM = -INFINITY;
+    for (int s = 0; s < p.nsplit; s++) GM = fmaxf(GM, __ldcg(&p.part_ml[pbase + (size_t)s * F + f]).x);
+    float GL = 0.0f;
+    float4 GA = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int s = 0; s < p.nsplit; s++) {   // fixed order: result independent of arrival order
+      const float2 ml = __ldcg(&p.part_ml[pbase + (size_t)s * F + f]);
+      const float e = (ml.x == -INFINITY) ? 0.0f : expf(ml.x - GM);
+      const float4 a = __ldcg(&p.part_acc[pbase + (size_t)s * F + f]);
+      GL += ml.y * e;
+      GA.x += a.x * e; GA.y += a.y * e; GA.z += a.z * e; GA.w += a.w * e;
+    }
+    *reinterpret_cast<float4*>(outp) = make_float4(GA.x / GL, GA.y / GL, GA.z / GL, GA.w / GL);
+  }
+  if (threadIdx.x == 0) p.counters[b * p.nseg + seg] = 0;  // self-reset for the next launch
+}
+
+}  // namespace tha
+
+// ------------------------------------------------------------------ launchers -------
+namespace tha {
+
+// Segment choice for the fused kernel: G whole heads with G*hs = 128*J floats, J in 1..8.
+// Returns J (0 = shape not supported by the fused kernel).
+static int fused_J(int n_heads, int head_size, int dim) {
+  if (head_size < 4 || head_size > 128 || (head_size & (head_size - 1))) return 0;  // power of two, <= 128
+  for (int J = 8; J >= 1; J--) {
+    const int seg = 128 * J;
+    if (seg % head_size == 0 && dim % seg == 0) return J;
+  }
+  return 0;
+}
+
+bool attn_fused_supported(int n_heads, int head_size, int dim, int kv_dim) {
+  return fused_J(n_heads, head_size, dim) != 0 && (kv_dim % 4 == 0);
+}
+
+int attn_fused_nsplit(int B, int nseg, int seq_len) {
+  int target = 296 / (B * nseg);   // about two CTAs per SM
+  int cap = seq_len / 32 > 0 ? seq_len / 32 : 1;
+  if (target > cap) target = cap;
+  if (target > 32) target = 32;
+  if (target < 1) target = 1;
+  return target;
+}
+
+// kc / vc are the caches already offset to the layer (base + loff).
+int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
+                      const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
+                      int head_size, int seq_len, bool pdl) {
+  const int dim = n_heads * head_size, kv_dim = n_kv_heads * head_size;
+  const int J = fused_J(n_heads, head_size, dim);
+  if (!J || kv_dim % 4) return THA_STATUS_NOT_SUPPORTED;
+  AttnP p;
+  p.pos = pos_d; p.q = q; p.out = out; p.kc = kc; p.vc = vc;
+  p.kv_batch_stride = kv_batch_stride; p.kv_dim = kv_dim; p.head_size = head_size;
+  p.kv_mul = n_heads / n_kv_heads; p.dim = dim;
+  p.nseg = dim / (128 * J);
+  p.nsplit = attn_fused_nsplit(B, p.nseg, seq_len);
+  const int F = 32 * J;
+  if (p.nsplit > 1) {
+    int st = ws_ensure_attn(ws, (size_t)B * p.nseg * p.nsplit * F, B * p.nseg);
+    if (st) return st;
+  }
+  p.part_acc = ws->part_acc; p.part_ml = ws->part_ml; p.counters = ws->counters;
+  dim3 grid(B, p.nseg, p.nsplit), block(256);
+  const size_t smem = (size_t)8 * F * (sizeof(float4) + sizeof(float2));
+  void (*k)(const AttnP) = nullptr;
+  switch (J) {
+    case 1: k = attn_fused_kernel<1>; break; case 2: k = attn_fused_kernel<2>; break;
+    case 3: k = attn_fused_kernel<3>; break; case 4: k = attn_fused_kernel<4>; break;
+    case 5: k = attn_fused_kernel<5>; break; case 6: k = attn_fused_kernel<6>; break;
+    case 7: k = attn_fused_kernel<7>; break; case 8: k = attn_fused_kernel<8>; break;
+  }
+  if (smem > 40 * 1024) THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  THA_CUDA_OK(launch(k, grid, block, smem, stream, pdl, p));
+  return THA_STATUS_SUCCESS;
+}
+
+}  // namespace tha
+
+using namespace tha;
+
+extern "C" int tha_mha_scores_v1_f32(void* stream, int n_batches, const int* pos_d, int n_heads, int n_layers,
+                                     const float* q, float* att, const float* key_cache, int head_size,
+                                     int seq_len, int loff, int kv_dim, int dim, int kv_mul) {
+  if (n_batches <= 0 || !pos_d || !q || !att || !key_cache) return THA_STATUS_INVALID_ARG;
+  mha_scores_kernel<<<dim3(n_heads, n_batches), 256, 0, (cudaStream_t)stream>>>(
+      pos_d, q, att, key_cache + loff, (long long)n_layers * seq_len * kv_dim, kv_dim, head_size, seq_len,
+      n_heads, dim, kv_mul);
+  count_launch();
+  THA_LAUNCH_OK();
+  return THA_STATUS_SUCCESS;
+}
+
+extern "C" int tha_mha_softmax_f32(void* stream, int n_batches, float* att, const int* pos_d, int seq_len, int n_heads) {
+  if (n_batches <= 0 || !pos_d || !att) return THA_STATUS_INVALID_ARG;
+  mha_softmax_kernel<<<dim3(n_heads, n_batches), 256, 0, (cudaStream_t)stream>>>(pos_d, att, seq_len, n_heads);
+  count_launch();
+  THA_LAUNCH_OK();
+  return THA_STATUS_SUCCESS;
+}
+
+extern "C" int tha_mha_weighted_v1_f32(void* stream, int n_batches, const int* pos_d, int n_heads, float* xb,
+                                       const float* att, const float* value_cache, int head_size, int seq_len,
+                                       int loff, int kv_dim, int kv_mul, int dim, int n_layers) {
+  if (n_batches <= 0 || !pos_d || !xb || !att || !value_cache) return THA_STATUS_INVALID_ARG;
+  mha_weighted_kernel<<<dim3(n_heads, n_batches), 256, 8 * head_size * sizeof(float), (cudaStream_t)stream>>>(
+      pos_d, xb, att, value_cache + loff, (long long)n_layers * seq_len * kv_dim, kv_dim, head_size, seq_len,
+      n_heads, dim, kv_mul);
+  count_launch();
+  THA_LAUNCH_OK();
+  return THA_STATUS_SUCCESS;
+}
+
+extern "C" int tha_mha_scores_v2_f32(void* stream, int n_batches, const int* pos_d, int n_heads, const float* q,
+                                     float* att, const float* key_cache, int head_size, int n_words, int kv_dim,
+                                     int dim, int kv_mul) {
+  if (n_batches <= 0 || !pos_d || !q || !att || !key_cache) return THA_STATUS_INVALID_ARG;
+  // time-major: row of (t, b) at t*B*kv_dim + b*kv_dim  (thaDNN_mha.cpp:78)
+  mha_scores_kernel<<<dim3(n_heads, n_batches), 256, 0, (cudaStream_t)stream>>>(
+      pos_d, q, att, key_cache, (long long)kv_dim, (long long)n_batches * kv_dim, head_size, n_words, n_heads,
+      dim, kv_mul);
+  count_launch();
+  THA_LAUNCH_OK();
+  return THA_STATUS_SUCCESS;
+}
+
+extern "C" int tha_mha_weighted_v2_f32(void* stream, int n_batches, const int* pos_d, int n_heads, float* xb,
+                                       const float* att, const float* value_cache, int head_size, int n_words,
+                                       int kv_dim, int kv_mul, int dim) {
+  if (n_batches <= 0 || !pos_d || !xb || !att || !value_cache) return THA_STATUS_INVALID_ARG;
+  mha_weighted_kernel<<<dim3(n_heads, n_batches), 256, 8 * head_size * sizeof(float), (cudaStream_t)stream>>>(
+      pos_d, xb, att, value_cache, (long long)kv_dim, (long long)n_batches * kv_dim, head_size, n_words, n_heads,
+      dim, kv_mul);
+  count_launch();
+  THA_LAUNCH_OK();
+  return THA_STATUS_SUCCESS;
+}
+
+extern "C" int tha_mha_fused_v1_f32(void* stream, int n_batches, const int* pos_d, int n_heads, int n_kv_heads,
+                                    int n_layers, const float* q, float* xb, const float* key_cache,
+                                    const float* value_cache, int head_size, int seq_len, int loff) {
+  if (n_batches <= 0 || !pos_d || !q || !xb || !key_cache || !value_cache || n_kv_heads <= 0) return THA_STATUS_INVALID_ARG;
+  Workspace* ws = workspace();
+  if (!ws) return THA_STATUS_EXECUTION_FAILED;
+  const int kv_dim = n_kv_heads * head_size;
+  return attn_fused_launch((cudaStream_t)stream, ws, n_batches, pos_d, n_heads, n_kv_heads, q, xb, key_cache + loff,
+                           value_cache + loff, (long long)n_layers * seq_len * kv_dim, head_size, seq_len, false);
+}

@@ -1,0 +1,342 @@
+// The batched decode step (thaDNN_s_forward_batch, src/thaDNN.cpp:13-81) as
+// 5 fused kernels per layer + embedding + classifier, replayed from a CUDA graph:
+//
+//   embed                       x[b] = tok_emb[token[b]]
+//   per layer l:
+//     gemv<QKV>     rmsnorm(x, rms_att[l]) -> wq|wk|wv -> RoPE -> q, K-cache[pos], V-cache[pos]
+//     attn_fused    QK^T / online softmax / PV over the cache rows 0..pos           -> xb
+//     gemv<RESID>   x += wo . xb
+//     gemv<SWIGLU>  rmsnorm(x, rms_ffn[l]) -> silu(w1 . xb) * (w3 . xb)             -> hb
+//     gemv<RESID>   x += w2 . hb
+//   gemv<PLAIN>    rmsnorm(x, rms_final) -> wcls                                   -> logits
+//   [argmax]       greedy next token on the device
+//
+// versus the reference's L*(12+4B)+2 launches, B blocking D2D copies, a per-step
+// hipMalloc/hipFree and a device-wide sync.  Every kernel carries the programmatic
+// dependent-launch attribute: its weight prefetch overlaps its predecessor's tail.
+#include "common.cuh"
+#include "gemv.cuh"
+#include "workspace.h"
+
+namespace tha {
+
+int embed_launch(cudaStream_t st, int B, float* x, const float* table, const int* token, const int* pos, int dim, bool pdl);
+int argmax_launch(cudaStream_t st, int B, const float* logits, int vocab, int* next, bool pdl);
+bool attn_fused_supported(int n_heads, int head_size, int dim, int kv_dim);
+int attn_fused_nsplit(int B, int nseg, int seq_len);
+int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
+                      const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
+                      int head_size, int seq_len, bool pdl);
+int launches_reset();
+int launches_get();
+
+static thread_local int g_last_step_launches = 0;
+
+struct StepArgs {
+  int B; tha_config_t cfg; tha_weights_f32_t w; tha_state_t s;
+  const int* token_d; const int* pos_d; float* logits_d; int* next_d; int pdl;
+};
+
+static unsigned long long fnv1a(const void* data, size_t n, unsigned long long h = 1469598103934665603ull) {
+  const unsigned char* p = (const unsigned char*)data;
+  for (size_t i = 0; i < n; i++) { h ^= p[i]; h *= 1099511628211ull; }
+  return h;
+}
+
+#define THA_TRY(expr) do { int _st = (expr); if (_st != THA_STATUS_SUCCESS) return _st; } while (0)
+
+// Issue the step directly, or (default) capture it once per distinct argument set into a
+// CUDA graph and replay it.  `key`/`key_len`: every value the launches depend on.
+template <typename IssueFn>
+static int run_step(cudaStream_t st, Workspace* ws, const void* key_data, size_t key_len, IssueFn issue) {
+  launches_reset();
+  const bool use_graph = graph_enabled() && st != nullptr && st != cudaStreamLegacy;
+  if (!use_graph) {
+    int rc2 = issue();
+    g_last_step_launches = launches_get();
+    return rc2;
+  }
+  const unsigned long long key = fnv1a(key_data, key_len);
+  auto it = ws->graphs.find(key);
+  if (it == ws->graphs.end()) {
+    cudaGraph_t graph = nullptr;
+    THA_CUDA_OK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    int rc2 = issue();
+    cudaError_t e = cudaStreamEndCapture(st, &graph);
+    if (rc2 != THA_STATUS_SUCCESS) { if (graph) cudaGraphDestroy(graph); return rc2; }
+    if (e != cudaSuccess) { set_last_error("cudaStreamEndCapture", e); return THA_STATUS_EXECUTION_FAILED; }
+    StepGraph sg;
+    sg.launches = launches_get();
+    e = cudaGraphInstantiate(&sg.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) { set_last_error("cudaGraphInstantiate", e); return THA_STATUS_EXECUTION_FAILED; }
+    it = ws->graphs.emplace(key, sg).first;
+  }
+  THA_CUDA_OK(cudaGraphLaunch(it->second.exec, st));
+  g_last_step_launches = it->second.launches;
+  return THA_STATUS_SUCCESS;
+}
+
+static int issue_step_f32(cudaStream_t st, Workspace* ws, const StepArgs& a, const float* rc, const float* rs) {
+  const tha_config_t& c = a.cfg;
+  const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads;
+  const int kv_mul = c.n_heads / c.n_kv_heads;
+  const long long kv_bs = (long long)c.n_layers * c.seq_len * kvd;
+  const bool pdl = a.pdl != 0;
+  const bool fused = attn_fused_supported(c.n_heads, hs, d, kvd);
+  THA_TRY(embed_launch(st, a.B, a.s.x, a.w.token_embedding_table, a.token_d, a.pos_d, d, pdl));
+  for (int l = 0; l < c.n_layers; l++) {
+    const int loff = l * c.seq_len * kvd;
+    GemvP p = {};
+    p.W0 = a.w.wq + (size_t)l * d * d; p.M0 = d;
+    p.W1 = a.w.wk + (size_t)l * d * kvd; p.M1 = kvd;
+    p.W2 = a.w.wv + (size_t)l * d * kvd; p.M2 = kvd;
+    p.K = d; p.B = a.B; p.X = a.s.x; p.x_stride = d;
+    p.rms_w = a.w.rms_att_weight + (size_t)l * d; p.pos = a.pos_d;
+    p.out = a.s.q; p.out_batch_stride = d;
+    p.kc = a.s.key_cache; p.vc = a.s.value_cache; p.kv_batch_stride = kv_bs; p.loff = loff;
+    p.kv_dim = kvd; p.head_size = hs; p.rope_cos = rc; p.rope_sin = rs;
+    THA_TRY(gemv_launch(st, GEMV_QKV, p, pdl));
+
+    if (fused) {
+      THA_TRY(attn_fused_launch(st, ws, a.B, a.pos_d, c.n_heads, c.n_kv_heads, a.s.q, a.s.xb, a.s.key_cache + loff,
+                                a.s.value_cache + loff, kv_bs, hs, c.seq_len, pdl));
+    } else {
+      THA_TRY(tha_mha_scores_v1_f32(st, a.B, a.pos_d, c.n_heads, c.n_layers, a.s.q, a.s.att, a.s.key_cache, hs,
+                                    c.seq_len, loff, kvd, d, kv_mul));
+      THA_TRY(tha_mha_softmax_f32(st, a.B, a.s.att, a.pos_d, c.seq_len, c.n_heads));
+      THA_TRY(tha_mha_weighted_v1_f32(st, a.B, a.pos_d, c.n_heads, a.s.xb, a.s.att, a.s.value_cache, hs, c.seq_len,
+                                      loff, kvd, kv_mul, d, c.n_layers));
+    }
+
+    GemvP o = {};
+    o.W0 = a.w.wo + (size_t)l * d * d; o.M0 = d; o.K = d; o.B = a.B; o.X = a.s.xb; o.x_stride = d;
+    o.pos = a.pos_d; o.out = a.s.x; o.out_batch_stride = d;
+    THA_TRY(gemv_launch(st, GEMV_RESID, o, pdl));
+
+    GemvP f = {};
+    f.W0 = a.w.w1 + (size_t)l * d * hd; f.W1 = a.w.w3 + (size_t)l * d * hd; f.M0 = hd; f.M1 = hd;
+    f.K = d; f.B = a.B; f.X = a.s.x; f.x_stride = d; f.rms_w = a.w.rms_ffn_weight + (size_t)l * d;
+    f.pos = a.pos_d; f.out = a.s.hb; f.out_batch_stride = hd;
+    THA_TRY(gemv_launch(st, GEMV_SWIGLU, f, pdl));
+
+    GemvP g = {};
+    g.W0 = a.w.w2 + (size_t)l * d * hd; g.M0 = d; g.K = hd; g.B = a.B; g.X = a.s.hb; g.x_stride = hd;
+    g.pos = a.pos_d; g.out = a.s.x; g.out_batch_stride = d;
+    THA_TRY(gemv_launch(st, GEMV_RESID, g, pdl));
+  }
+  float* logits = a.logits_d ? a.logits_d : a.s.logits;
+  GemvP cl = {};
+  cl.W0 = a.w.wcls; cl.M0 = c.vocab_size; cl.K = d; cl.B = a.B; cl.X = a.s.x; cl.x_stride = d;
+  cl.rms_w = a.w.rms_final_weight; cl.pos = a.pos_d; cl.out = logits; cl.out_batch_stride = c.vocab_size;
+  THA_TRY(gemv_launch(st, GEMV_PLAIN, cl, pdl));
+  if (a.next_d) {
+    THA_TRY(argmax_launch(st, a.B, logits, c.vocab_size, a.next_d, pdl));
+  }
+  return THA_STATUS_SUCCESS;
+}
+
+static int validate_f32(int B, const tha_config_t* c, const tha_weights_f32_t* w, const tha_state_t* s) {
+  if (B <= 0 || !c || !w || !s) return THA_STATUS_INVALID_ARG;
+  if (c->dim <= 0 || c->n_heads <= 0 || c->n_kv_heads <= 0 || c->dim % c->n_heads || c->n_heads % c->n_kv_heads)
+    return THA_STATUS_INVALID_ARG;
+  const int hs = c->dim / c->n_heads;
+  if (c->dim % 4 || c->hidden_dim % 4 || (hs & 1) || ((hs * c->n_kv_heads) % 4)) return THA_STATUS_NOT_SUPPORTED;
+  if (!w->token_embedding_table || !w->wq || !w->wk || !w->wv || !w->wo || !w->w1 || !w->w2 || !w->w3 || !w->wcls ||
+      !w->rms_att_weight || !w->rms_ffn_weight || !w->rms_final_weight)
+    return THA_STATUS_INVALID_ARG;
+  if (!s->x || !s->xb || !s->hb || !s->q || !s->key_cache || !s->value_cache) return THA_STATUS_INVALID_ARG;
+  return THA_STATUS_SUCCESS;
+}
+
+int decode_step_f32(cudaStream_t st, int B, const tha_config_t* cfg, const tha_weights_f32_t* w, const tha_state_t* s,
+                    const int* token_d, const int* pos_d, float* logits_d, int* next_d) {
+  THA_TRY(validate_f32(B, cfg, w, s));
+  if (!token_d || !pos_d || (!logits_d && !s->logits)) return THA_STATUS_INVALID_ARG;
+  Workspace* ws = workspace();
+  if (!ws) return THA_STATUS_EXECUTION_FAILED;
+  const int hs = cfg->dim / cfg->n_heads, kvd = hs * cfg->n_kv_heads;
+  const float *rc, *rs;
+  THA_TRY(ws_rope(ws, hs, cfg->seq_len, &rc, &rs));
+  const bool fused = attn_fused_supported(cfg->n_heads, hs, cfg->dim, kvd);
+  if (!fused && !s->att) return THA_STATUS_INVALID_ARG;
+  if (fused) {  // grow the split scratch now: no allocation may happen inside a capture
+    int J = 8;
+    for (; J >= 1; J--) if ((128 * J) % hs == 0 && cfg->dim % (128 * J) == 0) break;
+    const int nseg = cfg->dim / (128 * J);
+    const int nsplit = attn_fused_nsplit(B, nseg, cfg->seq_len);
+    if (nsplit > 1) THA_TRY(ws_ensure_attn(ws, (size_t)B * nseg * nsplit * 32 * J, B * nseg));
+  }
+  StepArgs a;
+  memset(&a, 0, sizeof(a));
+  a.B = B; a.cfg = *cfg; a.w = *w; a.s = *s; a.token_d = token_d; a.pos_d = pos_d; a.logits_d = logits_d;
+  a.next_d = next_d; a.pdl = pdl_enabled();
+
+  return run_step(st, ws, &a, sizeof(a), [&]() { return issue_step_f32(st, ws, a, rc, rs); });
+}
+
+// ---------------------------------------------------------------------------- Q8_0 ----
+int gemv_q8_launch(cudaStream_t stream, int mode, const GemvP& p, bool pdl);
+
+struct StepArgsQ8 {
+  int B; tha_config_t cfg; tha_weights_q8_t w; tha_state_t s;
+  const int* token_d; const int* pos_d; float* logits_d; int* next_d; int pdl;
+};
+
+// runq.c:344-481 with the same 5-kernels-per-layer structure; every matmul kernel
+// quantises its own input rows in its prologue (runq.c:367,437,450,465,478).
+static int issue_step_q8(cudaStream_t st, Workspace* ws, const StepArgsQ8& a, const float* rc, const float* rs) {
+  const tha_config_t& c = a.cfg;
+  const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads, gs = a.w.group_size;
+  const int kv_mul = c.n_heads / c.n_kv_heads;
+  const long long kv_bs = (long long)c.n_layers * c.seq_len * kvd;
+  const bool pdl = a.pdl != 0;
+  const bool fused = attn_fused_supported(c.n_heads, hs, d, kvd);
+  THA_TRY(embed_launch(st, a.B, a.s.x, a.w.token_embedding_table, a.token_d, a.pos_d, d, pdl));
+  for (int l = 0; l < c.n_layers; l++) {
+    const int loff = l * c.seq_len * kvd;
+    GemvP p = {};
+    p.gs = gs;
+    p.Q0 = a.w.wq.q + (size_t)l * d * d;   p.S0 = a.w.wq.s + (size_t)l * d * d / gs;   p.M0 = d;
+    p.Q1 = a.w.wk.q + (size_t)l * d * kvd; p.S1 = a.w.wk.s + (size_t)l * d * kvd / gs; p.M1 = kvd;
+    p.Q2 = a.w.wv.q + (size_t)l * d * kvd; p.S2 = a.w.wv.s + (size_t)l * d * kvd / gs; p.M2 = kvd;
+    p.K = d; p.B = a.B; p.X = a.s.x; p.x_stride = d;
+    p.rms_w = a.w.rms_att_weight + (size_t)l * d; p.pos = a.pos_d;
+    p.out = a.s.q; p.out_batch_stride = d;
+    p.kc = a.s.key_cache; p.vc = a.s.value_cache; p.kv_batch_stride = kv_bs; p.loff = loff;
+    p.kv_dim = kvd; p.head_size = hs; p.rope_cos = rc; p.rope_sin = rs;
+    THA_TRY(gemv_q8_launch(st, GEMV_QKV, p, pdl));
+
+    if (fused) {
+      THA_TRY(attn_fused_launch(st, ws, a.B, a.pos_d, c.n_heads, c.n_kv_heads, a.s.q, a.s.xb, a.s.key_cache + loff,
+                                a.s.value_cache + loff, kv_bs, hs, c.seq_len, pdl));
+    } else {
+      THA_TRY(tha_mha_scores_v1_f32(st, a.B, a.pos_d, c.n_heads, c.n_layers, a.s.q, a.s.att, a.s.key_cache, hs,
+                                    c.seq_len, loff, kvd, d, kv_mul));
+      THA_TRY(tha_mha_softmax_f32(st, a.B, a.s.att, a.pos_d, c.seq_len, c.n_heads));
+      THA_TRY(tha_mha_weighted_v1_f32(st, a.B, a.pos_d, c.n_heads, a.s.xb, a.s.att, a.s.value_cache, hs, c.seq_len,
+                                      loff, kvd, kv_mul, d, c.n_layers));
+    }
+
+    GemvP o = {};
+    o.gs = gs; o.Q0 = a.w.wo.q + (size_t)l * d * d; o.S0 = a.w.wo.s + (size_t)l * d * d / gs; o.M0 = d; o.K = d;
+    o.B = a.B; o.X = a.s.xb; o.x_stride = d; o.pos = a.pos_d; o.out = a.s.x; o.out_batch_stride = d;
+    THA_TRY(gemv_q8_launch(st, GEMV_RESID, o, pdl));
+
+    GemvP f = {};
+    f.gs = gs;
+    f.Q0 = a.w.w1.q + (size_t)l * d * hd; f.S0 = a.w.w1.s + (size_t)l * d * hd / gs; f.M0 = hd;
+    f.Q1 = a.w.w3.q + (size_t)l * d * hd; f.S1 = a.w.w3.s + (size_t)l * d * hd / gs; f.M1 = hd;
+    f.K = d; f.B = a.B; f.X = a.s.x; f.x_stride = d; f.rms_w = a.w.rms_ffn_weight + (size_t)l * d;
+    f.pos = a.pos_d; f.out = a.s.hb; f.out_batch_stride = hd;
+    THA_TRY(gemv_q8_launch(st, GEMV_SWIGLU, f, pdl));
+
+    GemvP g = {};
+    g.gs = gs; g.Q0 = a.w.w2.q + (size_t)l * d * hd; g.S0 = a.w.w2.s + (size_t)l * d * hd / gs; g.M0 = d; g.K = hd;
+    g.B = a.B; g.X = a.s.hb; g.x_stride = hd; g.pos = a.pos_d; g.out = a.s.x; g.out_batch_stride = d;
+    THA_TRY(gemv_q8_launch(st, GEMV_RESID, g, pdl));
+  }
+  float* logits = a.logits_d ? a.logits_d : a.s.logits;
+  GemvP cl = {};
+  cl.gs = gs; cl.Q0 = a.w.wcls.q; cl.S0 = a.w.wcls.s; cl.M0 = c.vocab_size; cl.K = d; cl.B = a.B; cl.X = a.s.x;
+  cl.x_stride = d; cl.rms_w = a.w.rms_final_weight; cl.pos = a.pos_d; cl.out = logits; cl.out_batch_stride = c.vocab_size;
+  THA_TRY(gemv_q8_launch(st, GEMV_PLAIN, cl, pdl));
+  if (a.next_d) THA_TRY(argmax_launch(st, a.B, logits, c.vocab_size, a.next_d, pdl));
+  return THA_STATUS_SUCCESS;
+}
+
+int decode_step_q8(cudaStream_t st, int B, const tha_config_t* cfg, const tha_weights_q8_t* w, const tha_state_t* s,
+                   const int* token_d, const int* pos_d, float* logits_d, int* next_d) {
+  if (B <= 0 || !cfg || !w || !s || !token_d || !pos_d || (!logits_d && !s->logits)) return THA_STATUS_INVALID_ARG;
+  if (cfg->dim <= 0 || cfg->n_heads <= 0 || cfg->n_kv_heads <= 0 || cfg->dim % cfg->n_heads ||
+      cfg->n_heads % cfg->n_kv_heads || w->group_size <= 0)
+    return THA_STATUS_INVALID_ARG;
+  const int hs = cfg->dim / cfg->n_heads, kvd = hs * cfg->n_kv_heads, gs = w->group_size;
+  if (cfg->dim % gs || cfg->hidden_dim % gs || cfg->dim % 16 || cfg->hidden_dim % 16 || (hs & 1) || kvd % 4)
+    return THA_STATUS_NOT_SUPPORTED;
+  if (!w->token_embedding_table || !w->wq.q || !w->wk.q || !w->wv.q || !w->wo.q || !w->w1.q || !w->w2.q || !w->w3.q ||
+      !w->wcls.q || !w->rms_att_weight || !w->rms_ffn_weight || !w->rms_final_weight)
+    return THA_STATUS_INVALID_ARG;
+  if (!s->x || !s->xb || !s->hb || !s->q || !s->key_cache || !s->value_cache) return THA_STATUS_INVALID_ARG;
+  Workspace* ws = workspace();
+  if (!ws) return THA_STATUS_EXECUTION_FAILED;
+  const float *rc, *rs;
+  THA_TRY(ws_rope(ws, hs, cfg->seq_len, &rc, &rs));
+  const bool fused = attn_fused_supported(cfg->n_heads, hs, cfg->dim, kvd);
+  if (!fused && !s->att) return THA_STATUS_INVALID_ARG;
+  if (fused) {
+    int J = 8;
+    for (; J >= 1; J--) if ((128 * J) % hs == 0 && cfg->dim % (128 * J) == 0) break;
+    const int nseg = cfg->dim / (128 * J);
+    const int nsplit = attn_fused_nsplit(B, nseg, cfg->seq_len);
+    if (nsplit > 1) THA_TRY(ws_ensure_attn(ws, (size_t)B * nseg * nsplit * 32 * J, B * nseg));
+  }
+  StepArgsQ8 a;
+  memset(&a, 0, sizeof(a));
+  a.B = B; a.cfg = *cfg; a.w = *w; a.s = *s; a.token_d = token_d; a.pos_d = pos_d; a.logits_d = logits_d;
+  a.next_d = next_d; a.pdl = pdl_enabled();
+  return run_step(st, ws, &a, sizeof(a), [&]() { return issue_step_q8(st, ws, a, rc, rs); });
+}
+
+int last_step_launches_get() { return g_last_step_launches; }
+void last_step_launches_set(int v) { g_last_step_launches = v; }
+
+// H2D of token/pos through the pinned staging block, step, D2H of the logits, sync.
+template <typename StepFn>
+static int forward_host(cudaStream_t st, int B, int vocab, float* state_logits, const int* token_host,
+                        const int* pos_host, float* logits_out, StepFn step) {
+  if (B <= 0 || !token_host || !pos_host || !logits_out) return THA_STATUS_INVALID_ARG;
+  Workspace* ws = workspace();
+  if (!ws) return THA_STATUS_EXECUTION_FAILED;
+  THA_TRY(ws_ensure_tokpos(ws, B));
+  const int cap = ws->tokpos_cap;
+  memcpy(ws->tokpos_h, token_host, B * sizeof(int));
+  memcpy(ws->tokpos_h + cap, pos_host, B * sizeof(int));
+  THA_CUDA_OK(cudaMemcpyAsync(ws->tok_d, ws->tokpos_h, 2 * cap * sizeof(int), cudaMemcpyHostToDevice, st));
+  float* target = state_logits ? state_logits : logits_out;
+  THA_TRY(step(ws->tok_d, ws->pos_d, target));
+  if (target != logits_out)
+    THA_CUDA_OK(cudaMemcpyAsync(logits_out, target, (size_t)B * vocab * sizeof(float), cudaMemcpyDefault, st));
+  THA_CUDA_OK(cudaStreamSynchronize(st));
+  return THA_STATUS_SUCCESS;
+}
+
+}  // namespace tha
+
+using namespace tha;
+
+extern "C" int tha_decode_step_f32(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_f32_t* w,
+                                   const tha_state_t* s, const int* token_d, const int* pos_d, float* logits_d,
+                                   int* next_d) {
+  return decode_step_f32((cudaStream_t)stream, n_batches, cfg, w, s, token_d, pos_d, logits_d, next_d);
+}
+
+extern "C" int tha_forward_batch_f32(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_f32_t* w,
+                                     const tha_state_t* s, const int* token_host, const int* pos_host,
+                                     float* logits_out) {
+  if (!cfg || !s) return THA_STATUS_INVALID_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  return forward_host(st, n_batches, cfg->vocab_size, s->logits, token_host, pos_host, logits_out,
+                      [&](const int* tok_d, const int* pos_d, float* target) {
+                        return decode_step_f32(st, n_batches, cfg, w, s, tok_d, pos_d, target, nullptr);
+                      });
+}
+
+extern "C" int tha_last_step_launches(void) { return last_step_launches_get(); }
+
+extern "C" int tha_decode_step_q8(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_q8_t* w,
+                                  const tha_state_t* s, const int* token_d, const int* pos_d, float* logits_d,
+                                  int* next_d) {
+  return decode_step_q8((cudaStream_t)stream, n_batches, cfg, w, s, token_d, pos_d, logits_d, next_d);
+}
+
+extern "C" int tha_forward_batch_q8(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_q8_t* w,
+                                    const tha_state_t* s, const int* token_host, const int* pos_host,
+                                    float* logits_out) {
+  if (!cfg || !s) return THA_STATUS_INVALID_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  return forward_host(st, n_batches, cfg->vocab_size, s->logits, token_host, pos_host, logits_out,
+                      [&](const int* tok_d, const int* pos_d, float* target) {
+                        return decode_step_q8(st, n_batches, cfg, w, s, tok_d, pos_d, target, nullptr);
+                      });
+}

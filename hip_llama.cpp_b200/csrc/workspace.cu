@@ -1,0 +1,128 @@
+// Library state: options, last error, per-device workspace.
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "common.cuh"
+#include "workspace.h"
+
+namespace tha {
+
+static thread_local char g_err[512] = "";
+static thread_local int g_launches = 0;
+static int g_pdl = -1, g_graph = -1;
+static std::mutex g_mu;
+static std::map<int, Workspace*> g_ws;
+
+void set_last_error(const char* where, cudaError_t e) {
+  snprintf(g_err, sizeof(g_err), "%s: %s (%s)", where, cudaGetErrorString(e), cudaGetErrorName(e));
+  cudaGetLastError();  // clear the sticky-free error so later calls are not poisoned
+}
+
+static int env_flag(const char* name, int dflt) {
+  const char* v = getenv(name);
+  if (!v || !*v) return dflt;
+  return atoi(v) != 0;
+}
+int pdl_enabled() {
+  if (g_pdl < 0) g_pdl = env_flag("THA_PDL", 1);
+  return g_pdl;
+}
+int graph_enabled() {
+  if (g_graph < 0) g_graph = env_flag("THA_GRAPH", 1);
+  return g_graph;
+}
+void count_launch(int n) { g_launches += n; }
+int launches_reset() { int v = g_launches; g_launches = 0; return v; }
+int launches_get() { return g_launches; }
+
+Workspace* workspace() {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) { set_last_error("cudaGetDevice", cudaGetLastError()); return nullptr; }
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto it = g_ws.find(dev);
+  if (it != g_ws.end()) return it->second;
+  Workspace* ws = new Workspace();
+  ws->device = dev;
+  g_ws[dev] = ws;
+  return ws;
+}
+
+int ws_ensure_attn(Workspace* ws, size_t part_slots, int n_counters) {
+  if (part_slots > ws->part_cap) {
+    if (ws->part_acc) { cudaFree(ws->part_acc); cudaFree(ws->part_ml); }
+    size_t cap = part_slots + part_slots / 4;
+    THA_CUDA_OK(cudaMalloc(&ws->part_acc, cap * sizeof(float4)));
+    THA_CUDA_OK(cudaMalloc(&ws->part_ml, cap * sizeof(float2)));
+    ws->part_cap = cap;
+    ws->graphs.clear();  // cached graphs captured the old pointers
+  }
+  if (n_counters > ws->counters_cap) {
+    if (ws->counters) cudaFree(ws->counters);
+    int cap = n_counters * 2;
+    THA_CUDA_OK(cudaMalloc(&ws->counters, cap * sizeof(int)));
+    THA_CUDA_OK(cudaMemset(ws->counters, 0, cap * sizeof(int)));
+    ws->counters_cap = cap;
+    ws->graphs.clear();
+  }
+  return THA_STATUS_SUCCESS;
+}
+
+int ws_ensure_tokpos(Workspace* ws, int n_batches) {
+  if (n_batches <= ws->tokpos_cap) return THA_STATUS_SUCCESS;
+  if (ws->tok_d) { cudaFree(ws->tok_d); cudaFreeHost(ws->tokpos_h); }
+  int cap = n_batches < 64 ? 64 : n_batches * 2;
+  THA_CUDA_OK(cudaMalloc(&ws->tok_d, 2 * cap * sizeof(int)));   // [tok | pos]
+  ws->pos_d = ws->tok_d + cap;
+  THA_CUDA_OK(cudaMallocHost(&ws->tokpos_h, 2 * cap * sizeof(int)));
+  ws->tokpos_cap = cap;
+  ws->graphs.clear();
+  return THA_STATUS_SUCCESS;
+}
+
+// cos/sin of pos * 10000^(-(2j)/hs), exactly as run.cc:271-277 evaluates them (float
+// powf / cosf / sinf of the host libm), so the fused RoPE is bit-identical to the CPU path.
+int ws_rope(Workspace* ws, int head_size, int seq_len, const float** cos_d, const float** sin_d) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto key = std::make_pair(head_size, seq_len);
+  auto it = ws->rope.find(key);
+  if (it == ws->rope.end()) {
+    const int half = head_size / 2;
+    std::vector<float> c((size_t)seq_len * half), s((size_t)seq_len * half);
+    for (int pos = 0; pos < seq_len; pos++)
+      for (int j = 0; j < half; j++) {
+        int head_dim = 2 * j;
+        float freq = 1.0f / powf(10000.0f, head_dim / (float)head_size);
+        float val = pos * freq;
+        c[(size_t)pos * half + j] = cosf(val);
+        s[(size_t)pos * half + j] = sinf(val);
+      }
+    RopeTable t;
+    THA_CUDA_OK(cudaMalloc(&t.cos_d, c.size() * sizeof(float)));
+    THA_CUDA_OK(cudaMalloc(&t.sin_d, s.size() * sizeof(float)));
+    THA_CUDA_OK(cudaMemcpy(t.cos_d, c.data(), c.size() * sizeof(float), cudaMemcpyHostToDevice));
+    THA_CUDA_OK(cudaMemcpy(t.sin_d, s.data(), s.size() * sizeof(float), cudaMemcpyHostToDevice));
+    it = ws->rope.emplace(key, t).first;
+  }
+  *cos_d = it->second.cos_d;
+  *sin_d = it->second.sin_d;
+  return THA_STATUS_SUCCESS;
+}
+
+const char* last_error_text() { return g_err; }
+void set_opt(int* which, int v) { *which = v; }
+int* opt_pdl() { return &g_pdl; }
+int* opt_graph() { return &g_graph; }
+
+}  // namespace tha
+
+extern "C" int tha_version(void) { return 100; }
+extern "C" const char* tha_last_error(void) { return tha::last_error_text(); }
+extern "C" int tha_set_option(const char* name, int value) {
+  if (!name) return THA_STATUS_INVALID_ARG;
+  if (!strcmp(name, "pdl")) { *tha::opt_pdl() = value != 0; return THA_STATUS_SUCCESS; }
+  if (!strcmp(name, "graph")) { *tha::opt_graph() = value != 0; return THA_STATUS_SUCCESS; }
+  return THA_STATUS_INVALID_ARG;
+}

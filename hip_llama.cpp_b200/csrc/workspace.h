@@ -1,0 +1,39 @@
+// Per-device scratch owned by the library (grown lazily, never inside a stream
+// capture): split-attention partials, device mirrors of token[]/pos[], RoPE
+// tables, Q8_0 activation scratch, cached CUDA graphs.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <map>
+#include <tuple>
+#include <vector>
+
+namespace tha {
+
+struct RopeTable { float* cos_d = nullptr; float* sin_d = nullptr; };
+
+struct StepGraph {
+  cudaGraphExec_t exec = nullptr;
+  int launches = 0;
+};
+
+struct Workspace {
+  int device = -1;
+  // split-attention partials
+  float4* part_acc = nullptr; float2* part_ml = nullptr; size_t part_cap = 0;  // in slots
+  int* counters = nullptr; int counters_cap = 0;
+  // device mirrors of the host token[] / pos[] arrays of thaDNN_s_forward_batch
+  int* tok_d = nullptr; int* pos_d = nullptr; int* tokpos_h = nullptr; int tokpos_cap = 0;
+  // RoPE cos/sin tables keyed by (head_size, seq_len); built on the host with libm so
+  // they are bit-identical to what run.cc:271-277 computes
+  std::map<std::pair<int, int>, RopeTable> rope;
+  // cached graphs of the decode step keyed by a hash of every launch argument
+  std::map<unsigned long long, StepGraph> graphs;
+};
+
+Workspace* workspace();   // for the current device (thread-safe)
+int ws_ensure_attn(Workspace* ws, size_t part_slots, int n_counters);
+int ws_ensure_tokpos(Workspace* ws, int n_batches);
+int ws_rope(Workspace* ws, int head_size, int seq_len, const float** cos_d, const float** sin_d);
+
+}  // namespace tha

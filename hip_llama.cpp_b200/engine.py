@@ -1,0 +1,153 @@
+"""Python mirror of the reference's model/state helpers, over the C-ABI.
+
+  DeviceWeights      ~ copy_weight_to_device            (src/models.cpp:86-125)
+  DeviceWeightsQ8    ~ the v2 loader of runq.c:174-251, uploaded
+  BatchState         ~ alloc_state_to_device_batch      (src/models.cpp:155-179)
+  forward_batch      ~ thaDNN_s_forward_batch           (src/thaDNN.cpp:13-81)
+
+torch is used for device memory, streams and pinned buffers only; every kernel that runs
+is one of ours, reached through hip_llama.cpp_b200/cabi.py.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import cabi
+from .checkpoint import Config
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _stream_ptr(stream=None):
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)
+
+
+def c_config(cfg: Config) -> cabi.Config:
+    return cabi.Config(cfg.dim, cfg.hidden_dim, cfg.n_layers, cfg.n_heads, cfg.n_kv_heads, cfg.vocab_size, cfg.seq_len)
+
+
+class DeviceWeights:
+    """fp32 weights resident in HBM, layer-major contiguous exactly as in the v0 file."""
+    NAMES = ("tok_emb", "rms_att", "rms_ffn", "wq", "wk", "wv", "wo", "w1", "w2", "w3", "rms_final")
+
+    def __init__(self, cfg: Config, w: dict, device="cuda", shared_classifier=True):
+        self.cfg = cfg
+        self.t = {}
+        for n in self.NAMES:
+            self.t[n] = torch.from_numpy(np.ascontiguousarray(w[n], dtype=np.float32)).to(device)
+        if shared_classifier or "wcls" not in w or w["wcls"] is w["tok_emb"]:
+            self.t["wcls"] = self.t["tok_emb"]
+        else:
+            self.t["wcls"] = torch.from_numpy(np.ascontiguousarray(w["wcls"], dtype=np.float32)).to(device)
+        t = self.t
+        self.c = cabi.WeightsF32(_ptr(t["tok_emb"]), _ptr(t["rms_att"]), _ptr(t["rms_ffn"]), _ptr(t["wq"]),
+                                 _ptr(t["wk"]), _ptr(t["wv"]), _ptr(t["wo"]), _ptr(t["w1"]), _ptr(t["w2"]),
+                                 _ptr(t["w3"]), _ptr(t["rms_final"]), _ptr(t["wcls"]))
+
+    def nbytes(self) -> int:
+        seen, n = set(), 0
+        for t in self.t.values():
+            if t.data_ptr() not in seen:
+                seen.add(t.data_ptr())
+                n += t.numel() * 4
+        return n
+
+
+class DeviceWeightsQ8:
+    """Q8_0 weights (runq.c:34-37): int8 [L, out*in] + fp32 scales [L, out*in/GS]; fp32 norms;
+    dequantised fp32 embedding table (runq.c:205-206)."""
+
+    def __init__(self, cfg: Config, gs: int, norms: dict, qt: dict, device="cuda"):
+        self.cfg, self.gs = cfg, gs
+        self.t = {}
+        for n in ("rms_att", "rms_ffn", "rms_final"):
+            self.t[n] = torch.from_numpy(np.ascontiguousarray(norms[n], dtype=np.float32)).to(device)
+        for n in ("wq", "wk", "wv", "wo", "w1", "w2", "w3", "tok_emb"):
+            q, s = qt[n]
+            self.t[n + ".q"] = torch.from_numpy(np.ascontiguousarray(q, dtype=np.int8)).to(device)
+            self.t[n + ".s"] = torch.from_numpy(np.ascontiguousarray(s, dtype=np.float32)).to(device)
+        if qt["wcls"] is qt["tok_emb"]:
+            self.t["wcls.q"], self.t["wcls.s"] = self.t["tok_emb.q"], self.t["tok_emb.s"]
+        else:
+            q, s = qt["wcls"]
+            self.t["wcls.q"] = torch.from_numpy(np.ascontiguousarray(q, dtype=np.int8)).to(device)
+            self.t["wcls.s"] = torch.from_numpy(np.ascontiguousarray(s, dtype=np.float32)).to(device)
+        # dequantise the embedding table: x = q * s[group]  (int8 -> fp32 product is exact)
+        q = self.t["tok_emb.q"].reshape(-1, gs).float()
+        self.t["tok_emb"] = (q * self.t["tok_emb.s"].reshape(-1, 1)).reshape(cfg.vocab_size, cfg.dim).contiguous()
+        t = self.t
+
+        def qten(n):
+            return cabi.QTensor(_ptr(t[n + ".q"]), _ptr(t[n + ".s"]))
+
+        self.c = cabi.WeightsQ8(_ptr(t["tok_emb"]), _ptr(t["rms_att"]), _ptr(t["rms_ffn"]), _ptr(t["rms_final"]),
+                                qten("wq"), qten("wk"), qten("wv"), qten("wo"), qten("w1"), qten("w2"), qten("w3"),
+                                qten("wcls"), gs)
+
+    def nbytes(self) -> int:
+        """Bytes one decode step must read: every quantised tensor once (classifier == embedding)."""
+        n = 0
+        for k, t in self.t.items():
+            if k == "tok_emb" or k.startswith("wcls"):
+                continue
+            n += t.numel() * t.element_size()
+        return n
+
+
+class BatchState:
+    """Batched RunState: every buffer x B (src/models.cpp:155-179); KV [B][L][S][kv_dim] fp32."""
+
+    def __init__(self, cfg: Config, batch: int, device="cuda", with_att=True):
+        self.cfg, self.B = cfg, batch
+        z = lambda *shape: torch.zeros(*shape, dtype=torch.float32, device=device)
+        self.x, self.xb, self.xb2, self.q = z(batch, cfg.dim), z(batch, cfg.dim), z(batch, cfg.dim), z(batch, cfg.dim)
+        self.hb, self.hb2 = z(batch, cfg.hidden_dim), z(batch, cfg.hidden_dim)
+        self.att = z(batch, cfg.n_heads, cfg.seq_len) if with_att else None
+        self.logits = z(batch, cfg.vocab_size)
+        self.key_cache = z(batch, cfg.n_layers, cfg.seq_len, cfg.kv_dim)
+        self.value_cache = z(batch, cfg.n_layers, cfg.seq_len, cfg.kv_dim)
+        self.c = cabi.State(_ptr(self.x), _ptr(self.xb), _ptr(self.xb2), _ptr(self.hb), _ptr(self.hb2), _ptr(self.q),
+                            None, None, _ptr(self.att), _ptr(self.logits), _ptr(self.key_cache),
+                            _ptr(self.value_cache), None, None, None, None)
+
+
+class Engine:
+    """One model replica on one GPU, B slots."""
+
+    def __init__(self, weights, batch: int, device="cuda", with_att=True):
+        self.lib = cabi.lib()
+        self.w = weights
+        self.cfg = weights.cfg
+        self.q8 = isinstance(weights, DeviceWeightsQ8)
+        self.B = batch
+        self.state = BatchState(self.cfg, batch, device, with_att)
+        self.ccfg = c_config(self.cfg)
+        self.device = device
+
+    def forward_batch(self, tokens, pos, logits_host=None, stream=None):
+        """The reference call: HOST token/pos in, [B, vocab] logits out in pinned host memory."""
+        tok = np.ascontiguousarray(tokens, dtype=np.int32)
+        ps = np.ascontiguousarray(pos, dtype=np.int32)
+        if logits_host is None:
+            logits_host = torch.empty(self.B, self.cfg.vocab_size, dtype=torch.float32).pin_memory()
+        fn = self.lib.c.tha_forward_batch_q8 if self.q8 else self.lib.c.tha_forward_batch_f32
+        st = fn(_stream_ptr(stream), self.B, C.byref(self.ccfg), C.byref(self.w.c), C.byref(self.state.c),
+                tok.ctypes.data_as(C.c_void_p), ps.ctypes.data_as(C.c_void_p), C.c_void_p(logits_host.data_ptr()))
+        self.lib.check(st, "tha_forward_batch")
+        return logits_host
+
+    def decode_step(self, token_d, pos_d, logits_d=None, next_d=None, stream=None):
+        """Resident step: device token/pos, optional device logits and greedy next tokens."""
+        fn = self.lib.c.tha_decode_step_q8 if self.q8 else self.lib.c.tha_decode_step_f32
+        st = fn(_stream_ptr(stream), self.B, C.byref(self.ccfg), C.byref(self.w.c), C.byref(self.state.c),
+                _ptr(token_d), _ptr(pos_d), _ptr(logits_d), _ptr(next_d))
+        self.lib.check(st, "tha_decode_step")
+
+    def last_step_launches(self) -> int:
+        return self.lib.c.tha_last_step_launches()

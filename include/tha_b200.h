@@ -1,0 +1,188 @@
+/* tha_b200.h -- the C-ABI boundary of the B200 (sm_100a) llama2 forward pass.
+ *
+ * Everything that touches the GPU goes through the `extern "C"` entry points
+ * declared here: plain pointers, ints and an opaque `void* stream`
+ * (a cudaStream_t; NULL = the legacy default stream).  No C++ or torch types.
+ * The C++ headers that keep the reference's names (include/thaBLAS.hpp,
+ * include/thaDNN.hpp, include/models.hpp, ...) are thin wrappers over these
+ * symbols; a Python / cgo / JNI caller binds the same symbols directly
+ * (see INTEGRATION.md).
+ *
+ * Citations are to the reference tree (/root/reference): each entry point names
+ * the reference interface it replaces.
+ *
+ * Return value: a thablasStatus_t value (include/thaBLAS.hpp:5-19 in the
+ * reference): 0 = success, 2 = ALLOC_FAILED (the reference's "invalid argument"
+ * code, src/thaBLAS.cpp:80-84), 5 = EXECUTION_FAILED (a CUDA launch error),
+ * 7 = NOT_SUPPORTED.  All pointers are DEVICE pointers unless named *_host.
+ * All ops are asynchronous on `stream` unless stated otherwise.
+ */
+#ifndef THA_B200_H
+#define THA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define THA_STATUS_SUCCESS 0
+#define THA_STATUS_INVALID_ARG 2   /* THABLAS_STATUS_ALLOC_FAILED, what the reference returns for bad args */
+#define THA_STATUS_EXECUTION_FAILED 5
+#define THA_STATUS_NOT_SUPPORTED 7
+
+/* ---- POD mirrors of include/models.hpp:10-60 (identical field order) ------ */
+typedef struct {
+  int dim, hidden_dim, n_layers, n_heads, n_kv_heads, vocab_size, seq_len;
+} tha_config_t; /* == Config; fread straight from the checkpoint (src/utils.cpp:155) */
+
+typedef struct {
+  float* token_embedding_table; /* (vocab, dim) */
+  float* rms_att_weight;        /* (layer, dim) */
+  float* rms_ffn_weight;        /* (layer, dim) */
+  float* wq;                    /* (layer, dim, dim) row-major [out, in] */
+  float* wk;                    /* (layer, kv_dim, dim) */
+  float* wv;                    /* (layer, kv_dim, dim) */
+  float* wo;                    /* (layer, dim, dim) */
+  float* w1;                    /* (layer, hidden, dim) */
+  float* w2;                    /* (layer, dim, hidden) */
+  float* w3;                    /* (layer, hidden, dim) */
+  float* rms_final_weight;      /* (dim) */
+  float* wcls;                  /* (vocab, dim) */
+} tha_weights_f32_t; /* == TransformerWeights */
+
+typedef struct {
+  float *x, *xb, *xb2, *hb, *hb2, *q, *k, *v, *att, *logits;
+  float *key_cache, *value_cache; /* [B][n_layers][seq_len][kv_dim] (src/models.cpp:176-177) */
+  float *key_matmul, *value_matmul, *key_layer_cache, *value_layer_cache;
+} tha_state_t; /* == RunState (batched: every activation buffer is [B, ...]) */
+
+/* Q8_0 weights, runq.c:34-37 format: int8 values [out,in] + one fp32 scale per
+ * `group_size` consecutive values.  Per-layer tensors are stored layer-major
+ * and contiguous (q: [L, out*in], s: [L, out*in/GS]). */
+typedef struct { int8_t* q; float* s; } tha_qtensor_t;
+typedef struct {
+  float* token_embedding_table; /* dequantised fp32 (runq.c:205-206) */
+  float *rms_att_weight, *rms_ffn_weight, *rms_final_weight;
+  tha_qtensor_t wq, wk, wv, wo, w1, w2, w3, wcls;
+  int group_size;
+} tha_weights_q8_t;
+
+/* ---- library ---------------------------------------------------------------- */
+int tha_version(void);
+const char* tha_last_error(void);       /* text of the last CUDA error seen by this library */
+int tha_set_option(const char* name, int value); /* "pdl" (0/1), "graph" (0/1) */
+
+/* ---- runtime shim: the only way the C++ host layer touches the CUDA runtime ---------
+ * (reference: hipSetDevice / hipMalloc / hipMemcpy / hipHostMalloc / hipStreamCreate /
+ *  hipDeviceSynchronize calls in src/models.cpp:86-179, src/llama.cpp:919-947, src/thaBLAS.cpp:49-58) */
+int tha_device_count(int* n);
+int tha_get_device(int* dev);
+int tha_set_device(int dev);
+int tha_device_sync(void);
+int tha_stream_create(void** stream);
+int tha_stream_destroy(void* stream);
+int tha_stream_sync(void* stream);
+int tha_malloc(void** dptr, size_t bytes);
+int tha_free(void* dptr);
+int tha_host_alloc(void** hptr, size_t bytes);   /* pinned */
+int tha_host_free(void* hptr);
+int tha_memset(void* dptr, int value, size_t bytes);
+int tha_memcpy_h2d(void* dst, const void* src, size_t bytes);                 /* blocking */
+int tha_memcpy_d2h(void* dst, const void* src, size_t bytes);                 /* blocking */
+int tha_memcpy_d2d(void* dst, const void* src, size_t bytes);                 /* blocking */
+int tha_memcpy_async(void* dst, const void* src, size_t bytes, void* stream); /* direction inferred */
+int tha_mem_info(size_t* free_bytes, size_t* total_bytes);
+
+/* ---- thaBLAS level 1/2 -------------------------------------------------------- */
+/* thablas_Svds, src/thaBLAS.cpp:72-95: B[i] = A[i] / val */
+int tha_svds_f32(void* stream, int n, const float* A, float* B, float val);
+/* thaBLAS_s_vecaddvec, src/thaBLAS.cpp:104-126: a[i] += b[i] */
+int tha_vecaddvec_f32(void* stream, float* a, const float* b, int size);
+/* thaBLAS_s_matmul_batch, src/thaBLAS.cpp:191-228 (the weight matmuls):
+ *   C_b[0:M] = A[M,K] . B_b[K];  C_b = C + Coff + has_pos*pos_d[b] + b*C_batch_size,
+ *   B_b = B + b*B_batch_size.  pos_d may be NULL when has_pos == 0. */
+int tha_matmul_batch_f32(void* stream, int n_batches, float* C_batch, const float* B_batch,
+                         const float* A, int K, int M, int Coff, int has_pos, const int* pos_d,
+                         int C_batch_size, int B_batch_size);
+/* thaDNN_s_matmulvec_v2 / thaBLAS_s_matmulvec, src/thaBLAS.cpp:241-277: C[M] = A[M,K] . B[K] */
+int tha_matmulvec_f32(void* stream, float* C, const float* B, const float* A, int K, int M);
+/* thaBLAS_s_matmul_reduction, src/thaBLAS.cpp:281-319: A row-major [M,K]; B holds N
+ * rows of length K; C holds N rows of length M: C[j*M+i] = sum_k A[i,k] B[j,k] */
+int tha_matmul_reduction_f32(void* stream, const float* A, const float* B, float* C, int M, int N, int K);
+/* thaBLAS_s_matmul, src/thaBLAS.cpp:134-170: C[M,N] = A[M,K] . B[K,N], all row-major */
+int tha_matmul_f32(void* stream, int m, int n, int k, const float* A, const float* B, float* C);
+
+/* ---- thaDNN ops ----------------------------------------------------------------- */
+/* thaDNN_s_rmsnorm_v2_batch, src/thaDNN/thaDNN_rmsnorm.cpp:35-83; rows `dim` apart, o may alias x */
+int tha_rmsnorm_batch_f32(void* stream, int n_batches, float* o, const float* x, const float* weight,
+                          int size, int dim);
+/* thaDNN_s_rope, src/thaDNN/thaDNN_rope.cpp:25-63 (powf/cosf/sinf on the device) */
+int tha_rope_f32(void* stream, int dim, int head_size, int kv_dim, int pos, float* q, float* k);
+/* thaDNN_s_softmax_v2, src/thaDNN/thaDNN_softmax.cpp:62-119: in place, one vector */
+int tha_softmax_f32(void* stream, float* x, int size);
+/* thaDNN_s_swiglu, src/thaDNN/thaDNN_swiglu.cpp:5-35: hb = hb*sigmoid(hb)*hb2 */
+int tha_swiglu_f32(void* stream, float* hb, const float* hb2, int hidden_dim);
+/* thaDNN_s_multiheads_{1,2,3}_v1_batch, src/thaDNN/thaDNN_mha.cpp:246-426:
+ * KV batch-major [B][n_layers][seq_len][kv_dim]; att scratch [B][n_heads][seq_len]. */
+int tha_mha_scores_v1_f32(void* stream, int n_batches, const int* pos_d, int n_heads, int n_layers,
+                          const float* q, float* att, const float* key_cache, int head_size,
+                          int seq_len, int loff, int kv_dim, int dim, int kv_mul);
+int tha_mha_softmax_f32(void* stream, int n_batches, float* att, const int* pos_d, int seq_len, int n_heads);
+int tha_mha_weighted_v1_f32(void* stream, int n_batches, const int* pos_d, int n_heads, float* xb,
+                            const float* att, const float* value_cache, int head_size, int seq_len,
+                            int loff, int kv_dim, int kv_mul, int dim, int n_layers);
+/* thaDNN_s_multiheads_{1,3}_v2_batch, src/thaDNN/thaDNN_mha.cpp:60-240: one layer's KV,
+ * time-major [t][B][kv_dim]; att rows `n_words` long. */
+int tha_mha_scores_v2_f32(void* stream, int n_batches, const int* pos_d, int n_heads, const float* q,
+                          float* att, const float* key_cache, int head_size, int n_words, int kv_dim,
+                          int dim, int kv_mul);
+int tha_mha_weighted_v2_f32(void* stream, int n_batches, const int* pos_d, int n_heads, float* xb,
+                            const float* att, const float* value_cache, int head_size, int n_words,
+                            int kv_dim, int kv_mul, int dim);
+/* Fused replacement of the three stages (QK^T / online softmax / PV in one kernel),
+ * v1 layout.  Slots with pos_d[b] < 0 are skipped. */
+int tha_mha_fused_v1_f32(void* stream, int n_batches, const int* pos_d, int n_heads, int n_kv_heads,
+                         int n_layers, const float* q, float* xb, const float* key_cache,
+                         const float* value_cache, int head_size, int seq_len, int loff);
+
+/* ---- Q8_0 (runq.c) ---------------------------------------------------------------- */
+/* quantize, runq.c:145-171, bit-exact: n = rows*cols values, groups of `gs` */
+int tha_quantize_q8(void* stream, int8_t* q, float* s, const float* x, int n, int gs);
+/* matmul, runq.c:317-342 for n_batches activation rows:
+ *   out[b*out_stride + i] = sum_g (float)(sum_k xq.wq) * ws[i,g] * xs[b,g] */
+int tha_matmul_batch_q8(void* stream, int n_batches, float* out, int out_stride, const int8_t* xq,
+                        const float* xs, const int8_t* wq, const float* ws, int K, int M, int gs);
+
+/* ---- the forward pass --------------------------------------------------------------- */
+/* thaDNN_s_forward_batch, src/thaDNN.cpp:13-81: one decode step for n_batches slots,
+ * slot b at its own pos_host[b] (pos < 0: idle slot, skipped).  token_host / pos_host
+ * are HOST arrays; logits_out receives [n_batches, vocab] fp32 and may be pinned host
+ * memory (as in the reference, src/llama.cpp:935-936) or device memory.  Synchronises
+ * `stream` before returning, like the reference's hipDeviceSynchronize (:78). */
+int tha_forward_batch_f32(void* stream, int n_batches, const tha_config_t* cfg,
+                          const tha_weights_f32_t* w, const tha_state_t* s, const int* token_host,
+                          const int* pos_host, float* logits_out);
+/* Same step with everything resident: token_d / pos_d are DEVICE arrays, nothing is
+ * copied and nothing synchronises.  logits_d (nullable) gets [B, vocab]; next_d
+ * (nullable) gets the greedy argmax per slot (first max wins, src/llama.cpp:275-286). */
+int tha_decode_step_f32(void* stream, int n_batches, const tha_config_t* cfg,
+                        const tha_weights_f32_t* w, const tha_state_t* s, const int* token_d,
+                        const int* pos_d, float* logits_d, int* next_d);
+/* Q8_0 counterparts (runq.c:344-481 semantics; fp32 KV cache, state as above) */
+int tha_forward_batch_q8(void* stream, int n_batches, const tha_config_t* cfg,
+                         const tha_weights_q8_t* w, const tha_state_t* s, const int* token_host,
+                         const int* pos_host, float* logits_out);
+int tha_decode_step_q8(void* stream, int n_batches, const tha_config_t* cfg,
+                       const tha_weights_q8_t* w, const tha_state_t* s, const int* token_d,
+                       const int* pos_d, float* logits_d, int* next_d);
+/* greedy sampler on the device: next[b] = first argmax of logits[b, :] */
+int tha_argmax_batch_f32(void* stream, int n_batches, const float* logits, int vocab, int* next_d);
+/* number of kernels the last tha_decode_step_* call on this thread launched */
+int tha_last_step_launches(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* THA_B200_H */

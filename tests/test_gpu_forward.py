@@ -1,0 +1,159 @@
+"""Forward-pass parity on the B200 through the reference-facing call
+(thaDNN_s_forward_batch -> tha_forward_batch_*): logits and KV cache against the committed
+golden vectors (produced by the reference's run.cc / runq.c) and against the oracle on
+seeded models.  Tolerances: fp32 logits 1e-4 abs-or-rel (scripts/test/thaDNN.test.cpp:224);
+Q8_0 logits 1e-3 abs-or-rel."""
+import os
+
+import numpy as np
+import pytest
+
+from gpu_util import assert_close, engine_from_v0, engine_from_v2, small_model_files, tdev
+from pkgload import load_pkg
+
+pytestmark = pytest.mark.gpu
+
+FP32_EPS = 1e-4
+Q8_EPS = 1e-3
+
+
+def kv_of_slot(state, b):
+    return state.key_cache[b].cpu().numpy().reshape(-1), state.value_cache[b].cpu().numpy().reshape(-1)
+
+
+@pytest.mark.parametrize("name", ["tinyA", "tinyB_gqa"])
+def test_fp32_matches_reference_golden(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, f"{name}_golden.npz"))
+    e = engine_from_v0(os.path.join(golden_dir, f"{name}_v0.bin"), 1)
+    for pos, tok in enumerate(g["tokens"]):
+        logits = e.forward_batch([tok], [pos]).numpy()[0]
+        assert_close(logits, g["logits_fp32"][pos], FP32_EPS, f"{name} step {pos}")
+        assert int(logits.argmax()) == int(g["logits_fp32"][pos].argmax())
+    kc, vc = kv_of_slot(e.state, 0)
+    assert_close(kc, g["key_cache_fp32"], 1e-5, "key cache")
+    assert_close(vc, g["value_cache_fp32"], 1e-5, "value cache")
+
+
+@pytest.mark.parametrize("name", ["tinyA", "tinyB_gqa"])
+def test_q8_matches_reference_golden(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, f"{name}_golden.npz"))
+    e = engine_from_v2(os.path.join(golden_dir, f"{name}_v2.bin"), 1)
+    assert e.w.gs == int(g["group_size"])
+    for pos, tok in enumerate(g["tokens"]):
+        logits = e.forward_batch([tok], [pos]).numpy()[0]
+        assert_close(logits, g["logits_q8"][pos], Q8_EPS, f"{name} q8 step {pos}")
+    kc, vc = kv_of_slot(e.state, 0)
+    assert_close(kc, g["key_cache_q8"], Q8_EPS, "key cache")
+    assert_close(vc, g["value_cache_q8"], Q8_EPS, "value cache")
+
+
+MODELS = {
+    # exercises the fused attention kernel (head_size 32, J=2) and 3 batch-tile templates
+    "fusedA": dict(dim=256, hidden_dim=704, n_layers=3, n_heads=8, n_kv_heads=8, vocab_size=512, seq_len=48),
+    "fusedGQA": dict(dim=256, hidden_dim=704, n_layers=2, n_heads=8, n_kv_heads=2, vocab_size=320, seq_len=40),
+}
+
+
+def run_ragged(e, m, n_steps, B, rng, eps, q8=False):
+    """Slot b joins at step b (idle before: pos = -1), all slots teacher-forced with their own
+    token stream; every step compared with the oracle run of the same sequence."""
+    seqs = [m.new_seq() for _ in range(B)]
+    toks = rng.integers(0, m.vocab_size, size=(B, n_steps)).astype(np.int32)
+    flips = 0
+    for step in range(n_steps):
+        tok = np.zeros(B, np.int32); pos = np.full(B, -1, np.int32)
+        for b in range(B):
+            if step >= b:
+                pos[b] = step - b
+                tok[b] = toks[b, step - b]
+        logits = e.forward_batch(tok, pos).numpy()
+        for b in range(B):
+            if pos[b] < 0:
+                continue
+            want = seqs[b].forward(tok[b], pos[b])
+            assert_close(logits[b], want, eps, f"step {step} slot {b} pos {pos[b]}")
+            flips += int(logits[b].argmax()) != int(want.argmax())
+    for b in range(B):
+        n = (n_steps - b)
+        kc = e.state.key_cache[b].cpu().numpy()[:, :n]   # [L, n, kvd]
+        want = seqs[b].buf("key_cache").reshape(m.n_layers, m.seq_len, m.kv_dim)[:, :n]
+        assert_close(kc, want, eps, f"key cache slot {b}")
+    return flips
+
+
+@pytest.mark.parametrize("name", list(MODELS))
+@pytest.mark.parametrize("B", [1, 2, 3, 8, 11])
+def test_fp32_batched_ragged_vs_oracle(oracle, tmp_path, name, B):
+    cfg, w, v0, v2 = small_model_files(str(tmp_path), name, MODELS[name])
+    e = engine_from_v0(v0, B)
+    m = oracle.open(v0)
+    flips = run_ragged(e, m, min(cfg.seq_len, 20), B, np.random.default_rng(B), FP32_EPS)
+    assert flips == 0
+
+
+@pytest.mark.parametrize("name", list(MODELS))
+@pytest.mark.parametrize("B", [1, 4, 9])
+def test_q8_batched_ragged_vs_oracle(oracle, tmp_path, name, B):
+    cfg, w, v0, v2 = small_model_files(str(tmp_path), name, MODELS[name])
+    e = engine_from_v2(v2, B)
+    m = oracle.open(v2, quantized=True)
+    run_ragged(e, m, min(cfg.seq_len, 16), B, np.random.default_rng(B), Q8_EPS, q8=True)
+
+
+def test_modes_agree_bit_for_bit(tmp_path):
+    """CUDA graph on/off and programmatic dependent launch on/off must not change a single bit;
+    the device argmax equals the argmax of the returned logits."""
+    import torch
+    cfg, w, v0, v2 = small_model_files(str(tmp_path), "fusedA", MODELS["fusedA"])
+    lib = load_pkg("cabi").lib()
+    B, steps = 4, 10
+    rng = np.random.default_rng(0)
+    toks = rng.integers(0, cfg.vocab_size, size=(steps, B)).astype(np.int32)
+    results = {}
+    for graph in (1, 0):
+        for pdl in (1, 0):
+            lib.check(lib.c.tha_set_option(b"graph", graph)); lib.check(lib.c.tha_set_option(b"pdl", pdl))
+            e = engine_from_v0(v0, B)
+            out = []
+            nxt = torch.zeros(B, dtype=torch.int32, device="cuda")
+            lg = torch.zeros(B, cfg.vocab_size, dtype=torch.float32, device="cuda")
+            s = torch.cuda.Stream()
+            with torch.cuda.stream(s):
+                for t in range(steps):
+                    tok_d = tdev(toks[t]); pos_d = tdev(np.full(B, t, np.int32))
+                    e.decode_step(tok_d, pos_d, lg, nxt)
+                    s.synchronize()
+                    out.append(lg.cpu().numpy().copy())
+                    assert nxt.cpu().numpy().tolist() == [int(r.argmax()) for r in out[-1]]
+            results[(graph, pdl)] = np.stack(out)
+            assert e.last_step_launches() == 5 * cfg.n_layers + 3
+    lib.check(lib.c.tha_set_option(b"graph", 1)); lib.check(lib.c.tha_set_option(b"pdl", 1))
+    base = results[(0, 0)]
+    for k, v in results.items():
+        assert np.array_equal(base, v), f"mode {k} differs from plain launches"
+
+
+@pytest.mark.parametrize("B", [1, 3])
+def test_stories110m_shape_vs_oracle(oracle, tmp_path, B):
+    """The headline architecture (random-init, seeded): logits at 1e-4 like the reference's own
+    full-forward check (scripts/test/thaDNN.test.cpp:541-548)."""
+    ck = load_pkg("checkpoint")
+    cfg = ck.STORIES110M
+    w = ck.random_weights(cfg, seed=1337, std=0.05)
+    v0 = str(tmp_path / "s110m_v0.bin")
+    ck.write_v0(v0, cfg, w)
+    e = engine_from_v0(v0, B)
+    m = oracle.open(v0)
+    run_ragged(e, m, 6, B, np.random.default_rng(7), FP32_EPS)
+
+
+def test_stories110m_shape_q8_vs_oracle(oracle, tmp_path):
+    ck = load_pkg("checkpoint")
+    cfg = ck.STORIES110M
+    w = ck.random_weights(cfg, seed=1337, std=0.05)
+    v2 = str(tmp_path / "s110m_v2.bin")
+    ck.write_v2(v2, cfg, w)
+    assert os.path.getsize(v2) == 116_432_128
+    e = engine_from_v2(v2, 2)
+    m = oracle.open(v2, quantized=True)
+    run_ragged(e, m, 5, 2, np.random.default_rng(8), Q8_EPS, q8=True)
