@@ -1,0 +1,401 @@
+#!/usr/bin/env python
+"""Headline benchmark: batched greedy decode tok/s of the stories110M architecture (fp32) on
+N B200s, sequences sharded over GPUs (replicated weights, no collective) -- BASELINE.json
+configs[1] -- with the HBM roofline of the decode step and the reference's CPU path beside it.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--model s110m|7b] [--quant f32|q8]
+    python bench.py --impl reference ...     # the reference's own CPU code (oracle/_ref) on the host cores
+
+One "step" = one decode position for every one of the B slots of a GPU (one call of
+thaDNN_s_forward_batch in the reference, src/thaDNN.cpp:13-81).
+
+  value      tokens/s, everything resident in HBM: token/pos on the device, greedy argmax and
+             slot bookkeeping on the device, one CUDA-graph replay per step.
+  e2e        tokens/s through the reference-facing call (tha_forward_batch_*: HOST token[] /
+             pos[] in, [B, vocab] logits into pinned HOST memory, host argmax), copies inside
+             the timed region.
+  roofline   algorithmic bytes of a decode step (weights once + KV rows read +
+             KV rows written + embedding rows + logits) / measured step time, against the
+             measured HBM copy bandwidth in MEASURED_PEAKS.json.
+  cpu_baseline  oracle/_ref (the reference's run.cc / runq.c compiled unmodified) on the
+             box's host cores, bounded sample.
+Data is synthetic: seeded random-init weights of the named architecture (no network, no
+checkpoint on the box), random prompt tokens.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "decode_tok_per_s"
+UNIT = "tok/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=256)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=int(os.environ.get("THA_BENCH_BATCH", "8")), help="slots per GPU")
+    ap.add_argument("--model", default="s110m", choices=["s110m", "s15m", "7b"])
+    ap.add_argument("--quant", default="f32", choices=["f32", "q8"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def model_config(name):
+    from pkgload import load_pkg
+    ck = load_pkg("checkpoint")
+    return {"s110m": ck.STORIES110M, "s15m": ck.STORIES15M, "7b": ck.LLAMA2_7B}[name], ck
+
+
+def model_label(name):
+    return {"s110m": "stories110M", "s15m": "stories15M", "7b": "Llama-2-7B"}[name]
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def step_bytes(cfg, weight_bytes, pos, B, elem_bytes_emb=4, write_logits=True):
+    """ALGORITHMIC bytes of one decode step with every slot at position `pos`."""
+    kv = 2 * cfg.n_layers * cfg.kv_dim * 4
+    b = weight_bytes + B * (kv * (pos + 1) + kv) + B * cfg.dim * elem_bytes_emb
+    if write_logits:
+        b += B * cfg.vocab_size * 4
+    return b
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------ model on the device ----
+def build_weights(args, device):
+    """Seeded random-init weights of the named architecture, resident in HBM.
+    Returns (cfg, device weights, host weight dict or None)."""
+    from pkgload import load_pkg
+    import torch
+    cfg, ck = model_config(args.model)
+    eng = load_pkg("engine")
+    if args.model == "7b":
+        # 26 GB of fp32 host RNG is too slow for a bench; fill on the device (same N(0, 0.02) law)
+        return cfg, eng.device_random_weights(cfg, q8=(args.quant == "q8"), seed=1337, device=device), None
+    w = ck.random_weights(cfg, seed=1337, std=0.02)
+    if args.quant == "q8":
+        gs = ck.v2_group_size(cfg)
+        qt = {}
+        for n in ck.V2_QORDER:
+            t = w[n]
+            if n == "tok_emb":
+                q, s = ck.quantize_q80(t, gs)
+                qt[n] = (q.reshape(t.shape), s)
+            else:
+                qs, ss = zip(*[ck.quantize_q80(t[l], gs) for l in range(cfg.n_layers)])
+                qt[n] = (np.stack(qs).reshape(t.shape), np.stack(ss))
+        qt["wcls"] = qt["tok_emb"]
+        norms = {k: w[k] for k in ("rms_att", "rms_ffn", "rms_final")}
+        return cfg, eng.DeviceWeightsQ8(cfg, gs, norms, qt, device=device), w
+    return cfg, eng.DeviceWeights(cfg, w, device=device), w
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from pkgload import load_pkg
+    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    device = f"cuda:{local_rank}"
+    eng = load_pkg("engine")
+    cfg, dw, host_w = build_weights(args, device)
+    B, K, W = args.batch, args.steps, args.warmup
+    if W + K + 1 > cfg.seq_len:
+        raise SystemExit(f"warmup+steps must stay below seq_len={cfg.seq_len}")
+    e = eng.Engine(dw, B, device=device, with_att=False)
+    wbytes = dw.nbytes()
+    rng = np.random.default_rng(1234 + rank)
+    tok0 = rng.integers(3, cfg.vocab_size, size=B).astype(np.int32)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- resident loop: value + roofline ----------------
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        tok = torch.from_numpy(tok0).to(device)
+        pos = torch.zeros(B, dtype=torch.int32, device=device)
+        nxt = torch.zeros(B, dtype=torch.int32, device=device)
+        logits = torch.zeros(B, cfg.vocab_size, dtype=torch.float32, device=device)
+
+        def step():
+            e.decode_step(tok, pos, logits, nxt, stream=stream)
+            e.advance(tok, pos, nxt, stream=stream)
+
+        for _ in range(W):
+            step()
+        stream.synchronize()
+        launches_per_step = e.last_step_launches() + 1
+        sampler = ClockSampler(local_rank)
+        barrier()
+        if rank == 0:
+            sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for _ in range(K):
+            step()
+        ev1.record(stream)
+        stream.synchronize()
+        barrier()
+        clocks = sampler.stop() if rank == 0 else None
+        ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_max = float(t.item())
+    else:
+        ms_max = ms
+    value = world * B * K / (ms_max * 1e-3)
+    # algorithmic bytes of the timed steps on this rank (positions W .. W+K-1)
+    total_bytes = sum(step_bytes(cfg, wbytes, p, B) for p in range(W, W + K))
+    achieved = total_bytes / (ms * 1e-3) / 1e9
+    peak, peak_src = measured_peak()
+
+    # ---------------- e2e: the reference-facing call with HOST buffers ----------------
+    e2e = None
+    if not args.no_e2e:
+        lg_host = torch.empty(B, cfg.vocab_size, dtype=torch.float32).pin_memory()
+        tok_h = tok0.copy()
+        pos_h = np.zeros(B, np.int32)
+        lg_np = lg_host.numpy()
+        Ke = min(K, 128)
+
+        def estep():
+            e.forward_batch(tok_h, pos_h, lg_host, stream=stream)   # H2D token/pos, step, D2H logits, sync
+            tok_h[:] = lg_np.argmax(axis=1)                         # greedy sampler on the host, as the driver does
+            pos_h[:] += 1
+
+        for _ in range(W):
+            estep()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(Ke):
+            estep()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], dtype=torch.float64, device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e2e = {"value": world * B * Ke / dt, "unit": UNIT, "h2d_bytes_per_step": int(2 * 4 * B),
+               "d2h_bytes_per_step": int(B * cfg.vocab_size * 4), "steps": Ke,
+               "api": "tha_forward_batch_%s (thaDNN_s_forward_batch)" % args.quant}
+    return dict(cfg=cfg, value=value, ms_per_step=ms_max / K, achieved=achieved, peak=peak, peak_src=peak_src,
+                bytes_per_step=total_bytes / K, wbytes=wbytes, clocks=clocks, e2e=e2e,
+                launches=launches_per_step * K, launches_per_step=launches_per_step, host_w=host_w)
+
+
+# ------------------------------------------------------------------ the reference's CPU path ----
+def cpu_reference(args, cfg, host_w, n_seqs, n_threads, max_steps, warmup, budget_s):
+    """Time oracle/_ref (run.cc / runq.c compiled unmodified; -O3 -mavx2 -mfma build) on the host.
+    fp32: run.cc has no OpenMP pragma, so threads run independent sequences (one forward() each per
+    step, the reference driver's one-thread-per-replica scheme); q8: runq.c's own OpenMP matmul.
+    Returns (tok/s, steps timed, kind, threads used)."""
+    from oracle_lib import Ref32, RefQ8, ref_available, cpu_has_avx2_fma
+    from pkgload import load_pkg
+    ck = load_pkg("checkpoint")
+    q8 = args.quant == "q8"
+    kindname = "q8" if q8 else "fp32"
+    fast = cpu_has_avx2_fma() and ref_available(kindname, fast=True)
+    if not ref_available(kindname, fast=fast):
+        raise RuntimeError("oracle/_ref is not built (run __graft_entry__.build() where /root/reference exists)")
+    if host_w is None:
+        host_w = ck.random_weights(cfg, seed=1337, std=0.02)
+    with tempfile.TemporaryDirectory() as td:
+        path = os.path.join(td, "model.bin")
+        (ck.write_v2 if q8 else ck.write_v0)(path, cfg, host_w)
+        ref = (RefQ8 if q8 else Ref32)(fast=fast)
+        h0, _ = ref.open(path)
+        hs = [h0] + [ref.lib.refq8_clone(h0) if q8 else ref.lib.ref32_clone(h0) for _ in range(n_seqs - 1)]
+        rng = np.random.default_rng(1234)
+        tok = rng.integers(3, cfg.vocab_size, size=n_seqs).astype(np.int32)
+        pos = np.zeros(n_seqs, np.int32)
+        vocab = cfg.vocab_size
+        import ctypes as C
+
+        def one_step():
+            ref.forward_many(hs, tok, pos, n_threads)
+            for i, h in enumerate(hs):   # greedy sampler (sample_argmax, run.cc:619-630)
+                lg = ref.lib.refq8_state_ptr(h, 7) if q8 else ref.lib.ref32_state_ptr(h, 7)
+                tok[i] = (ref.lib.refq8_argmax if q8 else ref.lib.ref32_argmax)(lg, vocab)
+            pos[:] += 1
+
+        if q8:
+            ref.lib.refq8_argmax.restype = C.c_int
+            ref.lib.refq8_argmax.argtypes = [C.POINTER(C.c_float), C.c_int]
+        for _ in range(warmup):
+            one_step()
+        t0 = time.perf_counter()
+        done = 0
+        while done < max_steps:
+            one_step()
+            done += 1
+            if budget_s and time.perf_counter() - t0 > budget_s:
+                break
+        dt = time.perf_counter() - t0
+    return n_seqs * done / dt, done, ("reference" if True else "port"), n_threads, fast
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def base_line(args, cfg, world):
+    B = args.batch
+    return {
+        "metric": METRIC, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if args.quant == "f32" else "int8+f32", "data": "synthetic",
+        "config": {
+            "workload": f"{model_label(args.model)} {'fp32' if args.quant == 'f32' else 'Q8_0'} batched greedy decode, "
+                        f"{B} slots per GPU, positions {args.warmup}..{args.warmup + args.steps - 1}, "
+                        "sequences sharded over GPUs (replicated weights, no collective)",
+            "batch_per_gpu": B, "global_batch": B * world, "vocab": cfg.vocab_size, "seq_len": cfg.seq_len,
+            "weights": "seeded random-init N(0,0.02) of the named architecture",
+            "l2": "inputs larger than L2 (weights read once per step: %d MB > 126 MB L2); no flush" %
+                  (0,),
+        },
+    }
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    cfg, _ = model_config(args.model)
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        cores = host_cores()
+        n_seqs = min(args.batch * max(world, 1), 2 * cores)
+        threads = cores if args.quant == "q8" else min(cores, n_seqs)
+        v, done, kind, used, fast = cpu_reference(args, cfg, None, n_seqs, threads, args.steps, min(args.warmup, 2), 150.0)
+        line = base_line(args, cfg, world)
+        sample = (f"{n_seqs} sequences x {done} greedy decode positions from pos 0 through oracle/_ref "
+                  f"({'runq.c' if args.quant == 'q8' else 'run.cc'} compiled unmodified, "
+                  f"{'-O3 -mavx2 -mfma' if fast else '-O2'}), {used} host threads")
+        line.update({"impl": "reference", "value": v, "ms_per_step": 1e3 * n_seqs / v, "steps": done,
+                     "cpu_baseline": {"value": v, "unit": UNIT, "cores": used, "kind": kind, "sample": sample},
+                     "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                     "gpu_launches": 0})
+        line["config"]["l2"] = "n/a (CPU)"
+        print(json.dumps(line), flush=True)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    r = run_ours(args, rank, world, local_rank)
+    if rank == 0:
+        line = base_line(args, cfg, world)
+        line["config"]["l2"] = ("inputs larger than L2: %.0f MB of weights streamed once per step vs 126 MB L2; no flush"
+                                % (r["wbytes"] / 1e6)) if r["wbytes"] > 126e6 else \
+            "weights (%.0f MB) fit the 126 MB L2: number is L2-assisted, not an HBM figure" % (r["wbytes"] / 1e6)
+        line.update({"value": r["value"], "ms_per_step": r["ms_per_step"], "e2e": r["e2e"],
+                     "gpu_launches": r["launches"], "clocks": r["clocks"]})
+        line["roofline"] = {"bound": "hbm", "achieved": r["achieved"], "peak": r["peak"], "unit": "GB/s",
+                            "frac": r["achieved"] / r["peak"], "traffic": None,
+                            "kernel": "decode step (%d kernels per step, CUDA-graph replay)" % r["launches_per_step"],
+                            "bytes_per_step": r["bytes_per_step"], "peak_source": r["peak_src"],
+                            "frac_of_nominal_8TBs": r["achieved"] / 8000.0}
+        if not args.no_cpu_baseline:
+            try:
+                if args.model == "7b":
+                    raise RuntimeError("7B CPU sample skipped (26 GB checkpoint on tmpfs)")
+                nth = 1 if args.quant == "f32" else host_cores()
+                v, done, kind, used, fast = cpu_reference(args, cfg, r["host_w"], 1, nth, 64, 1, args.cpu_seconds)
+                line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": used, "kind": kind,
+                                        "sample": f"1 sequence x {done} greedy decode positions from pos 0, oracle/_ref "
+                                                  f"({'runq.c' if args.quant == 'q8' else 'run.cc'} unmodified, "
+                                                  f"{'-O3 -mavx2 -mfma' if fast else '-O2'}); run.cc has no OpenMP pragma"}
+            except Exception as ex:  # the checker being absent must not hide the GPU number
+                line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

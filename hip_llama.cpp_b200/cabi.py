@@ -92,6 +92,7 @@ class Lib:
             "tha_forward_batch_q8": [vp, I, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), vp, vp, vp],
             "tha_decode_step_q8": [vp, I, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), vp, vp, vp, vp],
             "tha_argmax_batch_f32": [vp, I, vp, I, vp],
+            "tha_advance_slots": [vp, I, vp, vp, vp, I],
             "tha_malloc": [C.POINTER(vp), C.c_size_t],
             "tha_free": [vp],
             "tha_stream_create": [C.POINTER(vp)],

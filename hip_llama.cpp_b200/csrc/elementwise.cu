@@ -149,6 +149,20 @@ __global__ void quantize_q8_kernel(int8_t* __restrict__ q, float* __restrict__ s
   }
 }
 
+// Greedy decode bookkeeping on the device (the reference does this on the host,
+// src/llama.cpp:1027-1050): token[b] = next[b]; pos[b] += 1 for active slots.
+__global__ void advance_slots_kernel(int B, int* __restrict__ token, int* __restrict__ pos,
+                                     const int* __restrict__ next, int seq_len) {
+  pdl_wait();
+  pdl_trigger();
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  int p = pos[b];
+  if (p < 0) return;
+  token[b] = next[b];
+  pos[b] = (p + 1 < seq_len) ? p + 1 : -1;   // a slot that ran out of context goes idle
+}
+
 int embed_launch(cudaStream_t st, int B, float* x, const float* table, const int* token, const int* pos, int dim, bool pdl) {
   THA_CUDA_OK(launch(embed_kernel, dim3(B), dim3(256), 0, st, pdl, x, table, token, pos, dim));
   return THA_STATUS_SUCCESS;
@@ -218,6 +232,13 @@ extern "C" int tha_softmax_f32(void* stream, float* x, int size) {
 extern "C" int tha_argmax_batch_f32(void* stream, int n_batches, const float* logits, int vocab, int* next_d) {
   if (n_batches <= 0 || vocab <= 0 || !logits || !next_d) return THA_STATUS_INVALID_ARG;
   return argmax_launch((cudaStream_t)stream, n_batches, logits, vocab, next_d, false);
+}
+
+extern "C" int tha_advance_slots(void* stream, int n_batches, int* token_d, int* pos_d, const int* next_d, int seq_len) {
+  if (n_batches <= 0 || !token_d || !pos_d || !next_d) return THA_STATUS_INVALID_ARG;
+  THA_CUDA_OK(launch(advance_slots_kernel, dim3(ceil_div(n_batches, 128)), dim3(128), 0, (cudaStream_t)stream, false,
+                     n_batches, token_d, pos_d, next_d, seq_len));
+  return THA_STATUS_SUCCESS;
 }
 
 extern "C" int tha_quantize_q8(void* stream, int8_t* q, float* s, const float* x, int n, int gs) {

@@ -149,5 +149,11 @@ class Engine:
                 _ptr(token_d), _ptr(pos_d), _ptr(logits_d), _ptr(next_d))
         self.lib.check(st, "tha_decode_step")
 
+    def advance(self, token_d, pos_d, next_d, stream=None):
+        """Device-side greedy bookkeeping: token = next, pos += 1 (src/llama.cpp:1027-1050)."""
+        st = self.lib.c.tha_advance_slots(_stream_ptr(stream), self.B, _ptr(token_d), _ptr(pos_d), _ptr(next_d),
+                                          self.cfg.seq_len)
+        self.lib.check(st, "tha_advance_slots")
+
     def last_step_launches(self) -> int:
         return self.lib.c.tha_last_step_launches()

@@ -179,6 +179,9 @@ int tha_decode_step_q8(void* stream, int n_batches, const tha_config_t* cfg,
                        const int* pos_d, float* logits_d, int* next_d);
 /* greedy sampler on the device: next[b] = first argmax of logits[b, :] */
 int tha_argmax_batch_f32(void* stream, int n_batches, const float* logits, int vocab, int* next_d);
+/* greedy bookkeeping of the batching driver (src/llama.cpp:1027-1050) kept on the device:
+ * token_d[b] = next_d[b], pos_d[b] += 1 (a slot reaching seq_len goes idle: pos = -1) */
+int tha_advance_slots(void* stream, int n_batches, int* token_d, int* pos_d, const int* next_d, int seq_len);
 /* number of kernels the last tha_decode_step_* call on this thread launched */
 int tha_last_step_launches(void);
 

@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
-from gpu_util import P, assert_close, stream_ptr, tdev
+from gpu_util import assert_close_scaled, P, assert_close, stream_ptr, tdev
 from pkgload import load_pkg
 
 pytestmark = pytest.mark.gpu
@@ -276,5 +276,7 @@ def test_matmul_batch_q8(L, oracle, M, K, gs, B):
     sync()
     got = O.cpu().numpy()
     for b in range(B):
-        # integer group sums are exact; only the fp32 accumulation order over groups differs
-        assert_close(got[b], oracle.matmul_q8(wq, ws, xq[b], xs[b], gs), 1e-5, f"q8 matmul b{b}")
+        # integer group sums are exact; only the fp32 accumulation order over the K/gs group terms
+        # differs (two rows' lanes add in a tree, the CPU adds left to right): a few ulps of the
+        # largest partial sum, so the bound is stated relative to the output scale
+        assert_close_scaled(got[b], oracle.matmul_q8(wq, ws, xq[b], xs[b], gs), 4e-6, f"q8 matmul b{b}")
