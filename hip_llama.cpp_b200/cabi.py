@@ -89,6 +89,7 @@ class Lib:
             "tha_matmul_batch_q8": [vp, I, vp, I, vp, vp, vp, vp, I, I, I],
             "tha_forward_batch_f32": [vp, I, C.POINTER(Config), C.POINTER(WeightsF32), C.POINTER(State), vp, vp, vp],
             "tha_decode_step_f32": [vp, I, C.POINTER(Config), C.POINTER(WeightsF32), C.POINTER(State), vp, vp, vp, vp],
+            "tha_decode_greedy_f32": [vp, I, C.POINTER(Config), C.POINTER(WeightsF32), C.POINTER(State), vp, vp, vp, vp],
             "tha_forward_batch_q8": [vp, I, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), vp, vp, vp],
             "tha_decode_step_q8": [vp, I, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), vp, vp, vp, vp],
             "tha_argmax_batch_f32": [vp, I, vp, I, vp],

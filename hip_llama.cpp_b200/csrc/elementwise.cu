@@ -163,6 +163,10 @@ __global__ void advance_slots_kernel(int B, int* __restrict__ token, int* __rest
   pos[b] = (p + 1 < seq_len) ? p + 1 : -1;   // a slot that ran out of context goes idle
 }
 
+int advance_launch(cudaStream_t st, int B, int* token, int* pos, const int* next, int seq_len, bool pdl) {
+  THA_CUDA_OK(launch(advance_slots_kernel, dim3(ceil_div(B, 128)), dim3(128), 0, st, pdl, B, token, pos, next, seq_len));
+  return THA_STATUS_SUCCESS;
+}
 int embed_launch(cudaStream_t st, int B, float* x, const float* table, const int* token, const int* pos, int dim, bool pdl) {
   THA_CUDA_OK(launch(embed_kernel, dim3(B), dim3(256), 0, st, pdl, x, table, token, pos, dim));
   return THA_STATUS_SUCCESS;

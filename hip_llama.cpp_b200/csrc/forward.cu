@@ -29,12 +29,21 @@ int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_
                       int head_size, int seq_len, bool pdl);
 int launches_reset();
 int launches_get();
+// megastep.cu: the whole step as one persistent kernel (small models, B <= 8)
+int mega_enabled();
+void mega_set_enabled(int v);
+bool mega_supported(const tha_config_t* c, int B);
+int mega_step_launch(cudaStream_t st, Workspace* ws, int B, const tha_config_t* cfg, const tha_weights_f32_t* w,
+                     const tha_state_t* s, int* token_d, int* pos_d, float* logits_d, int* next_d, int advance,
+                     const float* rope_cos, const float* rope_sin, bool prepare_only);
+int mega_check_abort(int dev);
+int advance_launch(cudaStream_t st, int B, int* token, int* pos, const int* next, int seq_len, bool pdl);
 
 static thread_local int g_last_step_launches = 0;
 
 struct StepArgs {
   int B; tha_config_t cfg; tha_weights_f32_t w; tha_state_t s;
-  const int* token_d; const int* pos_d; float* logits_d; int* next_d; int pdl;
+  const int* token_d; const int* pos_d; float* logits_d; int* next_d; int pdl; int mega; int advance;
 };
 
 static unsigned long long fnv1a(const void* data, size_t n, unsigned long long h = 1469598103934665603ull) {
@@ -150,14 +159,29 @@ static int validate_f32(int B, const tha_config_t* c, const tha_weights_f32_t* w
 }
 
 int decode_step_f32(cudaStream_t st, int B, const tha_config_t* cfg, const tha_weights_f32_t* w, const tha_state_t* s,
-                    const int* token_d, const int* pos_d, float* logits_d, int* next_d) {
+                    const int* token_d, const int* pos_d, float* logits_d, int* next_d, int advance) {
   THA_TRY(validate_f32(B, cfg, w, s));
   if (!token_d || !pos_d || (!logits_d && !s->logits)) return THA_STATUS_INVALID_ARG;
+  if (advance && !next_d) return THA_STATUS_INVALID_ARG;
   Workspace* ws = workspace();
   if (!ws) return THA_STATUS_EXECUTION_FAILED;
   const int hs = cfg->dim / cfg->n_heads, kvd = hs * cfg->n_kv_heads;
   const float *rc, *rs;
   THA_TRY(ws_rope(ws, hs, cfg->seq_len, &rc, &rs));
+  StepArgs a;
+  memset(&a, 0, sizeof(a));
+  a.B = B; a.cfg = *cfg; a.w = *w; a.s = *s; a.token_d = token_d; a.pos_d = pos_d; a.logits_d = logits_d;
+  a.next_d = next_d; a.pdl = pdl_enabled(); a.advance = advance;
+  a.mega = mega_enabled() && mega_supported(cfg, B);
+  if (a.mega) {
+    // scratch is grown outside any capture; the kernel writes logits only where the caller wants them
+    THA_TRY(mega_step_launch(st, ws, B, cfg, w, s, nullptr, nullptr, nullptr, nullptr, 0, rc, rs, true));
+    float* lg = logits_d ? logits_d : (next_d ? nullptr : s->logits);
+    return run_step(st, ws, &a, sizeof(a), [&]() {
+      return mega_step_launch(st, ws, B, cfg, w, s, const_cast<int*>(token_d), const_cast<int*>(pos_d), lg, next_d,
+                              advance, rc, rs, false);
+    });
+  }
   const bool fused = attn_fused_supported(cfg->n_heads, hs, cfg->dim, kvd);
   if (!fused && !s->att) return THA_STATUS_INVALID_ARG;
   if (fused) {  // grow the split scratch now: no allocation may happen inside a capture
@@ -167,12 +191,11 @@ int decode_step_f32(cudaStream_t st, int B, const tha_config_t* cfg, const tha_w
     const int nsplit = attn_fused_nsplit(B, nseg, cfg->seq_len);
     if (nsplit > 1) THA_TRY(ws_ensure_attn(ws, (size_t)B * nseg * nsplit * 32 * J, B * nseg));
   }
-  StepArgs a;
-  memset(&a, 0, sizeof(a));
-  a.B = B; a.cfg = *cfg; a.w = *w; a.s = *s; a.token_d = token_d; a.pos_d = pos_d; a.logits_d = logits_d;
-  a.next_d = next_d; a.pdl = pdl_enabled();
-
-  return run_step(st, ws, &a, sizeof(a), [&]() { return issue_step_f32(st, ws, a, rc, rs); });
+  return run_step(st, ws, &a, sizeof(a), [&]() {
+    THA_TRY(issue_step_f32(st, ws, a, rc, rs));
+    if (advance) THA_TRY(advance_launch(st, B, const_cast<int*>(token_d), const_cast<int*>(pos_d), next_d, cfg->seq_len, a.pdl != 0));
+    return (int)THA_STATUS_SUCCESS;
+  });
 }
 
 // ---------------------------------------------------------------------------- Q8_0 ----
@@ -298,6 +321,10 @@ static int forward_host(cudaStream_t st, int B, int vocab, float* state_logits, 
   if (target != logits_out)
     THA_CUDA_OK(cudaMemcpyAsync(logits_out, target, (size_t)B * vocab * sizeof(float), cudaMemcpyDefault, st));
   THA_CUDA_OK(cudaStreamSynchronize(st));
+  if (mega_check_abort(ws->device)) {
+    set_last_error("persistent step kernel: a barrier wait timed out", cudaErrorLaunchTimeout);
+    return THA_STATUS_EXECUTION_FAILED;
+  }
   return THA_STATUS_SUCCESS;
 }
 
@@ -308,7 +335,12 @@ using namespace tha;
 extern "C" int tha_decode_step_f32(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_f32_t* w,
                                    const tha_state_t* s, const int* token_d, const int* pos_d, float* logits_d,
                                    int* next_d) {
-  return decode_step_f32((cudaStream_t)stream, n_batches, cfg, w, s, token_d, pos_d, logits_d, next_d);
+  return decode_step_f32((cudaStream_t)stream, n_batches, cfg, w, s, token_d, pos_d, logits_d, next_d, 0);
+}
+
+extern "C" int tha_decode_greedy_f32(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_f32_t* w,
+                                     const tha_state_t* s, int* token_d, int* pos_d, float* logits_d, int* next_d) {
+  return decode_step_f32((cudaStream_t)stream, n_batches, cfg, w, s, token_d, pos_d, logits_d, next_d, 1);
 }
 
 extern "C" int tha_forward_batch_f32(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_f32_t* w,
@@ -318,7 +350,7 @@ extern "C" int tha_forward_batch_f32(void* stream, int n_batches, const tha_conf
   cudaStream_t st = (cudaStream_t)stream;
   return forward_host(st, n_batches, cfg->vocab_size, s->logits, token_host, pos_host, logits_out,
                       [&](const int* tok_d, const int* pos_d, float* target) {
-                        return decode_step_f32(st, n_batches, cfg, w, s, tok_d, pos_d, target, nullptr);
+                        return decode_step_f32(st, n_batches, cfg, w, s, tok_d, pos_d, target, nullptr, 0);
                       });
 }
 

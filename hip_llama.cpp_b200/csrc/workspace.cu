@@ -10,6 +10,8 @@
 
 namespace tha {
 
+void mega_set_enabled(int v);
+
 static thread_local char g_err[512] = "";
 static thread_local int g_launches = 0;
 static int g_pdl = -1, g_graph = -1;
@@ -124,5 +126,6 @@ extern "C" int tha_set_option(const char* name, int value) {
   if (!name) return THA_STATUS_INVALID_ARG;
   if (!strcmp(name, "pdl")) { *tha::opt_pdl() = value != 0; return THA_STATUS_SUCCESS; }
   if (!strcmp(name, "graph")) { *tha::opt_graph() = value != 0; return THA_STATUS_SUCCESS; }
+  if (!strcmp(name, "mega")) { tha::mega_set_enabled(value); return THA_STATUS_SUCCESS; }
   return THA_STATUS_INVALID_ARG;
 }

@@ -149,6 +149,18 @@ class Engine:
                 _ptr(token_d), _ptr(pos_d), _ptr(logits_d), _ptr(next_d))
         self.lib.check(st, "tha_decode_step")
 
+    def decode_greedy(self, token_d, pos_d, next_d, logits_d=None, stream=None):
+        """Resident greedy step: the step, the argmax and the slot bookkeeping (token = next,
+        pos += 1) without leaving the device -- one launch where the persistent kernel applies."""
+        if self.q8:
+            self.decode_step(token_d, pos_d, logits_d, next_d, stream)
+            self.advance(token_d, pos_d, next_d, stream)
+            return
+        st = self.lib.c.tha_decode_greedy_f32(_stream_ptr(stream), self.B, C.byref(self.ccfg), C.byref(self.w.c),
+                                              C.byref(self.state.c), _ptr(token_d), _ptr(pos_d), _ptr(logits_d),
+                                              _ptr(next_d))
+        self.lib.check(st, "tha_decode_greedy")
+
     def advance(self, token_d, pos_d, next_d, stream=None):
         """Device-side greedy bookkeeping: token = next, pos += 1 (src/llama.cpp:1027-1050)."""
         st = self.lib.c.tha_advance_slots(_stream_ptr(stream), self.B, _ptr(token_d), _ptr(pos_d), _ptr(next_d),

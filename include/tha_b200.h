@@ -72,7 +72,7 @@ typedef struct {
 /* ---- library ---------------------------------------------------------------- */
 int tha_version(void);
 const char* tha_last_error(void);       /* text of the last CUDA error seen by this library */
-int tha_set_option(const char* name, int value); /* "pdl" (0/1), "graph" (0/1) */
+int tha_set_option(const char* name, int value); /* "pdl", "graph", "mega" (0/1) */
 
 /* ---- runtime shim: the only way the C++ host layer touches the CUDA runtime ---------
  * (reference: hipSetDevice / hipMalloc / hipMemcpy / hipHostMalloc / hipStreamCreate /
@@ -170,6 +170,13 @@ int tha_forward_batch_f32(void* stream, int n_batches, const tha_config_t* cfg,
 int tha_decode_step_f32(void* stream, int n_batches, const tha_config_t* cfg,
                         const tha_weights_f32_t* w, const tha_state_t* s, const int* token_d,
                         const int* pos_d, float* logits_d, int* next_d);
+/* The greedy loop of the batching driver kept on the device: the step above with
+ * next_d, then token_d[b] = next_d[b] and pos_d[b] += 1 (src/llama.cpp:1027-1050); a slot
+ * that reaches seq_len goes idle (pos = -1).  One kernel launch per step for models the
+ * persistent step kernel covers (B <= 8, dim <= 1024, hidden_dim <= 2048). */
+int tha_decode_greedy_f32(void* stream, int n_batches, const tha_config_t* cfg,
+                          const tha_weights_f32_t* w, const tha_state_t* s, int* token_d,
+                          int* pos_d, float* logits_d, int* next_d);
 /* Q8_0 counterparts (runq.c:344-481 semantics; fp32 KV cache, state as above) */
 int tha_forward_batch_q8(void* stream, int n_batches, const tha_config_t* cfg,
                          const tha_weights_q8_t* w, const tha_state_t* s, const int* token_host,
