@@ -354,7 +354,54 @@ extern "C" int tha_forward_batch_f32(void* stream, int n_batches, const tha_conf
                       });
 }
 
+// Greedy variant of the host-facing step: argmax on the device, B ints back instead of B*vocab floats.
+template <typename StepFn>
+static int forward_host_greedy(cudaStream_t st, int B, const int* token_host, const int* pos_host, int* next_host,
+                               StepFn step) {
+  if (B <= 0 || !token_host || !pos_host || !next_host) return THA_STATUS_INVALID_ARG;
+  Workspace* ws = workspace();
+  if (!ws) return THA_STATUS_EXECUTION_FAILED;
+  THA_TRY(ws_ensure_tokpos(ws, B));
+  const int cap = ws->tokpos_cap;
+  memcpy(ws->tokpos_h, token_host, B * sizeof(int));
+  memcpy(ws->tokpos_h + cap, pos_host, B * sizeof(int));
+  THA_CUDA_OK(cudaMemcpyAsync(ws->tok_d, ws->tokpos_h, 2 * cap * sizeof(int), cudaMemcpyHostToDevice, st));
+  THA_TRY(step(ws->tok_d, ws->pos_d, ws->next_d));
+  THA_CUDA_OK(cudaMemcpyAsync(ws->next_h, ws->next_d, B * sizeof(int), cudaMemcpyDeviceToHost, st));
+  THA_CUDA_OK(cudaStreamSynchronize(st));
+  if (mega_check_abort(ws->device)) {
+    set_last_error("persistent step kernel: a barrier wait timed out", cudaErrorLaunchTimeout);
+    return THA_STATUS_EXECUTION_FAILED;
+  }
+  memcpy(next_host, ws->next_h, B * sizeof(int));
+  return THA_STATUS_SUCCESS;
+}
+
+extern "C" int tha_forward_greedy_f32(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_f32_t* w,
+                                      const tha_state_t* s, const int* token_host, const int* pos_host, int* next_host) {
+  cudaStream_t st = (cudaStream_t)stream;
+  return forward_host_greedy(st, n_batches, token_host, pos_host, next_host,
+                             [&](const int* tok_d, const int* pos_d, int* next_d) {
+                               return decode_step_f32(st, n_batches, cfg, w, s, tok_d, pos_d, nullptr, next_d, 0);
+                             });
+}
+
+extern "C" int tha_forward_greedy_q8(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_q8_t* w,
+                                     const tha_state_t* s, const int* token_host, const int* pos_host, int* next_host) {
+  cudaStream_t st = (cudaStream_t)stream;
+  return forward_host_greedy(st, n_batches, token_host, pos_host, next_host,
+                             [&](const int* tok_d, const int* pos_d, int* next_d) {
+                               return decode_step_q8(st, n_batches, cfg, w, s, tok_d, pos_d, nullptr, next_d);
+                             });
+}
+
 extern "C" int tha_last_step_launches(void) { return last_step_launches_get(); }
+
+extern "C" int tha_step_needs_att_scratch(const tha_config_t* cfg) {
+  if (!cfg || cfg->n_heads <= 0 || cfg->dim % cfg->n_heads) return 1;
+  const int hs = cfg->dim / cfg->n_heads;
+  return attn_fused_supported(cfg->n_heads, hs, cfg->dim, hs * cfg->n_kv_heads) ? 0 : 1;
+}
 
 extern "C" int tha_decode_step_q8(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_q8_t* w,
                                   const tha_state_t* s, const int* token_d, const int* pos_d, float* logits_d,

@@ -76,9 +76,11 @@ int ws_ensure_tokpos(Workspace* ws, int n_batches) {
   if (n_batches <= ws->tokpos_cap) return THA_STATUS_SUCCESS;
   if (ws->tok_d) { cudaFree(ws->tok_d); cudaFreeHost(ws->tokpos_h); }
   int cap = n_batches < 64 ? 64 : n_batches * 2;
-  THA_CUDA_OK(cudaMalloc(&ws->tok_d, 2 * cap * sizeof(int)));   // [tok | pos]
+  THA_CUDA_OK(cudaMalloc(&ws->tok_d, 3 * cap * sizeof(int)));   // [tok | pos | next]
   ws->pos_d = ws->tok_d + cap;
-  THA_CUDA_OK(cudaMallocHost(&ws->tokpos_h, 2 * cap * sizeof(int)));
+  ws->next_d = ws->tok_d + 2 * cap;
+  THA_CUDA_OK(cudaMallocHost(&ws->tokpos_h, 3 * cap * sizeof(int)));
+  ws->next_h = ws->tokpos_h + 2 * cap;
   ws->tokpos_cap = cap;
   ws->graphs.clear();
   return THA_STATUS_SUCCESS;

@@ -24,6 +24,7 @@ struct Workspace {
   int* counters = nullptr; int counters_cap = 0;
   // device mirrors of the host token[] / pos[] arrays of thaDNN_s_forward_batch
   int* tok_d = nullptr; int* pos_d = nullptr; int* tokpos_h = nullptr; int tokpos_cap = 0;
+  int* next_d = nullptr; int* next_h = nullptr;   // greedy token per slot (device, pinned host)
   // RoPE cos/sin tables keyed by (head_size, seq_len); built on the host with libm so
   // they are bit-identical to what run.cc:271-277 computes
   std::map<std::pair<int, int>, RopeTable> rope;

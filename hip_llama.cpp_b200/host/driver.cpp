@@ -1,0 +1,218 @@
+// The batching driver (reference: test_data_parallelism, src/llama.cpp:891-1083) and request
+// file IO (:424-505).
+//
+// Same control flow as the reference -- one host thread per GPU, replicated weights, requests
+// pulled from one shared queue, B slots per GPU refilled as requests finish, prompts forced
+// token by token, stop on BOS/EOS or seq_len, gen_cnt += pos - 1 -- with these differences:
+//   * slot state lives in a BatchManager (slot table + KV block accounting);
+//   * idle slots carry pos = -1 and are skipped by the step (the reference computes them);
+//   * greedy runs (temperature 0) read back B token ids per step instead of B*vocab logits;
+//   * fp32 (v0) and Q8_0 (v2) checkpoints both run on the GPU.
+#include <omp.h>
+#include <stdio.h>
+#include <string.h>
+#include <time.h>
+
+#include <algorithm>
+#include <atomic>
+#include <fstream>
+
+#include "llama_driver.hpp"
+#include "tha_b200.h"
+
+long time_in_ms() {
+  struct timespec t;
+  clock_gettime(CLOCK_REALTIME, &t);
+  return t.tv_sec * 1000 + t.tv_nsec / 1000000;
+}
+
+// ---- request files ----------------------------------------------------------------------
+int read_inputfile(const char* input_filename, int max_token_len, int max_seq_len, Requests* reqs) {
+  printf("max_token_len: %d, max_seq_len: %d\n", max_token_len, max_seq_len);
+  std::ifstream in(input_filename);
+  if (!in.is_open()) { fprintf(stderr, "cannot open the file: %s\n", input_filename); exit(EXIT_FAILURE); }
+  std::string line;
+  std::getline(in, line);
+  const int n = atoi(line.c_str());
+  reqs->num_reqs = n;
+  reqs->max_token_len = max_token_len;
+  reqs->max_seq_len = max_seq_len;
+  reqs->str_reqs.assign(n, std::string());   // fewer body lines than N: the rest are empty prompts (BOS only)
+  reqs->str_gens.assign(n, std::string());
+  reqs->tok_gens.assign(n, std::vector<int>());
+  for (int idx = 0; idx < n && std::getline(in, line); idx++) reqs->str_reqs[idx] = line;
+  return 0;
+}
+
+int write_outputfile(const char* output_filename, Requests* reqs) {
+  std::ofstream out(output_filename);
+  if (!out.is_open()) { fprintf(stderr, "cannot write the file: %s\n", output_filename); exit(EXIT_FAILURE); }
+  out << reqs->num_reqs << "\n";
+  for (int i = 0; i < reqs->num_reqs; i++) out << reqs->str_gens[i] << "\n";
+  return 0;
+}
+
+int write_tokenfile(const char* output_filename, Requests* reqs) {
+  std::ofstream out(output_filename);
+  if (!out.is_open()) { fprintf(stderr, "cannot write the file: %s\n", output_filename); exit(EXIT_FAILURE); }
+  out << reqs->num_reqs << "\n";
+  for (int i = 0; i < reqs->num_reqs; i++) {
+    for (size_t j = 0; j < reqs->tok_gens[i].size(); j++) out << (j ? " " : "") << reqs->tok_gens[i][j];
+    out << "\n";
+  }
+  return 0;
+}
+
+// ---- the driver ---------------------------------------------------------------------------
+namespace {
+struct Slot {
+  std::vector<int> prompt;   // prompt token ids (BOS first)
+  std::string text;          // generated text so far
+  std::vector<int> ids;      // every token fed or produced, in order
+  int steps = 0;             // position limit
+};
+}  // namespace
+
+int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenizer_path, Requests* requests,
+                      const DriverOptions& opt, DriverStats* stats) {
+  const Config cfg = t32 ? t32->config : tq8->config;
+  const int vocab = cfg.vocab_size, B = opt.batch_size;
+  int n_devices = 0;
+  CHECK_THA(tha_device_count(&n_devices));
+  if (opt.n_devices > 0 && opt.n_devices < n_devices) n_devices = opt.n_devices;
+  if (n_devices < 1) { fprintf(stderr, "no CUDA device\n"); exit(EXIT_FAILURE); }
+  fprintf(stderr, "\n DATA PARALLELISM \n\n Num Devices %d\n\n Batch Size %d\n", n_devices, B);
+
+  // one sampler per REQUEST so that the output does not depend on slot or device (src/llama.cpp:895-900)
+  std::vector<Sampler> samplers(requests->num_reqs);
+  for (auto& s : samplers) build_sampler(&s, vocab, opt.temperature, opt.topp, opt.seed);
+
+  std::atomic<int> next_idx(opt.device_offset);
+  long long gen_cnt = 0, n_steps = 0;
+  double load_s = 0, loop_s = 0;
+  const bool greedy = opt.temperature == 0.0f && opt.resident_greedy;
+
+#pragma omp parallel for num_threads(n_devices) reduction(+ : gen_cnt, n_steps) reduction(max : load_s, loop_s)
+  for (int gid = 0; gid < n_devices; gid++) {
+    CHECK_THA(tha_set_device(gid));
+    Tokenizer tok;
+    build_tokenizer(&tok, tokenizer_path, vocab);
+    thablasHandle_t handle;
+    thablasCreate(&handle);
+
+    const long t_load0 = time_in_ms();
+    TransformerWeights* w_d = nullptr;
+    TransformerWeightsQ8* wq_d = nullptr;
+    if (t32) copy_weight_to_device(t32, w_d);
+    else copy_weight_to_device_q8(tq8, wq_d);
+    CHECK_THA(tha_device_sync());
+    load_s = (time_in_ms() - t_load0) / 1000.0;
+    fprintf(stdout, "\nLoad model time thread %d: %f\n", gid, load_s);
+
+    RunState* s_d = nullptr;
+    alloc_state_to_device_batch_cfg(&cfg, s_d, B, tha_step_needs_att_scratch((const tha_config_t*)&cfg));
+    float* logits_host = nullptr;
+    if (!greedy) CHECK_THA(tha_host_alloc((void**)&logits_host, (size_t)B * vocab * sizeof(float)));
+
+    const int kvd = cfg.dim * cfg.n_kv_heads / cfg.n_heads;
+    BatchManager bm(B, cfg.seq_len, cfg.n_layers, kvd);
+    bm.bind(s_d);
+    std::vector<Slot> slots(B);
+    std::vector<int> token(B, 0), pos(B, -1), next(B, 0);
+    Config cfg_local = cfg;
+
+    const long t_loop0 = time_in_ms();
+    for (;;) {
+      // ---- refill free slots from the shared queue
+      bool queue_empty = false;
+      for (int s = 0; s < B && !queue_empty; s++) {
+        if (bm.request_of(s) >= 0) continue;
+        const int req = next_idx.fetch_add(opt.device_stride);
+        if (req >= requests->num_reqs) { queue_empty = true; break; }
+        const int got = bm.acquire_slot(req);   // lowest free slot == s
+        Slot& sl = slots[got];
+        const std::string& prompt = requests->str_reqs[req];
+        sl.prompt.assign(prompt.size() + 3, 0);
+        int n_prompt = 0;
+        encode(&tok, prompt.c_str(), 1, 0, sl.prompt.data(), &n_prompt);
+        if (n_prompt < 1) { fprintf(stderr, "something is wrong, expected at least 1 prompt token\n"); exit(EXIT_FAILURE); }
+        sl.prompt.resize(n_prompt);
+        sl.text.clear();
+        sl.ids.assign(1, sl.prompt[0]);
+        sl.steps = requests->max_seq_len;
+        if (opt.max_new_positions > 0 && opt.max_new_positions < sl.steps) sl.steps = opt.max_new_positions;
+        token[got] = sl.prompt[0];
+        pos[got] = 0;
+        if (opt.verbose) fprintf(stderr, "\nDevice %d - seq id %d in batch, Request %d\n", gid, got, req);
+      }
+      if (bm.active_slots() == 0) break;
+
+      // ---- one decode step for every active slot
+      int rc;
+      if (greedy) {
+        rc = t32 ? tha_forward_greedy_f32((void*)handle.calc_stream, B, (const tha_config_t*)&cfg_local, (const tha_weights_f32_t*)w_d,
+                                          (const tha_state_t*)s_d, token.data(), pos.data(), next.data())
+                 : tha_forward_greedy_q8((void*)handle.calc_stream, B, (const tha_config_t*)&cfg_local, (const tha_weights_q8_t*)wq_d,
+                                         (const tha_state_t*)s_d, token.data(), pos.data(), next.data());
+      } else {
+        rc = t32 ? (int)thaDNN_s_forward_batch(handle, handle, handle, B, &cfg_local, w_d, s_d, token.data(), pos.data(), logits_host)
+                 : (int)thaDNN_q8_forward_batch(handle, B, &cfg_local, wq_d, s_d, token.data(), pos.data(), logits_host);
+      }
+      CHECK_THA(rc);
+      n_steps++;
+
+      // ---- advance the state machine of every slot (src/llama.cpp:1025-1050)
+      for (int s = 0; s < B; s++) {
+        const int req = bm.request_of(s);
+        if (req < 0) continue;
+        Slot& sl = slots[s];
+        int nx;
+        if (pos[s] < (int)sl.prompt.size() - 1) nx = sl.prompt[pos[s] + 1];            // still inside the prompt
+        else if (greedy) nx = next[s];
+        else nx = sample(&samplers[req], logits_host + (size_t)s * vocab);
+        bm.advance(s);
+        pos[s] += 1;
+        bool done = false;
+        if ((nx == 1 || nx == 2) && !opt.ignore_stop) {
+          done = true;
+        } else {
+          append_str(decode(&tok, token[s], nx), sl.text);
+          sl.ids.push_back(nx);
+          token[s] = nx;
+          if (pos[s] >= sl.steps) done = true;
+        }
+        if (done) {
+          requests->str_gens[req] = sl.text + "\n";
+          requests->tok_gens[req] = sl.ids;
+          gen_cnt += pos[s] - 1;
+          bm.release_slot(s);
+          pos[s] = -1;
+          token[s] = 0;
+          if (opt.verbose) fprintf(stderr, "\nThread %d DONE Request %d \n", gid, req);
+        }
+      }
+    }
+    loop_s = (time_in_ms() - t_loop0) / 1000.0;
+
+    if (logits_host) tha_host_free(logits_host);
+    free_state_on_device(s_d);
+    if (w_d) free_weight_on_device(w_d, w_d->wcls == w_d->token_embedding_table);
+    if (wq_d) free_weight_on_device_q8(wq_d, 1);
+    thablasDestroy(handle);
+    free_tokenizer(&tok);
+  }
+
+  for (auto& s : samplers) free_sampler(&s);
+  if (stats) { stats->gen_tokens = gen_cnt; stats->steps = n_steps; stats->load_seconds = load_s; stats->loop_seconds = loop_s; }
+  return (int)gen_cnt;
+}
+
+// The reference's entry point, same signature (src/llama.cpp:891): test-mode sampling
+// (temperature 1.0, top-p 0.9, seed 314028 for every request).
+int test_data_parallelism(Transformer* transformer, Tokenizer* tokenizer, const char* tokenizer_path, Requests* requests,
+                          int batch_size) {
+  (void)tokenizer;  // every device thread builds its own, as in the reference (:930-931)
+  DriverOptions opt;
+  opt.batch_size = batch_size;
+  return run_data_parallel(transformer, nullptr, tokenizer_path, requests, opt, nullptr);
+}

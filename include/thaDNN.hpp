@@ -1,0 +1,47 @@
+// thaDNN.hpp -- the forward pass of the reference (include/thaDNN.hpp:1-79, src/thaDNN.cpp:13-81).
+#pragma once
+#include "thaBLAS.hpp"
+#include "utils.hpp"
+#include "thaDNN/thaDNN_rmsnorm.hpp"
+#include "thaDNN/thaDNN_rope.hpp"
+#include "thaDNN/thaDNN_mha.hpp"
+#include "thaDNN/thaDNN_softmax.hpp"
+#include "thaDNN/thaDNN_swiglu.hpp"
+
+// include/thaDNN.hpp:15-28 (never returned by any function of the reference; kept for source compatibility)
+typedef enum {
+  thaDNNStatusSuccess = 0,
+  thaDNNStatusNotInitialized = 1,
+  thaDNNStatusInvalidValue = 2,
+  thaDNNStatusBadParm = 3,
+  thaDNNStatusAllocFailed = 4,
+  thaDNNStatusInternalError = 5,
+  thaDNNStatusNotImplemented = 6,
+  thaDNNStatusUnknownError = 7,
+  thaDNNStatusUnsupportedOp = 8,
+  thaDNNStatusGpuOperationsSkipped = 9,
+  thaDNNStatusVersionMismatch = 10,
+} thaDNNStatus_t;
+
+// One decode step for n_batches independent slots, slot b at its own pos[b]
+// (src/thaDNN.cpp:13-81).  token[] / pos[] are HOST arrays; logits_host receives
+// [n_batches, vocab_size] fp32 and is pinned host memory allocated by the caller
+// (src/llama.cpp:935-936).  Only handle1 is used, as in the reference (:40).  Returns after
+// the logits have landed (the reference ends with hipDeviceSynchronize, :78).
+// Differences, all on the safe side: a slot with pos[b] < 0 is idle and skipped (the reference
+// computes garbage rows for idle slots); nothing is allocated per call.
+thablasStatus_t thaDNN_s_forward_batch(thablasHandle_t handle1, thablasHandle_t handle2, thablasHandle_t handle3,
+                                       int n_batches, Config* p, TransformerWeights* w, RunState* s_batch,
+                                       int token[], int pos[], float* logits_host);
+
+// Same step for a Q8_0 model (runq.c:344-481 semantics, which the reference runs on the CPU only).
+thablasStatus_t thaDNN_q8_forward_batch(thablasHandle_t handle, int n_batches, Config* p, TransformerWeightsQ8* w,
+                                        RunState* s_batch, int token[], int pos[], float* logits_host);
+
+// Resident greedy step of the batching driver: token_d / pos_d are DEVICE arrays; the step
+// picks the first-maximum token per slot on the device (sample_argmax, src/llama.cpp:275-286),
+// stores it in next_d, and (advance != 0) moves every active slot on: token = next, pos += 1.
+// Nothing is copied and nothing synchronises.  logits_d may be NULL.
+thablasStatus_t thaDNN_s_decode_greedy_batch(thablasHandle_t* handle, int n_batches, Config* p, TransformerWeights* w,
+                                             RunState* s_batch, int* token_d, int* pos_d, int* next_d,
+                                             float* logits_d, int advance);

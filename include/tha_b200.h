@@ -184,11 +184,21 @@ int tha_forward_batch_q8(void* stream, int n_batches, const tha_config_t* cfg,
 int tha_decode_step_q8(void* stream, int n_batches, const tha_config_t* cfg,
                        const tha_weights_q8_t* w, const tha_state_t* s, const int* token_d,
                        const int* pos_d, float* logits_d, int* next_d);
+/* thaDNN_s_forward_batch + sample_argmax (src/llama.cpp:275-286) in one call: HOST token / pos
+ * in, HOST next[] out (first maximum per active slot; idle slots are left untouched on the
+ * device and read back as whatever they held).  B ints cross PCIe instead of B*vocab floats. */
+int tha_forward_greedy_f32(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_f32_t* w,
+                           const tha_state_t* s, const int* token_host, const int* pos_host, int* next_host);
+int tha_forward_greedy_q8(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_q8_t* w,
+                          const tha_state_t* s, const int* token_host, const int* pos_host, int* next_host);
 /* greedy sampler on the device: next[b] = first argmax of logits[b, :] */
 int tha_argmax_batch_f32(void* stream, int n_batches, const float* logits, int vocab, int* next_d);
 /* greedy bookkeeping of the batching driver (src/llama.cpp:1027-1050) kept on the device:
  * token_d[b] = next_d[b], pos_d[b] += 1 (a slot reaching seq_len goes idle: pos = -1) */
 int tha_advance_slots(void* stream, int n_batches, int* token_d, int* pos_d, const int* next_d, int seq_len);
+/* 1 when the step for this shape falls back to the three attention stages and therefore needs
+ * tha_state_t.att ([B, n_heads, seq_len]); 0 when the fused attention kernel covers it */
+int tha_step_needs_att_scratch(const tha_config_t* cfg);
 /* number of kernels the last tha_decode_step_* call on this thread launched */
 int tha_last_step_launches(void);
 
