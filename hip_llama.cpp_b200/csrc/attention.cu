@@ -84,7 +84,19 @@ struct AttnP {
   long long kv_batch_stride; int kv_dim, head_size, kv_mul, dim;
   int nseg, nsplit;
   float4* part_acc; float2* part_ml; int* counters;
+  float* out_hi; float* out_lo;             // nullable: the tf32 hi/lo split of `out` for the tensor-core wo matmul
 };
+
+__device__ __forceinline__ float attn_tf32(float v) { return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u); }
+__device__ __forceinline__ void attn_store(const AttnP& p, float* outp, float4 r) {
+  *reinterpret_cast<float4*>(outp) = r;
+  if (p.out_hi) {
+    const size_t off = outp - p.out;
+    const float4 h = make_float4(attn_tf32(r.x), attn_tf32(r.y), attn_tf32(r.z), attn_tf32(r.w));
+    *reinterpret_cast<float4*>(p.out_hi + off) = h;
+    *reinterpret_cast<float4*>(p.out_lo + off) = make_float4(r.x - h.x, r.y - h.y, r.z - h.z, r.w - h.w);
+  }
+}
 
 // J = float4 slots per lane; a CTA covers a segment of 128*J query floats (whole heads).
 template <int J>
@@ -188,7 +200,7 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   }
   float* outp = p.out + (size_t)b * p.dim + seg * (128 * J) + 4 * f;
   if (p.nsplit == 1) {
-    if (f < F) *reinterpret_cast<float4*>(outp) = make_float4(A.x / L, A.y / L, A.z / L, A.w / L);
+    if (f < F) attn_store(p, outp, make_float4(A.x / L, A.y / L, A.z / L, A.w / L));
     return;
   }
 
@@ -219,7 +231,7 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
       GL += ml.y * e;
       GA.x += a.x * e; GA.y += a.y * e; GA.z += a.z * e; GA.w += a.w * e;
     }
-    *reinterpret_cast<float4*>(outp) = make_float4(GA.x / GL, GA.y / GL, GA.z / GL, GA.w / GL);
+    attn_store(p, outp, make_float4(GA.x / GL, GA.y / GL, GA.z / GL, GA.w / GL));
   }
   if (threadIdx.x == 0) p.counters[b * p.nseg + seg] = 0;  // self-reset for the next launch
 }
@@ -256,12 +268,12 @@ int attn_fused_nsplit(int B, int nseg, int seq_len) {
 // kc / vc are the caches already offset to the layer (base + loff).
 int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
-                      int head_size, int seq_len, bool pdl) {
+                      int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo) {
   const int dim = n_heads * head_size, kv_dim = n_kv_heads * head_size;
   const int J = fused_J(n_heads, head_size, dim);
   if (!J || kv_dim % 4) return THA_STATUS_NOT_SUPPORTED;
   AttnP p;
-  p.pos = pos_d; p.q = q; p.out = out; p.kc = kc; p.vc = vc;
+  p.pos = pos_d; p.q = q; p.out = out; p.kc = kc; p.vc = vc; p.out_hi = out_hi; p.out_lo = out_lo;
   p.kv_batch_stride = kv_batch_stride; p.kv_dim = kv_dim; p.head_size = head_size;
   p.kv_mul = n_heads / n_kv_heads; p.dim = dim;
   p.nseg = dim / (128 * J);
@@ -355,5 +367,5 @@ extern "C" int tha_mha_fused_v1_f32(void* stream, int n_batches, const int* pos_
   if (!ws) return THA_STATUS_EXECUTION_FAILED;
   const int kv_dim = n_kv_heads * head_size;
   return attn_fused_launch((cudaStream_t)stream, ws, n_batches, pos_d, n_heads, n_kv_heads, q, xb, key_cache + loff,
-                           value_cache + loff, (long long)n_layers * seq_len * kv_dim, head_size, seq_len, false);
+                           value_cache + loff, (long long)n_layers * seq_len * kv_dim, head_size, seq_len, false, nullptr, nullptr);
 }

@@ -26,7 +26,7 @@ bool attn_fused_supported(int n_heads, int head_size, int dim, int kv_dim);
 int attn_fused_nsplit(int B, int nseg, int seq_len);
 int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
-                      int head_size, int seq_len, bool pdl);
+                      int head_size, int seq_len, bool pdl, float* out_hi = nullptr, float* out_lo = nullptr);
 int launches_reset();
 int launches_get();
 // megastep.cu: the whole step as one persistent kernel (small models, B <= 8)
@@ -37,6 +37,14 @@ int mega_step_launch(cudaStream_t st, Workspace* ws, int B, const tha_config_t* 
                      const tha_state_t* s, int* token_d, int* pos_d, float* logits_d, int* next_d, int advance,
                      const float* rope_cos, const float* rope_sin, bool prepare_only);
 int mega_check_abort(int dev);
+// step_tc.cu: the step with tensor-core weight matmuls (more than 8 slots)
+bool step_tc_supported(const tha_config_t* c, int B);
+int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B);
+int step_tc_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_f32_t& w,
+                  const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
+                  const float* rc, const float* rs, bool pdl);
+int gemm_tc_check_error();
+int tc_mode();   // -1 auto (B > 8), 0 never, 1 whenever the shape allows
 int advance_launch(cudaStream_t st, int B, int* token, int* pos, const int* next, int seq_len, bool pdl);
 
 static thread_local int g_last_step_launches = 0;
@@ -172,7 +180,9 @@ int decode_step_f32(cudaStream_t st, int B, const tha_config_t* cfg, const tha_w
   memset(&a, 0, sizeof(a));
   a.B = B; a.cfg = *cfg; a.w = *w; a.s = *s; a.token_d = token_d; a.pos_d = pos_d; a.logits_d = logits_d;
   a.next_d = next_d; a.pdl = pdl_enabled(); a.advance = advance;
-  a.mega = mega_enabled() && mega_supported(cfg, B);
+  const int tcm = tc_mode();
+  const bool use_tc = tcm != 0 && (tcm == 1 || B > 8) && step_tc_supported(cfg, B);
+  a.mega = !use_tc && mega_enabled() && mega_supported(cfg, B);
   if (a.mega) {
     // scratch is grown outside any capture; the kernel writes logits only where the caller wants them
     THA_TRY(mega_step_launch(st, ws, B, cfg, w, s, nullptr, nullptr, nullptr, nullptr, 0, rc, rs, true));
@@ -180,6 +190,16 @@ int decode_step_f32(cudaStream_t st, int B, const tha_config_t* cfg, const tha_w
     return run_step(st, ws, &a, sizeof(a), [&]() {
       return mega_step_launch(st, ws, B, cfg, w, s, const_cast<int*>(token_d), const_cast<int*>(pos_d), lg, next_d,
                               advance, rc, rs, false);
+    });
+  }
+  if (use_tc) {
+    THA_TRY(step_tc_prepare(ws, cfg, B));
+    a.mega = 2;   // part of the graph key
+    float* lg = logits_d ? logits_d : s->logits;
+    return run_step(st, ws, &a, sizeof(a), [&]() {
+      THA_TRY(step_tc_issue(st, ws, B, *cfg, *w, *s, token_d, pos_d, lg, next_d, rc, rs, a.pdl != 0));
+      if (advance) THA_TRY(advance_launch(st, B, const_cast<int*>(token_d), const_cast<int*>(pos_d), next_d, cfg->seq_len, a.pdl != 0));
+      return (int)THA_STATUS_SUCCESS;
     });
   }
   const bool fused = attn_fused_supported(cfg->n_heads, hs, cfg->dim, kvd);
@@ -323,6 +343,10 @@ static int forward_host(cudaStream_t st, int B, int vocab, float* state_logits, 
   THA_CUDA_OK(cudaStreamSynchronize(st));
   if (mega_check_abort(ws->device)) {
     set_last_error("persistent step kernel: a barrier wait timed out", cudaErrorLaunchTimeout);
+    return THA_STATUS_EXECUTION_FAILED;
+  }
+  if (gemm_tc_check_error()) {
+    set_last_error("tensor-core matmul: a pipeline barrier wait timed out", cudaErrorLaunchTimeout);
     return THA_STATUS_EXECUTION_FAILED;
   }
   return THA_STATUS_SUCCESS;

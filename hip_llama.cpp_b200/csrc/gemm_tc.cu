@@ -1,0 +1,557 @@
+// Weight matmul on the 5th-generation tensor cores (tcgen05 + TMEM + TMA), fp32 in / fp32 out.
+//
+//   out[n, row] = sum_k W[row, k] * X[n, k]          W: [M, K] row-major fp32 (the checkpoint layout)
+//                                                    X: [N, K] row-major fp32 (N = batch slots or prompt tokens)
+//
+// Used where the GEMV family stops being HBM-bound on CUDA cores: multi-sequence decode with more
+// than 8 slots and batched prefill (replaces thaBLAS_s_matmul_batch,
+// src/thaBLAS.cpp:191-228, whose grid re-reads every weight row once per slot).
+//
+// Precision: tcgen05 has no fp32 kind.  kind::tf32 reads 32-bit operands and uses 10 mantissa
+// bits, which alone would put logits ~1e-3 off the CPU reference.  The kernel therefore runs the
+// error-compensated 3xTF32 scheme: every operand v is split in shared memory into
+// hi = tf32(v) (round to nearest) and lo = v - hi, and each k-block issues
+//   D += Whi.Xhi + Wlo.Xhi + Whi.Xlo        (the lo.lo term is below fp32 rounding)
+// with fp32 accumulation in TMEM.  Results agree with an fp32 FMA loop to ~1e-6 relative.
+//
+// Structure (one 128-row weight tile x NT columns per CTA, optional split-K over blockIdx.z):
+//   warp 0      TMA producer: per k-block (32 floats = one 128-byte swizzle row) one
+//               cp.async.bulk.tensor for the W tile [128 x 32] and one for the X tile [NT x 32],
+//               SWIZZLE_128B, into a ring of stages; completion on the stage's `full` mbarrier.
+//   warps 4-15  converters (3 groups of 4 warps, k-blocks round-robin): thread = weight row; read the
+//               landed fp32 row (swizzle-aware, conflict-free), split into hi = tf32(w), lo = w - hi
+//               and store both into the TMEM operand ring (tcgen05.st); arrive on `ready`.
+//   warp 1      MMA issuer: one elected lane issues 4 (K=8 each) x 3 tcgen05.mma.kind::tf32 per
+//               k-block, accumulator [128 lanes x NT columns] fp32 in TMEM; tcgen05.commit frees
+//               the stage (`empty`) and finally signals the epilogue (`accum`).
+//   warp 2      TMEM allocation / release.
+//   warps 4-7   epilogue: tcgen05.ld (32 lanes x 32-bit x 16 columns per instruction), optional
+//               per-column scale (the 1/rms factor of a folded RMSNorm), coalesced stores
+//               out[n * ldo + off + row] (a warp writes 32 consecutive rows of one column).
+// Up to three weight matrices with the same K are stacked in one launch (wq|wk|wv, w1|w3); a tile
+// never straddles two matrices.
+#include <cuda.h>
+#include <stdlib.h>
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "common.cuh"
+#include "gemm_tc.h"
+
+namespace tha {
+
+constexpr int TC_BM = 128;          // weight rows per tile = UMMA M
+constexpr int TC_BK = 32;           // floats per k-block: 128 bytes, the swizzle width
+constexpr int TC_CGROUPS = 3;       // converter/epilogue warp groups (4 warps each), k-blocks dealt round-robin
+constexpr int TC_THREADS = 128 + 128 * TC_CGROUPS;
+constexpr int TC_SMEM_LIMIT = 227 * 1024;
+
+// ------------------------------------------------------------------ PTX wrappers ----
+__device__ __forceinline__ uint32_t tc_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void tc_mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tc_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void tc_mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tc_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tc_mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tc_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool tc_mbar_try(uint64_t* bar, unsigned parity) {
+  unsigned ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(tc_smem_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
+// Bounded wait: a broken pipeline must end the kernel (and fail the parity test), never hang the GPU.
+__device__ __forceinline__ bool tc_mbar_wait(uint64_t* bar, unsigned parity, int* abort_flag) {
+  for (unsigned n = 0; !tc_mbar_try(bar, parity); n++) {
+    if (n > (1u << 22)) { *abort_flag = 1; return false; }
+    if ((n & 1023u) == 1023u && *((volatile int*)abort_flag)) return false;
+  }
+  return true;
+}
+__device__ __forceinline__ void tc_tma_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(tc_smem_u32(dst)), "l"(map), "r"(tc_smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_tma_2d_hint(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar, uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(tc_smem_u32(dst)), "l"(map), "r"(tc_smem_u32(bar)), "r"(c0), "r"(c1), "l"(pol) : "memory");
+}
+// K-major operand tile, 128-byte rows, SWIZZLE_128B: 8-row groups 1024 bytes apart (cute::UMMA::SmemDescriptor).
+__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);          // start address, 16-byte units
+  d |= (uint64_t)1 << 16;                            // leading byte offset: unused for swizzled K-major
+  d |= (uint64_t)(1024 >> 4) << 32;                  // stride byte offset between 8-row groups
+  d |= (uint64_t)1 << 46;                            // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                            // SWIZZLE_128B
+  return d;
+}
+// kind::tf32, fp32 accumulate, both operands K-major, M = 128, N = nt (cute::UMMA::InstrDescriptor)
+__host__ __device__ constexpr uint32_t tc_idesc(int nt) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(nt >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// A operand in TMEM (lane = row of the 128-row tile, one tf32 per 32-bit column), B through a shared-memory descriptor
+__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+        "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]),
+        "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]),
+        "r"(v[30]), "r"(v[31]) : "memory");
+}
+__device__ __forceinline__ void tc_tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(tc_smem_u32(bar)) : "memory");
+}
+// round to nearest (ties away from zero) onto the 10-bit tf32 mantissa == cvt.rna.tf32.f32, with two
+// full-rate integer instructions instead of one quarter-rate conversion
+__device__ __forceinline__ float tc_tf32(float v) {
+  return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u);
+}
+
+template <int NT>
+struct TcSmem {
+  static constexpr int W_BYTES = TC_BM * 128;                        // one weight k-block, raw fp32, swizzled rows
+  static constexpr int X_BYTES = NT * 128;
+  static constexpr int XS_BYTES = 2 * X_BYTES;                       // Xhi | Xlo
+  static constexpr bool SPLIT_ACC = NT <= 128;                       // lo-terms in their own accumulator
+  static constexpr int ACC_COLS = SPLIT_ACC ? 2 * NT : NT;
+  static constexpr int A_COLS = 2 * TC_BK;                           // per operand slot: W hi (32 columns) | W lo (32 columns)
+  // Three rings.  W (shared memory): filled by TMA, freed as soon as a converter has read the rows -- it only has
+  // to cover the HBM latency, so it is as deep as shared memory allows (>= 96 KB in flight per SM).  A (TMEM) and
+  // X (shared memory): written by converter / TMA, freed by the MMAs' commit.  SW and SA are multiples of the
+  // number of converter groups so that a ring slot is always served by the same group (a waiter must never be
+  // two barrier phases ahead of the barrier).
+  // Both shared-memory rings are sized to cover their load latency at the HBM rate of one SM (16 KB of W per
+  // ~0.37 us): W from HBM (~2 us under load: >= 6 slots), X from L2 (~1 us: >= 48 KB).
+  // The operand ring (A slot in TMEM + X slot in shared memory, same index) has ONE full barrier (4 converter
+  // warps + the X bytes) and ONE empty barrier (the MMAs' commit): the single MMA-issuing thread pays one wait and
+  // one commit per k-block.
+  static constexpr int SA = NT <= 64 ? 6 : 3;
+  static constexpr int SX = SA;
+  static constexpr int SW_RAW = (TC_SMEM_LIMIT - 2048 - SX * XS_BYTES) / W_BYTES;
+  static constexpr int SW = SW_RAW >= 12 ? 12 : (SW_RAW / TC_CGROUPS) * TC_CGROUPS;
+  static constexpr int NBARS = 2 * SW + 2 * SA + 1;
+  static constexpr int TOTAL = SW * W_BYTES + SX * XS_BYTES + 1024 /*alignment slack*/ + NBARS * 8 + 64;
+  static constexpr int TMEM_COLS = 512;
+  static_assert(SW >= TC_CGROUPS && SW % TC_CGROUPS == 0 && SA % TC_CGROUPS == 0, "ring / group mismatch");
+  static_assert(ACC_COLS + SA * A_COLS <= 512, "TMEM overflow");
+  static_assert(TOTAL <= TC_SMEM_LIMIT, "shared memory overflow");
+};
+
+template <int NT>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__ CUtensorMap mw1,
+                   const __grid_constant__ CUtensorMap mw2, const __grid_constant__ CUtensorMap mxh,
+                   const __grid_constant__ CUtensorMap mxl, const TcP p) {
+  using S = TcSmem<NT>;
+  extern __shared__ unsigned char tc_smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~(uintptr_t)1023);
+  unsigned char* wring = smem;
+  unsigned char* xring = smem + S::SW * S::W_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(xring + S::SX * S::XS_BYTES);
+  uint64_t* wfull = bars;                     // W k-block landed
+  uint64_t* wfree = wfull + S::SW;            // its rows are in registers: the slot may be refilled
+  uint64_t* ready = wfree + S::SW;            // operand slot full: W hi/lo in TMEM (4 warps) + X hi/lo landed (TMA bytes)
+  uint64_t* aempty = ready + S::SA;           // MMAs that read the operand slot have completed
+  uint64_t* accum = aempty + S::SA;           // accumulator complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+  int* abort_flag = reinterpret_cast<int*>(tmem_slot + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // ---- which tile
+  int tile = blockIdx.x, mat = 0;
+  if (tile >= p.tiles[0]) { tile -= p.tiles[0]; mat = 1; if (tile >= p.tiles[1]) { tile -= p.tiles[1]; mat = 2; } }
+  const CUtensorMap* mw = (mat == 0) ? &mw0 : (mat == 1 ? &mw1 : &mw2);
+  const int row0 = tile * TC_BM;
+  const int n0 = blockIdx.y * NT;
+  const int kb0 = blockIdx.z * p.kblocks_per_split;
+  int nkb = p.kblocks_total - kb0;
+  if (nkb > p.kblocks_per_split) nkb = p.kblocks_per_split;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S::SW; s++) { tc_mbar_init(&wfull[s], 1); tc_mbar_init(&wfree[s], 4); }
+    for (int s = 0; s < S::SA; s++) { tc_mbar_init(&ready[s], 5); tc_mbar_init(&aempty[s], 1); }
+    tc_mbar_init(accum, 1);
+    *abort_flag = 0;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(mw) : "memory");
+  if (warp == 3 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mxh) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mxl) : "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem_u32(tmem_slot)), "r"(S::TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_d = tmem_base;                               // main accumulator (hi.hi terms)
+  const uint32_t tmem_dl = tmem_base + (S::SPLIT_ACC ? NT : 0);    // lo-term accumulator
+  const uint32_t tmem_a = tmem_base + S::ACC_COLS;                 // W operand ring
+
+  if (warp == 0) {
+    // ===== W producer: weights never depend on the previous kernel, so no programmatic-dependency wait here --
+    // with PDL the whole ring is already in flight while the predecessor drains.
+    if (lane == 0) {
+      uint64_t pol_w;
+      asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
+      for (int i = 0; i < nkb; i++) {
+        const int s = i % S::SW;
+        if (i >= S::SW && !tc_mbar_wait(&wfree[s], ((i / S::SW) & 1u) ^ 1u, abort_flag)) break;
+        if (p.dbg & 8) { tc_mbar_arrive(&wfull[s]); continue; }
+        tc_mbar_expect_tx(&wfull[s], S::W_BYTES);
+        tc_tma_2d_hint(wring + s * S::W_BYTES, mw, (kb0 + i) * TC_BK, row0, &wfull[s], pol_w);
+      }
+    }
+  } else if (warp == 3) {
+    // ===== X producer (activations: written by the previous kernel)
+    if (lane == 0) {
+      pdl_wait();
+      for (int i = 0; i < nkb; i++) {
+        const int s = i % S::SX;
+        if (i >= S::SX && !tc_mbar_wait(&aempty[s], ((i / S::SX) & 1u) ^ 1u, abort_flag)) break;
+        unsigned char* st = xring + s * S::XS_BYTES;
+        if (p.dbg & 4) { tc_mbar_arrive(&ready[s]); continue; }
+        tc_mbar_expect_tx(&ready[s], S::XS_BYTES);
+        tc_tma_2d(st, &mxh, (kb0 + i) * TC_BK, n0, &ready[s]);
+        tc_tma_2d(st + S::X_BYTES, &mxl, (kb0 + i) * TC_BK, n0, &ready[s]);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: A (weights, hi / lo) from TMEM, B (activations, hi / lo) from shared memory
+    if (lane == 0) {
+      constexpr uint32_t idesc = tc_idesc(NT);
+      for (int i = 0; i < nkb; i++) {
+        const int sa = i % S::SA, sx = sa;
+        if (!tc_mbar_wait(&ready[sa], (i / S::SA) & 1u, abort_flag)) break;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t xb = tc_smem_u32(xring + sx * S::XS_BYTES);
+        const uint64_t xhi = tc_smem_desc(xb), xlo = tc_smem_desc(xb + S::X_BYTES);
+        const uint32_t ahi = tmem_a + sa * S::A_COLS, alo = ahi + TC_BK;
+        if (p.dbg & 16) {          // experiment: hi.hi chain first, then the lo chain
+#pragma unroll
+          for (int k = 0; k < TC_BK / 8; k++) tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xhi + (uint64_t)(k * 2), idesc, (i | k) != 0);
+#pragma unroll
+          for (int k = 0; k < TC_BK / 8; k++) {
+            tc_mma_tf32_ts(tmem_dl, alo + 8 * k, xhi + (uint64_t)(k * 2), idesc, S::SPLIT_ACC ? (uint32_t)((i | k) != 0) : 1u);
+            tc_mma_tf32_ts(tmem_dl, ahi + 8 * k, xlo + (uint64_t)(k * 2), idesc, 1u);
+          }
+        } else if (p.dbg & 32) {   // experiment: one accumulator
+#pragma unroll
+          for (int k = 0; k < TC_BK / 8; k++) {
+            tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xhi + (uint64_t)(k * 2), idesc, (i | k) != 0);
+            tc_mma_tf32_ts(tmem_d, alo + 8 * k, xhi + (uint64_t)(k * 2), idesc, 1u);
+            tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xlo + (uint64_t)(k * 2), idesc, 1u);
+          }
+        } else if (p.dbg & 64) {   // experiment: hi.hi only (plain TF32)
+#pragma unroll
+          for (int k = 0; k < TC_BK / 8; k++) tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xhi + (uint64_t)(k * 2), idesc, (i | k) != 0);
+        } else
+        if (!(p.dbg & 1))
+#pragma unroll
+        for (int k = 0; k < TC_BK / 8; k++) {           // UMMA K = 8 tf32: 8 TMEM columns of A, 32 bytes (2 descriptor units) of B
+          const uint64_t adv = (uint64_t)(k * 2);
+          const uint32_t first = (i | k) != 0;
+          tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xhi + adv, idesc, first);
+          tc_mma_tf32_ts(tmem_dl, alo + 8 * k, xhi + adv, idesc, S::SPLIT_ACC ? first : 1u);
+          tc_mma_tf32_ts(tmem_dl, ahi + 8 * k, xlo + adv, idesc, 1u);
+        }
+        tc_commit(&aempty[sa]);
+      }
+      tc_commit(accum);
+    }
+  } else if (warp >= 4) {
+    // ===== converters (shared -> hi/lo -> TMEM), then epilogue.  Thread = weight row of the tile.
+    const int q = warp & 3;                             // this warp's 32-lane quarter of TMEM
+    const int r = q * 32 + lane;
+    const int grp = (warp >> 2) - 1;                    // converter group 0..TC_CGROUPS-1
+    bool ok = true;
+    for (int i = grp; i < nkb && ok; i += TC_CGROUPS) {
+      const int sw = i % S::SW, sa = i % S::SA;
+      ok = tc_mbar_wait(&wfull[sw], (i / S::SW) & 1u, abort_flag);
+      const unsigned char* wrow = wring + sw * S::W_BYTES + r * 128;
+      uint32_t hi[32], lo[32];
+#pragma unroll
+      for (int j = 0; j < 8; j++) {                      // logical 16-byte chunk j lives at j ^ (row & 7) (SWIZZLE_128B)
+        const float4 v = *reinterpret_cast<const float4*>(wrow + ((j ^ (r & 7)) << 4));
+        const float h0 = tc_tf32(v.x), h1 = tc_tf32(v.y), h2 = tc_tf32(v.z), h3 = tc_tf32(v.w);
+        hi[4 * j + 0] = __float_as_uint(h0); hi[4 * j + 1] = __float_as_uint(h1);
+        hi[4 * j + 2] = __float_as_uint(h2); hi[4 * j + 3] = __float_as_uint(h3);
+        lo[4 * j + 0] = __float_as_uint(v.x - h0); lo[4 * j + 1] = __float_as_uint(v.y - h1);
+        lo[4 * j + 2] = __float_as_uint(v.z - h2); lo[4 * j + 3] = __float_as_uint(v.w - h3);
+      }
+      if (i >= S::SA && ok) ok = tc_mbar_wait(&aempty[sa], ((i / S::SA) & 1u) ^ 1u, abort_flag);
+      const uint32_t ta = tmem_a + sa * S::A_COLS + ((uint32_t)(q * 32) << 16);
+      if (!(p.dbg & 2)) {
+      tc_tmem_st32(ta, hi);                              // consumes every loaded value: the shared-memory reads are complete
+      tc_tmem_st32(ta + TC_BK, lo);
+      }
+      __syncwarp();
+      if (lane == 0) tc_mbar_arrive(&wfree[sw]);         // the W slot can be refilled while the stores drain
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) tc_mbar_arrive(&ready[sa]);
+    }
+    // ---- epilogue: lane = weight row within this warp's 32-lane TMEM quarter
+    pdl_trigger();
+    pdl_wait();   // returns at once (the X producer already waited); makes the predecessor's writes visible to these threads
+    if (ok) ok = tc_mbar_wait(accum, 0, abort_flag);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const int row = row0 + r;
+    const bool row_ok = row < p.M[mat];
+    float* outz = p.out + (size_t)blockIdx.z * p.zstride + p.out_off[mat] + row;
+    if (ok) {
+#pragma unroll 1
+      for (int c = 16 * grp; c < NT; c += 16 * TC_CGROUPS) {
+        uint32_t v[16], w[16];
+        const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c;
+        tc_tmem_ld16(taddr, v);
+        if (S::SPLIT_ACC) tc_tmem_ld16(taddr + NT, w);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+          const int n = n0 + c + j;
+          if (n < p.N && row_ok) {
+            float x = __uint_as_float(v[j]);
+            if (S::SPLIT_ACC) x += __uint_as_float(w[j]);
+            if (p.colscale) x *= p.colscale[n];
+            outz[(size_t)n * p.ldo] = x;
+          }
+        }
+      }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp == 2) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(S::TMEM_COLS));
+  }
+  if (threadIdx.x == 0 && *abort_flag && p.error_flag) atomicExch(p.error_flag, 1);
+}
+
+// x -> hi = tf32(x), lo = x - hi (the activation side of the 3xTF32 split) for callers that hand in plain fp32 rows
+__global__ void split_hilo_kernel(const float* __restrict__ x, long long ldx, float* __restrict__ hi, float* __restrict__ lo, int K) {
+  const int n = blockIdx.y;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < K; k += gridDim.x * blockDim.x) {
+    const float v = x[(size_t)n * ldx + k];
+    const float h = tc_tf32(v);
+    hi[(size_t)n * K + k] = h;
+    lo[(size_t)n * K + k] = v - h;
+  }
+}
+
+// ------------------------------------------------------------------ host side ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+static int tc_env(const char* n, int d) { const char* v = getenv(n); return (v && *v) ? atoi(v) : d; }
+static std::mutex g_tc_mu;
+static std::map<std::tuple<const void*, long long, int, long long, int>, CUtensorMap> g_maps;
+static std::map<int, int*> g_err_flags;   // per device
+
+static int tc_get_encode() {
+  if (g_encode) return THA_STATUS_SUCCESS;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  THA_CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+  if (!fn || qres != cudaDriverEntryPointSuccess) { set_last_error("cuTensorMapEncodeTiled unavailable", cudaErrorNotSupported); return THA_STATUS_NOT_SUPPORTED; }
+  g_encode = (EncodeTiledFn)fn;
+  return THA_STATUS_SUCCESS;
+}
+
+// fp32 row-major [rows, K] with row pitch `ld` floats; box = [box_rows x 32 floats], 128-byte swizzle.
+static int tc_map(const float* ptr, long long rows, int K, long long ld, int box_rows, CUtensorMap* out) {
+  std::lock_guard<std::mutex> lk(g_tc_mu);
+  THA_TRY_RC(tc_get_encode());
+  auto key = std::make_tuple((const void*)ptr, rows, K, ld, box_rows);
+  auto it = g_maps.find(key);
+  if (it != g_maps.end()) { *out = it->second; return THA_STATUS_SUCCESS; }
+  CUtensorMap m;
+  const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
+  const cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        (CUtensorMapL2promotion)tc_env("THA_TC_PROMO", (int)CU_TENSOR_MAP_L2_PROMOTION_L2_256B),
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_last_error("cuTensorMapEncodeTiled", cudaErrorInvalidValue); return THA_STATUS_EXECUTION_FAILED; }
+  if (g_maps.size() > 4096) g_maps.clear();
+  g_maps[key] = m;
+  *out = m;
+  return THA_STATUS_SUCCESS;
+}
+
+// Per-device error flag (allocated on first use; callers that capture graphs call this beforehand).
+int gemm_tc_init(int** flag_out) {
+  int dev = 0;
+  THA_CUDA_OK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(g_tc_mu);
+  auto it = g_err_flags.find(dev);
+  if (it == g_err_flags.end()) {
+    int* f = nullptr;
+    THA_CUDA_OK(cudaMalloc(&f, sizeof(int)));
+    THA_CUDA_OK(cudaMemset(f, 0, sizeof(int)));
+    THA_CUDA_OK(cudaDeviceSynchronize());
+    it = g_err_flags.emplace(dev, f).first;
+  }
+  if (flag_out) *flag_out = it->second;
+  return THA_STATUS_SUCCESS;
+}
+
+bool gemm_tc_ok(const TcArgs& a) {
+  if (a.K % 4 || a.ldx % 4 || a.K < TC_BK || a.N < 1) return false;
+  for (int i = 0; i < a.n_mats; i++)
+    if (!a.W[i] || (reinterpret_cast<uintptr_t>(a.W[i]) & 15u) || a.M[i] < 1) return false;
+  return a.Xhi && a.Xlo && (reinterpret_cast<uintptr_t>(a.Xhi) & 15u) == 0 && (reinterpret_cast<uintptr_t>(a.Xlo) & 15u) == 0;
+}
+
+int gemm_tc_pick_nt(int N) { return N <= 16 ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128)); }   // wider N: more column tiles (grid.y)
+
+template <int NT>
+static int tc_launch_nt(cudaStream_t st, const TcArgs& a, const CUtensorMap* mw, const CUtensorMap& mxh, const CUtensorMap& mxl, const TcP& p, dim3 grid, bool pdl) {
+  using S = TcSmem<NT>;
+  auto k = gemm_tf32x3_kernel<NT>;
+  THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+  THA_CUDA_OK(launch(k, grid, dim3(TC_THREADS), (size_t)S::TOTAL, st, pdl, mw[0], mw[1], mw[2], mxh, mxl, p));
+  return THA_STATUS_SUCCESS;
+}
+
+int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl) {
+  if (!gemm_tc_ok(a) || a.n_mats < 1 || a.n_mats > 3 || !a.out) return THA_STATUS_INVALID_ARG;
+  const int NT = gemm_tc_pick_nt(a.N);
+  CUtensorMap mw[3], mxh, mxl;
+  TcP p = {};
+  int tiles = 0;
+  for (int i = 0; i < 3; i++) {
+    if (i < a.n_mats) {
+      THA_TRY_RC(tc_map(a.W[i], a.M[i], a.K, a.K, TC_BM, &mw[i]));
+      p.M[i] = a.M[i]; p.tiles[i] = ceil_div(a.M[i], TC_BM); p.out_off[i] = a.out_off[i];
+    } else {
+      mw[i] = mw[0]; p.M[i] = 0; p.tiles[i] = 0; p.out_off[i] = 0;
+    }
+    tiles += p.tiles[i];
+  }
+  THA_TRY_RC(tc_map(a.Xhi, a.N, a.K, a.ldx, NT, &mxh));
+  THA_TRY_RC(tc_map(a.Xlo, a.N, a.K, a.ldx, NT, &mxl));
+  p.K = a.K; p.N = a.N;
+  p.kblocks_total = ceil_div(a.K, TC_BK);
+  const int splits = a.splits < 1 ? 1 : a.splits;
+  p.kblocks_per_split = ceil_div(p.kblocks_total, splits);
+  const int zdim = ceil_div(p.kblocks_total, p.kblocks_per_split);
+  if (zdim != splits) return THA_STATUS_INVALID_ARG;   // caller sizes its partial buffers by `splits`
+  p.out = a.out; p.ldo = a.ldo; p.zstride = a.zstride; p.colscale = a.colscale;
+  p.w_hint = tc_env("THA_TC_HINT", 1);
+  p.dbg = tc_env("THA_TC_DBG", 0);
+  THA_TRY_RC(gemm_tc_init(&p.error_flag));
+  dim3 grid(tiles, ceil_div(a.N, NT), zdim);
+  switch (NT) {
+    case 16: return tc_launch_nt<16>(st, a, mw, mxh, mxl, p, grid, pdl);
+    case 32: return tc_launch_nt<32>(st, a, mw, mxh, mxl, p, grid, pdl);
+    case 64: return tc_launch_nt<64>(st, a, mw, mxh, mxl, p, grid, pdl);
+    default: return tc_launch_nt<128>(st, a, mw, mxh, mxl, p, grid, pdl);
+  }
+}
+
+// 1 if any tensor-core GEMM on this device gave up on a barrier since the last check (clears the flag).
+int gemm_tc_check_error() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 1;
+  int* f = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_tc_mu);
+    auto it = g_err_flags.find(dev);
+    if (it == g_err_flags.end()) return 0;
+    f = it->second;
+  }
+  int h = 0;
+  if (cudaMemcpy(&h, f, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) return 1;
+  if (h) cudaMemset(f, 0, sizeof(int));
+  return h;
+}
+
+// Forget tensor maps (call when buffers they describe are freed and their addresses may be reused
+// with another shape -- the key includes the shape, so reuse with the same shape stays valid).
+void gemm_tc_forget() {
+  std::lock_guard<std::mutex> lk(g_tc_mu);
+  g_maps.clear();
+}
+
+}  // namespace tha
+
+using namespace tha;
+
+// C-ABI: out[n*ldo + row] = sum_k W[row,k] X[n,k]   (N rows of activations against one weight matrix)
+static std::map<int, std::pair<float*, size_t>> g_split_scratch;   // per device: [hi | lo]
+
+extern "C" int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const float* W, int M, int K, const float* X, int N,
+                               long long ldx) {
+  if (!out || !W || !X || M < 1 || N < 1 || K < 1) return THA_STATUS_INVALID_ARG;
+  if (K % 4 || K < 32 || (reinterpret_cast<uintptr_t>(W) & 15u)) return THA_STATUS_NOT_SUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  int dev = 0;
+  THA_CUDA_OK(cudaGetDevice(&dev));
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_tc_mu);
+    auto& e = g_split_scratch[dev];
+    const size_t need = (size_t)2 * N * K;
+    if (need > e.second) {
+      if (e.first) THA_CUDA_OK(cudaFree(e.first));
+      THA_CUDA_OK(cudaMalloc(&e.first, need * sizeof(float)));
+      e.second = need;
+    }
+    scratch = e.first;
+  }
+  float* hi = scratch;
+  float* lo = scratch + (size_t)N * K;
+  split_hilo_kernel<<<dim3(ceil_div(K, 256) < 8 ? ceil_div(K, 256) : 8, N), 256, 0, st>>>(X, ldx, hi, lo, K);
+  count_launch();
+  THA_LAUNCH_OK();
+  TcArgs a = {};
+  a.n_mats = 1; a.W[0] = W; a.M[0] = M; a.out_off[0] = 0; a.K = K; a.Xhi = hi; a.Xlo = lo; a.N = N; a.ldx = K;
+  a.out = out; a.ldo = ldo; a.zstride = 0; a.splits = 1; a.colscale = nullptr;
+  if (!gemm_tc_ok(a)) return THA_STATUS_NOT_SUPPORTED;
+  return gemm_tc_launch(st, a, false);
+}
+extern "C" int tha_gemm_check_error(void) { return gemm_tc_check_error(); }

@@ -1,0 +1,36 @@
+// Host-side interface of the tcgen05 weight matmul (gemm_tc.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+namespace tha {
+
+#define THA_TRY_RC(expr) do { int _st = (expr); if (_st != THA_STATUS_SUCCESS) return _st; } while (0)
+
+struct TcArgs {
+  int n_mats;                 // 1..3 stacked weight matrices with the same K
+  const float* W[3]; int M[3]; int out_off[3];   // rows of matrix i land at out[n*ldo + out_off[i] + row]
+  int K;
+  const float* Xhi; const float* Xlo; int N; long long ldx;   // activations [N, ldx] split: hi = tf32(x), lo = x - hi
+  float* out; long long ldo; long long zstride;  // split z writes out + z*zstride (partials, summed by the consumer)
+  int splits;                 // split-K factor (>= 1); must divide the k-blocks into exactly `splits` non-empty parts
+  const float* colscale;      // nullable [N]: out *= colscale[n]  (the 1/rms factor of a folded RMSNorm)
+};
+
+struct TcP {                  // kernel parameter block
+  int M[3]; int tiles[3]; int out_off[3];
+  int K, N, kblocks_total, kblocks_per_split;
+  float* out; long long ldo; long long zstride;
+  const float* colscale;
+  int* error_flag;
+  int dbg;
+  int w_hint;                 // weight loads carry an L2 evict-first hint
+};
+
+bool gemm_tc_ok(const TcArgs& a);
+int gemm_tc_pick_nt(int N);
+int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl);
+int gemm_tc_check_error();
+int gemm_tc_init(int** flag_out);   // allocate the per-device error flag (outside any stream capture)
+void gemm_tc_forget();
+
+}  // namespace tha

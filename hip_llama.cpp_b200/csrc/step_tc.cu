@@ -1,0 +1,297 @@
+// The decode step for MORE than 8 slots (and, with n = prompt positions, the building block of
+// batched prefill): weight matmuls on the tensor cores (gemm_tc.cu), everything else fused
+// into four small kernels.  Per layer:
+//
+//   prep          x += sum_z partial[z]  (the residual add of the previous wo / w2 matmul; layer 0: the
+//                 embedding gather, src/thaDNN.cpp:31-36), then RMSNorm folded: xg = x * g split
+//                 into tf32 hi/lo, 1/rms kept aside as the matmul's column scale (run.cc:196-209)
+//   gemm          wq|wk|wv (one launch, split-K partials)                     (src/thaDNN.cpp:44-46)
+//   rope_scatter  sum the partials, RoPE on q and k, K/V rows into the cache  (src/thaDNN.cpp:48-49)
+//   attention     fused QK^T / online softmax / PV (attention.cu), output also written as hi/lo
+//   gemm          wo  -> partials (the add happens in the next prep)          (src/thaDNN.cpp:56-59)
+//   prep          x += partials, RMSNorm(ffn) folded, split
+//   gemm          w1|w3 (one launch)                                          (src/thaDNN.cpp:63-64)
+//   swiglu_split  silu(w1.x) * (w3.x) -> hi/lo                                (src/thaDNN.cpp:66-67)
+//   gemm          w2  -> partials                                             (src/thaDNN.cpp:69-72)
+// then prep(final norm) -> gemm(wcls) -> logits (-> argmax).
+//
+// Split-K partials are summed by their consumer in a fixed order, so the step is bit-reproducible
+// run to run (no floating-point atomics anywhere).
+#include <map>
+#include <mutex>
+
+#include "common.cuh"
+#include "gemm_tc.h"
+#include "workspace.h"
+
+namespace tha {
+
+int argmax_launch(cudaStream_t st, int B, const float* logits, int vocab, int* next, bool pdl);
+bool attn_fused_supported(int n_heads, int head_size, int dim, int kv_dim);
+int attn_fused_nsplit(int B, int nseg, int seq_len);
+int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
+                      const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
+                      int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo);
+
+__device__ __forceinline__ float st_tf32(float v) { return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u); }
+
+// One block per slot.  x row: embedding row (token != nullptr) or x + sum of nz partials.
+__global__ void __launch_bounds__(256) tc_prep_kernel(float* __restrict__ x, const float* __restrict__ part, int nz,
+                                                      long long zstride, const float* __restrict__ emb,
+                                                      const int* __restrict__ token, const int* __restrict__ pos,
+                                                      const float* __restrict__ gain, int d, float* __restrict__ xh,
+                                                      float* __restrict__ xl, float* __restrict__ scale) {
+  __shared__ float red[33];
+  pdl_wait();
+  pdl_trigger();
+  const int b = blockIdx.x;
+  const int d4 = d >> 2;
+  float4* xr = reinterpret_cast<float4*>(x + (size_t)b * d);
+  float4* hr = reinterpret_cast<float4*>(xh + (size_t)b * d);
+  float4* lr = reinterpret_cast<float4*>(xl + (size_t)b * d);
+  if (pos[b] < 0) {   // idle slot: feed zeros to the matmul
+    for (int i = threadIdx.x; i < d4; i += blockDim.x) { hr[i] = make_float4(0.f, 0.f, 0.f, 0.f); lr[i] = hr[i]; }
+    if (threadIdx.x == 0) scale[b] = 0.0f;
+    return;
+  }
+  const float4* er = emb ? reinterpret_cast<const float4*>(emb + (size_t)token[b] * d) : nullptr;
+  float ss = 0.0f;
+  for (int i = threadIdx.x; i < d4; i += blockDim.x) {
+    float4 v;
+    if (er) v = er[i];
+    else {
+      v = xr[i];
+      for (int z = 0; z < nz; z++) {   // fixed order
+        const float4 pz = *reinterpret_cast<const float4*>(part + (size_t)z * zstride + (size_t)b * d + 4 * i);
+        v.x += pz.x; v.y += pz.y; v.z += pz.z; v.w += pz.w;
+      }
+    }
+    if (er || nz) xr[i] = v;
+    ss = dot4(v, v, ss);
+    const float4 g = reinterpret_cast<const float4*>(gain)[i];
+    v.x *= g.x; v.y *= g.y; v.z *= g.z; v.w *= g.w;
+    const float4 h = make_float4(st_tf32(v.x), st_tf32(v.y), st_tf32(v.z), st_tf32(v.w));
+    hr[i] = h;
+    lr[i] = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
+  }
+  const float tot = block_sum(ss, red);
+  if (threadIdx.x == 0) {
+    float m = tot / d;
+    m += 1e-5f;
+    scale[b] = 1.0f / sqrtf(m);
+  }
+}
+
+// q|k|v rows of every slot (sum of nz partials): RoPE on q and k pairs (run.cc:271-286 with the host-built
+// cos/sin tables), q -> state, k/v -> the cache row of pos[b].  grid (pairs / 256, B).
+__global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __restrict__ part, int nz, long long zstride,
+                                                              int ld, const int* __restrict__ pos, int d, int kvd, int hs,
+                                                              const float* __restrict__ rc, const float* __restrict__ rs,
+                                                              float* __restrict__ q, float* __restrict__ kc,
+                                                              float* __restrict__ vc, long long kv_bs, int loff) {
+  pdl_wait();
+  pdl_trigger();
+  const int b = blockIdx.y, pb = pos[b];
+  if (pb < 0) return;
+  const int pair = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = pair * 2;
+  if (i >= d + 2 * kvd) return;
+  float2 v = make_float2(0.f, 0.f);
+  for (int z = 0; z < nz; z++) {
+    const float2 pz = *reinterpret_cast<const float2*>(part + (size_t)z * zstride + (size_t)b * ld + i);
+    v.x += pz.x; v.y += pz.y;
+  }
+  if (i < d + kvd) {
+    const int li = (i < d) ? i : i - d;
+    const int j = (li % hs) >> 1;
+    const float c = rc[(size_t)pb * (hs >> 1) + j], s = rs[(size_t)pb * (hs >> 1) + j];
+    const float r0 = v.x * c - v.y * s, r1 = v.x * s + v.y * c;
+    if (i < d) *reinterpret_cast<float2*>(q + (size_t)b * d + li) = make_float2(r0, r1);
+    else *reinterpret_cast<float2*>(kc + (size_t)b * kv_bs + loff + (size_t)pb * kvd + li) = make_float2(r0, r1);
+  } else {
+    *reinterpret_cast<float2*>(vc + (size_t)b * kv_bs + loff + (size_t)pb * kvd + (i - d - kvd)) = v;
+  }
+}
+
+// hb = silu(a) * c with a = w1.x, c = w3.x (sum of nz partials each), written as tf32 hi/lo.  grid (h / 256, B)
+__global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __restrict__ part, int nz, long long zstride,
+                                                              int ld, const int* __restrict__ pos, int h,
+                                                              float* __restrict__ hh, float* __restrict__ hl) {
+  pdl_wait();
+  pdl_trigger();
+  const int b = blockIdx.y;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= h) return;
+  float r = 0.0f;
+  if (pos[b] >= 0) {
+    float a = 0.0f, c = 0.0f;
+    for (int z = 0; z < nz; z++) {
+      a += part[(size_t)z * zstride + (size_t)b * ld + i];
+      c += part[(size_t)z * zstride + (size_t)b * ld + h + i];
+    }
+    r = a;
+    r *= (1.0f / (1.0f + expf(-r)));   // run.cc:344-347 operation order
+    r *= c;
+  }
+  const float hi = st_tf32(r);
+  hh[(size_t)b * h + i] = hi;
+  hl[(size_t)b * h + i] = r - hi;
+}
+
+// ---- scratch ----------------------------------------------------------------------------
+struct TcScratch {
+  float *xh = nullptr, *xl = nullptr, *hh = nullptr, *hl = nullptr, *scale = nullptr, *part = nullptr;
+  size_t n_x = 0, n_xl = 0, n_h = 0, n_hl = 0, n_part = 0; int n_b = 0;
+};
+static std::map<int, TcScratch> g_tc_scratch;
+static std::mutex g_tc_scratch_mu;
+
+static int grow(float** p, size_t* cap, size_t need, Workspace* ws) {
+  if (need <= *cap) return THA_STATUS_SUCCESS;
+  if (*p) THA_CUDA_OK(cudaFree(*p));
+  THA_CUDA_OK(cudaMalloc(p, need * sizeof(float)));
+  *cap = need;
+  ws->graphs.clear();   // cached graphs captured the old pointers
+  gemm_tc_forget();
+  return THA_STATUS_SUCCESS;
+}
+
+struct TcPlan { int z_qkv, z_wo, z_w13, z_w2; size_t part_floats; };
+
+// split-K factor: enough CTAs to pull HBM bandwidth from small matrices, at least 4 k-blocks per split
+static int pick_splits(int rows_total_tiles, int K) {
+  const int kb = ceil_div(K, 32);
+  int want = ceil_div(148, rows_total_tiles);
+  int maxz = kb / 4 > 0 ? kb / 4 : 1;
+  if (want > maxz) want = maxz;
+  if (want > 16) want = 16;
+  if (want < 1) want = 1;
+  // the kernel needs every split non-empty: kb split into `want` parts of ceil(kb / want)
+  while (want > 1 && ceil_div(kb, ceil_div(kb, want)) != want) want--;
+  return want;
+}
+
+static TcPlan make_plan(const tha_config_t& c, int B) {
+  const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads;
+  TcPlan p;
+  p.z_qkv = pick_splits(ceil_div(d, 128) + 2 * ceil_div(kvd, 128), d);
+  p.z_wo = pick_splits(ceil_div(d, 128), d);
+  p.z_w13 = pick_splits(2 * ceil_div(hd, 128), d);
+  p.z_w2 = pick_splits(ceil_div(d, 128), hd);
+  size_t m = (size_t)p.z_qkv * (d + 2 * kvd);
+  if ((size_t)p.z_wo * d > m) m = (size_t)p.z_wo * d;
+  if ((size_t)p.z_w13 * 2 * hd > m) m = (size_t)p.z_w13 * 2 * hd;
+  if ((size_t)p.z_w2 * d > m) m = (size_t)p.z_w2 * d;
+  p.part_floats = m * B;
+  return p;
+}
+
+bool step_tc_supported(const tha_config_t* c, int B) {
+  if (B < 1) return false;
+  const int d = c->dim, hd = c->hidden_dim;
+  if (d % c->n_heads || c->n_heads % c->n_kv_heads) return false;
+  const int hs = d / c->n_heads, kvd = hs * c->n_kv_heads;
+  if (d % 4 || hd % 4 || kvd % 4 || (hs & 1) || d < 32 || hd < 32) return false;
+  return attn_fused_supported(c->n_heads, hs, d, kvd);
+}
+
+// Allocate / grow everything the step needs (never inside a stream capture).
+int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B) {
+  THA_TRY_RC(gemm_tc_init(nullptr));
+  std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
+  TcScratch& s = g_tc_scratch[ws->device];
+  const TcPlan pl = make_plan(*c, B);
+  THA_TRY_RC(grow(&s.xh, &s.n_x, (size_t)B * c->dim, ws));
+  THA_TRY_RC(grow(&s.xl, &s.n_xl, (size_t)B * c->dim, ws));
+  THA_TRY_RC(grow(&s.hh, &s.n_h, (size_t)B * c->hidden_dim, ws));
+  THA_TRY_RC(grow(&s.hl, &s.n_hl, (size_t)B * c->hidden_dim, ws));
+  THA_TRY_RC(grow(&s.part, &s.n_part, pl.part_floats, ws));
+  if (B > s.n_b) {
+    if (s.scale) cudaFree(s.scale);
+    THA_CUDA_OK(cudaMalloc(&s.scale, (size_t)B * sizeof(float)));
+    s.n_b = B;
+    ws->graphs.clear();
+  }
+  const int hs = c->dim / c->n_heads;
+  int J = 8;
+  for (; J >= 1; J--) if ((128 * J) % hs == 0 && c->dim % (128 * J) == 0) break;
+  const int nseg = c->dim / (128 * J);
+  const int nsplit = attn_fused_nsplit(B, nseg, c->seq_len);
+  if (nsplit > 1) THA_TRY_RC(ws_ensure_attn(ws, (size_t)B * nseg * nsplit * 32 * J, B * nseg));
+  return THA_STATUS_SUCCESS;
+}
+
+static int gemm(cudaStream_t st, bool pdl, int n_mats, const float* const* W, const int* M, const int* off, int K,
+                const float* xh, const float* xl, int N, float* out, long long ldo, long long zstride, int splits,
+                const float* colscale) {
+  TcArgs a = {};
+  a.n_mats = n_mats;
+  for (int i = 0; i < n_mats; i++) { a.W[i] = W[i]; a.M[i] = M[i]; a.out_off[i] = off[i]; }
+  a.K = K; a.Xhi = xh; a.Xlo = xl; a.N = N; a.ldx = K; a.out = out; a.ldo = ldo; a.zstride = zstride; a.splits = splits;
+  a.colscale = colscale;
+  return gemm_tc_launch(st, a, pdl);
+}
+
+int step_tc_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_f32_t& w,
+                  const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
+                  const float* rc, const float* rs, bool pdl) {
+  TcScratch sc;
+  {
+    std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
+    sc = g_tc_scratch[ws->device];
+  }
+  const TcPlan pl = make_plan(c, B);
+  const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads, L = c.n_layers;
+  const long long kv_bs = (long long)L * c.seq_len * kvd;
+  const int ld_qkv = d + 2 * kvd, ld_h = 2 * hd;
+  int prev_z = 0;                 // partials waiting to be added into x
+  long long prev_zs = 0;
+  for (int l = 0; l < L; l++) {
+    const int loff = l * c.seq_len * kvd;
+    THA_CUDA_OK(launch(tc_prep_kernel, dim3(B), dim3(256), 0, st, pdl, s.x, (const float*)sc.part, prev_z, prev_zs,
+                       l == 0 ? w.token_embedding_table : (const float*)nullptr, token_d, pos_d,
+                       w.rms_att_weight + (size_t)l * d, d, sc.xh, sc.xl, sc.scale));
+    {
+      const float* W[3] = {w.wq + (size_t)l * d * d, w.wk + (size_t)l * d * kvd, w.wv + (size_t)l * d * kvd};
+      const int M[3] = {d, kvd, kvd}, off[3] = {0, d, d + kvd};
+      THA_TRY_RC(gemm(st, pdl, 3, W, M, off, d, sc.xh, sc.xl, B, sc.part, ld_qkv, (long long)B * ld_qkv, pl.z_qkv, sc.scale));
+    }
+    THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld_qkv / 2, 256), B), dim3(256), 0, st, pdl, (const float*)sc.part,
+                       pl.z_qkv, (long long)B * ld_qkv, ld_qkv, pos_d, d, kvd, hs, rc, rs, s.q, s.key_cache, s.value_cache,
+                       kv_bs, loff));
+    THA_TRY_RC(attn_fused_launch(st, ws, B, pos_d, c.n_heads, c.n_kv_heads, s.q, s.xb, s.key_cache + loff, s.value_cache + loff,
+                                 kv_bs, hs, c.seq_len, pdl, sc.xh, sc.xl));
+    {
+      const float* W[1] = {w.wo + (size_t)l * d * d};
+      const int M[1] = {d}, off[1] = {0};
+      THA_TRY_RC(gemm(st, pdl, 1, W, M, off, d, sc.xh, sc.xl, B, sc.part, d, (long long)B * d, pl.z_wo, nullptr));
+    }
+    THA_CUDA_OK(launch(tc_prep_kernel, dim3(B), dim3(256), 0, st, pdl, s.x, (const float*)sc.part, pl.z_wo, (long long)B * d,
+                       (const float*)nullptr, token_d, pos_d, w.rms_ffn_weight + (size_t)l * d, d, sc.xh, sc.xl, sc.scale));
+    {
+      const float* W[2] = {w.w1 + (size_t)l * d * hd, w.w3 + (size_t)l * d * hd};
+      const int M[2] = {hd, hd}, off[2] = {0, hd};
+      THA_TRY_RC(gemm(st, pdl, 2, W, M, off, d, sc.xh, sc.xl, B, sc.part, ld_h, (long long)B * ld_h, pl.z_w13, sc.scale));
+    }
+    THA_CUDA_OK(launch(tc_swiglu_split_kernel, dim3(ceil_div(hd, 256), B), dim3(256), 0, st, pdl, (const float*)sc.part, pl.z_w13,
+                       (long long)B * ld_h, ld_h, pos_d, hd, sc.hh, sc.hl));
+    {
+      const float* W[1] = {w.w2 + (size_t)l * d * hd};
+      const int M[1] = {d}, off[1] = {0};
+      THA_TRY_RC(gemm(st, pdl, 1, W, M, off, hd, sc.hh, sc.hl, B, sc.part, d, (long long)B * d, pl.z_w2, nullptr));
+    }
+    prev_z = pl.z_w2;
+    prev_zs = (long long)B * d;
+  }
+  THA_CUDA_OK(launch(tc_prep_kernel, dim3(B), dim3(256), 0, st, pdl, s.x, (const float*)sc.part, prev_z, prev_zs,
+                     (const float*)nullptr, token_d, pos_d, w.rms_final_weight, d, sc.xh, sc.xl, sc.scale));
+  {
+    const float* W[1] = {w.wcls};
+    const int M[1] = {c.vocab_size}, off[1] = {0};
+    THA_TRY_RC(gemm(st, pdl, 1, W, M, off, d, sc.xh, sc.xl, B, logits, c.vocab_size, 0, 1, sc.scale));
+  }
+  if (next_d) THA_TRY_RC(argmax_launch(st, B, logits, c.vocab_size, next_d, pdl));
+  return THA_STATUS_SUCCESS;
+}
+
+}  // namespace tha

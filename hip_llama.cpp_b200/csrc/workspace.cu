@@ -14,7 +14,7 @@ void mega_set_enabled(int v);
 
 static thread_local char g_err[512] = "";
 static thread_local int g_launches = 0;
-static int g_pdl = -1, g_graph = -1;
+static int g_pdl = -1, g_graph = -1, g_tc = -2;
 static std::mutex g_mu;
 static std::map<int, Workspace*> g_ws;
 
@@ -36,6 +36,11 @@ int graph_enabled() {
   if (g_graph < 0) g_graph = env_flag("THA_GRAPH", 1);
   return g_graph;
 }
+int tc_mode() {
+  if (g_tc == -2) { const char* v = getenv("THA_TC"); g_tc = (v && *v) ? atoi(v) : -1; }
+  return g_tc;
+}
+int* opt_tc() { return &g_tc; }
 void count_launch(int n) { g_launches += n; }
 int launches_reset() { int v = g_launches; g_launches = 0; return v; }
 int launches_get() { return g_launches; }
@@ -128,6 +133,7 @@ extern "C" int tha_set_option(const char* name, int value) {
   if (!name) return THA_STATUS_INVALID_ARG;
   if (!strcmp(name, "pdl")) { *tha::opt_pdl() = value != 0; return THA_STATUS_SUCCESS; }
   if (!strcmp(name, "graph")) { *tha::opt_graph() = value != 0; return THA_STATUS_SUCCESS; }
+  if (!strcmp(name, "tc")) { *tha::opt_tc() = value; return THA_STATUS_SUCCESS; }
   if (!strcmp(name, "mega")) { tha::mega_set_enabled(value); return THA_STATUS_SUCCESS; }
   return THA_STATUS_INVALID_ARG;
 }

@@ -72,7 +72,8 @@ typedef struct {
 /* ---- library ---------------------------------------------------------------- */
 int tha_version(void);
 const char* tha_last_error(void);       /* text of the last CUDA error seen by this library */
-int tha_set_option(const char* name, int value); /* "pdl", "graph", "mega" (0/1) */
+int tha_set_option(const char* name, int value); /* "pdl", "graph", "mega" (0/1); "tc": -1 auto (tensor-core
+                                                    matmuls for more than 8 slots), 0 never, 1 whenever supported */
 
 /* ---- runtime shim: the only way the C++ host layer touches the CUDA runtime ---------
  * (reference: hipSetDevice / hipMalloc / hipMemcpy / hipHostMalloc / hipStreamCreate /
@@ -113,6 +114,15 @@ int tha_matmulvec_f32(void* stream, float* C, const float* B, const float* A, in
 int tha_matmul_reduction_f32(void* stream, const float* A, const float* B, float* C, int M, int N, int K);
 /* thaBLAS_s_matmul, src/thaBLAS.cpp:134-170: C[M,N] = A[M,K] . B[K,N], all row-major */
 int tha_matmul_f32(void* stream, int m, int n, int k, const float* A, const float* B, float* C);
+
+/* Tensor-core form (tcgen05, error-compensated 3xTF32, fp32 in / fp32 out) of the skinny matmul
+ * thaBLAS_s_matmul_reduction, src/thaBLAS.cpp:281-319: out[n*ldo + i] = sum_k W[i,k] X[n*ldx + k]
+ * for N activation rows against an [M, K] row-major weight matrix.  NOT_SUPPORTED unless
+ * K % 4 == 0, K >= 32 and W is 16-byte aligned. */
+int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const float* W, int M, int K, const float* X, int N,
+                    long long ldx);
+/* 1 if a tensor-core matmul on the current device gave up on a pipeline barrier since the last call */
+int tha_gemm_check_error(void);
 
 /* ---- thaDNN ops ----------------------------------------------------------------- */
 /* thaDNN_s_rmsnorm_v2_batch, src/thaDNN/thaDNN_rmsnorm.cpp:35-83; rows `dim` apart, o may alias x */

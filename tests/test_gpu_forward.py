@@ -112,6 +112,32 @@ def test_fp32_batched_ragged_vs_oracle(oracle, tmp_path, name, B):
 
 
 @pytest.mark.parametrize("name", list(MODELS))
+@pytest.mark.parametrize("B", [9, 16, 33, 70, 130])
+def test_fp32_tensor_core_step_vs_oracle(oracle, tmp_path, name, B):
+    """More than 8 slots: the step runs its weight matmuls on the tensor cores (step_tc.cu, 3xTF32).
+    Same comparison, same 1e-4 tolerance as the GEMV path."""
+    cfg, w, v0, v2 = small_model_files(str(tmp_path), name, MODELS[name])
+    e = engine_from_v0(v0, B)
+    m = oracle.open(v0)
+    flips = run_ragged(e, m, min(cfg.seq_len, 12), B, np.random.default_rng(B), FP32_EPS)
+    assert e.last_step_launches() > 1
+    assert flips == 0
+
+
+def test_fp32_tensor_core_step_forced_small_batch(oracle, tmp_path):
+    """tha_set_option("tc", 1): the tensor-core step for 3 slots agrees with the oracle too."""
+    lib = load_pkg("cabi").lib()
+    cfg, w, v0, v2 = small_model_files(str(tmp_path), "fusedA", MODELS["fusedA"])
+    lib.c.tha_set_option(b"tc", 1)
+    try:
+        e = engine_from_v0(v0, 3)
+        flips = run_ragged(e, oracle.open(v0), 16, 3, np.random.default_rng(0), FP32_EPS)
+    finally:
+        lib.c.tha_set_option(b"tc", -1)
+    assert flips == 0
+
+
+@pytest.mark.parametrize("name", list(MODELS))
 @pytest.mark.parametrize("B", [1, 4, 9])
 def test_q8_batched_ragged_vs_oracle(oracle, tmp_path, name, B):
     cfg, w, v0, v2 = small_model_files(str(tmp_path), name, MODELS[name])

@@ -280,3 +280,32 @@ def test_matmul_batch_q8(L, oracle, M, K, gs, B):
         # differs (two rows' lanes add in a tree, the CPU adds left to right): a few ulps of the
         # largest partial sum, so the bound is stated relative to the output scale
         assert_close_scaled(got[b], oracle.matmul_q8(wq, ws, xq[b], xs[b], gs), 4e-6, f"q8 matmul b{b}")
+
+
+# ---- tensor-core weight matmul (tcgen05, 3xTF32) ------------------------------------------
+@pytest.mark.parametrize("M,K,N", [(128, 32, 1), (100, 132, 5), (768, 768, 9), (2304, 768, 33), (768, 2048, 64),
+                                   (4096, 768, 128), (1000, 1000, 130), (512, 4096, 257)])
+def test_gemm_tf32x3_vs_oracle(L, oracle, M, K, N):
+    """out[n, i] = sum_k W[i, k] X[n, k] on the tensor cores against the CPU matmul (run.cc:217-228) at the
+    reference's matmul tolerance 1e-3 abs-or-rel (scripts/test/thaBLAS.test.cpp) -- and, tighter, within 5e-5 of the
+    largest output (3xTF32 keeps fp32-level accuracy; plain TF32 would sit at ~1e-3)."""
+    import torch
+    rng = np.random.default_rng(M + K + N)
+    w = (rng.random((M, K), dtype=np.float32) - 0.5)
+    x = (rng.random((N, K), dtype=np.float32) - 0.5)
+    W, X, O = tdev(w), tdev(x), tdev(np.full((N, M), np.nan, np.float32))
+    sync()
+    L.check(L.c.tha_gemm_tf32x3(stream_ptr(), P(O), M, P(W), M, K, P(X), N, K), "tha_gemm_tf32x3")
+    sync()
+    assert L.c.tha_gemm_check_error() == 0
+    got = O.cpu().numpy()
+    want = np.stack([oracle.matmul(w, x[n]) for n in range(min(N, 6))])
+    assert_close(got[: want.shape[0]], want, 1e-3, f"gemm {M}x{K}x{N}")
+    full = x.astype(np.float64) @ w.astype(np.float64).T
+    assert np.abs(got - full).max() <= 5e-5 * np.abs(full).max()
+
+
+def test_gemm_tf32x3_rejects_bad_shapes(L):
+    W, X, O = tdev(np.zeros((8, 30), np.float32)), tdev(np.zeros((2, 30), np.float32)), tdev(np.zeros((2, 8), np.float32))
+    assert L.c.tha_gemm_tf32x3(stream_ptr(), P(O), 8, P(W), 8, 30, P(X), 2, 30) == 7      # K % 4 != 0: NOT_SUPPORTED
+    assert L.c.tha_gemm_tf32x3(stream_ptr(), P(O), 8, P(W), 0, 32, P(X), 2, 32) == 2      # M < 1: invalid argument
