@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=int(os.environ.get("THA_BENCH_BATCH", "8")), help="slots per GPU")
     ap.add_argument("--model", default="s110m", choices=["s110m", "s15m", "7b"])
     ap.add_argument("--quant", default="f32", choices=["f32", "q8"])
+    ap.add_argument("--seq-len", type=int, default=0, help="override the context length (KV slab size) of the architecture")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
@@ -139,6 +140,9 @@ def build_weights(args, device):
     import torch
     cfg, ck = model_config(args.model)
     eng = load_pkg("engine")
+    if args.seq_len:
+        import dataclasses
+        cfg = dataclasses.replace(cfg, seq_len=args.seq_len)
     if args.model == "7b":
         # 26 GB of fp32 host RNG is too slow for a bench; fill on the device (same N(0, 0.02) law)
         return cfg, eng.device_random_weights(cfg, q8=(args.quant == "q8"), seed=1337, device=device), None
@@ -366,6 +370,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
     r = run_ours(args, rank, world, local_rank)
     if rank == 0:
+        cfg = r["cfg"]
         line = base_line(args, cfg, world)
         line["config"]["l2"] = ("inputs larger than L2: %.0f MB of weights streamed once per step vs 126 MB L2; no flush"
                                 % (r["wbytes"] / 1e6)) if r["wbytes"] > 126e6 else \

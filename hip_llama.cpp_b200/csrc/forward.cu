@@ -220,6 +220,8 @@ int decode_step_f32(cudaStream_t st, int B, const tha_config_t* cfg, const tha_w
 
 // ---------------------------------------------------------------------------- Q8_0 ----
 int gemv_q8_launch(cudaStream_t stream, int mode, const GemvP& p, bool pdl);
+int q8_prep_launch(cudaStream_t st, int B, const float* X, int x_stride, const float* rms_w, const int* pos, int K, int gs,
+                   int8_t* xq, float* xs, bool pdl);
 
 struct StepArgsQ8 {
   int B; tha_config_t cfg; tha_weights_q8_t w; tha_state_t s;
@@ -248,6 +250,8 @@ static int issue_step_q8(cudaStream_t st, Workspace* ws, const StepArgsQ8& a, co
     p.out = a.s.q; p.out_batch_stride = d;
     p.kc = a.s.key_cache; p.vc = a.s.value_cache; p.kv_batch_stride = kv_bs; p.loff = loff;
     p.kv_dim = kvd; p.head_size = hs; p.rope_cos = rc; p.rope_sin = rs;
+    THA_TRY(q8_prep_launch(st, a.B, a.s.x, d, p.rms_w, a.pos_d, d, gs, ws->q8_xq, ws->q8_xs, pdl));
+    p.XQ = ws->q8_xq; p.XS = ws->q8_xs;
     THA_TRY(gemv_q8_launch(st, GEMV_QKV, p, pdl));
 
     if (fused) {
@@ -264,6 +268,8 @@ static int issue_step_q8(cudaStream_t st, Workspace* ws, const StepArgsQ8& a, co
     GemvP o = {};
     o.gs = gs; o.Q0 = a.w.wo.q + (size_t)l * d * d; o.S0 = a.w.wo.s + (size_t)l * d * d / gs; o.M0 = d; o.K = d;
     o.B = a.B; o.X = a.s.xb; o.x_stride = d; o.pos = a.pos_d; o.out = a.s.x; o.out_batch_stride = d;
+    THA_TRY(q8_prep_launch(st, a.B, a.s.xb, d, nullptr, a.pos_d, d, gs, ws->q8_xq, ws->q8_xs, pdl));
+    o.XQ = ws->q8_xq; o.XS = ws->q8_xs;
     THA_TRY(gemv_q8_launch(st, GEMV_RESID, o, pdl));
 
     GemvP f = {};
@@ -272,17 +278,23 @@ static int issue_step_q8(cudaStream_t st, Workspace* ws, const StepArgsQ8& a, co
     f.Q1 = a.w.w3.q + (size_t)l * d * hd; f.S1 = a.w.w3.s + (size_t)l * d * hd / gs; f.M1 = hd;
     f.K = d; f.B = a.B; f.X = a.s.x; f.x_stride = d; f.rms_w = a.w.rms_ffn_weight + (size_t)l * d;
     f.pos = a.pos_d; f.out = a.s.hb; f.out_batch_stride = hd;
+    THA_TRY(q8_prep_launch(st, a.B, a.s.x, d, f.rms_w, a.pos_d, d, gs, ws->q8_xq, ws->q8_xs, pdl));
+    f.XQ = ws->q8_xq; f.XS = ws->q8_xs;
     THA_TRY(gemv_q8_launch(st, GEMV_SWIGLU, f, pdl));
 
     GemvP g = {};
     g.gs = gs; g.Q0 = a.w.w2.q + (size_t)l * d * hd; g.S0 = a.w.w2.s + (size_t)l * d * hd / gs; g.M0 = d; g.K = hd;
     g.B = a.B; g.X = a.s.hb; g.x_stride = hd; g.pos = a.pos_d; g.out = a.s.x; g.out_batch_stride = d;
+    THA_TRY(q8_prep_launch(st, a.B, a.s.hb, hd, nullptr, a.pos_d, hd, gs, ws->q8_xq, ws->q8_xs, pdl));
+    g.XQ = ws->q8_xq; g.XS = ws->q8_xs;
     THA_TRY(gemv_q8_launch(st, GEMV_RESID, g, pdl));
   }
   float* logits = a.logits_d ? a.logits_d : a.s.logits;
   GemvP cl = {};
   cl.gs = gs; cl.Q0 = a.w.wcls.q; cl.S0 = a.w.wcls.s; cl.M0 = c.vocab_size; cl.K = d; cl.B = a.B; cl.X = a.s.x;
   cl.x_stride = d; cl.rms_w = a.w.rms_final_weight; cl.pos = a.pos_d; cl.out = logits; cl.out_batch_stride = c.vocab_size;
+  THA_TRY(q8_prep_launch(st, a.B, a.s.x, d, cl.rms_w, a.pos_d, d, gs, ws->q8_xq, ws->q8_xs, pdl));
+  cl.XQ = ws->q8_xq; cl.XS = ws->q8_xs;
   THA_TRY(gemv_q8_launch(st, GEMV_PLAIN, cl, pdl));
   if (a.next_d) THA_TRY(argmax_launch(st, a.B, logits, c.vocab_size, a.next_d, pdl));
   return THA_STATUS_SUCCESS;
@@ -314,6 +326,7 @@ int decode_step_q8(cudaStream_t st, int B, const tha_config_t* cfg, const tha_we
     const int nsplit = attn_fused_nsplit(B, nseg, cfg->seq_len);
     if (nsplit > 1) THA_TRY(ws_ensure_attn(ws, (size_t)B * nseg * nsplit * 32 * J, B * nseg));
   }
+  THA_TRY(ws_ensure_q8(ws, B, cfg->dim > cfg->hidden_dim ? cfg->dim : cfg->hidden_dim, gs));
   StepArgsQ8 a;
   memset(&a, 0, sizeof(a));
   a.B = B; a.cfg = *cfg; a.w = *w; a.s = *s; a.token_d = token_d; a.pos_d = pos_d; a.logits_d = logits_d;

@@ -91,6 +91,18 @@ int ws_ensure_tokpos(Workspace* ws, int n_batches) {
   return THA_STATUS_SUCCESS;
 }
 
+int ws_ensure_q8(Workspace* ws, int n_batches, int kmax, int gs) {
+  const size_t need = (size_t)n_batches * kmax;
+  if (need <= ws->q8_cap) return THA_STATUS_SUCCESS;
+  if (ws->q8_xq) { cudaFree(ws->q8_xq); cudaFree(ws->q8_xs); }
+  THA_CUDA_OK(cudaMalloc(&ws->q8_xq, need));
+  (void)gs;   // groups are at least 16 values (the kernel's requirement): need / 16 scales always suffice
+  THA_CUDA_OK(cudaMalloc(&ws->q8_xs, (need / 16 + 1) * sizeof(float)));
+  ws->q8_cap = need;
+  ws->graphs.clear();
+  return THA_STATUS_SUCCESS;
+}
+
 // cos/sin of pos * 10000^(-(2j)/hs), exactly as run.cc:271-277 evaluates them (float
 // powf / cosf / sinf of the host libm), so the fused RoPE is bit-identical to the CPU path.
 int ws_rope(Workspace* ws, int head_size, int seq_len, const float** cos_d, const float** sin_d) {

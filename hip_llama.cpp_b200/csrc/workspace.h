@@ -3,6 +3,7 @@
 // tables, Q8_0 activation scratch, cached CUDA graphs.
 #pragma once
 #include <cuda_runtime.h>
+#include <stdint.h>
 
 #include <map>
 #include <tuple>
@@ -25,6 +26,8 @@ struct Workspace {
   // device mirrors of the host token[] / pos[] arrays of thaDNN_s_forward_batch
   int* tok_d = nullptr; int* pos_d = nullptr; int* tokpos_h = nullptr; int tokpos_cap = 0;
   int* next_d = nullptr; int* next_h = nullptr;   // greedy token per slot (device, pinned host)
+  // Q8_0: quantised activations of the current matmul input ([B, K] int8 + [B, K/gs] scales)
+  int8_t* q8_xq = nullptr; float* q8_xs = nullptr; size_t q8_cap = 0;
   // RoPE cos/sin tables keyed by (head_size, seq_len); built on the host with libm so
   // they are bit-identical to what run.cc:271-277 computes
   std::map<std::pair<int, int>, RopeTable> rope;
@@ -35,6 +38,7 @@ struct Workspace {
 Workspace* workspace();   // for the current device (thread-safe)
 int ws_ensure_attn(Workspace* ws, size_t part_slots, int n_counters);
 int ws_ensure_tokpos(Workspace* ws, int n_batches);
+int ws_ensure_q8(Workspace* ws, int n_batches, int kmax, int gs);
 int ws_rope(Workspace* ws, int head_size, int seq_len, const float** cos_d, const float** sin_d);
 
 }  // namespace tha

@@ -100,6 +100,63 @@ class DeviceWeightsQ8:
         return n
 
 
+def device_random_weights(cfg: Config, q8: bool = False, seed: int = 1337, device="cuda", std: float = 0.02, gs: int = 64):
+    """Random-init weights of the named architecture generated ON the device (benchmarks of models whose
+    host-side generation would take minutes: Llama-2-7B is 26 GB in fp32).  Same N(0, std) law as
+    checkpoint.random_weights; Q8_0 tensors are quantised on the device with the exporter's rule
+    (train/export.py:57-63: scale = max|w| / 127 per group, round half to even)."""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    L, d, h, kvd, V = cfg.n_layers, cfg.dim, cfg.hidden_dim, cfg.kv_dim, cfg.vocab_size
+    shapes = {"tok_emb": (V, d), "wq": (L, d, d), "wk": (L, kvd, d), "wv": (L, kvd, d), "wo": (L, d, d),
+              "w1": (L, h, d), "w2": (L, d, h), "w3": (L, h, d)}
+    norms = {"rms_att": torch.ones(L, d, device=device), "rms_ffn": torch.ones(L, d, device=device),
+             "rms_final": torch.ones(d, device=device)}
+
+    def gen(shape):
+        t = torch.empty(shape, dtype=torch.float32, device=device)
+        t.normal_(0.0, std, generator=g)
+        return t
+
+    if not q8:
+        w = DeviceWeights.__new__(DeviceWeights)
+        w.cfg = cfg
+        w.t = {n: gen(sh) for n, sh in shapes.items()}
+        w.t.update(norms)
+        w.t["wcls"] = w.t["tok_emb"]
+        t = w.t
+        w.c = cabi.WeightsF32(_ptr(t["tok_emb"]), _ptr(t["rms_att"]), _ptr(t["rms_ffn"]), _ptr(t["wq"]), _ptr(t["wk"]),
+                              _ptr(t["wv"]), _ptr(t["wo"]), _ptr(t["w1"]), _ptr(t["w2"]), _ptr(t["w3"]),
+                              _ptr(t["rms_final"]), _ptr(t["wcls"]))
+        return w
+    w = DeviceWeightsQ8.__new__(DeviceWeightsQ8)
+    w.cfg, w.gs = cfg, gs
+    w.t = dict(norms)
+    for n, sh in shapes.items():
+        lead = sh[0] if len(sh) == 3 else 1
+        per = int(np.prod(sh)) // lead
+        q = torch.empty(lead, per, dtype=torch.int8, device=device)
+        sc = torch.empty(lead, per // gs, dtype=torch.float32, device=device)
+        for l in range(lead):   # one layer at a time: bounded fp32 scratch
+            x = gen((per // gs, gs))
+            m = x.abs().amax(dim=1)
+            scale = m / 127.0
+            sc[l] = scale
+            q[l] = torch.round(x / scale[:, None]).to(torch.int8).reshape(-1)
+            del x
+        w.t[n + ".q"], w.t[n + ".s"] = q.reshape(sh), sc
+    w.t["wcls.q"], w.t["wcls.s"] = w.t["tok_emb.q"], w.t["tok_emb.s"]
+    w.t["tok_emb"] = (w.t["tok_emb.q"].reshape(-1, gs).float() * w.t["tok_emb.s"].reshape(-1, 1)).reshape(V, d).contiguous()
+    t = w.t
+
+    def qten(n):
+        return cabi.QTensor(_ptr(t[n + ".q"]), _ptr(t[n + ".s"]))
+
+    w.c = cabi.WeightsQ8(_ptr(t["tok_emb"]), _ptr(t["rms_att"]), _ptr(t["rms_ffn"]), _ptr(t["rms_final"]), qten("wq"),
+                         qten("wk"), qten("wv"), qten("wo"), qten("w1"), qten("w2"), qten("w3"), qten("wcls"), gs)
+    return w
+
+
 class BatchState:
     """Batched RunState: every buffer x B (src/models.cpp:155-179); KV [B][L][S][kv_dim] fp32."""
 
