@@ -214,12 +214,7 @@ def run_ours(args, rank, world, local_rank):
         barrier()
         clocks = sampler.stop() if rank == 0 else None
         ms = ev0.elapsed_time(ev1)
-    if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device=device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_max = float(t.item())
-    else:
-        ms_max = ms
+    ms_max = load_pkg("dp").max_over_ranks(ms, device)   # the job runs at the pace of its slowest rank
     value = world * B * K / (ms_max * 1e-3)
     # algorithmic bytes of the timed steps on this rank (positions W .. W+K-1)
     total_bytes = sum(step_bytes(cfg, wbytes, p, B) for p in range(W, W + K))
@@ -248,10 +243,7 @@ def run_ours(args, rank, world, local_rank):
             estep()
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
-        if world > 1:
-            t = torch.tensor([dt], dtype=torch.float64, device=device)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dt = float(t.item())
+        dt = load_pkg("dp").max_over_ranks(dt, device)
         e2e = {"value": world * B * Ke / dt, "unit": UNIT, "h2d_bytes_per_step": int(2 * 4 * B),
                "d2h_bytes_per_step": int(B * cfg.vocab_size * 4), "steps": Ke,
                "api": "tha_forward_batch_%s (thaDNN_s_forward_batch)" % args.quant}
