@@ -140,33 +140,36 @@ __device__ __forceinline__ float tc_tf32(float v) {
   return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u);
 }
 
+__device__ __forceinline__ long long tc_clock() { long long t; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t)); return t; }
+#define TC_TRACE(slot, i) do { if (p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (i) < 64) p.trace[(slot) * 64 + (i)] = tc_clock(); } while (0)
+
 template <int NT>
 struct TcSmem {
   static constexpr int W_BYTES = TC_BM * 128;                        // one weight k-block, raw fp32, swizzled rows
   static constexpr int X_BYTES = NT * 128;
-  static constexpr int XS_BYTES = 2 * X_BYTES;                       // Xhi | Xlo
-  static constexpr bool SPLIT_ACC = NT <= 128;                       // lo-terms in their own accumulator
-  static constexpr int ACC_COLS = SPLIT_ACC ? 2 * NT : NT;
-  static constexpr int A_COLS = 2 * TC_BK;                           // per operand slot: W hi (32 columns) | W lo (32 columns)
+  static constexpr int XS_BYTES = 2 * X_BYTES;                       // Xhi | Xlo of one k-block (one 2*NT-row MMA operand)
+  static constexpr bool SPLIT_ACC = true;                            // lo-terms in their own accumulator columns [NT, 2NT)
+  static constexpr int ACC_COLS = 2 * NT;
+  static constexpr int A_COLS = 2 * TC_BK;                           // per k-block: W hi (32 columns) | W lo (32 columns)
+  // A pipeline STAGE is KG k-blocks: the single MMA-issuing thread pays its fixed per-stage cost (barrier wait,
+  // fence, commit: ~380 cycles measured) once per KG x 8 MMAs (~60 cycles each).
+  static constexpr int KG = NT <= 64 ? 2 : 1;
+  static constexpr int W_STAGE = KG * W_BYTES, XS_STAGE = KG * XS_BYTES, A_STAGE = KG * A_COLS;
   // Three rings.  W (shared memory): filled by TMA, freed as soon as a converter has read the rows -- it only has
-  // to cover the HBM latency, so it is as deep as shared memory allows (>= 96 KB in flight per SM).  A (TMEM) and
-  // X (shared memory): written by converter / TMA, freed by the MMAs' commit.  SW and SA are multiples of the
-  // number of converter groups so that a ring slot is always served by the same group (a waiter must never be
-  // two barrier phases ahead of the barrier).
-  // Both shared-memory rings are sized to cover their load latency at the HBM rate of one SM (16 KB of W per
-  // ~0.37 us): W from HBM (~2 us under load: >= 6 slots), X from L2 (~1 us: >= 48 KB).
-  // The operand ring (A slot in TMEM + X slot in shared memory, same index) has ONE full barrier (4 converter
-  // warps + the X bytes) and ONE empty barrier (the MMAs' commit): the single MMA-issuing thread pays one wait and
-  // one commit per k-block.
-  static constexpr int SA = NT <= 64 ? 6 : 3;
+  // to cover the HBM latency.  A (TMEM, converter -> MMA) and X (shared memory, TMA -> MMA) share one index, one
+  // full barrier (4 converter warps + the X bytes) and one empty barrier (the MMAs' commit).  Ring lengths are
+  // multiples of the number of converter groups so that a slot is always served by the same group (a waiter must
+  // never be two barrier phases ahead of the barrier).
+  static constexpr int SA_RAW = (512 - ACC_COLS) / A_STAGE;
+  static constexpr int SA = SA_RAW >= 6 ? 6 : 3;
   static constexpr int SX = SA;
-  static constexpr int SW_RAW = (TC_SMEM_LIMIT - 2048 - SX * XS_BYTES) / W_BYTES;
+  static constexpr int SW_RAW = (TC_SMEM_LIMIT - 2048 - SX * XS_STAGE) / W_STAGE;
   static constexpr int SW = SW_RAW >= 12 ? 12 : (SW_RAW / TC_CGROUPS) * TC_CGROUPS;
   static constexpr int NBARS = 2 * SW + 2 * SA + 1;
-  static constexpr int TOTAL = SW * W_BYTES + SX * XS_BYTES + 1024 /*alignment slack*/ + NBARS * 8 + 64;
+  static constexpr int TOTAL = SW * W_STAGE + SX * XS_STAGE + 1024 /*alignment slack*/ + NBARS * 8 + 64;
   static constexpr int TMEM_COLS = 512;
   static_assert(SW >= TC_CGROUPS && SW % TC_CGROUPS == 0 && SA % TC_CGROUPS == 0, "ring / group mismatch");
-  static_assert(ACC_COLS + SA * A_COLS <= 512, "TMEM overflow");
+  static_assert(ACC_COLS + SA * A_STAGE <= 512, "TMEM overflow");
   static_assert(TOTAL <= TC_SMEM_LIMIT, "shared memory overflow");
 };
 
@@ -179,8 +182,8 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
   extern __shared__ unsigned char tc_smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~(uintptr_t)1023);
   unsigned char* wring = smem;
-  unsigned char* xring = smem + S::SW * S::W_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(xring + S::SX * S::XS_BYTES);
+  unsigned char* xring = smem + S::SW * S::W_STAGE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(xring + S::SX * S::XS_STAGE);
   uint64_t* wfull = bars;                     // W k-block landed
   uint64_t* wfree = wfull + S::SW;            // its rows are in registers: the slot may be refilled
   uint64_t* ready = wfree + S::SW;            // operand slot full: W hi/lo in TMEM (4 warps) + X hi/lo landed (TMA bytes)
@@ -200,6 +203,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
   const int kb0 = blockIdx.z * p.kblocks_per_split;
   int nkb = p.kblocks_total - kb0;
   if (nkb > p.kblocks_per_split) nkb = p.kblocks_per_split;
+  const int nst = (nkb + S::KG - 1) / S::KG;   // pipeline stages of KG k-blocks (the last one may be short)
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S::SW; s++) { tc_mbar_init(&wfull[s], 1); tc_mbar_init(&wfree[s], 4); }
@@ -232,68 +236,65 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
     if (lane == 0) {
       uint64_t pol_w;
       asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
-      for (int i = 0; i < nkb; i++) {
+      for (int i = 0; i < nst; i++) {
         const int s = i % S::SW;
         if (i >= S::SW && !tc_mbar_wait(&wfree[s], ((i / S::SW) & 1u) ^ 1u, abort_flag)) break;
-        if (p.dbg & 8) { tc_mbar_arrive(&wfull[s]); continue; }
-        tc_mbar_expect_tx(&wfull[s], S::W_BYTES);
-        tc_tma_2d_hint(wring + s * S::W_BYTES, mw, (kb0 + i) * TC_BK, row0, &wfull[s], pol_w);
+        const int nk = (nkb - i * S::KG) < S::KG ? (nkb - i * S::KG) : S::KG;
+        tc_mbar_expect_tx(&wfull[s], nk * S::W_BYTES);
+        TC_TRACE(0, i);
+        for (int kk = 0; kk < nk; kk++)
+          tc_tma_2d_hint(wring + s * S::W_STAGE + kk * S::W_BYTES, mw, (kb0 + i * S::KG + kk) * TC_BK, row0, &wfull[s], pol_w);
       }
     }
   } else if (warp == 3) {
     // ===== X producer (activations: written by the previous kernel)
     if (lane == 0) {
       pdl_wait();
-      for (int i = 0; i < nkb; i++) {
+      for (int i = 0; i < nst; i++) {
         const int s = i % S::SX;
         if (i >= S::SX && !tc_mbar_wait(&aempty[s], ((i / S::SX) & 1u) ^ 1u, abort_flag)) break;
-        unsigned char* st = xring + s * S::XS_BYTES;
-        if (p.dbg & 4) { tc_mbar_arrive(&ready[s]); continue; }
-        tc_mbar_expect_tx(&ready[s], S::XS_BYTES);
-        tc_tma_2d(st, &mxh, (kb0 + i) * TC_BK, n0, &ready[s]);
-        tc_tma_2d(st + S::X_BYTES, &mxl, (kb0 + i) * TC_BK, n0, &ready[s]);
+        const int nk = (nkb - i * S::KG) < S::KG ? (nkb - i * S::KG) : S::KG;
+        TC_TRACE(1, i);
+        tc_mbar_expect_tx(&ready[s], nk * S::XS_BYTES);
+        for (int kk = 0; kk < nk; kk++) {
+          unsigned char* st = xring + s * S::XS_STAGE + kk * S::XS_BYTES;
+          tc_tma_2d(st, &mxh, (kb0 + i * S::KG + kk) * TC_BK, n0, &ready[s]);
+          tc_tma_2d(st + S::X_BYTES, &mxl, (kb0 + i * S::KG + kk) * TC_BK, n0, &ready[s]);
+        }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer: A (weights, hi / lo) from TMEM, B (activations, hi / lo) from shared memory
     if (lane == 0) {
-      constexpr uint32_t idesc = tc_idesc(NT);
-      for (int i = 0; i < nkb; i++) {
-        const int sa = i % S::SA, sx = sa;
+      constexpr uint32_t idesc = tc_idesc(NT), idesc2 = tc_idesc(2 * NT);
+      for (int i = 0; i < nst; i++) {
+        const int sa = i % S::SA;
+        TC_TRACE(8, i);
         if (!tc_mbar_wait(&ready[sa], (i / S::SA) & 1u, abort_flag)) break;
+        TC_TRACE(9, i);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t xb = tc_smem_u32(xring + sx * S::XS_BYTES);
-        const uint64_t xhi = tc_smem_desc(xb), xlo = tc_smem_desc(xb + S::X_BYTES);
-        const uint32_t ahi = tmem_a + sa * S::A_COLS, alo = ahi + TC_BK;
-        if (p.dbg & 16) {          // experiment: hi.hi chain first, then the lo chain
+        TC_TRACE(5, i);
+        const int nk = (nkb - i * S::KG) < S::KG ? (nkb - i * S::KG) : S::KG;
+        // Per K = 8 step TWO MMAs instead of three: the X tile is stored [Xhi rows | Xlo rows], so one
+        // descriptor over 2*NT rows gives D[:, 0:NT] += Whi.Xhi and D[:, NT:2NT] += Whi.Xlo in a single
+        // instruction (an MMA of this shape costs ~60 cycles for any N <= 128); Wlo.Xhi then adds into the
+        // second half.  Columns [NT, 2NT) hold the small correction terms, [0, NT) the main sum.
 #pragma unroll
-          for (int k = 0; k < TC_BK / 8; k++) tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xhi + (uint64_t)(k * 2), idesc, (i | k) != 0);
+        for (int kk = 0; kk < S::KG; kk++) {
+          if (kk < nk) {
+            const uint64_t xhi = tc_smem_desc(tc_smem_u32(xring + sa * S::XS_STAGE + kk * S::XS_BYTES));
+            const uint32_t ahi = tmem_a + sa * S::A_STAGE + kk * S::A_COLS, alo = ahi + TC_BK;
 #pragma unroll
-          for (int k = 0; k < TC_BK / 8; k++) {
-            tc_mma_tf32_ts(tmem_dl, alo + 8 * k, xhi + (uint64_t)(k * 2), idesc, S::SPLIT_ACC ? (uint32_t)((i | k) != 0) : 1u);
-            tc_mma_tf32_ts(tmem_dl, ahi + 8 * k, xlo + (uint64_t)(k * 2), idesc, 1u);
+            for (int k = 0; k < TC_BK / 8; k++) {       // UMMA K = 8 tf32: 8 TMEM columns of A, 32 bytes (2 descriptor units) of B
+              const uint64_t adv = (uint64_t)(k * 2);
+              tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xhi + adv, idesc2, (uint32_t)((i | kk | k) != 0));
+              tc_mma_tf32_ts(tmem_dl, alo + 8 * k, xhi + adv, idesc, 1u);
+            }
           }
-        } else if (p.dbg & 32) {   // experiment: one accumulator
-#pragma unroll
-          for (int k = 0; k < TC_BK / 8; k++) {
-            tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xhi + (uint64_t)(k * 2), idesc, (i | k) != 0);
-            tc_mma_tf32_ts(tmem_d, alo + 8 * k, xhi + (uint64_t)(k * 2), idesc, 1u);
-            tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xlo + (uint64_t)(k * 2), idesc, 1u);
-          }
-        } else if (p.dbg & 64) {   // experiment: hi.hi only (plain TF32)
-#pragma unroll
-          for (int k = 0; k < TC_BK / 8; k++) tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xhi + (uint64_t)(k * 2), idesc, (i | k) != 0);
-        } else
-        if (!(p.dbg & 1))
-#pragma unroll
-        for (int k = 0; k < TC_BK / 8; k++) {           // UMMA K = 8 tf32: 8 TMEM columns of A, 32 bytes (2 descriptor units) of B
-          const uint64_t adv = (uint64_t)(k * 2);
-          const uint32_t first = (i | k) != 0;
-          tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xhi + adv, idesc, first);
-          tc_mma_tf32_ts(tmem_dl, alo + 8 * k, xhi + adv, idesc, S::SPLIT_ACC ? first : 1u);
-          tc_mma_tf32_ts(tmem_dl, ahi + 8 * k, xlo + adv, idesc, 1u);
         }
+        TC_TRACE(6, i);
         tc_commit(&aempty[sa]);
+        TC_TRACE(7, i);
       }
       tc_commit(accum);
     }
@@ -303,31 +304,38 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
     const int r = q * 32 + lane;
     const int grp = (warp >> 2) - 1;                    // converter group 0..TC_CGROUPS-1
     bool ok = true;
-    for (int i = grp; i < nkb && ok; i += TC_CGROUPS) {
+    for (int i = grp; i < nst && ok; i += TC_CGROUPS) {
       const int sw = i % S::SW, sa = i % S::SA;
+      const int nk = (nkb - i * S::KG) < S::KG ? (nkb - i * S::KG) : S::KG;
       ok = tc_mbar_wait(&wfull[sw], (i / S::SW) & 1u, abort_flag);
-      const unsigned char* wrow = wring + sw * S::W_BYTES + r * 128;
-      uint32_t hi[32], lo[32];
+      if (threadIdx.x == 128 + 128 * grp) TC_TRACE(2, i);
 #pragma unroll
-      for (int j = 0; j < 8; j++) {                      // logical 16-byte chunk j lives at j ^ (row & 7) (SWIZZLE_128B)
-        const float4 v = *reinterpret_cast<const float4*>(wrow + ((j ^ (r & 7)) << 4));
-        const float h0 = tc_tf32(v.x), h1 = tc_tf32(v.y), h2 = tc_tf32(v.z), h3 = tc_tf32(v.w);
-        hi[4 * j + 0] = __float_as_uint(h0); hi[4 * j + 1] = __float_as_uint(h1);
-        hi[4 * j + 2] = __float_as_uint(h2); hi[4 * j + 3] = __float_as_uint(h3);
-        lo[4 * j + 0] = __float_as_uint(v.x - h0); lo[4 * j + 1] = __float_as_uint(v.y - h1);
-        lo[4 * j + 2] = __float_as_uint(v.z - h2); lo[4 * j + 3] = __float_as_uint(v.w - h3);
-      }
-      if (i >= S::SA && ok) ok = tc_mbar_wait(&aempty[sa], ((i / S::SA) & 1u) ^ 1u, abort_flag);
-      const uint32_t ta = tmem_a + sa * S::A_COLS + ((uint32_t)(q * 32) << 16);
-      if (!(p.dbg & 2)) {
-      tc_tmem_st32(ta, hi);                              // consumes every loaded value: the shared-memory reads are complete
-      tc_tmem_st32(ta + TC_BK, lo);
+      for (int kk = 0; kk < S::KG; kk++) {
+        if (kk < nk) {
+          const unsigned char* wrow = wring + sw * S::W_STAGE + kk * S::W_BYTES + r * 128;
+          uint32_t hi[32], lo[32];
+#pragma unroll
+          for (int j = 0; j < 8; j++) {                  // logical 16-byte chunk j lives at j ^ (row & 7) (SWIZZLE_128B)
+            const float4 v = *reinterpret_cast<const float4*>(wrow + ((j ^ (r & 7)) << 4));
+            const float h0 = tc_tf32(v.x), h1 = tc_tf32(v.y), h2 = tc_tf32(v.z), h3 = tc_tf32(v.w);
+            hi[4 * j + 0] = __float_as_uint(h0); hi[4 * j + 1] = __float_as_uint(h1);
+            hi[4 * j + 2] = __float_as_uint(h2); hi[4 * j + 3] = __float_as_uint(h3);
+            lo[4 * j + 0] = __float_as_uint(v.x - h0); lo[4 * j + 1] = __float_as_uint(v.y - h1);
+            lo[4 * j + 2] = __float_as_uint(v.z - h2); lo[4 * j + 3] = __float_as_uint(v.w - h3);
+          }
+          if (kk == 0 && i >= S::SA && ok) ok = tc_mbar_wait(&aempty[sa], ((i / S::SA) & 1u) ^ 1u, abort_flag);
+          if (kk == 0 && threadIdx.x == 128 + 128 * grp) TC_TRACE(3, i);
+          const uint32_t ta = tmem_a + sa * S::A_STAGE + kk * S::A_COLS + ((uint32_t)(q * 32) << 16);
+          tc_tmem_st32(ta, hi);                          // consumes every loaded value: the shared-memory reads are complete
+          tc_tmem_st32(ta + TC_BK, lo);
+        }
       }
       __syncwarp();
       if (lane == 0) tc_mbar_arrive(&wfree[sw]);         // the W slot can be refilled while the stores drain
       asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
+      if (threadIdx.x == 128 + 128 * grp) TC_TRACE(4, i);
       if (lane == 0) tc_mbar_arrive(&ready[sa]);
     }
     // ---- epilogue: lane = weight row within this warp's 32-lane TMEM quarter
@@ -384,6 +392,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static EncodeTiledFn g_encode = nullptr;
+static long long* g_trace = nullptr;   // development aid: tha_gemm_trace()
 static int tc_env(const char* n, int d) { const char* v = getenv(n); return (v && *v) ? atoi(v) : d; }
 static std::mutex g_tc_mu;
 static std::map<std::tuple<const void*, long long, int, long long, int>, CUtensorMap> g_maps;
@@ -483,6 +492,7 @@ int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl) {
   p.out = a.out; p.ldo = a.ldo; p.zstride = a.zstride; p.colscale = a.colscale;
   p.w_hint = tc_env("THA_TC_HINT", 1);
   p.dbg = tc_env("THA_TC_DBG", 0);
+  p.trace = g_trace;
   THA_TRY_RC(gemm_tc_init(&p.error_flag));
   dim3 grid(tiles, ceil_div(a.N, NT), zdim);
   switch (NT) {
@@ -555,3 +565,16 @@ extern "C" int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const fl
   return gemm_tc_launch(st, a, false);
 }
 extern "C" int tha_gemm_check_error(void) { return gemm_tc_check_error(); }
+
+// Development aid: per-k-block clock64 stamps of CTA (0,0,0) of the next tensor-core matmuls.
+// out_host[8][64]: 0 W load issued, 1 X load issued, 2 converter saw W, 3 converter got the TMEM slot,
+// 4 converter stores complete, 5 MMA thread saw the slot full, 6 MMAs issued, 7 commit issued.
+extern "C" int tha_gemm_trace(long long* out_host, int enable) {
+  if (enable && !g_trace) {
+    THA_CUDA_OK(cudaMalloc(&g_trace, 10 * 64 * sizeof(long long)));
+    THA_CUDA_OK(cudaMemset(g_trace, 0, 10 * 64 * sizeof(long long)));
+  }
+  if (out_host && g_trace) THA_CUDA_OK(cudaMemcpy(out_host, g_trace, 10 * 64 * sizeof(long long), cudaMemcpyDeviceToHost));
+  if (!enable && g_trace) { cudaFree(g_trace); g_trace = nullptr; }
+  return THA_STATUS_SUCCESS;
+}

@@ -23,6 +23,7 @@ struct TcP {                  // kernel parameter block
   const float* colscale;
   int* error_flag;
   int dbg;
+  long long* trace;           // development aid (tha_gemm_trace)
   int w_hint;                 // weight loads carry an L2 evict-first hint
 };
 

@@ -61,7 +61,8 @@ __global__ void __launch_bounds__(256) tc_prep_kernel(float* __restrict__ x, con
     if (er) v = er[i];
     else {
       v = xr[i];
-      for (int z = 0; z < nz; z++) {   // fixed order
+#pragma unroll 4
+      for (int z = 0; z < nz; z++) {   // fixed order; unrolled so the loads of several partials are in flight together
         const float4 pz = *reinterpret_cast<const float4*>(part + (size_t)z * zstride + (size_t)b * d + 4 * i);
         v.x += pz.x; v.y += pz.y; v.z += pz.z; v.w += pz.w;
       }
@@ -97,6 +98,7 @@ __global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __res
   const int i = pair * 2;
   if (i >= d + 2 * kvd) return;
   float2 v = make_float2(0.f, 0.f);
+#pragma unroll 4
   for (int z = 0; z < nz; z++) {
     const float2 pz = *reinterpret_cast<const float2*>(part + (size_t)z * zstride + (size_t)b * ld + i);
     v.x += pz.x; v.y += pz.y;
@@ -125,6 +127,7 @@ __global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __res
   float r = 0.0f;
   if (pos[b] >= 0) {
     float a = 0.0f, c = 0.0f;
+#pragma unroll 4
     for (int z = 0; z < nz; z++) {
       a += part[(size_t)z * zstride + (size_t)b * ld + i];
       c += part[(size_t)z * zstride + (size_t)b * ld + h + i];
@@ -158,17 +161,23 @@ static int grow(float** p, size_t* cap, size_t need, Workspace* ws) {
 
 struct TcPlan { int z_qkv, z_wo, z_w13, z_w2; size_t part_floats; };
 
-// split-K factor: enough CTAs to pull HBM bandwidth from small matrices, at least 4 k-blocks per split
-static int pick_splits(int rows_total_tiles, int K) {
+// Split-K factor.  Every CTA streams its share of the weights at the same rate, so the matmul runs at
+// (CTAs / (waves * 148)) of the achievable bandwidth: pick the split count that fills whole waves of the 148 SMs
+// (one CTA per SM), with at least 4 k-blocks per split and a small charge per split for the partials the consumer
+// has to sum.  E.g. 7B wq|wk|wv: 96 tiles -> z = 3 (288 CTAs, 2 waves at 97 %) instead of z = 2 (192 CTAs, 65 %).
+static int pick_splits(int tiles, int K) {
   const int kb = ceil_div(K, 32);
-  int want = ceil_div(148, rows_total_tiles);
-  int maxz = kb / 4 > 0 ? kb / 4 : 1;
-  if (want > maxz) want = maxz;
-  if (want > 16) want = 16;
-  if (want < 1) want = 1;
-  // the kernel needs every split non-empty: kb split into `want` parts of ceil(kb / want)
-  while (want > 1 && ceil_div(kb, ceil_div(kb, want)) != want) want--;
-  return want;
+  int best = 1;
+  float best_score = -1.0f;
+  for (int z = 1; z <= 16; z++) {
+    if (z > 1 && kb / z < 4) break;
+    if (ceil_div(kb, ceil_div(kb, z)) != z) continue;   // the kernel needs every split non-empty
+    const int ctas = tiles * z;
+    const float eff = (float)ctas / (float)(ceil_div(ctas, 148) * 148);
+    const float score = eff - 0.012f * (z - 1);
+    if (score > best_score) { best_score = score; best = z; }
+  }
+  return best;
 }
 
 static TcPlan make_plan(const tha_config_t& c, int B) {
