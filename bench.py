@@ -48,7 +48,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=256)
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=int(os.environ.get("THA_BENCH_BATCH", "8")), help="slots per GPU")
+    ap.add_argument("--batch", type=int, default=int(os.environ.get("THA_BENCH_BATCH", "256")), help="slots per GPU")
     ap.add_argument("--model", default="s110m", choices=["s110m", "s15m", "7b"])
     ap.add_argument("--quant", default="f32", choices=["f32", "q8"])
     ap.add_argument("--seq-len", type=int, default=0, help="override the context length (KV slab size) of the architecture")
@@ -74,6 +74,17 @@ def measured_peak():
         return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     except Exception:
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def measured_traffic(args):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one decode step, from the committed ncu capture of this
+    exact configuration (profiles/traffic.json, keyed model/quant/B<slots>); None when it was not captured."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        return t.get(f"{args.model}/{args.quant}/B{args.batch}", {}).get("bytes_per_step")
+    except OSError:
+        return None
 
 
 def step_bytes(cfg, weight_bytes, pos, B, elem_bytes_emb=4, write_logits=True):
@@ -227,12 +238,11 @@ def run_ours(args, rank, world, local_rank):
         lg_host = torch.empty(B, cfg.vocab_size, dtype=torch.float32).pin_memory()
         tok_h = tok0.copy()
         pos_h = np.zeros(B, np.int32)
-        lg_np = lg_host.numpy()
         Ke = min(K, 128)
 
         def estep():
             e.forward_batch(tok_h, pos_h, lg_host, stream=stream)   # H2D token/pos, step, D2H logits, sync
-            tok_h[:] = lg_np.argmax(axis=1)                         # greedy sampler on the host, as the driver does
+            tok_h[:] = lg_host.argmax(dim=1).numpy()                # greedy sampler on the host cores, as the driver does
             pos_h[:] += 1
 
         for _ in range(W):
@@ -370,7 +380,7 @@ def main():
         line.update({"value": r["value"], "ms_per_step": r["ms_per_step"], "e2e": r["e2e"],
                      "gpu_launches": r["launches"], "clocks": r["clocks"]})
         line["roofline"] = {"bound": "hbm", "achieved": r["achieved"], "peak": r["peak"], "unit": "GB/s",
-                            "frac": r["achieved"] / r["peak"], "traffic": None,
+                            "frac": r["achieved"] / r["peak"], "traffic": measured_traffic(args),
                             "kernel": ("mega_step_kernel (whole decode step, 1 persistent launch)" if r["launches_per_step"] == 1 else
                                        "decode step (%d kernels per step, CUDA-graph replay)" % r["launches_per_step"]),
                             "bytes_per_step": r["bytes_per_step"], "peak_source": r["peak_src"],

@@ -43,6 +43,10 @@ int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B);
 int step_tc_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_f32_t& w,
                   const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
                   const float* rc, const float* rs, bool pdl);
+bool prefill_tc_supported(const tha_config_t* c);
+int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_f32_t& w,
+                    const tha_state_t& s, int n_seqs, const int* slot, const int* pos0, const int* len,
+                    const int* tokens, float* logits, int* next_d, const float* rc, const float* rs);
 int gemm_tc_check_error();
 int tc_mode();   // -1 auto (B > 8), 0 never, 1 whenever the shape allows
 int advance_launch(cudaStream_t st, int B, int* token, int* pos, const int* next, int seq_len, bool pdl);
@@ -431,6 +435,27 @@ extern "C" int tha_forward_greedy_q8(void* stream, int n_batches, const tha_conf
                                return decode_step_q8(st, n_batches, cfg, w, s, tok_d, pos_d, nullptr, next_d);
                              });
 }
+
+// Batched prompt ingestion: what the reference does one forced-prompt step at a time
+// (src/llama.cpp:1029-1030) in one pass of tensor-core matmuls over all prompt positions.
+extern "C" int tha_prefill_f32(void* stream, const tha_config_t* cfg, const tha_weights_f32_t* w, const tha_state_t* s,
+                               int n_seqs, const int* slot_host, const int* pos0_host, const int* len_host,
+                               const int* tokens_host, float* logits_d, int* next_d) {
+  if (!cfg || !w || !s || n_seqs < 1 || !slot_host || !pos0_host || !len_host || !tokens_host) return THA_STATUS_INVALID_ARG;
+  THA_TRY(validate_f32(1, cfg, w, s));
+  if (!prefill_tc_supported(cfg)) return THA_STATUS_NOT_SUPPORTED;
+  Workspace* ws = workspace();
+  if (!ws) return THA_STATUS_EXECUTION_FAILED;
+  const float *rc, *rs;
+  THA_TRY(ws_rope(ws, cfg->dim / cfg->n_heads, cfg->seq_len, &rc, &rs));
+  launches_reset();
+  const int rcode = step_tc_prefill((cudaStream_t)stream, ws, *cfg, *w, *s, n_seqs, slot_host, pos0_host, len_host, tokens_host,
+                                    logits_d, next_d, rc, rs);
+  last_step_launches_set(launches_get());
+  return rcode;
+}
+
+extern "C" int tha_prefill_supported(const tha_config_t* cfg) { return (cfg && prefill_tc_supported(cfg)) ? 1 : 0; }
 
 extern "C" int tha_last_step_launches(void) { return last_step_launches_get(); }
 

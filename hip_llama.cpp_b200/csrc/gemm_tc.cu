@@ -141,7 +141,7 @@ __device__ __forceinline__ float tc_tf32(float v) {
 }
 
 __device__ __forceinline__ long long tc_clock() { long long t; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t)); return t; }
-#define TC_TRACE(slot, i) do { if (p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (i) < 64) p.trace[(slot) * 64 + (i)] = tc_clock(); } while (0)
+#define TC_TRACE(slot, i) do { if (p.trace && blockIdx.x == 0 && blockIdx.z == 0 && (i) < 64) p.trace[(slot) * 64 + (i)] = tc_clock(); } while (0)
 
 template <int NT>
 struct TcSmem {
@@ -195,11 +195,13 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   // ---- which tile
-  int tile = blockIdx.x, mat = 0;
+  // blockIdx.x = tile * ny + column tile: the CTAs that share a weight tile are neighbours in launch order, so the
+  // tile comes from HBM once and from L2 for the others (activations stay L2-resident across weight tiles)
+  int tile = blockIdx.x / p.ny, mat = 0;
   if (tile >= p.tiles[0]) { tile -= p.tiles[0]; mat = 1; if (tile >= p.tiles[1]) { tile -= p.tiles[1]; mat = 2; } }
   const CUtensorMap* mw = (mat == 0) ? &mw0 : (mat == 1 ? &mw1 : &mw2);
   const int row0 = tile * TC_BM;
-  const int n0 = blockIdx.y * NT;
+  const int n0 = (blockIdx.x % p.ny) * NT;
   const int kb0 = blockIdx.z * p.kblocks_per_split;
   int nkb = p.kblocks_total - kb0;
   if (nkb > p.kblocks_per_split) nkb = p.kblocks_per_split;
@@ -494,7 +496,8 @@ int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl) {
   p.dbg = tc_env("THA_TC_DBG", 0);
   p.trace = g_trace;
   THA_TRY_RC(gemm_tc_init(&p.error_flag));
-  dim3 grid(tiles, ceil_div(a.N, NT), zdim);
+  p.ny = ceil_div(a.N, NT);
+  dim3 grid(tiles * p.ny, 1, zdim);
   switch (NT) {
     case 16: return tc_launch_nt<16>(st, a, mw, mxh, mxl, p, grid, pdl);
     case 32: return tc_launch_nt<32>(st, a, mw, mxh, mxl, p, grid, pdl);

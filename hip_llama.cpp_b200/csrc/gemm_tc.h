@@ -18,7 +18,7 @@ struct TcArgs {
 
 struct TcP {                  // kernel parameter block
   int M[3]; int tiles[3]; int out_off[3];
-  int K, N, kblocks_total, kblocks_per_split;
+  int K, N, ny, kblocks_total, kblocks_per_split;   // ny = column tiles
   float* out; long long ldo; long long zstride;
   const float* colscale;
   int* error_flag;

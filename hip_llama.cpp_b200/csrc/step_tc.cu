@@ -1,6 +1,7 @@
-// The decode step for MORE than 8 slots (and, with n = prompt positions, the building block of
-// batched prefill): weight matmuls on the tensor cores (gemm_tc.cu), everything else fused
-// into four small kernels.  Per layer:
+// The decode step for MORE than 8 slots, and batched prompt ingestion (prefill): weight matmuls on
+// the tensor cores (gemm_tc.cu), everything else fused into four small kernels.  The unit of work
+// is a ROW = one (slot, position, token): a decode step has one row per slot, a prefill chunk one row
+// per prompt position (rows of a sequence are contiguous, positions ascending).  Per layer:
 //
 //   prep          x += sum_z partial[z]  (the residual add of the previous wo / w2 matmul; layer 0: the
 //                 embedding gather, src/thaDNN.cpp:31-36), then RMSNorm folded: xg = x * g split
@@ -13,12 +14,15 @@
 //   gemm          w1|w3 (one launch)                                          (src/thaDNN.cpp:63-64)
 //   swiglu_split  silu(w1.x) * (w3.x) -> hi/lo                                (src/thaDNN.cpp:66-67)
 //   gemm          w2  -> partials                                             (src/thaDNN.cpp:69-72)
-// then prep(final norm) -> gemm(wcls) -> logits (-> argmax).
+// then prep(final norm) -> gemm(wcls) -> logits (-> argmax); prefill runs the classifier only on the last
+// row of each sequence (gathered by the final prep), and its attention is attn_prefill.cu (one pass over the
+// cache per 64 query rows) instead of the per-row decode kernel.
 //
 // Split-K partials are summed by their consumer in a fixed order, so the step is bit-reproducible
 // run to run (no floating-point atomics anywhere).
 #include <map>
 #include <mutex>
+#include <vector>
 
 #include "common.cuh"
 #include "gemm_tc.h"
@@ -33,25 +37,35 @@ int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
                       int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo);
 
+bool attn_prefill_supported(int head_size, int kv_dim);
+int attn_prefill_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_heads, int head_size, const float* q,
+                        float* out, float* out_hi, float* out_lo, const float* kc, const float* vc,
+                        long long kv_batch_stride, const int* row_slot, const int* row_pos, const int* tile_row0,
+                        const int* tile_n, bool pdl);
+
 __device__ __forceinline__ float st_tf32(float v) { return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u); }
 
-// One block per slot.  x row: embedding row (token != nullptr) or x + sum of nz partials.
+// One block per output row.  x row: embedding row (emb != nullptr) or x + sum of nz partials.  With `gather`
+// output row r is computed from source row gather[r] (the classifier input of a prefill chunk: the last
+// row of every sequence) and x is left untouched.
 __global__ void __launch_bounds__(256) tc_prep_kernel(float* __restrict__ x, const float* __restrict__ part, int nz,
                                                       long long zstride, const float* __restrict__ emb,
                                                       const int* __restrict__ token, const int* __restrict__ pos,
                                                       const float* __restrict__ gain, int d, float* __restrict__ xh,
-                                                      float* __restrict__ xl, float* __restrict__ scale) {
+                                                      float* __restrict__ xl, float* __restrict__ scale,
+                                                      const int* __restrict__ gather) {
   __shared__ float red[33];
   pdl_wait();
   pdl_trigger();
-  const int b = blockIdx.x;
+  const int ob = blockIdx.x;
+  const int b = gather ? gather[ob] : ob;
   const int d4 = d >> 2;
   float4* xr = reinterpret_cast<float4*>(x + (size_t)b * d);
-  float4* hr = reinterpret_cast<float4*>(xh + (size_t)b * d);
-  float4* lr = reinterpret_cast<float4*>(xl + (size_t)b * d);
+  float4* hr = reinterpret_cast<float4*>(xh + (size_t)ob * d);
+  float4* lr = reinterpret_cast<float4*>(xl + (size_t)ob * d);
   if (pos[b] < 0) {   // idle slot: feed zeros to the matmul
     for (int i = threadIdx.x; i < d4; i += blockDim.x) { hr[i] = make_float4(0.f, 0.f, 0.f, 0.f); lr[i] = hr[i]; }
-    if (threadIdx.x == 0) scale[b] = 0.0f;
+    if (threadIdx.x == 0) scale[ob] = 0.0f;
     return;
   }
   const float4* er = emb ? reinterpret_cast<const float4*>(emb + (size_t)token[b] * d) : nullptr;
@@ -67,7 +81,7 @@ __global__ void __launch_bounds__(256) tc_prep_kernel(float* __restrict__ x, con
         v.x += pz.x; v.y += pz.y; v.z += pz.z; v.w += pz.w;
       }
     }
-    if (er || nz) xr[i] = v;
+    if ((er || nz) && !gather) xr[i] = v;
     ss = dot4(v, v, ss);
     const float4 g = reinterpret_cast<const float4*>(gain)[i];
     v.x *= g.x; v.y *= g.y; v.z *= g.z; v.w *= g.w;
@@ -79,7 +93,7 @@ __global__ void __launch_bounds__(256) tc_prep_kernel(float* __restrict__ x, con
   if (threadIdx.x == 0) {
     float m = tot / d;
     m += 1e-5f;
-    scale[b] = 1.0f / sqrtf(m);
+    scale[ob] = 1.0f / sqrtf(m);
   }
 }
 
@@ -89,11 +103,13 @@ __global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __res
                                                               int ld, const int* __restrict__ pos, int d, int kvd, int hs,
                                                               const float* __restrict__ rc, const float* __restrict__ rs,
                                                               float* __restrict__ q, float* __restrict__ kc,
-                                                              float* __restrict__ vc, long long kv_bs, int loff) {
+                                                              float* __restrict__ vc, long long kv_bs, int loff,
+                                                              const int* __restrict__ slot) {
   pdl_wait();
   pdl_trigger();
   const int b = blockIdx.y, pb = pos[b];
   if (pb < 0) return;
+  const int sb = slot ? slot[b] : b;   // cache slab of this row
   const int pair = blockIdx.x * blockDim.x + threadIdx.x;
   const int i = pair * 2;
   if (i >= d + 2 * kvd) return;
@@ -109,9 +125,9 @@ __global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __res
     const float c = rc[(size_t)pb * (hs >> 1) + j], s = rs[(size_t)pb * (hs >> 1) + j];
     const float r0 = v.x * c - v.y * s, r1 = v.x * s + v.y * c;
     if (i < d) *reinterpret_cast<float2*>(q + (size_t)b * d + li) = make_float2(r0, r1);
-    else *reinterpret_cast<float2*>(kc + (size_t)b * kv_bs + loff + (size_t)pb * kvd + li) = make_float2(r0, r1);
+    else *reinterpret_cast<float2*>(kc + (size_t)sb * kv_bs + loff + (size_t)pb * kvd + li) = make_float2(r0, r1);
   } else {
-    *reinterpret_cast<float2*>(vc + (size_t)b * kv_bs + loff + (size_t)pb * kvd + (i - d - kvd)) = v;
+    *reinterpret_cast<float2*>(vc + (size_t)sb * kv_bs + loff + (size_t)pb * kvd + (i - d - kvd)) = v;
   }
 }
 
@@ -144,7 +160,9 @@ __global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __res
 // ---- scratch ----------------------------------------------------------------------------
 struct TcScratch {
   float *xh = nullptr, *xl = nullptr, *hh = nullptr, *hl = nullptr, *scale = nullptr, *part = nullptr;
-  size_t n_x = 0, n_xl = 0, n_h = 0, n_hl = 0, n_part = 0; int n_b = 0;
+  float *xr = nullptr, *qr = nullptr, *xbr = nullptr;   // row-major activations of a prefill chunk (decode uses RunState's)
+  int* tab = nullptr;                                   // prefill row / tile tables
+  size_t n_x = 0, n_xl = 0, n_h = 0, n_hl = 0, n_part = 0, n_xr = 0, n_qr = 0, n_xbr = 0, n_tab = 0; int n_b = 0;
 };
 static std::map<int, TcScratch> g_tc_scratch;
 static std::mutex g_tc_scratch_mu;
@@ -163,35 +181,38 @@ struct TcPlan { int z_qkv, z_wo, z_w13, z_w2; size_t part_floats; };
 
 // Split-K factor.  Every CTA streams its share of the weights at the same rate, so the matmul runs at
 // (CTAs / (waves * 148)) of the achievable bandwidth: pick the split count that fills whole waves of the 148 SMs
-// (one CTA per SM), with at least 4 k-blocks per split and a small charge per split for the partials the consumer
-// has to sum.  E.g. 7B wq|wk|wv: 96 tiles -> z = 3 (288 CTAs, 2 waves at 97 %) instead of z = 2 (192 CTAs, 65 %).
-static int pick_splits(int tiles, int K) {
+// (one CTA per SM), with at least 4 k-blocks per split and a charge per split for the partials the consumer
+// has to sum (their bytes relative to the weight bytes: z * N / K).  E.g. 7B wq|wk|wv at 64 rows: 96 tiles ->
+// z = 3 (288 CTAs, 2 waves at 97 %) instead of z = 2 (192 CTAs, 65 %).
+static int pick_splits(int tiles, int K, int N) {
   const int kb = ceil_div(K, 32);
   int best = 1;
   float best_score = -1.0f;
+  const float charge = 0.012f + 0.25f * (float)N / (float)K / 16.0f;
   for (int z = 1; z <= 16; z++) {
     if (z > 1 && kb / z < 4) break;
     if (ceil_div(kb, ceil_div(kb, z)) != z) continue;   // the kernel needs every split non-empty
     const int ctas = tiles * z;
     const float eff = (float)ctas / (float)(ceil_div(ctas, 148) * 148);
-    const float score = eff - 0.012f * (z - 1);
+    const float score = eff - charge * (z - 1);
     if (score > best_score) { best_score = score; best = z; }
   }
   return best;
 }
 
-static TcPlan make_plan(const tha_config_t& c, int B) {
+static TcPlan make_plan(const tha_config_t& c, int R) {
   const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads;
+  const int ny = ceil_div(R, gemm_tc_pick_nt(R));
   TcPlan p;
-  p.z_qkv = pick_splits(ceil_div(d, 128) + 2 * ceil_div(kvd, 128), d);
-  p.z_wo = pick_splits(ceil_div(d, 128), d);
-  p.z_w13 = pick_splits(2 * ceil_div(hd, 128), d);
-  p.z_w2 = pick_splits(ceil_div(d, 128), hd);
+  p.z_qkv = pick_splits((ceil_div(d, 128) + 2 * ceil_div(kvd, 128)) * ny, d, R);
+  p.z_wo = pick_splits(ceil_div(d, 128) * ny, d, R);
+  p.z_w13 = pick_splits(2 * ceil_div(hd, 128) * ny, d, R);
+  p.z_w2 = pick_splits(ceil_div(d, 128) * ny, hd, R);
   size_t m = (size_t)p.z_qkv * (d + 2 * kvd);
   if ((size_t)p.z_wo * d > m) m = (size_t)p.z_wo * d;
   if ((size_t)p.z_w13 * 2 * hd > m) m = (size_t)p.z_w13 * 2 * hd;
   if ((size_t)p.z_w2 * d > m) m = (size_t)p.z_w2 * d;
-  p.part_floats = m * B;
+  p.part_floats = m * R;
   return p;
 }
 
@@ -204,31 +225,50 @@ bool step_tc_supported(const tha_config_t* c, int B) {
   return attn_fused_supported(c->n_heads, hs, d, kvd);
 }
 
-// Allocate / grow everything the step needs (never inside a stream capture).
-int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B) {
+bool prefill_tc_supported(const tha_config_t* c) {
+  if (!step_tc_supported(c, 1)) return false;
+  const int hs = c->dim / c->n_heads;
+  return attn_prefill_supported(hs, hs * c->n_kv_heads);
+}
+
+// Allocate / grow everything R rows need (never inside a stream capture).
+static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefill, int n_tab) {
   THA_TRY_RC(gemm_tc_init(nullptr));
   std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
   TcScratch& s = g_tc_scratch[ws->device];
-  const TcPlan pl = make_plan(*c, B);
-  THA_TRY_RC(grow(&s.xh, &s.n_x, (size_t)B * c->dim, ws));
-  THA_TRY_RC(grow(&s.xl, &s.n_xl, (size_t)B * c->dim, ws));
-  THA_TRY_RC(grow(&s.hh, &s.n_h, (size_t)B * c->hidden_dim, ws));
-  THA_TRY_RC(grow(&s.hl, &s.n_hl, (size_t)B * c->hidden_dim, ws));
+  const TcPlan pl = make_plan(*c, R);
+  THA_TRY_RC(grow(&s.xh, &s.n_x, (size_t)R * c->dim, ws));
+  THA_TRY_RC(grow(&s.xl, &s.n_xl, (size_t)R * c->dim, ws));
+  THA_TRY_RC(grow(&s.hh, &s.n_h, (size_t)R * c->hidden_dim, ws));
+  THA_TRY_RC(grow(&s.hl, &s.n_hl, (size_t)R * c->hidden_dim, ws));
   THA_TRY_RC(grow(&s.part, &s.n_part, pl.part_floats, ws));
-  if (B > s.n_b) {
+  if (R > s.n_b) {
     if (s.scale) cudaFree(s.scale);
-    THA_CUDA_OK(cudaMalloc(&s.scale, (size_t)B * sizeof(float)));
-    s.n_b = B;
+    THA_CUDA_OK(cudaMalloc(&s.scale, (size_t)R * sizeof(float)));
+    s.n_b = R;
     ws->graphs.clear();
+  }
+  if (prefill) {
+    THA_TRY_RC(grow(&s.xr, &s.n_xr, (size_t)R * c->dim, ws));
+    THA_TRY_RC(grow(&s.qr, &s.n_qr, (size_t)R * c->dim, ws));
+    THA_TRY_RC(grow(&s.xbr, &s.n_xbr, (size_t)R * c->dim, ws));
+    if ((size_t)n_tab > s.n_tab) {
+      if (s.tab) THA_CUDA_OK(cudaFree(s.tab));
+      THA_CUDA_OK(cudaMalloc(&s.tab, (size_t)n_tab * sizeof(int)));
+      s.n_tab = n_tab;
+    }
+    return THA_STATUS_SUCCESS;
   }
   const int hs = c->dim / c->n_heads;
   int J = 8;
   for (; J >= 1; J--) if ((128 * J) % hs == 0 && c->dim % (128 * J) == 0) break;
   const int nseg = c->dim / (128 * J);
-  const int nsplit = attn_fused_nsplit(B, nseg, c->seq_len);
-  if (nsplit > 1) THA_TRY_RC(ws_ensure_attn(ws, (size_t)B * nseg * nsplit * 32 * J, B * nseg));
+  const int nsplit = attn_fused_nsplit(R, nseg, c->seq_len);
+  if (nsplit > 1) THA_TRY_RC(ws_ensure_attn(ws, (size_t)R * nseg * nsplit * 32 * J, R * nseg));
   return THA_STATUS_SUCCESS;
 }
+
+int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B) { return prepare_rows(ws, c, B, false, 0); }
 
 static int gemm(cudaStream_t st, bool pdl, int n_mats, const float* const* W, const int* M, const int* off, int K,
                 const float* xh, const float* xl, int N, float* out, long long ldo, long long zstride, int splits,
@@ -241,66 +281,135 @@ static int gemm(cudaStream_t st, bool pdl, int n_mats, const float* const* W, co
   return gemm_tc_launch(st, a, pdl);
 }
 
-int step_tc_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_f32_t& w,
-                  const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
-                  const float* rc, const float* rs, bool pdl) {
+// What differs between a decode step and a prefill chunk.
+struct RowsIO {
+  int R;                                   // rows
+  float *x, *q, *xb;                       // [R, d] residual stream / rotated queries / attention output
+  const int *token, *pos, *slot;           // [R]; slot == nullptr: row r lives in cache slab r (decode)
+  int n_tiles; const int *tile_row0, *tile_n;   // prefill attention tiles (n_tiles == 0: per-row decode attention)
+  int n_out; const int* out_rows;          // classifier rows (out_rows == nullptr: every row)
+  float* logits; int* next;                // [n_out, vocab] (nullable: skip the classifier), [n_out] (nullable)
+};
+
+static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_f32_t& w,
+                      const tha_state_t& s, const RowsIO& io, const float* rc, const float* rs, bool pdl) {
   TcScratch sc;
   {
     std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
     sc = g_tc_scratch[ws->device];
   }
-  const TcPlan pl = make_plan(c, B);
+  const int R = io.R;
+  const TcPlan pl = make_plan(c, R);
   const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads, L = c.n_layers;
   const long long kv_bs = (long long)L * c.seq_len * kvd;
   const int ld_qkv = d + 2 * kvd, ld_h = 2 * hd;
+  const int* nogather = nullptr;
   int prev_z = 0;                 // partials waiting to be added into x
   long long prev_zs = 0;
   for (int l = 0; l < L; l++) {
     const int loff = l * c.seq_len * kvd;
-    THA_CUDA_OK(launch(tc_prep_kernel, dim3(B), dim3(256), 0, st, pdl, s.x, (const float*)sc.part, prev_z, prev_zs,
-                       l == 0 ? w.token_embedding_table : (const float*)nullptr, token_d, pos_d,
-                       w.rms_att_weight + (size_t)l * d, d, sc.xh, sc.xl, sc.scale));
+    THA_CUDA_OK(launch(tc_prep_kernel, dim3(R), dim3(256), 0, st, pdl, io.x, (const float*)sc.part, prev_z, prev_zs,
+                       l == 0 ? w.token_embedding_table : (const float*)nullptr, io.token, io.pos,
+                       w.rms_att_weight + (size_t)l * d, d, sc.xh, sc.xl, sc.scale, nogather));
     {
       const float* W[3] = {w.wq + (size_t)l * d * d, w.wk + (size_t)l * d * kvd, w.wv + (size_t)l * d * kvd};
       const int M[3] = {d, kvd, kvd}, off[3] = {0, d, d + kvd};
-      THA_TRY_RC(gemm(st, pdl, 3, W, M, off, d, sc.xh, sc.xl, B, sc.part, ld_qkv, (long long)B * ld_qkv, pl.z_qkv, sc.scale));
+      THA_TRY_RC(gemm(st, pdl, 3, W, M, off, d, sc.xh, sc.xl, R, sc.part, ld_qkv, (long long)R * ld_qkv, pl.z_qkv, sc.scale));
     }
-    THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld_qkv / 2, 256), B), dim3(256), 0, st, pdl, (const float*)sc.part,
-                       pl.z_qkv, (long long)B * ld_qkv, ld_qkv, pos_d, d, kvd, hs, rc, rs, s.q, s.key_cache, s.value_cache,
-                       kv_bs, loff));
-    THA_TRY_RC(attn_fused_launch(st, ws, B, pos_d, c.n_heads, c.n_kv_heads, s.q, s.xb, s.key_cache + loff, s.value_cache + loff,
-                                 kv_bs, hs, c.seq_len, pdl, sc.xh, sc.xl));
+    THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld_qkv / 2, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part,
+                       pl.z_qkv, (long long)R * ld_qkv, ld_qkv, io.pos, d, kvd, hs, rc, rs, io.q, s.key_cache, s.value_cache,
+                       kv_bs, loff, io.slot));
+    if (!io.logits && l == L - 1) return THA_STATUS_SUCCESS;   // cache-only ingestion: the last layer's K/V rows are in place
+    if (io.n_tiles > 0) {
+      THA_TRY_RC(attn_prefill_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, sc.xh, sc.xl, s.key_cache + loff,
+                                     s.value_cache + loff, kv_bs, io.slot, io.pos, io.tile_row0, io.tile_n, pdl));
+    } else {
+      THA_TRY_RC(attn_fused_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, s.key_cache + loff,
+                                   s.value_cache + loff, kv_bs, hs, c.seq_len, pdl, sc.xh, sc.xl));
+    }
     {
       const float* W[1] = {w.wo + (size_t)l * d * d};
       const int M[1] = {d}, off[1] = {0};
-      THA_TRY_RC(gemm(st, pdl, 1, W, M, off, d, sc.xh, sc.xl, B, sc.part, d, (long long)B * d, pl.z_wo, nullptr));
+      THA_TRY_RC(gemm(st, pdl, 1, W, M, off, d, sc.xh, sc.xl, R, sc.part, d, (long long)R * d, pl.z_wo, nullptr));
     }
-    THA_CUDA_OK(launch(tc_prep_kernel, dim3(B), dim3(256), 0, st, pdl, s.x, (const float*)sc.part, pl.z_wo, (long long)B * d,
-                       (const float*)nullptr, token_d, pos_d, w.rms_ffn_weight + (size_t)l * d, d, sc.xh, sc.xl, sc.scale));
+    THA_CUDA_OK(launch(tc_prep_kernel, dim3(R), dim3(256), 0, st, pdl, io.x, (const float*)sc.part, pl.z_wo, (long long)R * d,
+                       (const float*)nullptr, io.token, io.pos, w.rms_ffn_weight + (size_t)l * d, d, sc.xh, sc.xl, sc.scale,
+                       nogather));
     {
       const float* W[2] = {w.w1 + (size_t)l * d * hd, w.w3 + (size_t)l * d * hd};
       const int M[2] = {hd, hd}, off[2] = {0, hd};
-      THA_TRY_RC(gemm(st, pdl, 2, W, M, off, d, sc.xh, sc.xl, B, sc.part, ld_h, (long long)B * ld_h, pl.z_w13, sc.scale));
+      THA_TRY_RC(gemm(st, pdl, 2, W, M, off, d, sc.xh, sc.xl, R, sc.part, ld_h, (long long)R * ld_h, pl.z_w13, sc.scale));
     }
-    THA_CUDA_OK(launch(tc_swiglu_split_kernel, dim3(ceil_div(hd, 256), B), dim3(256), 0, st, pdl, (const float*)sc.part, pl.z_w13,
-                       (long long)B * ld_h, ld_h, pos_d, hd, sc.hh, sc.hl));
+    THA_CUDA_OK(launch(tc_swiglu_split_kernel, dim3(ceil_div(hd, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part, pl.z_w13,
+                       (long long)R * ld_h, ld_h, io.pos, hd, sc.hh, sc.hl));
     {
       const float* W[1] = {w.w2 + (size_t)l * d * hd};
       const int M[1] = {d}, off[1] = {0};
-      THA_TRY_RC(gemm(st, pdl, 1, W, M, off, hd, sc.hh, sc.hl, B, sc.part, d, (long long)B * d, pl.z_w2, nullptr));
+      THA_TRY_RC(gemm(st, pdl, 1, W, M, off, hd, sc.hh, sc.hl, R, sc.part, d, (long long)R * d, pl.z_w2, nullptr));
     }
     prev_z = pl.z_w2;
-    prev_zs = (long long)B * d;
+    prev_zs = (long long)R * d;
   }
-  THA_CUDA_OK(launch(tc_prep_kernel, dim3(B), dim3(256), 0, st, pdl, s.x, (const float*)sc.part, prev_z, prev_zs,
-                     (const float*)nullptr, token_d, pos_d, w.rms_final_weight, d, sc.xh, sc.xl, sc.scale));
+  THA_CUDA_OK(launch(tc_prep_kernel, dim3(io.n_out), dim3(256), 0, st, pdl, io.x, (const float*)sc.part, prev_z, prev_zs,
+                     (const float*)nullptr, io.token, io.pos, w.rms_final_weight, d, sc.xh, sc.xl, sc.scale, io.out_rows));
   {
     const float* W[1] = {w.wcls};
     const int M[1] = {c.vocab_size}, off[1] = {0};
-    THA_TRY_RC(gemm(st, pdl, 1, W, M, off, d, sc.xh, sc.xl, B, logits, c.vocab_size, 0, 1, sc.scale));
+    THA_TRY_RC(gemm(st, pdl, 1, W, M, off, d, sc.xh, sc.xl, io.n_out, io.logits, c.vocab_size, 0, 1, sc.scale));
   }
-  if (next_d) THA_TRY_RC(argmax_launch(st, B, logits, c.vocab_size, next_d, pdl));
+  if (io.next) THA_TRY_RC(argmax_launch(st, io.n_out, io.logits, c.vocab_size, io.next, pdl));
   return THA_STATUS_SUCCESS;
+}
+
+int step_tc_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_f32_t& w,
+                  const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
+                  const float* rc, const float* rs, bool pdl) {
+  RowsIO io = {};
+  io.R = B; io.x = s.x; io.q = s.q; io.xb = s.xb; io.token = token_d; io.pos = pos_d; io.slot = nullptr;
+  io.n_tiles = 0; io.n_out = B; io.out_rows = nullptr; io.logits = logits; io.next = next_d;
+  return issue_rows(st, ws, c, w, s, io, rc, rs, pdl);
+}
+
+// Batched prompt ingestion.  Host arrays: sequence i occupies cache slab slot[i], its len[i] tokens (consecutive
+// in `tokens`) go to positions pos0[i] .. pos0[i]+len[i]-1.  Every row's K/V lands in the cache; with `logits`
+// the classifier runs on the last row of each sequence ([n_seqs, vocab], and argmax -> next[n_seqs]).
+int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_f32_t& w,
+                    const tha_state_t& s, int n_seqs, const int* slot, const int* pos0, const int* len,
+                    const int* tokens, float* logits, int* next_d, const float* rc, const float* rs) {
+  if (!prefill_tc_supported(&c)) return THA_STATUS_NOT_SUPPORTED;
+  long long R = 0, T = 0;
+  for (int i = 0; i < n_seqs; i++) {
+    if (len[i] < 1 || pos0[i] < 0 || slot[i] < 0 || (long long)pos0[i] + len[i] > c.seq_len) return THA_STATUS_INVALID_ARG;
+    R += len[i];
+    T += ceil_div(len[i], 64);
+  }
+  if (R < 1 || R > (1 << 20)) return THA_STATUS_INVALID_ARG;
+  // tables: [slot R | pos R | token R | tile_row0 T | tile_n T | last n_seqs]
+  std::vector<int> tab((size_t)3 * R + 2 * T + n_seqs);
+  int *h_slot = tab.data(), *h_pos = h_slot + R, *h_tok = h_pos + R, *h_t0 = h_tok + R, *h_tn = h_t0 + T, *h_last = h_tn + T;
+  int r = 0, t = 0;
+  for (int i = 0; i < n_seqs; i++) {
+    for (int j = 0; j < len[i]; j += 64) { h_t0[t] = r + j; h_tn[t] = (len[i] - j < 64) ? len[i] - j : 64; t++; }
+    for (int j = 0; j < len[i]; j++, r++) {
+      h_slot[r] = slot[i]; h_pos[r] = pos0[i] + j; h_tok[r] = tokens[r];
+      if (tokens[r] < 0 || tokens[r] >= c.vocab_size) return THA_STATUS_INVALID_ARG;
+    }
+    h_last[i] = r - 1;
+  }
+  THA_TRY_RC(prepare_rows(ws, &c, (int)R, true, (int)tab.size()));
+  TcScratch sc;
+  {
+    std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
+    sc = g_tc_scratch[ws->device];
+  }
+  // pageable source: the copy is staged before the call returns, so `tab` may go out of scope
+  THA_CUDA_OK(cudaMemcpyAsync(sc.tab, tab.data(), tab.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  RowsIO io = {};
+  io.R = (int)R; io.x = sc.xr; io.q = sc.qr; io.xb = sc.xbr;
+  io.slot = sc.tab; io.pos = sc.tab + R; io.token = sc.tab + 2 * R;
+  io.n_tiles = (int)T; io.tile_row0 = sc.tab + 3 * R; io.tile_n = sc.tab + 3 * R + T;
+  io.n_out = n_seqs; io.out_rows = sc.tab + 3 * R + 2 * T; io.logits = logits; io.next = logits ? next_d : nullptr;
+  return issue_rows(st, ws, c, w, s, io, rc, rs, true);
 }
 
 }  // namespace tha

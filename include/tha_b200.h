@@ -208,6 +208,18 @@ int tha_argmax_batch_f32(void* stream, int n_batches, const float* logits, int v
 int tha_advance_slots(void* stream, int n_batches, int* token_d, int* pos_d, const int* next_d, int seq_len);
 /* 1 when the step for this shape falls back to the three attention stages and therefore needs
  * tha_state_t.att ([B, n_heads, seq_len]); 0 when the fused attention kernel covers it */
+/* Batched prompt ingestion ("prefill").  The reference feeds a prompt one forced token per
+ * decode step (src/llama.cpp:1029-1030); this runs all prompt positions of n_seqs sequences through the tcgen05
+ * matmuls in one pass.  HOST arrays: sequence i lives in cache slab slot_host[i]; its len_host[i] tokens (concatenated
+ * in tokens_host, sequence after sequence) go to positions pos0_host[i] .. pos0_host[i]+len_host[i]-1.  Every row's K/V
+ * is written to the cache exactly where the decode step would have put it.  logits_d (device, [n_seqs, vocab], nullable):
+ * logits of the LAST position of each sequence; next_d (device, [n_seqs], nullable): their argmax.  With logits_d == NULL
+ * the call only fills the cache.  Asynchronous on `stream`; the host arrays may be reused when it returns. */
+int tha_prefill_f32(void* stream, const tha_config_t* cfg, const tha_weights_f32_t* w, const tha_state_t* s, int n_seqs,
+                    const int* slot_host, const int* pos0_host, const int* len_host, const int* tokens_host,
+                    float* logits_d, int* next_d);
+int tha_prefill_supported(const tha_config_t* cfg); /* 1 when tha_prefill_f32 handles this architecture */
+
 int tha_step_needs_att_scratch(const tha_config_t* cfg);
 /* number of kernels the last tha_decode_step_* call on this thread launched */
 int tha_last_step_launches(void);

@@ -137,6 +137,57 @@ def test_fp32_tensor_core_step_forced_small_batch(oracle, tmp_path):
     assert flips == 0
 
 
+MODELS_PREFILL = dict(MODELS)
+# head sizes 64 and 16 (the other two prefill attention templates), prompts longer than one 64-row query tile
+MODELS_PREFILL["hs64"] = dict(dim=256, hidden_dim=512, n_layers=2, n_heads=4, n_kv_heads=2, vocab_size=300, seq_len=200)
+MODELS_PREFILL["hs16"] = dict(dim=128, hidden_dim=320, n_layers=2, n_heads=8, n_kv_heads=8, vocab_size=300, seq_len=150)
+
+
+@pytest.mark.parametrize("name", list(MODELS_PREFILL))
+def test_fp32_prefill_vs_oracle(oracle, tmp_path, name):
+    """Batched prompt ingestion (tha_prefill_f32): ragged prompts of several sequences in one call, one of them
+    appended at pos0 > 0 to a cache that a first call filled.  Last-position logits and every K/V row against the
+    oracle's token-by-token forward (same 1e-4), then decode steps continue from the prefilled cache."""
+    import torch
+    cfg, w, v0, v2 = small_model_files(str(tmp_path), name, MODELS_PREFILL[name])
+    m = oracle.open(v0)
+    B = 5
+    e = engine_from_v0(v0, B)
+    rng = np.random.default_rng(7)
+    S = cfg.seq_len
+    lens = [1, 7, min(S - 8, 70), min(S - 8, 129), 33]
+    prompts = [rng.integers(0, cfg.vocab_size, size=n).astype(np.int32) for n in lens]
+    seqs = [m.new_seq() for _ in range(B)]
+    want_last = []
+    for b in range(B):
+        for p_, t in enumerate(prompts[b]):
+            lg = seqs[b].forward(int(t), p_)
+        want_last.append(lg.copy())
+    logits = torch.zeros(B, cfg.vocab_size, device="cuda")
+    nxt = torch.zeros(B, dtype=torch.int32, device="cuda")
+    # slot 4: first 20 positions in one call (cache only), the remaining 13 appended by the second call
+    e.prefill([(4, 0, prompts[4][:20])])
+    e.prefill([(b, 0, prompts[b]) for b in range(4)] + [(4, 20, prompts[4][20:])], logits, nxt)
+    torch.cuda.synchronize()
+    assert load_pkg("cabi").lib().c.tha_gemm_check_error() == 0
+    got = logits.cpu().numpy()
+    for b in range(B):
+        assert_close(got[b], want_last[b], FP32_EPS, f"prefill logits slot {b} ({lens[b]} positions)")
+        assert int(nxt[b]) == int(got[b].argmax())
+        n = lens[b]
+        for cache in ("key_cache", "value_cache"):
+            have = getattr(e.state, cache)[b].cpu().numpy()[:, :n]
+            want = seqs[b].buf(cache).reshape(m.n_layers, m.seq_len, m.kv_dim)[:, :n]
+            assert_close(have, want, FP32_EPS, f"{cache} slot {b}")
+    # decode continues where the prompts ended
+    for step in range(3):
+        tok = rng.integers(0, cfg.vocab_size, size=B).astype(np.int32)
+        pos = np.array([lens[b] + step for b in range(B)], np.int32)
+        lg = e.forward_batch(tok, pos).numpy()
+        for b in range(B):
+            assert_close(lg[b], seqs[b].forward(int(tok[b]), int(pos[b])), FP32_EPS, f"decode after prefill, slot {b} step {step}")
+
+
 @pytest.mark.parametrize("name", list(MODELS))
 @pytest.mark.parametrize("B", [1, 4, 9])
 def test_q8_batched_ragged_vs_oracle(oracle, tmp_path, name, B):
