@@ -6,7 +6,7 @@
 //
 // Options (reference :1490-1510): -t temperature, -p top-p, -s seed, -n steps, -i prompt,
 // -z tokenizer path, -m mode (generate|test), -f/-o files, -b batch size.  Additions: -g <n>
-// number of GPUs, -k <file> write the generated token ids, -x 1 ignore stop tokens (timing),
+// number of GPUs, -k <file> write the generated token ids, -x 1 ignore stop tokens (timing), -r 0 prompt token by token,
 // and in test mode -t/-p/-s are honoured when given (-t 0 = greedy).  The checkpoint may be a
 // v0 fp32 file or a v2 Q8_0 file; the version is detected from the header.
 #include <stdio.h>
@@ -34,6 +34,7 @@ static void error_usage() {
   fprintf(stderr, "  -g <int>    number of GPUs (default: all)\n");
   fprintf(stderr, "  -k <string> also write the generated token ids to this file\n");
   fprintf(stderr, "  -x <0|1>    ignore stop tokens (fixed-length timing runs)\n");
+  fprintf(stderr, "  -r <0|1>    fp32 models: ingest prompts in one tensor-core pass (default 1); 0 = one decode step per prompt token\n");
   exit(EXIT_FAILURE);
 }
 
@@ -42,7 +43,7 @@ int main(int argc, char* argv[]) {
   char* checkpoint_path = nullptr;
   const char* tokenizer_path = "./assets/tokenizer.bin";
   float temperature = 1.0f, topp = 0.9f;
-  int steps = 256, batch = 1, n_gpus = 0, ignore_stop = 0;
+  int steps = 256, batch = 1, n_gpus = 0, ignore_stop = 0, prefill = 1;
   const char* prompt = nullptr;
   unsigned long long rng_seed = 0;
   const char* mode = "generate";
@@ -68,6 +69,7 @@ int main(int argc, char* argv[]) {
     else if (f == 'g') n_gpus = atoi(v);
     else if (f == 'k') token_filename = v;
     else if (f == 'x') ignore_stop = atoi(v);
+    else if (f == 'r') prefill = atoi(v);
     else error_usage();
   }
   if (rng_seed == 0) rng_seed = (unsigned int)time(nullptr);
@@ -89,6 +91,7 @@ int main(int argc, char* argv[]) {
   opt.batch_size = batch;
   opt.n_devices = n_gpus;
   opt.ignore_stop = ignore_stop;
+  opt.prefill = prefill;
 
   if (strcmp(mode, "generate") == 0) {
     // one request through the same driver (the reference's generate() is the single-sequence loop, :1087-1147 of run.cc)

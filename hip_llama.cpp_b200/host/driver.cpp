@@ -88,11 +88,11 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
   for (auto& s : samplers) build_sampler(&s, vocab, opt.temperature, opt.topp, opt.seed);
 
   std::atomic<int> next_idx(opt.device_offset);
-  long long gen_cnt = 0, n_steps = 0;
+  long long gen_cnt = 0, n_steps = 0, n_prefill_rows = 0;
   double load_s = 0, loop_s = 0;
   const bool greedy = opt.temperature == 0.0f && opt.resident_greedy;
 
-#pragma omp parallel for num_threads(n_devices) reduction(+ : gen_cnt, n_steps) reduction(max : load_s, loop_s)
+#pragma omp parallel for num_threads(n_devices) reduction(+ : gen_cnt, n_steps, n_prefill_rows) reduction(max : load_s, loop_s)
   for (int gid = 0; gid < n_devices; gid++) {
     CHECK_THA(tha_set_device(gid));
     Tokenizer tok;
@@ -121,10 +121,14 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
     std::vector<int> token(B, 0), pos(B, -1), next(B, 0);
     Config cfg_local = cfg;
 
+    const bool use_prefill = opt.prefill && t32 && tha_prefill_supported((const tha_config_t*)&cfg_local);
+    std::vector<int> pf_slot, pf_pos0, pf_len, pf_tokens;
+
     const long t_loop0 = time_in_ms();
     for (;;) {
       // ---- refill free slots from the shared queue
       bool queue_empty = false;
+      pf_slot.clear(); pf_pos0.clear(); pf_len.clear(); pf_tokens.clear();
       for (int s = 0; s < B && !queue_empty; s++) {
         if (bm.request_of(s) >= 0) continue;
         const int req = next_idx.fetch_add(opt.device_stride);
@@ -143,9 +147,31 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
         if (opt.max_new_positions > 0 && opt.max_new_positions < sl.steps) sl.steps = opt.max_new_positions;
         token[got] = sl.prompt[0];
         pos[got] = 0;
+        // Prompt ingestion in one pass: positions 0..m-1 go through tha_prefill_f32 (cache rows only), the slot
+        // then joins the step loop at position m with the prompt's token m -- the state the reference reaches
+        // after m forced-prompt steps (src/llama.cpp:1029-1030), text and ids included.
+        int m = use_prefill ? n_prompt - 1 : 0;
+        if (m > sl.steps - 1) m = sl.steps - 1;
+        if (m >= 1) {
+          pf_slot.push_back(got); pf_pos0.push_back(0); pf_len.push_back(m);
+          pf_tokens.insert(pf_tokens.end(), sl.prompt.begin(), sl.prompt.begin() + m);
+          for (int j = 1; j <= m; j++) {
+            append_str(decode(&tok, sl.prompt[j - 1], sl.prompt[j]), sl.text);
+            sl.ids.push_back(sl.prompt[j]);
+            bm.advance(got);
+          }
+          token[got] = sl.prompt[m];
+          pos[got] = m;
+        }
         if (opt.verbose) fprintf(stderr, "\nDevice %d - seq id %d in batch, Request %d\n", gid, got, req);
       }
       if (bm.active_slots() == 0) break;
+      if (!pf_slot.empty()) {
+        CHECK_THA(tha_prefill_f32((void*)handle.calc_stream, (const tha_config_t*)&cfg_local, (const tha_weights_f32_t*)w_d,
+                                  (const tha_state_t*)s_d, (int)pf_slot.size(), pf_slot.data(), pf_pos0.data(), pf_len.data(),
+                                  pf_tokens.data(), nullptr, nullptr));
+        n_prefill_rows += (long long)pf_tokens.size();
+      }
 
       // ---- one decode step for every active slot
       int rc;
@@ -203,7 +229,7 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
   }
 
   for (auto& s : samplers) free_sampler(&s);
-  if (stats) { stats->gen_tokens = gen_cnt; stats->steps = n_steps; stats->load_seconds = load_s; stats->loop_seconds = loop_s; }
+  if (stats) { stats->gen_tokens = gen_cnt; stats->steps = n_steps; stats->prefill_rows = n_prefill_rows; stats->load_seconds = load_s; stats->loop_seconds = loop_s; }
   return (int)gen_cnt;
 }
 

@@ -115,6 +115,14 @@ thablasStatus_t thaDNN_q8_forward_batch(thablasHandle_t handle, int n_batches, C
                                  (const tha_weights_q8_t*)w, (const tha_state_t*)s_batch, token, pos, logits_host));
 }
 
+thablasStatus_t thaDNN_s_prefill_batch(thablasHandle_t* handle, Config* p, TransformerWeights* w, RunState* s_batch,
+                                       int n_seqs, int slot[], int pos0[], int len[], int tokens[], float* logits_d,
+                                       int* next_d) {
+  if (!handle) return THABLAS_STATUS_HANDLE_IS_NULLPTR;
+  return st(tha_prefill_f32(calc(handle), (const tha_config_t*)p, (const tha_weights_f32_t*)w, (const tha_state_t*)s_batch,
+                            n_seqs, slot, pos0, len, tokens, logits_d, next_d));
+}
+
 thablasStatus_t thaDNN_s_decode_greedy_batch(thablasHandle_t* handle, int n_batches, Config* p, TransformerWeights* w,
                                              RunState* s_batch, int* token_d, int* pos_d, int* next_d,
                                              float* logits_d, int advance) {

@@ -72,11 +72,14 @@ struct DriverOptions {
   int ignore_stop = 0;         // keep going through BOS/EOS (fixed-length timing runs)
   int resident_greedy = 1;     // temperature == 0: keep token/pos/argmax on the device, read back token ids only
   int device_offset = 0, device_stride = 1;  // request sharding across processes: this process serves requests r with r % stride == offset
+  int prefill = 1;             // fp32 models: ingest a new request's prompt in one tensor-core pass (tha_prefill_f32) instead of
+                               // one forced-prompt decode step per token (src/llama.cpp:1029-1030); 0 = the reference's scheme
   int verbose = 0;
 };
 struct DriverStats {
   long long gen_tokens = 0;    // sum over requests of (pos - 1), the reference's count (src/llama.cpp:1062)
   long long steps = 0;         // forward calls issued, all devices
+  long long prefill_rows = 0;  // prompt positions ingested through tha_prefill_f32
   double load_seconds = 0;     // weight upload, max over devices
   double loop_seconds = 0;     // step loop, max over devices
 };

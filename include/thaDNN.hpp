@@ -38,6 +38,14 @@ thablasStatus_t thaDNN_s_forward_batch(thablasHandle_t handle1, thablasHandle_t 
 thablasStatus_t thaDNN_q8_forward_batch(thablasHandle_t handle, int n_batches, Config* p, TransformerWeightsQ8* w,
                                         RunState* s_batch, int token[], int pos[], float* logits_host);
 
+// Batched prompt ingestion (additive).  HOST arrays: sequence i lives in cache slab slot[i];
+// its len[i] tokens (concatenated in tokens[]) go to positions pos0[i]..pos0[i]+len[i]-1 in one pass of tensor-core
+// matmuls, leaving the cache as len[i] forced-prompt steps of thaDNN_s_forward_batch would (src/llama.cpp:1029-1030).
+// logits_d / next_d (DEVICE, nullable): last-position logits [n_seqs, vocab] and their argmax.  Asynchronous.
+thablasStatus_t thaDNN_s_prefill_batch(thablasHandle_t* handle, Config* p, TransformerWeights* w, RunState* s_batch,
+                                       int n_seqs, int slot[], int pos0[], int len[], int tokens[], float* logits_d,
+                                       int* next_d);
+
 // Resident greedy step of the batching driver: token_d / pos_d are DEVICE arrays; the step
 // picks the first-maximum token per slot on the device (sample_argmax, src/llama.cpp:275-286),
 // stores it in next_d, and (advance != 0) moves every active slot on: token = next, pos += 1.
