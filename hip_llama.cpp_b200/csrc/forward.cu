@@ -44,9 +44,14 @@ int step_tc_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, 
                   const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
                   const float* rc, const float* rs, bool pdl);
 bool prefill_tc_supported(const tha_config_t* c);
-int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_f32_t& w,
-                    const tha_state_t& s, int n_seqs, const int* slot, const int* pos0, const int* len,
-                    const int* tokens, float* logits, int* next_d, const float* rc, const float* rs);
+int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_f32_t* w32,
+                    const tha_weights_q8_t* wq, const tha_state_t& s, int n_seqs, const int* slot, const int* pos0,
+                    const int* len, const int* tokens, float* logits, int* next_d, const float* rc, const float* rs);
+bool step_tc_q8_supported(const tha_config_t* c, int B, int gs);
+int step_tc_q8_prepare(Workspace* ws, const tha_config_t* c, int B);
+int step_tc_q8_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_q8_t& wq,
+                     const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
+                     const float* rc, const float* rs, bool pdl);
 int gemm_tc_check_error();
 int tc_mode();   // -1 auto (B > 8), 0 never, 1 whenever the shape allows
 int advance_launch(cudaStream_t st, int B, int* token, int* pos, const int* next, int seq_len, bool pdl);
@@ -229,7 +234,7 @@ int q8_prep_launch(cudaStream_t st, int B, const float* X, int x_stride, const f
 
 struct StepArgsQ8 {
   int B; tha_config_t cfg; tha_weights_q8_t w; tha_state_t s;
-  const int* token_d; const int* pos_d; float* logits_d; int* next_d; int pdl;
+  const int* token_d; const int* pos_d; float* logits_d; int* next_d; int pdl; int tc;
 };
 
 // runq.c:344-481 with the same 5-kernels-per-layer structure; every matmul kernel
@@ -321,6 +326,22 @@ int decode_step_q8(cudaStream_t st, int B, const tha_config_t* cfg, const tha_we
   if (!ws) return THA_STATUS_EXECUTION_FAILED;
   const float *rc, *rs;
   THA_TRY(ws_rope(ws, hs, cfg->seq_len, &rc, &rs));
+  StepArgsQ8 a;
+  memset(&a, 0, sizeof(a));
+  a.B = B; a.cfg = *cfg; a.w = *w; a.s = *s; a.token_d = token_d; a.pos_d = pos_d; a.logits_d = logits_d;
+  a.next_d = next_d; a.pdl = pdl_enabled();
+  // More than 8 slots: int8 weights through the tensor-core matmul (dequantised in its converter warps) instead of
+  // one GEMV pass over the weights per batch tile of 8.
+  const int tcm = tc_mode();
+  if (tcm != 0 && (tcm == 1 || B > 8) && step_tc_q8_supported(cfg, B, gs)) {
+    THA_TRY(step_tc_q8_prepare(ws, cfg, B));
+    a.tc = 1;   // part of the graph key
+    float* lg = logits_d ? logits_d : s->logits;
+    if (!lg) return THA_STATUS_INVALID_ARG;
+    return run_step(st, ws, &a, sizeof(a), [&]() {
+      return step_tc_q8_issue(st, ws, B, *cfg, *w, *s, token_d, pos_d, lg, next_d, rc, rs, a.pdl != 0);
+    });
+  }
   const bool fused = attn_fused_supported(cfg->n_heads, hs, cfg->dim, kvd);
   if (!fused && !s->att) return THA_STATUS_INVALID_ARG;
   if (fused) {
@@ -331,10 +352,6 @@ int decode_step_q8(cudaStream_t st, int B, const tha_config_t* cfg, const tha_we
     if (nsplit > 1) THA_TRY(ws_ensure_attn(ws, (size_t)B * nseg * nsplit * 32 * J, B * nseg));
   }
   THA_TRY(ws_ensure_q8(ws, B, cfg->dim > cfg->hidden_dim ? cfg->dim : cfg->hidden_dim, gs));
-  StepArgsQ8 a;
-  memset(&a, 0, sizeof(a));
-  a.B = B; a.cfg = *cfg; a.w = *w; a.s = *s; a.token_d = token_d; a.pos_d = pos_d; a.logits_d = logits_d;
-  a.next_d = next_d; a.pdl = pdl_enabled();
   return run_step(st, ws, &a, sizeof(a), [&]() { return issue_step_q8(st, ws, a, rc, rs); });
 }
 
@@ -449,8 +466,29 @@ extern "C" int tha_prefill_f32(void* stream, const tha_config_t* cfg, const tha_
   const float *rc, *rs;
   THA_TRY(ws_rope(ws, cfg->dim / cfg->n_heads, cfg->seq_len, &rc, &rs));
   launches_reset();
-  const int rcode = step_tc_prefill((cudaStream_t)stream, ws, *cfg, *w, *s, n_seqs, slot_host, pos0_host, len_host, tokens_host,
-                                    logits_d, next_d, rc, rs);
+  const int rcode = step_tc_prefill((cudaStream_t)stream, ws, *cfg, w, nullptr, *s, n_seqs, slot_host, pos0_host, len_host,
+                                    tokens_host, logits_d, next_d, rc, rs);
+  last_step_launches_set(launches_get());
+  return rcode;
+}
+
+extern "C" int tha_prefill_q8(void* stream, const tha_config_t* cfg, const tha_weights_q8_t* w, const tha_state_t* s, int n_seqs,
+                              const int* slot_host, const int* pos0_host, const int* len_host, const int* tokens_host,
+                              float* logits_d, int* next_d) {
+  if (!cfg || !w || !s || n_seqs < 1 || !slot_host || !pos0_host || !len_host || !tokens_host) return THA_STATUS_INVALID_ARG;
+  if (cfg->dim <= 0 || cfg->n_heads <= 0 || cfg->dim % cfg->n_heads || cfg->n_kv_heads <= 0 || w->group_size <= 0)
+    return THA_STATUS_INVALID_ARG;
+  if (!w->token_embedding_table || !w->wq.q || !w->wk.q || !w->wv.q || !w->wo.q || !w->w1.q || !w->w2.q || !w->w3.q ||
+      !w->wcls.q || !w->rms_att_weight || !w->rms_ffn_weight || !w->rms_final_weight || !s->key_cache || !s->value_cache)
+    return THA_STATUS_INVALID_ARG;
+  if (!prefill_tc_supported(cfg) || !step_tc_q8_supported(cfg, 1, w->group_size)) return THA_STATUS_NOT_SUPPORTED;
+  Workspace* ws = workspace();
+  if (!ws) return THA_STATUS_EXECUTION_FAILED;
+  const float *rc, *rs;
+  THA_TRY(ws_rope(ws, cfg->dim / cfg->n_heads, cfg->seq_len, &rc, &rs));
+  launches_reset();
+  const int rcode = step_tc_prefill((cudaStream_t)stream, ws, *cfg, nullptr, w, *s, n_seqs, slot_host, pos0_host, len_host,
+                                    tokens_host, logits_d, next_d, rc, rs);
   last_step_launches_set(launches_get());
   return rcode;
 }

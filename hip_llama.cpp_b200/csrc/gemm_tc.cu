@@ -173,7 +173,10 @@ struct TcSmem {
   static_assert(TOTAL <= TC_SMEM_LIMIT, "shared memory overflow");
 };
 
-template <int NT>
+// Q8 = true: the weight tile arrives as int8 ([128 rows x 128 values] per 16 KB ring slot = four k-blocks, runq.c
+// format) and the converters dequantise (value * group scale, fp32) before the same hi/lo split -- the weights cross
+// HBM at 1.0625 bytes each while the activations (already the dequantised int8 rows) and the accumulation stay fp32.
+template <int NT, bool Q8>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__ CUtensorMap mw1,
                    const __grid_constant__ CUtensorMap mw2, const __grid_constant__ CUtensorMap mxh,
@@ -208,7 +211,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
   const int nst = (nkb + S::KG - 1) / S::KG;   // pipeline stages of KG k-blocks (the last one may be short)
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < S::SW; s++) { tc_mbar_init(&wfull[s], 1); tc_mbar_init(&wfree[s], 4); }
+    for (int s = 0; s < S::SW; s++) { tc_mbar_init(&wfull[s], 1); tc_mbar_init(&wfree[s], Q8 ? 4 * (4 / S::KG) : 4); }
     for (int s = 0; s < S::SA; s++) { tc_mbar_init(&ready[s], 5); tc_mbar_init(&aempty[s], 1); }
     tc_mbar_init(accum, 1);
     *abort_flag = 0;
@@ -238,6 +241,15 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
     if (lane == 0) {
       uint64_t pol_w;
       asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
+      if (Q8) {
+        const int nslots = (nkb + 3) >> 2;               // ring slot = 128 int8 per row = four k-blocks
+        for (int j = 0; j < nslots; j++) {
+          const int s = j % S::SW;
+          if (j >= S::SW && !tc_mbar_wait(&wfree[s], ((j / S::SW) & 1u) ^ 1u, abort_flag)) break;
+          tc_mbar_expect_tx(&wfull[s], S::W_BYTES);      // the box is always delivered whole (zero-filled past K)
+          tc_tma_2d_hint(wring + s * S::W_BYTES, mw, (kb0 + 4 * j) * TC_BK, row0, &wfull[s], pol_w);
+        }
+      } else
       for (int i = 0; i < nst; i++) {
         const int s = i % S::SW;
         if (i >= S::SW && !tc_mbar_wait(&wfree[s], ((i / S::SW) & 1u) ^ 1u, abort_flag)) break;
@@ -306,24 +318,68 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
     const int r = q * 32 + lane;
     const int grp = (warp >> 2) - 1;                    // converter group 0..TC_CGROUPS-1
     bool ok = true;
+    // Q8: this thread's row of group scales (rows past M are zero-filled by TMA: any valid scale will do)
+    const float* srow = nullptr;
+    float sc_next[S::KG];
+    if (Q8) {
+      const int rr = (row0 + r < p.M[mat]) ? row0 + r : p.M[mat] - 1;
+      srow = p.S[mat] + (size_t)rr * p.ngrp;
+#pragma unroll
+      for (int kk = 0; kk < S::KG; kk++) {
+        const int kb = grp * S::KG + kk;
+        sc_next[kk] = (kb < nkb) ? __ldg(srow + ((kb0 + kb) * TC_BK) / p.gs) : 0.0f;
+      }
+    }
     for (int i = grp; i < nst && ok; i += TC_CGROUPS) {
-      const int sw = i % S::SW, sa = i % S::SA;
+      const int sw = Q8 ? ((i * S::KG) >> 2) % S::SW : i % S::SW, sa = i % S::SA;
+      const unsigned wpar = Q8 ? ((((i * S::KG) >> 2) / S::SW) & 1u) : ((i / S::SW) & 1u);
       const int nk = (nkb - i * S::KG) < S::KG ? (nkb - i * S::KG) : S::KG;
-      ok = tc_mbar_wait(&wfull[sw], (i / S::SW) & 1u, abort_flag);
+      float sc[S::KG];
+      if (Q8) {
+#pragma unroll
+        for (int kk = 0; kk < S::KG; kk++) {
+          sc[kk] = sc_next[kk];
+          const int kb = (i + TC_CGROUPS) * S::KG + kk;   // this group's next stage: the load has a whole stage to land
+          sc_next[kk] = (kb < nkb) ? __ldg(srow + ((kb0 + kb) * TC_BK) / p.gs) : 0.0f;
+        }
+      }
+      ok = tc_mbar_wait(&wfull[sw], wpar, abort_flag);
       if (threadIdx.x == 128 + 128 * grp) TC_TRACE(2, i);
 #pragma unroll
       for (int kk = 0; kk < S::KG; kk++) {
         if (kk < nk) {
-          const unsigned char* wrow = wring + sw * S::W_STAGE + kk * S::W_BYTES + r * 128;
           uint32_t hi[32], lo[32];
+          if (Q8) {
+            const int sub = (i * S::KG + kk) & 3;          // k-block within the slot: logical 16-byte chunks 2*sub, 2*sub+1
+            const unsigned char* wrow = wring + sw * S::W_BYTES + r * 128;
 #pragma unroll
-          for (int j = 0; j < 8; j++) {                  // logical 16-byte chunk j lives at j ^ (row & 7) (SWIZZLE_128B)
-            const float4 v = *reinterpret_cast<const float4*>(wrow + ((j ^ (r & 7)) << 4));
-            const float h0 = tc_tf32(v.x), h1 = tc_tf32(v.y), h2 = tc_tf32(v.z), h3 = tc_tf32(v.w);
-            hi[4 * j + 0] = __float_as_uint(h0); hi[4 * j + 1] = __float_as_uint(h1);
-            hi[4 * j + 2] = __float_as_uint(h2); hi[4 * j + 3] = __float_as_uint(h3);
-            lo[4 * j + 0] = __float_as_uint(v.x - h0); lo[4 * j + 1] = __float_as_uint(v.y - h1);
-            lo[4 * j + 2] = __float_as_uint(v.z - h2); lo[4 * j + 3] = __float_as_uint(v.w - h3);
+            for (int j = 0; j < 2; j++) {
+              const int4 v = *reinterpret_cast<const int4*>(wrow + (((2 * sub + j) ^ (r & 7)) << 4));
+              const int wv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+              for (int e = 0; e < 4; e++) {
+                const uint32_t u = (uint32_t)wv[e] ^ 0x80808080u;   // int8 -> biased byte; 0x4B0000uu = 2^23 + uu exactly
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                  const float f = __uint_as_float(__byte_perm(u, 0x4B000000u, 0x7650 + b)) - 8388736.0f;   // = (float)int8
+                  const float w = f * sc[kk];                       // the dequantised weight (runq.c:139-143)
+                  const float h = tc_tf32(w);
+                  hi[16 * j + 4 * e + b] = __float_as_uint(h);
+                  lo[16 * j + 4 * e + b] = __float_as_uint(w - h);
+                }
+              }
+            }
+          } else {
+            const unsigned char* wrow = wring + sw * S::W_STAGE + kk * S::W_BYTES + r * 128;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {                  // logical 16-byte chunk j lives at j ^ (row & 7) (SWIZZLE_128B)
+              const float4 v = *reinterpret_cast<const float4*>(wrow + ((j ^ (r & 7)) << 4));
+              const float h0 = tc_tf32(v.x), h1 = tc_tf32(v.y), h2 = tc_tf32(v.z), h3 = tc_tf32(v.w);
+              hi[4 * j + 0] = __float_as_uint(h0); hi[4 * j + 1] = __float_as_uint(h1);
+              hi[4 * j + 2] = __float_as_uint(h2); hi[4 * j + 3] = __float_as_uint(h3);
+              lo[4 * j + 0] = __float_as_uint(v.x - h0); lo[4 * j + 1] = __float_as_uint(v.y - h1);
+              lo[4 * j + 2] = __float_as_uint(v.z - h2); lo[4 * j + 3] = __float_as_uint(v.w - h3);
+            }
           }
           if (kk == 0 && i >= S::SA && ok) ok = tc_mbar_wait(&aempty[sa], ((i / S::SA) & 1u) ^ 1u, abort_flag);
           if (kk == 0 && threadIdx.x == 128 + 128 * grp) TC_TRACE(3, i);
@@ -397,7 +453,7 @@ static EncodeTiledFn g_encode = nullptr;
 static long long* g_trace = nullptr;   // development aid: tha_gemm_trace()
 static int tc_env(const char* n, int d) { const char* v = getenv(n); return (v && *v) ? atoi(v) : d; }
 static std::mutex g_tc_mu;
-static std::map<std::tuple<const void*, long long, int, long long, int>, CUtensorMap> g_maps;
+static std::map<std::tuple<const void*, long long, int, long long, int, int>, CUtensorMap> g_maps;
 static std::map<int, int*> g_err_flags;   // per device
 
 static int tc_get_encode() {
@@ -411,18 +467,20 @@ static int tc_get_encode() {
 }
 
 // fp32 row-major [rows, K] with row pitch `ld` floats; box = [box_rows x 32 floats], 128-byte swizzle.
-static int tc_map(const float* ptr, long long rows, int K, long long ld, int box_rows, CUtensorMap* out) {
+// (elem_bytes = 1: int8 row-major [rows, K], box = [box_rows x 128 values] -- the same 128-byte swizzled rows.)
+static int tc_map(const void* ptr, long long rows, int K, long long ld, int box_rows, CUtensorMap* out, int elem_bytes = 4) {
   std::lock_guard<std::mutex> lk(g_tc_mu);
   THA_TRY_RC(tc_get_encode());
-  auto key = std::make_tuple((const void*)ptr, rows, K, ld, box_rows);
+  auto key = std::make_tuple((const void*)ptr, rows, K, ld, box_rows, elem_bytes);
   auto it = g_maps.find(key);
   if (it != g_maps.end()) { *out = it->second; return THA_STATUS_SUCCESS; }
   CUtensorMap m;
   const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
-  const cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
-  const cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)ld * elem_bytes};
+  const cuuint32_t box[2] = {(cuuint32_t)(128 / elem_bytes), (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
-  CUresult r = g_encode(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+  CUresult r = g_encode(&m, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 2,
+                        const_cast<void*>(ptr), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                         (CUtensorMapL2promotion)tc_env("THA_TC_PROMO", (int)CU_TENSOR_MAP_L2_PROMOTION_L2_256B),
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -452,20 +510,28 @@ int gemm_tc_init(int** flag_out) {
 
 bool gemm_tc_ok(const TcArgs& a) {
   if (a.K % 4 || a.ldx % 4 || a.K < TC_BK || a.N < 1) return false;
-  for (int i = 0; i < a.n_mats; i++)
-    if (!a.W[i] || (reinterpret_cast<uintptr_t>(a.W[i]) & 15u) || a.M[i] < 1) return false;
+  const bool q8 = a.Wq[0] != nullptr;
+  if (q8 && (a.gs < TC_BK || a.gs % TC_BK || a.K % a.gs || a.K < 128)) return false;   // a k-block lies inside one group
+  for (int i = 0; i < a.n_mats; i++) {
+    const void* wp = q8 ? (const void*)a.Wq[i] : (const void*)a.W[i];
+    if (!wp || (reinterpret_cast<uintptr_t>(wp) & 15u) || a.M[i] < 1 || (q8 && !a.Ws[i])) return false;
+  }
   return a.Xhi && a.Xlo && (reinterpret_cast<uintptr_t>(a.Xhi) & 15u) == 0 && (reinterpret_cast<uintptr_t>(a.Xlo) & 15u) == 0;
 }
 
 int gemm_tc_pick_nt(int N) { return N <= 16 ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128)); }   // wider N: more column tiles (grid.y)
 
-template <int NT>
-static int tc_launch_nt(cudaStream_t st, const TcArgs& a, const CUtensorMap* mw, const CUtensorMap& mxh, const CUtensorMap& mxl, const TcP& p, dim3 grid, bool pdl) {
+template <int NT, bool Q8>
+static int tc_launch_ntq(cudaStream_t st, const CUtensorMap* mw, const CUtensorMap& mxh, const CUtensorMap& mxl, const TcP& p, dim3 grid, bool pdl) {
   using S = TcSmem<NT>;
-  auto k = gemm_tf32x3_kernel<NT>;
+  auto k = gemm_tf32x3_kernel<NT, Q8>;
   THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
   THA_CUDA_OK(launch(k, grid, dim3(TC_THREADS), (size_t)S::TOTAL, st, pdl, mw[0], mw[1], mw[2], mxh, mxl, p));
   return THA_STATUS_SUCCESS;
+}
+template <int NT>
+static int tc_launch_nt(cudaStream_t st, const TcArgs& a, const CUtensorMap* mw, const CUtensorMap& mxh, const CUtensorMap& mxl, const TcP& p, dim3 grid, bool pdl) {
+  return a.Wq[0] ? tc_launch_ntq<NT, true>(st, mw, mxh, mxl, p, grid, pdl) : tc_launch_ntq<NT, false>(st, mw, mxh, mxl, p, grid, pdl);
 }
 
 int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl) {
@@ -474,9 +540,12 @@ int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl) {
   CUtensorMap mw[3], mxh, mxl;
   TcP p = {};
   int tiles = 0;
+  const bool q8 = a.Wq[0] != nullptr;
+  if (q8) { p.gs = a.gs; p.ngrp = a.K / a.gs; }
   for (int i = 0; i < 3; i++) {
     if (i < a.n_mats) {
-      THA_TRY_RC(tc_map(a.W[i], a.M[i], a.K, a.K, TC_BM, &mw[i]));
+      if (q8) { THA_TRY_RC(tc_map(a.Wq[i], a.M[i], a.K, a.K, TC_BM, &mw[i], 1)); p.S[i] = a.Ws[i]; }
+      else THA_TRY_RC(tc_map(a.W[i], a.M[i], a.K, a.K, TC_BM, &mw[i]));
       p.M[i] = a.M[i]; p.tiles[i] = ceil_div(a.M[i], TC_BM); p.out_off[i] = a.out_off[i];
     } else {
       mw[i] = mw[0]; p.M[i] = 0; p.tiles[i] = 0; p.out_off[i] = 0;
@@ -489,6 +558,7 @@ int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl) {
   p.kblocks_total = ceil_div(a.K, TC_BK);
   const int splits = a.splits < 1 ? 1 : a.splits;
   p.kblocks_per_split = ceil_div(p.kblocks_total, splits);
+  if (q8) p.kblocks_per_split = (p.kblocks_per_split + 3) & ~3;   // a split starts on a ring-slot boundary (128 int8 per row)
   const int zdim = ceil_div(p.kblocks_total, p.kblocks_per_split);
   if (zdim != splits) return THA_STATUS_INVALID_ARG;   // caller sizes its partial buffers by `splits`
   p.out = a.out; p.ldo = a.ldo; p.zstride = a.zstride; p.colscale = a.colscale;
@@ -537,10 +607,11 @@ using namespace tha;
 // C-ABI: out[n*ldo + row] = sum_k W[row,k] X[n,k]   (N rows of activations against one weight matrix)
 static std::map<int, std::pair<float*, size_t>> g_split_scratch;   // per device: [hi | lo]
 
-extern "C" int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const float* W, int M, int K, const float* X, int N,
-                               long long ldx) {
-  if (!out || !W || !X || M < 1 || N < 1 || K < 1) return THA_STATUS_INVALID_ARG;
-  if (K % 4 || K < 32 || (reinterpret_cast<uintptr_t>(W) & 15u)) return THA_STATUS_NOT_SUPPORTED;
+static int gemm_any(void* stream, float* out, long long ldo, const float* W, const int8_t* Wq, const float* Ws, int gs, int M,
+                    int K, const float* X, int N, long long ldx) {
+  const void* wp = Wq ? (const void*)Wq : (const void*)W;
+  if (!out || !wp || !X || M < 1 || N < 1 || K < 1 || (Wq && (!Ws || gs < 1))) return THA_STATUS_INVALID_ARG;
+  if (K % 4 || K < 32 || (reinterpret_cast<uintptr_t>(wp) & 15u)) return THA_STATUS_NOT_SUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
   int dev = 0;
   THA_CUDA_OK(cudaGetDevice(&dev));
@@ -562,10 +633,19 @@ extern "C" int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const fl
   count_launch();
   THA_LAUNCH_OK();
   TcArgs a = {};
-  a.n_mats = 1; a.W[0] = W; a.M[0] = M; a.out_off[0] = 0; a.K = K; a.Xhi = hi; a.Xlo = lo; a.N = N; a.ldx = K;
+  a.n_mats = 1; a.W[0] = W; a.Wq[0] = Wq; a.Ws[0] = Ws; a.gs = gs; a.M[0] = M; a.out_off[0] = 0; a.K = K; a.Xhi = hi; a.Xlo = lo;
+  a.N = N; a.ldx = K;
   a.out = out; a.ldo = ldo; a.zstride = 0; a.splits = 1; a.colscale = nullptr;
   if (!gemm_tc_ok(a)) return THA_STATUS_NOT_SUPPORTED;
   return gemm_tc_launch(st, a, false);
+}
+extern "C" int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const float* W, int M, int K, const float* X, int N,
+                               long long ldx) {
+  return gemm_any(stream, out, ldo, W, nullptr, nullptr, 0, M, K, X, N, ldx);
+}
+extern "C" int tha_gemm_q8_tf32x3(void* stream, float* out, long long ldo, const int8_t* Wq, const float* Ws, int gs, int M, int K,
+                                  const float* X, int N, long long ldx) {
+  return gemm_any(stream, out, ldo, nullptr, Wq, Ws, gs, M, K, X, N, ldx);
 }
 extern "C" int tha_gemm_check_error(void) { return gemm_tc_check_error(); }
 

@@ -1,6 +1,7 @@
 // Host-side interface of the tcgen05 weight matmul (gemm_tc.cu).
 #pragma once
 #include <cuda_runtime.h>
+#include <stdint.h>
 
 namespace tha {
 
@@ -9,6 +10,7 @@ namespace tha {
 struct TcArgs {
   int n_mats;                 // 1..3 stacked weight matrices with the same K
   const float* W[3]; int M[3]; int out_off[3];   // rows of matrix i land at out[n*ldo + out_off[i] + row]
+  const int8_t* Wq[3]; const float* Ws[3]; int gs;   // Q8_0 weights instead of W (Wq[0] != nullptr): int8 [M, K] + scales [M, K/gs]
   int K;
   const float* Xhi; const float* Xlo; int N; long long ldx;   // activations [N, ldx] split: hi = tf32(x), lo = x - hi
   float* out; long long ldo; long long zstride;  // split z writes out + z*zstride (partials, summed by the consumer)
@@ -21,6 +23,7 @@ struct TcP {                  // kernel parameter block
   int K, N, ny, kblocks_total, kblocks_per_split;   // ny = column tiles
   float* out; long long ldo; long long zstride;
   const float* colscale;
+  const float* S[3]; int ngrp, gs;   // Q8_0: group scales of each matrix
   int* error_flag;
   int dbg;
   long long* trace;           // development aid (tha_gemm_trace)

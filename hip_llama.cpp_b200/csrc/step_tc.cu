@@ -157,6 +157,121 @@ __global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __res
   hl[(size_t)b * h + i] = r - hi;
 }
 
+
+// ---- Q8_0 rows (runq.c:344-481 on the tensor cores) ---------------------------------------------------------------
+// The activation that enters a matmul is quantised exactly as runq.c:145-171 does (scale = max|x| / 127 per group,
+// round half away from zero) -- the int8 values and scales are bit-identical to q8_prep_kernel's for the same input --
+// and handed to the matmul as its dequantised fp32 value q * scale split into tf32 hi/lo.
+
+__device__ __forceinline__ void q8_group_split(const float* v, int n_per_lane, float* __restrict__ oh, float* __restrict__ ol,
+                                               int base, int lane) {
+  float amax = 0.0f;
+  for (int j = 0; j < n_per_lane; j++) amax = fmaxf(amax, fabsf(v[j]));
+  amax = warp_max(amax);
+  const float scale = __fdiv_rn(amax, 127.0f);
+  for (int j = 0; j < n_per_lane; j++) {
+    const float r = __fdiv_rn(v[j], scale);
+    const int q = (r != r) ? 0 : __float2int_rn(roundf(r));
+    const float deq = (float)(int8_t)q * scale;
+    const float hi = st_tf32(deq);
+    oh[base + lane + 32 * j] = hi;
+    ol[base + lane + 32 * j] = deq - hi;
+  }
+}
+
+// One block per output row: x row = embedding row or x + sum of partials (written back), RMSNorm in the reference's
+// order w * (ss * x) (run.cc:196-209), group quantisation, dequantised hi/lo out.  gs in {32, 64, 128}.
+__global__ void __launch_bounds__(256) tc_prep_q8_kernel(float* __restrict__ x, const float* __restrict__ part, int nz,
+                                                         long long zstride, const float* __restrict__ emb,
+                                                         const int* __restrict__ token, const int* __restrict__ pos,
+                                                         const float* __restrict__ gain, int d, int gs,
+                                                         float* __restrict__ xh, float* __restrict__ xl,
+                                                         const int* __restrict__ gather) {
+  __shared__ float red[33];
+  pdl_wait();
+  pdl_trigger();
+  const int ob = blockIdx.x;
+  const int b = gather ? gather[ob] : ob;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* xr = x + (size_t)b * d;
+  float* hr = xh + (size_t)ob * d;
+  float* lr = xl + (size_t)ob * d;
+  if (pos[b] < 0) {
+    for (int i = threadIdx.x; i < d; i += blockDim.x) { hr[i] = 0.0f; lr[i] = 0.0f; }
+    return;
+  }
+  const float* er = emb ? emb + (size_t)token[b] * d : nullptr;
+  float ss = 0.0f;
+  for (int i = threadIdx.x; i < d; i += blockDim.x) {   // same thread/element mapping as q8_prep_kernel: same sum order
+    float v;
+    if (er) v = er[i];
+    else {
+      v = xr[i];
+#pragma unroll 4
+      for (int z = 0; z < nz; z++) v += part[(size_t)z * zstride + (size_t)b * d + i];
+    }
+    if ((er || nz) && !gather) xr[i] = v;
+    ss = fmaf(v, v, ss);
+  }
+  ss = block_sum(ss, red);
+  ss /= d; ss += 1e-5f;
+  const float ssn = 1.0f / sqrtf(ss);
+  const int npl = gs >> 5;
+  for (int g = warp; g < d / gs; g += 8) {
+    float v[4];
+    for (int j = 0; j < npl; j++) {
+      const int i = g * gs + lane + 32 * j;
+      float t;
+      if (er) t = er[i];
+      else {
+        t = xr[i];
+        if (gather || !(er || nz)) {   // x was not rewritten: redo the sum (same order, same value)
+#pragma unroll 4
+          for (int z = 0; z < nz; z++) t += part[(size_t)z * zstride + (size_t)b * d + i];
+        }
+      }
+      v[j] = gain[i] * (ssn * t);
+    }
+    q8_group_split(v, npl, hr, lr, g * gs, lane);
+  }
+}
+
+// Warp per group: src row (attention output), or with h > 0 the SwiGLU of the w1|w3 partials (run.cc:344-347 order),
+// quantised per group and written as dequantised hi/lo.  grid (ceil(K / gs / 8), rows)
+__global__ void __launch_bounds__(256) tc_quant_split_kernel(const float* __restrict__ src, long long ld, int nz,
+                                                             long long zstride, int h, const int* __restrict__ pos, int K,
+                                                             int gs, float* __restrict__ oh, float* __restrict__ ol) {
+  pdl_wait();
+  pdl_trigger();
+  const int b = blockIdx.y, lane = threadIdx.x & 31;
+  const int g = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (g >= K / gs) return;
+  const int npl = gs >> 5;
+  float v[4];
+  const bool live = pos[b] >= 0;
+  for (int j = 0; j < npl; j++) {
+    const int i = g * gs + lane + 32 * j;
+    float r = 0.0f;
+    if (live) {
+      if (h > 0) {
+        float a = 0.0f, c = 0.0f;
+#pragma unroll 4
+        for (int z = 0; z < nz; z++) {
+          a += src[(size_t)z * zstride + (size_t)b * ld + i];
+          c += src[(size_t)z * zstride + (size_t)b * ld + h + i];
+        }
+        r = a;
+        r *= (1.0f / (1.0f + expf(-r)));
+        r *= c;
+      } else {
+        r = src[(size_t)b * ld + i];
+      }
+    }
+    v[j] = r;
+  }
+  q8_group_split(v, npl, oh + (size_t)b * K, ol + (size_t)b * K, g * gs, lane);
+}
+
 // ---- scratch ----------------------------------------------------------------------------
 struct TcScratch {
   float *xh = nullptr, *xl = nullptr, *hh = nullptr, *hl = nullptr, *scale = nullptr, *part = nullptr;
@@ -184,14 +299,15 @@ struct TcPlan { int z_qkv, z_wo, z_w13, z_w2; size_t part_floats; };
 // (one CTA per SM), with at least 4 k-blocks per split and a charge per split for the partials the consumer
 // has to sum (their bytes relative to the weight bytes: z * N / K).  E.g. 7B wq|wk|wv at 64 rows: 96 tiles ->
 // z = 3 (288 CTAs, 2 waves at 97 %) instead of z = 2 (192 CTAs, 65 %).
-static int pick_splits(int tiles, int K, int N) {
+static int pick_splits(int tiles, int K, int N, int align) {
   const int kb = ceil_div(K, 32);
   int best = 1;
   float best_score = -1.0f;
   const float charge = 0.012f + 0.25f * (float)N / (float)K / 16.0f;
   for (int z = 1; z <= 16; z++) {
     if (z > 1 && kb / z < 4) break;
-    if (ceil_div(kb, ceil_div(kb, z)) != z) continue;   // the kernel needs every split non-empty
+    const int per = ceil_div(ceil_div(kb, z), align) * align;   // Q8_0: a split starts on a 4-k-block ring slot
+    if (ceil_div(kb, per) != z) continue;                        // the kernel needs every split non-empty
     const int ctas = tiles * z;
     const float eff = (float)ctas / (float)(ceil_div(ctas, 148) * 148);
     const float score = eff - charge * (z - 1);
@@ -200,14 +316,15 @@ static int pick_splits(int tiles, int K, int N) {
   return best;
 }
 
-static TcPlan make_plan(const tha_config_t& c, int R) {
+static TcPlan make_plan(const tha_config_t& c, int R, bool q8) {
+  const int al = q8 ? 4 : 1;
   const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads;
   const int ny = ceil_div(R, gemm_tc_pick_nt(R));
   TcPlan p;
-  p.z_qkv = pick_splits((ceil_div(d, 128) + 2 * ceil_div(kvd, 128)) * ny, d, R);
-  p.z_wo = pick_splits(ceil_div(d, 128) * ny, d, R);
-  p.z_w13 = pick_splits(2 * ceil_div(hd, 128) * ny, d, R);
-  p.z_w2 = pick_splits(ceil_div(d, 128) * ny, hd, R);
+  p.z_qkv = pick_splits((ceil_div(d, 128) + 2 * ceil_div(kvd, 128)) * ny, d, R, al);
+  p.z_wo = pick_splits(ceil_div(d, 128) * ny, d, R, al);
+  p.z_w13 = pick_splits(2 * ceil_div(hd, 128) * ny, d, R, al);
+  p.z_w2 = pick_splits(ceil_div(d, 128) * ny, hd, R, al);
   size_t m = (size_t)p.z_qkv * (d + 2 * kvd);
   if ((size_t)p.z_wo * d > m) m = (size_t)p.z_wo * d;
   if ((size_t)p.z_w13 * 2 * hd > m) m = (size_t)p.z_w13 * 2 * hd;
@@ -232,11 +349,11 @@ bool prefill_tc_supported(const tha_config_t* c) {
 }
 
 // Allocate / grow everything R rows need (never inside a stream capture).
-static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefill, int n_tab) {
+static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefill, int n_tab, bool q8) {
   THA_TRY_RC(gemm_tc_init(nullptr));
   std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
   TcScratch& s = g_tc_scratch[ws->device];
-  const TcPlan pl = make_plan(*c, R);
+  const TcPlan pl = make_plan(*c, R, q8);
   THA_TRY_RC(grow(&s.xh, &s.n_x, (size_t)R * c->dim, ws));
   THA_TRY_RC(grow(&s.xl, &s.n_xl, (size_t)R * c->dim, ws));
   THA_TRY_RC(grow(&s.hh, &s.n_h, (size_t)R * c->hidden_dim, ws));
@@ -268,7 +385,15 @@ static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefil
   return THA_STATUS_SUCCESS;
 }
 
-int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B) { return prepare_rows(ws, c, B, false, 0); }
+int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B) { return prepare_rows(ws, c, B, false, 0, false); }
+int step_tc_q8_prepare(Workspace* ws, const tha_config_t* c, int B) { return prepare_rows(ws, c, B, false, 0, true); }
+
+// Q8_0 on the tensor cores: group size a multiple of the 32-value k-block (32 / 64 / 128), dims a multiple of it and >= 128.
+bool step_tc_q8_supported(const tha_config_t* c, int B, int gs) {
+  if (!step_tc_supported(c, B)) return false;
+  if (gs != 32 && gs != 64 && gs != 128) return false;
+  return c->dim % gs == 0 && c->hidden_dim % gs == 0 && c->dim >= 128 && c->hidden_dim >= 128;
+}
 
 static int gemm(cudaStream_t st, bool pdl, int n_mats, const float* const* W, const int* M, const int* off, int K,
                 const float* xh, const float* xl, int N, float* out, long long ldo, long long zstride, int splits,
@@ -278,6 +403,16 @@ static int gemm(cudaStream_t st, bool pdl, int n_mats, const float* const* W, co
   for (int i = 0; i < n_mats; i++) { a.W[i] = W[i]; a.M[i] = M[i]; a.out_off[i] = off[i]; }
   a.K = K; a.Xhi = xh; a.Xlo = xl; a.N = N; a.ldx = K; a.out = out; a.ldo = ldo; a.zstride = zstride; a.splits = splits;
   a.colscale = colscale;
+  return gemm_tc_launch(st, a, pdl);
+}
+
+static int gemm_q8(cudaStream_t st, bool pdl, int n_mats, const int8_t* const* Wq, const float* const* Ws, int gs, const int* M,
+                   const int* off, int K, const float* xh, const float* xl, int N, float* out, long long ldo, long long zstride,
+                   int splits) {
+  TcArgs a = {};
+  a.n_mats = n_mats;
+  for (int i = 0; i < n_mats; i++) { a.Wq[i] = Wq[i]; a.Ws[i] = Ws[i]; a.M[i] = M[i]; a.out_off[i] = off[i]; }
+  a.gs = gs; a.K = K; a.Xhi = xh; a.Xlo = xl; a.N = N; a.ldx = K; a.out = out; a.ldo = ldo; a.zstride = zstride; a.splits = splits;
   return gemm_tc_launch(st, a, pdl);
 }
 
@@ -291,71 +426,109 @@ struct RowsIO {
   float* logits; int* next;                // [n_out, vocab] (nullable: skip the classifier), [n_out] (nullable)
 };
 
+// `wq` != nullptr: Q8_0 weights (then `w` only lends its embedding table and norm gains).
 static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_f32_t& w,
-                      const tha_state_t& s, const RowsIO& io, const float* rc, const float* rs, bool pdl) {
+                      const tha_weights_q8_t* wq, const tha_state_t& s, const RowsIO& io, const float* rc, const float* rs,
+                      bool pdl) {
   TcScratch sc;
   {
     std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
     sc = g_tc_scratch[ws->device];
   }
   const int R = io.R;
-  const TcPlan pl = make_plan(c, R);
+  const TcPlan pl = make_plan(c, R, wq != nullptr);
   const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads, L = c.n_layers;
   const long long kv_bs = (long long)L * c.seq_len * kvd;
   const int ld_qkv = d + 2 * kvd, ld_h = 2 * hd;
   const int* nogather = nullptr;
+  const int gs = wq ? wq->group_size : 0;
+  // the (fused RMSNorm +) split that feeds a matmul whose input is the residual stream
+  auto prep = [&](int rows, int nz, long long zs, const float* emb, const float* gain, const int* gather) -> int {
+    if (wq) {
+      THA_CUDA_OK(launch(tc_prep_q8_kernel, dim3(rows), dim3(256), 0, st, pdl, io.x, (const float*)sc.part, nz, zs, emb, io.token,
+                         io.pos, gain, d, gs, sc.xh, sc.xl, gather));
+    } else {
+      THA_CUDA_OK(launch(tc_prep_kernel, dim3(rows), dim3(256), 0, st, pdl, io.x, (const float*)sc.part, nz, zs, emb, io.token,
+                         io.pos, gain, d, sc.xh, sc.xl, sc.scale, gather));
+    }
+    return THA_STATUS_SUCCESS;
+  };
+  // n stacked matrices of layer l: fp32 pointers or (int8, scales) pairs
+  auto mm = [&](int n, const float* const* W, const tha_qtensor_t* const* Q, size_t per_layer, int l, const int* M, const int* off,
+                int K, const float* xh, const float* xl, int N, float* out, long long ldo, long long zs, int z,
+                const float* colscale) -> int {
+    if (!wq) return gemm(st, pdl, n, W, M, off, K, xh, xl, N, out, ldo, zs, z, colscale);
+    const int8_t* q[3]; const float* sc3[3];
+    for (int i = 0; i < n; i++) {
+      const size_t elems = (size_t)M[i] * K;
+      (void)per_layer;
+      q[i] = Q[i]->q + (size_t)l * elems;
+      sc3[i] = Q[i]->s + (size_t)l * (elems / gs);
+    }
+    return gemm_q8(st, pdl, n, q, sc3, gs, M, off, K, xh, xl, N, out, ldo, zs, z);
+  };
   int prev_z = 0;                 // partials waiting to be added into x
   long long prev_zs = 0;
   for (int l = 0; l < L; l++) {
     const int loff = l * c.seq_len * kvd;
-    THA_CUDA_OK(launch(tc_prep_kernel, dim3(R), dim3(256), 0, st, pdl, io.x, (const float*)sc.part, prev_z, prev_zs,
-                       l == 0 ? w.token_embedding_table : (const float*)nullptr, io.token, io.pos,
-                       w.rms_att_weight + (size_t)l * d, d, sc.xh, sc.xl, sc.scale, nogather));
+    THA_TRY_RC(prep(R, prev_z, prev_zs, l == 0 ? w.token_embedding_table : (const float*)nullptr,
+                    w.rms_att_weight + (size_t)l * d, nogather));
     {
-      const float* W[3] = {w.wq + (size_t)l * d * d, w.wk + (size_t)l * d * kvd, w.wv + (size_t)l * d * kvd};
+      const float* W[3] = {nullptr, nullptr, nullptr};
+      if (!wq) { W[0] = w.wq + (size_t)l * d * d; W[1] = w.wk + (size_t)l * d * kvd; W[2] = w.wv + (size_t)l * d * kvd; }
+      const tha_qtensor_t* Q[3] = {wq ? &wq->wq : nullptr, wq ? &wq->wk : nullptr, wq ? &wq->wv : nullptr};
       const int M[3] = {d, kvd, kvd}, off[3] = {0, d, d + kvd};
-      THA_TRY_RC(gemm(st, pdl, 3, W, M, off, d, sc.xh, sc.xl, R, sc.part, ld_qkv, (long long)R * ld_qkv, pl.z_qkv, sc.scale));
+      THA_TRY_RC(mm(3, W, Q, 0, l, M, off, d, sc.xh, sc.xl, R, sc.part, ld_qkv, (long long)R * ld_qkv, pl.z_qkv, sc.scale));
     }
     THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld_qkv / 2, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part,
                        pl.z_qkv, (long long)R * ld_qkv, ld_qkv, io.pos, d, kvd, hs, rc, rs, io.q, s.key_cache, s.value_cache,
                        kv_bs, loff, io.slot));
     if (!io.logits && l == L - 1) return THA_STATUS_SUCCESS;   // cache-only ingestion: the last layer's K/V rows are in place
     if (io.n_tiles > 0) {
-      THA_TRY_RC(attn_prefill_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, sc.xh, sc.xl, s.key_cache + loff,
-                                     s.value_cache + loff, kv_bs, io.slot, io.pos, io.tile_row0, io.tile_n, pdl));
+      THA_TRY_RC(attn_prefill_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, wq ? nullptr : sc.xh,
+                                     wq ? nullptr : sc.xl, s.key_cache + loff, s.value_cache + loff, kv_bs, io.slot, io.pos,
+                                     io.tile_row0, io.tile_n, pdl));
     } else {
       THA_TRY_RC(attn_fused_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, s.key_cache + loff,
-                                   s.value_cache + loff, kv_bs, hs, c.seq_len, pdl, sc.xh, sc.xl));
+                                   s.value_cache + loff, kv_bs, hs, c.seq_len, pdl, wq ? nullptr : sc.xh, wq ? nullptr : sc.xl));
     }
+    if (wq)   // runq.c:437: the attention output is quantised before wo
+      THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(d / gs, 8), R), dim3(256), 0, st, pdl, (const float*)io.xb, (long long)d,
+                         0, 0LL, 0, io.pos, d, gs, sc.xh, sc.xl));
     {
-      const float* W[1] = {w.wo + (size_t)l * d * d};
+      const float* W[1] = {wq ? nullptr : w.wo + (size_t)l * d * d};
+      const tha_qtensor_t* Q[1] = {wq ? &wq->wo : nullptr};
       const int M[1] = {d}, off[1] = {0};
-      THA_TRY_RC(gemm(st, pdl, 1, W, M, off, d, sc.xh, sc.xl, R, sc.part, d, (long long)R * d, pl.z_wo, nullptr));
+      THA_TRY_RC(mm(1, W, Q, 0, l, M, off, d, sc.xh, sc.xl, R, sc.part, d, (long long)R * d, pl.z_wo, nullptr));
     }
-    THA_CUDA_OK(launch(tc_prep_kernel, dim3(R), dim3(256), 0, st, pdl, io.x, (const float*)sc.part, pl.z_wo, (long long)R * d,
-                       (const float*)nullptr, io.token, io.pos, w.rms_ffn_weight + (size_t)l * d, d, sc.xh, sc.xl, sc.scale,
-                       nogather));
+    THA_TRY_RC(prep(R, pl.z_wo, (long long)R * d, nullptr, w.rms_ffn_weight + (size_t)l * d, nogather));
     {
-      const float* W[2] = {w.w1 + (size_t)l * d * hd, w.w3 + (size_t)l * d * hd};
+      const float* W[2] = {wq ? nullptr : w.w1 + (size_t)l * d * hd, wq ? nullptr : w.w3 + (size_t)l * d * hd};
+      const tha_qtensor_t* Q[2] = {wq ? &wq->w1 : nullptr, wq ? &wq->w3 : nullptr};
       const int M[2] = {hd, hd}, off[2] = {0, hd};
-      THA_TRY_RC(gemm(st, pdl, 2, W, M, off, d, sc.xh, sc.xl, R, sc.part, ld_h, (long long)R * ld_h, pl.z_w13, sc.scale));
+      THA_TRY_RC(mm(2, W, Q, 0, l, M, off, d, sc.xh, sc.xl, R, sc.part, ld_h, (long long)R * ld_h, pl.z_w13, sc.scale));
     }
-    THA_CUDA_OK(launch(tc_swiglu_split_kernel, dim3(ceil_div(hd, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part, pl.z_w13,
-                       (long long)R * ld_h, ld_h, io.pos, hd, sc.hh, sc.hl));
+    if (wq)   // runq.c:457-465: SwiGLU, then quantise hb
+      THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(hd / gs, 8), R), dim3(256), 0, st, pdl, (const float*)sc.part,
+                         (long long)ld_h, pl.z_w13, (long long)R * ld_h, hd, io.pos, hd, gs, sc.hh, sc.hl));
+    else
+      THA_CUDA_OK(launch(tc_swiglu_split_kernel, dim3(ceil_div(hd, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part, pl.z_w13,
+                         (long long)R * ld_h, ld_h, io.pos, hd, sc.hh, sc.hl));
     {
-      const float* W[1] = {w.w2 + (size_t)l * d * hd};
+      const float* W[1] = {wq ? nullptr : w.w2 + (size_t)l * d * hd};
+      const tha_qtensor_t* Q[1] = {wq ? &wq->w2 : nullptr};
       const int M[1] = {d}, off[1] = {0};
-      THA_TRY_RC(gemm(st, pdl, 1, W, M, off, hd, sc.hh, sc.hl, R, sc.part, d, (long long)R * d, pl.z_w2, nullptr));
+      THA_TRY_RC(mm(1, W, Q, 0, l, M, off, hd, sc.hh, sc.hl, R, sc.part, d, (long long)R * d, pl.z_w2, nullptr));
     }
     prev_z = pl.z_w2;
     prev_zs = (long long)R * d;
   }
-  THA_CUDA_OK(launch(tc_prep_kernel, dim3(io.n_out), dim3(256), 0, st, pdl, io.x, (const float*)sc.part, prev_z, prev_zs,
-                     (const float*)nullptr, io.token, io.pos, w.rms_final_weight, d, sc.xh, sc.xl, sc.scale, io.out_rows));
+  THA_TRY_RC(prep(io.n_out, prev_z, prev_zs, nullptr, w.rms_final_weight, io.out_rows));
   {
-    const float* W[1] = {w.wcls};
+    const float* W[1] = {wq ? nullptr : w.wcls};
+    const tha_qtensor_t* Q[1] = {wq ? &wq->wcls : nullptr};
     const int M[1] = {c.vocab_size}, off[1] = {0};
-    THA_TRY_RC(gemm(st, pdl, 1, W, M, off, d, sc.xh, sc.xl, io.n_out, io.logits, c.vocab_size, 0, 1, sc.scale));
+    THA_TRY_RC(mm(1, W, Q, 0, 0, M, off, d, sc.xh, sc.xl, io.n_out, io.logits, c.vocab_size, 0, 1, sc.scale));
   }
   if (io.next) THA_TRY_RC(argmax_launch(st, io.n_out, io.logits, c.vocab_size, io.next, pdl));
   return THA_STATUS_SUCCESS;
@@ -367,16 +540,34 @@ int step_tc_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, 
   RowsIO io = {};
   io.R = B; io.x = s.x; io.q = s.q; io.xb = s.xb; io.token = token_d; io.pos = pos_d; io.slot = nullptr;
   io.n_tiles = 0; io.n_out = B; io.out_rows = nullptr; io.logits = logits; io.next = next_d;
-  return issue_rows(st, ws, c, w, s, io, rc, rs, pdl);
+  return issue_rows(st, ws, c, w, nullptr, s, io, rc, rs, pdl);
+}
+
+static tha_weights_f32_t q8_norms_view(const tha_weights_q8_t& wq) {
+  tha_weights_f32_t w = {};
+  w.token_embedding_table = wq.token_embedding_table;
+  w.rms_att_weight = wq.rms_att_weight; w.rms_ffn_weight = wq.rms_ffn_weight; w.rms_final_weight = wq.rms_final_weight;
+  return w;
+}
+
+int step_tc_q8_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_q8_t& wq,
+                     const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
+                     const float* rc, const float* rs, bool pdl) {
+  RowsIO io = {};
+  io.R = B; io.x = s.x; io.q = s.q; io.xb = s.xb; io.token = token_d; io.pos = pos_d; io.slot = nullptr;
+  io.n_tiles = 0; io.n_out = B; io.out_rows = nullptr; io.logits = logits; io.next = next_d;
+  return issue_rows(st, ws, c, q8_norms_view(wq), &wq, s, io, rc, rs, pdl);
 }
 
 // Batched prompt ingestion.  Host arrays: sequence i occupies cache slab slot[i], its len[i] tokens (consecutive
 // in `tokens`) go to positions pos0[i] .. pos0[i]+len[i]-1.  Every row's K/V lands in the cache; with `logits`
 // the classifier runs on the last row of each sequence ([n_seqs, vocab], and argmax -> next[n_seqs]).
-int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_f32_t& w,
-                    const tha_state_t& s, int n_seqs, const int* slot, const int* pos0, const int* len,
-                    const int* tokens, float* logits, int* next_d, const float* rc, const float* rs) {
+int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_f32_t* w32,
+                    const tha_weights_q8_t* wq, const tha_state_t& s, int n_seqs, const int* slot, const int* pos0,
+                    const int* len, const int* tokens, float* logits, int* next_d, const float* rc, const float* rs) {
   if (!prefill_tc_supported(&c)) return THA_STATUS_NOT_SUPPORTED;
+  if (wq && !step_tc_q8_supported(&c, 1, wq->group_size)) return THA_STATUS_NOT_SUPPORTED;
+  const tha_weights_f32_t w = wq ? q8_norms_view(*wq) : *w32;
   long long R = 0, T = 0;
   for (int i = 0; i < n_seqs; i++) {
     if (len[i] < 1 || pos0[i] < 0 || slot[i] < 0 || (long long)pos0[i] + len[i] > c.seq_len) return THA_STATUS_INVALID_ARG;
@@ -396,7 +587,7 @@ int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const
     }
     h_last[i] = r - 1;
   }
-  THA_TRY_RC(prepare_rows(ws, &c, (int)R, true, (int)tab.size()));
+  THA_TRY_RC(prepare_rows(ws, &c, (int)R, true, (int)tab.size(), wq != nullptr));
   TcScratch sc;
   {
     std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
@@ -409,7 +600,7 @@ int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const
   io.slot = sc.tab; io.pos = sc.tab + R; io.token = sc.tab + 2 * R;
   io.n_tiles = (int)T; io.tile_row0 = sc.tab + 3 * R; io.tile_n = sc.tab + 3 * R + T;
   io.n_out = n_seqs; io.out_rows = sc.tab + 3 * R + 2 * T; io.logits = logits; io.next = logits ? next_d : nullptr;
-  return issue_rows(st, ws, c, w, s, io, rc, rs, true);
+  return issue_rows(st, ws, c, w, wq, s, io, rc, rs, true);
 }
 
 }  // namespace tha

@@ -221,8 +221,6 @@ class Engine:
     def prefill(self, seqs, logits_d=None, next_d=None, stream=None):
         """Batched prompt ingestion: seqs = [(slot, pos0, tokens), ...]; every position's K/V goes to the cache in
         one pass of tensor-core matmuls; logits_d [n_seqs, vocab] / next_d [n_seqs] get the last position of each."""
-        if self.q8:
-            raise NotImplementedError("prefill is wired for fp32 weights")
         slot = np.ascontiguousarray([s[0] for s in seqs], dtype=np.int32)
         pos0 = np.ascontiguousarray([s[1] for s in seqs], dtype=np.int32)
         ln = np.ascontiguousarray([len(s[2]) for s in seqs], dtype=np.int32)
@@ -230,10 +228,11 @@ class Engine:
         if slot.size and (slot.min() < 0 or slot.max() >= self.B):
             raise ValueError("slot out of range")
         vp = C.c_void_p
-        st = self.lib.c.tha_prefill_f32(_stream_ptr(stream), C.byref(self.ccfg), C.byref(self.w.c), C.byref(self.state.c),
+        fn = self.lib.c.tha_prefill_q8 if self.q8 else self.lib.c.tha_prefill_f32
+        st = fn(_stream_ptr(stream), C.byref(self.ccfg), C.byref(self.w.c), C.byref(self.state.c),
                                         len(seqs), slot.ctypes.data_as(vp), pos0.ctypes.data_as(vp), ln.ctypes.data_as(vp),
                                         toks.ctypes.data_as(vp), _ptr(logits_d), _ptr(next_d))
-        self.lib.check(st, "tha_prefill_f32")
+        self.lib.check(st, "tha_prefill")
 
     def advance(self, token_d, pos_d, next_d, stream=None):
         """Device-side greedy bookkeeping: token = next, pos += 1 (src/llama.cpp:1027-1050)."""

@@ -123,6 +123,10 @@ int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const float* W, int
                     long long ldx);
 /* 1 if a tensor-core matmul on the current device gave up on a pipeline barrier since the last call */
 int tha_gemm_check_error(void);
+/* Same with Q8_0 weights (int8 Wq[M,K] + scales Ws[M, K/gs], runq.c:34-37): out = dequantize(W) . X; the int8 rows are
+ * dequantised inside the kernel, so the weights cross HBM at 1.0625 bytes each.  gs in {32, 64, 128}, K % gs == 0, K >= 128. */
+int tha_gemm_q8_tf32x3(void* stream, float* out, long long ldo, const int8_t* Wq, const float* Ws, int gs, int M, int K,
+                       const float* X, int N, long long ldx);
 
 /* ---- thaDNN ops ----------------------------------------------------------------- */
 /* thaDNN_s_rmsnorm_v2_batch, src/thaDNN/thaDNN_rmsnorm.cpp:35-83; rows `dim` apart, o may alias x */
@@ -218,6 +222,10 @@ int tha_advance_slots(void* stream, int n_batches, int* token_d, int* pos_d, con
 int tha_prefill_f32(void* stream, const tha_config_t* cfg, const tha_weights_f32_t* w, const tha_state_t* s, int n_seqs,
                     const int* slot_host, const int* pos0_host, const int* len_host, const int* tokens_host,
                     float* logits_d, int* next_d);
+/* Same for a Q8_0 model (runq.c semantics: every matmul input quantised per group first). */
+int tha_prefill_q8(void* stream, const tha_config_t* cfg, const tha_weights_q8_t* w, const tha_state_t* s, int n_seqs,
+                   const int* slot_host, const int* pos0_host, const int* len_host, const int* tokens_host,
+                   float* logits_d, int* next_d);
 int tha_prefill_supported(const tha_config_t* cfg); /* 1 when tha_prefill_f32 handles this architecture */
 
 int tha_step_needs_att_scratch(const tha_config_t* cfg);

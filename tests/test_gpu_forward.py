@@ -65,18 +65,19 @@ MODELS = {
 }
 
 
-def run_ragged(e, m, n_steps, B, rng, eps, q8=False):
-    """Slot b joins at step b (idle before: pos = -1), all slots teacher-forced with their own
-    token stream; every step compared with the oracle run of the same sequence."""
+def run_ragged(e, m, n_steps, B, rng, eps, q8=False, stagger=0):
+    """Slot b joins at step b (with stagger: at step b % stagger; idle before: pos = -1), all slots
+    teacher-forced with their own token stream; every step compared with the oracle run of the same sequence."""
+    join = [(b % stagger if stagger else b) for b in range(B)]
     seqs = [m.new_seq() for _ in range(B)]
     toks = rng.integers(0, m.vocab_size, size=(B, n_steps)).astype(np.int32)
     flips = 0
     for step in range(n_steps):
         tok = np.zeros(B, np.int32); pos = np.full(B, -1, np.int32)
         for b in range(B):
-            if step >= b:
-                pos[b] = step - b
-                tok[b] = toks[b, step - b]
+            if step >= join[b]:
+                pos[b] = step - join[b]
+                tok[b] = toks[b, step - join[b]]
         logits = e.forward_batch(tok, pos).numpy()
         for b in range(B):
             if pos[b] < 0:
@@ -85,7 +86,9 @@ def run_ragged(e, m, n_steps, B, rng, eps, q8=False):
             (assert_close_scaled if q8 else assert_close)(logits[b], want, eps, f"step {step} slot {b} pos {pos[b]}")
             flips += int(logits[b].argmax()) != int(want.argmax())
     for b in range(B):
-        n = (n_steps - b)
+        n = (n_steps - join[b])
+        if n <= 0:
+            continue
         kc = e.state.key_cache[b].cpu().numpy()[:, :n]   # [L, n, kvd]
         want = seqs[b].buf("key_cache").reshape(m.n_layers, m.seq_len, m.kv_dim)[:, :n]
         if q8:
@@ -195,6 +198,73 @@ def test_q8_batched_ragged_vs_oracle(oracle, tmp_path, name, B):
     e = engine_from_v2(v2, B)
     m = oracle.open(v2, quantized=True)
     run_ragged(e, m, min(cfg.seq_len, 16), B, np.random.default_rng(B), Q8_E2E_EPS, q8=True)
+
+
+@pytest.mark.parametrize("name", list(MODELS))
+@pytest.mark.parametrize("B", [16, 40])
+def test_q8_tensor_core_step_vs_oracle(oracle, tmp_path, name, B):
+    """More than 8 slots with Q8_0 weights: the int8 rows go through the tensor-core matmul (dequantised in its
+    converter warps); activations are quantised exactly as runq.c does.  Same statement as the GEMV path."""
+    cfg, w, v0, v2 = small_model_files(str(tmp_path), name, MODELS[name])
+    e = engine_from_v2(v2, B)
+    m = oracle.open(v2, quantized=True)
+    run_ragged(e, m, 14, B, np.random.default_rng(B), Q8_E2E_EPS, q8=True, stagger=5)
+    assert load_pkg("cabi").lib().c.tha_gemm_check_error() == 0
+
+
+def test_q8_tensor_core_step_matches_gemv_step(tmp_path):
+    """The two Q8_0 paths (GEMV with int8 dot products, tensor cores with dequantised operands) on the same slots:
+    first step from identical state agrees to fp32 noise (no quantiser flip can have happened yet in layer 0's inputs)."""
+    lib = load_pkg("cabi").lib()
+    cfg, w, v0, v2 = small_model_files(str(tmp_path), "fusedA", MODELS["fusedA"])
+    B = 6
+    tok = np.arange(B, dtype=np.int32) + 5
+    pos = np.zeros(B, np.int32)
+    out = {}
+    try:
+        for tc in (0, 1):
+            lib.c.tha_set_option(b"tc", tc)
+            e = engine_from_v2(v2, B)
+            out[tc] = e.forward_batch(tok, pos).numpy().copy()
+            out[tc, "k"] = e.state.key_cache[:, 0, 0].cpu().numpy().copy()   # layer 0, position 0
+    finally:
+        lib.c.tha_set_option(b"tc", -1)
+    assert_close(out[1, "k"], out[0, "k"], 1e-5, "layer-0 K rows")
+    assert_close_scaled(out[1], out[0], Q8_E2E_EPS, "logits")
+
+
+@pytest.mark.parametrize("name", ["fusedA", "hs64"])
+def test_q8_prefill_vs_oracle(oracle, tmp_path, name):
+    """tha_prefill_q8: prompts of several sequences in one pass; K/V rows and last-position logits against runq.c's
+    token-by-token forward (norm-wise Q8_0 statement, layer-0 rows tight)."""
+    import torch
+    cfg, w, v0, v2 = small_model_files(str(tmp_path), name, MODELS_PREFILL[name])
+    m = oracle.open(v2, quantized=True)
+    B = 3
+    e = engine_from_v2(v2, B)
+    rng = np.random.default_rng(11)
+    lens = [5, min(cfg.seq_len - 4, 70), 23]
+    prompts = [rng.integers(0, cfg.vocab_size, size=n).astype(np.int32) for n in lens]
+    seqs = [m.new_seq() for _ in range(B)]
+    want_last = []
+    for b in range(B):
+        for p_, t in enumerate(prompts[b]):
+            lg = seqs[b].forward(int(t), p_)
+        want_last.append(lg.copy())
+    logits = torch.zeros(B, cfg.vocab_size, device="cuda")
+    e.prefill([(b, 0, prompts[b]) for b in range(B)], logits, None)
+    torch.cuda.synchronize()
+    assert load_pkg("cabi").lib().c.tha_gemm_check_error() == 0
+    got = logits.cpu().numpy()
+    for b in range(B):
+        assert_close_scaled(got[b], want_last[b], Q8_E2E_EPS, f"q8 prefill logits slot {b}")
+        n = lens[b]
+        have = e.state.key_cache[b].cpu().numpy()[:, :n]
+        want = seqs[b].buf("key_cache").reshape(m.n_layers, m.seq_len, m.kv_dim)[:, :n]
+        assert_close_scaled(have, want, Q8_E2E_EPS, f"key cache slot {b}")
+        scale = np.abs(want[0]).max()
+        row_err = np.abs(have[0] - want[0]).max(axis=1)
+        assert (row_err > 1e-4 * scale).mean() <= 0.25 and row_err.max() <= 1e-2 * scale, f"layer-0 key rows slot {b}"
 
 
 def test_modes_agree_bit_for_bit(tmp_path):
