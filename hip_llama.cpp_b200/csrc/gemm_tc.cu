@@ -593,6 +593,275 @@ int gemm_tc_check_error() {
   return h;
 }
 
+// =====================================================================================================
+// Q8_0 x Q8_0 on the INT8 tensor cores: runq.c:317-342 evaluated exactly as written.
+//
+//   out[n, m] = sum_g  (float)( sum_{k in g} Wq[m,k] * Xq[n,k] )  *  Ws[m,g]  *  Xs[n,g]        (groups ascending)
+//
+// The inner integer sum of a group is ONE accumulator pass of tcgen05.mma.kind::i8 (int8 x int8 -> int32, exact;
+// K = 32 per instruction, gs/32 instructions per group) with BOTH operands read straight from the TMA-written
+// shared-memory tiles: no conversion warps, weights cross HBM and shared memory as the int8 bytes of the file.
+// Each finished group accumulator [128 rows x NT columns] is pulled out of TMEM by the epilogue warps
+// (thread = weight row), converted exactly, scaled by the row's weight scale and the column's activation scale in
+// the reference's order and added in fp32 -- so without split-K the result is bit-identical to runq.c's loop
+// (compiled without FMA contraction).  TMEM holds a ring of group accumulators so the MMAs of the next groups
+// overlap the scaling of the previous one; shared memory holds a ring of [W 128x128 | X NTx128] int8 slots.
+//   warp 0  TMA producer (weights first: they do not depend on the previous kernel)   warp 1  MMA issuer
+//   warp 2  TMEM allocation     warps 4-11  epilogue: 2 warps per 32-lane TMEM quarter, NT/2 columns each
+constexpr int Q8I_THREADS = 384;
+
+struct Q8iP {
+  int M[3]; int tiles[3]; int out_off[3];
+  const float* S[3];                 // weight group scales [M, ngrp]
+  const float* xsT; int ldxs;        // activation group scales, transposed: xsT[g * ldxs + n]
+  int K, N, ny, gs, ngrp;
+  int slots_total, slots_per_split;  // ring slots of 128 values
+  float* out; long long ldo; long long zstride;
+  int* error_flag;
+};
+
+template <int NT>
+struct Q8iSmem {
+  static constexpr int W_BYTES = TC_BM * 128, X_BYTES = NT * 128, SLOT = W_BYTES + X_BYTES;
+  static constexpr int NSLOT_RAW = (TC_SMEM_LIMIT - 3072) / SLOT;
+  static constexpr int NSLOT = NSLOT_RAW > 10 ? 10 : NSLOT_RAW;
+  static constexpr int NBUF = (512 / NT) > 8 ? 8 : (512 / NT);
+  static constexpr int TMEM_COLS = NBUF * NT < 32 ? 32 : NBUF * NT;   // 128, 256, 512, 512: powers of two
+  static constexpr int TOTAL = NSLOT * SLOT + 1024 + (2 * NSLOT + 2 * NBUF) * 8 + 64;
+  static_assert(TOTAL <= TC_SMEM_LIMIT, "shared memory overflow");
+};
+
+__host__ __device__ constexpr uint32_t q8i_idesc(int nt) {   // kind::i8: D = S32 (2), A = B = signed 8-bit (1), K-major, M = 128
+  return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(nt >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+}
+__device__ __forceinline__ void q8i_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "r"(taddr));
+}
+
+template <int NT>
+__global__ void __launch_bounds__(Q8I_THREADS, 1)
+gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__ CUtensorMap mw1,
+                const __grid_constant__ CUtensorMap mw2, const __grid_constant__ CUtensorMap mx, const Q8iP p) {
+  using S = Q8iSmem<NT>;
+  constexpr int CH = NT / 2;   // accumulator columns per epilogue thread
+  extern __shared__ unsigned char tc_smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::NSLOT * S::SLOT);
+  uint64_t* full = bars;                 // slot landed (W + X bytes)
+  uint64_t* empty = full + S::NSLOT;     // the MMAs that read the slot have completed
+  uint64_t* afull = empty + S::NSLOT;    // group accumulator complete
+  uint64_t* aempty = afull + S::NBUF;    // group accumulator read out by the 8 epilogue warps
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aempty + S::NBUF);
+  int* abort_flag = reinterpret_cast<int*>(tmem_slot + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int tile = blockIdx.x / p.ny, mat = 0;
+  if (tile >= p.tiles[0]) { tile -= p.tiles[0]; mat = 1; if (tile >= p.tiles[1]) { tile -= p.tiles[1]; mat = 2; } }
+  const CUtensorMap* mw = (mat == 0) ? &mw0 : (mat == 1 ? &mw1 : &mw2);
+  const int row0 = tile * TC_BM;
+  const int n0 = (blockIdx.x % p.ny) * NT;
+  const int slot0 = blockIdx.z * p.slots_per_split;
+  int nslots = p.slots_total - slot0;
+  if (nslots > p.slots_per_split) nslots = p.slots_per_split;
+  int nsub = p.K / 32 - slot0 * 4;               // K = 32 sub-blocks (one MMA each) of this split
+  if (nsub > nslots * 4) nsub = nslots * 4;
+  const int mpg = p.gs >> 5;                     // MMAs per group
+  const int ng = nsub / mpg;                     // groups of this split
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S::NSLOT; s++) { tc_mbar_init(&full[s], 1); tc_mbar_init(&empty[s], 1); }
+    for (int b = 0; b < S::NBUF; b++) { tc_mbar_init(&afull[b], 1); tc_mbar_init(&aempty[b], 8); }
+    *abort_flag = 0;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(mw) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mx) : "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem_u32(tmem_slot)), "r"(S::TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint64_t pol_w;
+      asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
+      // the first ring of weight tiles goes out before the dependency wait (transaction bytes may land before the
+      // matching expect_tx: the phase cannot complete until the arrival below)
+      const int pre = nslots < S::NSLOT ? nslots : S::NSLOT;
+      for (int j = 0; j < pre; j++)
+        tc_tma_2d_hint(smem + j * S::SLOT, mw, (slot0 + j) * 128, row0, &full[j], pol_w);
+      pdl_wait();
+      for (int j = 0; j < pre; j++) {
+        tc_mbar_expect_tx(&full[j], S::SLOT);
+        tc_tma_2d(smem + j * S::SLOT + S::W_BYTES, &mx, (slot0 + j) * 128, n0, &full[j]);
+      }
+      for (int j = pre; j < nslots; j++) {
+        const int s = j % S::NSLOT;
+        if (!tc_mbar_wait(&empty[s], ((j / S::NSLOT) & 1u) ^ 1u, abort_flag)) break;
+        tc_mbar_expect_tx(&full[s], S::SLOT);
+        tc_tma_2d_hint(smem + s * S::SLOT, mw, (slot0 + j) * 128, row0, &full[s], pol_w);
+        tc_tma_2d(smem + s * S::SLOT + S::W_BYTES, &mx, (slot0 + j) * 128, n0, &full[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = q8i_idesc(NT);
+      int gsub = 0, gi = 0;                       // sub-block index within the split, group index
+      bool ok = true;
+      for (int j = 0; j < nslots && ok; j++) {
+        const int s = j % S::NSLOT;
+        if (!tc_mbar_wait(&full[s], (j / S::NSLOT) & 1u, abort_flag)) break;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint64_t adesc = tc_smem_desc(tc_smem_u32(smem + s * S::SLOT));
+        const uint64_t bdesc = tc_smem_desc(tc_smem_u32(smem + s * S::SLOT + S::W_BYTES));
+        for (int sub = 0; sub < 4 && gsub < nsub; sub++, gsub++) {
+          const int in_g = gsub % mpg;
+          const int buf = gi % S::NBUF;
+          if (in_g == 0 && gi >= S::NBUF) {
+            ok = tc_mbar_wait(&aempty[buf], ((gi / S::NBUF) & 1u) ^ 1u, abort_flag);
+            if (!ok) break;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          }
+          q8i_mma(tmem_base + buf * NT, adesc + (uint64_t)(sub * 2), bdesc + (uint64_t)(sub * 2), idesc, (uint32_t)(in_g != 0));
+          if (in_g == mpg - 1) { tc_commit(&afull[buf]); gi++; }
+        }
+        tc_commit(&empty[s]);
+      }
+    }
+  } else if (warp >= 4) {
+    const int q = warp & 3, chalf = (warp - 4) >> 2;
+    const int r = q * 32 + lane;
+    const int row = row0 + r;
+    const bool row_ok = row < p.M[mat];
+    const int g0 = (slot0 * 128) / p.gs;
+    const float* srow = p.S[mat] + (size_t)(row_ok ? row : p.M[mat] - 1) * p.ngrp + g0;
+    float acc[CH];
+#pragma unroll
+    for (int c = 0; c < CH; c++) acc[c] = 0.0f;
+    float ws_next = ng > 0 ? __ldg(srow) : 0.0f;
+    pdl_trigger();
+    pdl_wait();                                   // the activation scales come from the previous kernel
+    const float* xs0 = p.xsT + (size_t)g0 * p.ldxs + n0 + chalf * CH;
+    bool ok = true;
+    for (int gi = 0; gi < ng && ok; gi++) {
+      const float ws = ws_next;
+      if (gi + 1 < ng) ws_next = __ldg(srow + gi + 1);
+      float xs[CH];
+#pragma unroll
+      for (int c = 0; c < CH; c += 4) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(xs0 + (size_t)gi * p.ldxs + c));
+        xs[c] = t.x; xs[c + 1] = t.y; xs[c + 2] = t.z; xs[c + 3] = t.w;
+      }
+      const int buf = gi % S::NBUF;
+      ok = tc_mbar_wait(&afull[buf], (gi / S::NBUF) & 1u, abort_flag);
+      if (!ok) break;
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      uint32_t v[CH];
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * NT + chalf * CH);
+      if constexpr (CH == 8) {
+        tc_tmem_ld8(taddr, *reinterpret_cast<uint32_t(*)[8]>(&v[0]));
+      } else {
+#pragma unroll
+        for (int c = 0; c < CH; c += 16) tc_tmem_ld16(taddr + c, *reinterpret_cast<uint32_t(*)[16]>(&v[c]));
+      }
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) tc_mbar_arrive(&aempty[buf]);
+#pragma unroll
+      for (int c = 0; c < CH; c++) {
+        // |group sum| <= 128 * 127 * 127 < 2^22: 1.5 * 2^23 + i is exact in fp32, so this IS (float)i -- two full-rate
+        // instructions instead of a quarter-rate I2F
+        const float f = __int_as_float(0x4B400000 + (int)v[c]) - 12582912.0f;
+        acc[c] = __fadd_rn(acc[c], __fmul_rn(__fmul_rn(f, ws), xs[c]));   // runq.c:334, no contraction
+      }
+    }
+    float* outz = p.out + (size_t)blockIdx.z * p.zstride + p.out_off[mat] + row;
+    if (ok && row_ok) {
+#pragma unroll
+      for (int c = 0; c < CH; c++) {
+        const int n = n0 + chalf * CH + c;
+        if (n < p.N) outz[(size_t)n * p.ldo] = acc[c];
+      }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp == 2) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(S::TMEM_COLS));
+  }
+  if (threadIdx.x == 0 && *abort_flag && p.error_flag) atomicExch(p.error_flag, 1);
+}
+
+bool gemm_q8i_ok(const Q8iArgs& a) {
+  if (a.gs != 32 && a.gs != 64 && a.gs != 128) return false;
+  if (a.K % a.gs || a.K < 128 || a.K % 16 || a.N < 1 || a.n_mats < 1 || a.n_mats > 3 || !a.Xq || !a.xsT || !a.out) return false;
+  if ((reinterpret_cast<uintptr_t>(a.Xq) & 15u) || (reinterpret_cast<uintptr_t>(a.xsT) & 15u) || a.ldxs % 4) return false;
+  for (int i = 0; i < a.n_mats; i++)
+    if (!a.Wq[i] || !a.Ws[i] || (reinterpret_cast<uintptr_t>(a.Wq[i]) & 15u) || a.M[i] < 1) return false;
+  return true;
+}
+
+int gemm_q8i_pick_nt(int N) { return N <= 16 ? 16 : (N <= 32 ? 32 : 64); }
+
+template <int NT>
+static int q8i_launch_nt(cudaStream_t st, const CUtensorMap* mw, const CUtensorMap& mx, const Q8iP& p, dim3 grid, bool pdl) {
+  using S = Q8iSmem<NT>;
+  auto k = gemm_q8i_kernel<NT>;
+  THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+  THA_CUDA_OK(launch(k, grid, dim3(Q8I_THREADS), (size_t)S::TOTAL, st, pdl, mw[0], mw[1], mw[2], mx, p));
+  return THA_STATUS_SUCCESS;
+}
+
+int gemm_q8i_launch(cudaStream_t st, const Q8iArgs& a, bool pdl) {
+  if (!gemm_q8i_ok(a)) return THA_STATUS_INVALID_ARG;
+  const int NT = gemm_q8i_pick_nt(a.N);
+  if (a.ldxs < ceil_div(a.N, NT) * NT) return THA_STATUS_INVALID_ARG;   // a column tile reads NT scales per group
+  CUtensorMap mw[3], mx;
+  Q8iP p = {};
+  int tiles = 0;
+  for (int i = 0; i < 3; i++) {
+    if (i < a.n_mats) {
+      THA_TRY_RC(tc_map(a.Wq[i], a.M[i], a.K, a.K, TC_BM, &mw[i], 1));
+      p.M[i] = a.M[i]; p.tiles[i] = ceil_div(a.M[i], TC_BM); p.out_off[i] = a.out_off[i]; p.S[i] = a.Ws[i];
+    } else {
+      mw[i] = mw[0];
+    }
+    tiles += p.tiles[i];
+  }
+  THA_TRY_RC(tc_map(a.Xq, a.N, a.K, a.K, NT, &mx, 1));
+  p.xsT = a.xsT; p.ldxs = a.ldxs; p.K = a.K; p.N = a.N; p.gs = a.gs; p.ngrp = a.K / a.gs;
+  p.slots_total = ceil_div(a.K, 128);
+  const int splits = a.splits < 1 ? 1 : a.splits;
+  p.slots_per_split = ceil_div(p.slots_total, splits);
+  if (ceil_div(p.slots_total, p.slots_per_split) != splits) return THA_STATUS_INVALID_ARG;
+  p.out = a.out; p.ldo = a.ldo; p.zstride = a.zstride;
+  THA_TRY_RC(gemm_tc_init(&p.error_flag));
+  p.ny = ceil_div(a.N, NT);
+  dim3 grid(tiles * p.ny, 1, splits);
+  switch (NT) {
+    case 16: return q8i_launch_nt<16>(st, mw, mx, p, grid, pdl);
+    case 32: return q8i_launch_nt<32>(st, mw, mx, p, grid, pdl);
+    default: return q8i_launch_nt<64>(st, mw, mx, p, grid, pdl);
+  }
+}
+
 // Forget tensor maps (call when buffers they describe are freed and their addresses may be reused
 // with another shape -- the key includes the shape, so reuse with the same shape stays valid).
 void gemm_tc_forget() {
@@ -646,6 +915,15 @@ extern "C" int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const fl
 extern "C" int tha_gemm_q8_tf32x3(void* stream, float* out, long long ldo, const int8_t* Wq, const float* Ws, int gs, int M, int K,
                                   const float* X, int N, long long ldx) {
   return gemm_any(stream, out, ldo, nullptr, Wq, Ws, gs, M, K, X, N, ldx);
+}
+extern "C" int tha_matmul_q8_tc(void* stream, float* out, long long ldo, const int8_t* Wq, const float* Ws, int gs, int M, int K,
+                                const int8_t* Xq, const float* XsT, int ldxs, int N) {
+  if (!out || !Wq || !Ws || !Xq || !XsT || M < 1 || N < 1 || K < 1 || gs < 1) return THA_STATUS_INVALID_ARG;
+  Q8iArgs a = {};
+  a.n_mats = 1; a.Wq[0] = Wq; a.Ws[0] = Ws; a.M[0] = M; a.out_off[0] = 0; a.K = K; a.gs = gs; a.Xq = Xq; a.xsT = XsT;
+  a.ldxs = ldxs; a.N = N; a.out = out; a.ldo = ldo; a.zstride = 0; a.splits = 1;
+  if (!gemm_q8i_ok(a)) return THA_STATUS_NOT_SUPPORTED;
+  return gemm_q8i_launch((cudaStream_t)stream, a, false);
 }
 extern "C" int tha_gemm_check_error(void) { return gemm_tc_check_error(); }
 

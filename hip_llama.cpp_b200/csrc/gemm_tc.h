@@ -30,6 +30,17 @@ struct TcP {                  // kernel parameter block
   int w_hint;                 // weight loads carry an L2 evict-first hint
 };
 
+// Q8_0 weights x Q8_0 activations on the int8 tensor cores (gemm_q8i_kernel)
+struct Q8iArgs {
+  int n_mats; const int8_t* Wq[3]; const float* Ws[3]; int M[3]; int out_off[3];
+  int K, gs;
+  const int8_t* Xq; const float* xsT; int ldxs; int N;   // activations int8 [N, K]; scales transposed [K/gs, ldxs]
+  float* out; long long ldo; long long zstride; int splits;   // split over 128-value slots
+};
+bool gemm_q8i_ok(const Q8iArgs& a);
+int gemm_q8i_pick_nt(int N);
+int gemm_q8i_launch(cudaStream_t st, const Q8iArgs& a, bool pdl);
+
 bool gemm_tc_ok(const TcArgs& a);
 int gemm_tc_pick_nt(int N);
 int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl);

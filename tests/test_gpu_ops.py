@@ -327,6 +327,37 @@ def test_gemm_q8_tf32x3(L, M, K, N, gs):
     assert np.abs(got - full).max() <= 5e-5 * np.abs(full).max()
 
 
+@pytest.mark.parametrize("M,K,N,gs", [(128, 128, 1, 64), (100, 192, 5, 64), (768, 768, 9, 64), (2304, 704, 33, 64), (768, 2048, 64, 64),
+                                      (4096, 768, 100, 128), (1000, 1024, 130, 32), (512, 4096, 70, 64), (4096, 11008, 3, 64)])
+def test_matmul_q8_int8_tensor_cores_bit_exact(L, oracle, M, K, N, gs):
+    """runq.c's matmul (317-342) on the int8 tensor cores: exact int32 group sums, scaled and accumulated in the
+    reference's order -- every output BIT-IDENTICAL to the oracle's loop (built with -ffp-contract=off)."""
+    rng = np.random.default_rng(M + K + N)
+    wq, ws = oracle.quantize(rng.standard_normal(M * K).astype(np.float32), gs)
+    wq = wq.reshape(M, K)
+    x = rng.standard_normal((N, K)).astype(np.float32) * rng.uniform(0.1, 4.0, size=(N, 1)).astype(np.float32)
+    xq = np.zeros((N, K), np.int8); xs = np.zeros((N, K // gs), np.float32)
+    for n in range(N):
+        xq[n], xs[n] = oracle.quantize(x[n], gs)
+    ldxs = ((N + 63) // 64) * 64
+    xsT = np.zeros((K // gs, ldxs), np.float32)
+    xsT[:, :N] = xs.T
+    WQ, WS, XQ, XST, O = tdev(wq), tdev(ws), tdev(xq), tdev(xsT), tdev(np.full((N, M), np.nan, np.float32))
+    sync()
+    L.check(L.c.tha_matmul_q8_tc(stream_ptr(), P(O), M, P(WQ), P(WS), gs, M, K, P(XQ), P(XST), ldxs, N), "tha_matmul_q8_tc")
+    sync()
+    assert L.c.tha_gemm_check_error() == 0
+    got = O.cpu().numpy()
+    for n in range(min(N, 5)):
+        want = oracle.matmul_q8(wq, ws, xq[n], xs[n], gs)
+        assert np.array_equal(got[n].view(np.uint32), want.view(np.uint32)), \
+            f"row {n}: {np.count_nonzero(got[n] != want)} of {M} outputs differ, max |d| {np.abs(got[n] - want).max()}"
+    # all rows: against the exact group arithmetic in fp64
+    full = np.einsum("mgk,ngk->nmg", wq.reshape(M, -1, gs).astype(np.float64), xq.reshape(N, -1, gs).astype(np.float64))
+    full = (full * ws.reshape(M, -1).astype(np.float64)[None] * xs.astype(np.float64)[:, None, :]).sum(-1)
+    assert np.abs(got - full).max() <= 2e-6 * np.abs(full).max()
+
+
 def test_gemm_tf32x3_rejects_bad_shapes(L):
     W, X, O = tdev(np.zeros((8, 30), np.float32)), tdev(np.zeros((2, 30), np.float32)), tdev(np.zeros((2, 8), np.float32))
     assert L.c.tha_gemm_tf32x3(stream_ptr(), P(O), 8, P(W), 8, 30, P(X), 2, 30) == 7      # K % 4 != 0: NOT_SUPPORTED
