@@ -247,7 +247,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
           const int s = j % S::SW;
           if (j >= S::SW && !tc_mbar_wait(&wfree[s], ((j / S::SW) & 1u) ^ 1u, abort_flag)) break;
           tc_mbar_expect_tx(&wfull[s], S::W_BYTES);      // the box is always delivered whole (zero-filled past K)
-          tc_tma_2d_hint(wring + s * S::W_BYTES, mw, (kb0 + 4 * j) * TC_BK, row0, &wfull[s], pol_w);
+          tc_tma_2d_hint(wring + s * S::W_BYTES, mw, (kb0 + 4 * j) * (TC_BK / 4), row0, &wfull[s], pol_w);
         }
       } else
       for (int i = 0; i < nst; i++) {
@@ -475,11 +475,12 @@ static int tc_map(const void* ptr, long long rows, int K, long long ld, int box_
   auto it = g_maps.find(key);
   if (it != g_maps.end()) { *out = it->second; return THA_STATUS_SUCCESS; }
   CUtensorMap m;
-  const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  // int8 rows are described as 32-bit words (same bytes, same swizzle): coordinates along K are then in words
+  const cuuint64_t dims[2] = {(cuuint64_t)(elem_bytes == 4 ? K : K / 4), (cuuint64_t)rows};
   const cuuint64_t strides[1] = {(cuuint64_t)ld * elem_bytes};
-  const cuuint32_t box[2] = {(cuuint32_t)(128 / elem_bytes), (cuuint32_t)box_rows};
+  const cuuint32_t box[2] = {(cuuint32_t)32, (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
-  CUresult r = g_encode(&m, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 2,
+  CUresult r = g_encode(&m, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT32, 2,
                         const_cast<void*>(ptr), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                         (CUtensorMapL2promotion)tc_env("THA_TC_PROMO", (int)CU_TENSOR_MAP_L2_PROMOTION_L2_256B),
@@ -606,9 +607,12 @@ int gemm_tc_check_error() {
 // the reference's order and added in fp32 -- so without split-K the result is bit-identical to runq.c's loop
 // (compiled without FMA contraction).  TMEM holds a ring of group accumulators so the MMAs of the next groups
 // overlap the scaling of the previous one; shared memory holds a ring of [W 128x128 | X NTx128] int8 slots.
-//   warp 0  TMA producer (weights first: they do not depend on the previous kernel)   warp 1  MMA issuer
-//   warp 2  TMEM allocation     warps 4-11  epilogue: 2 warps per 32-lane TMEM quarter, NT/2 columns each
-constexpr int Q8I_THREADS = 384;
+//   warp 0  TMA producer (weights first: they do not depend on the previous kernel)   warps 1, 3  MMA issuers
+//   warp 2  TMEM allocation     warps 4-7  epilogue: one warp per 32-lane TMEM quarter, thread = weight row
+// Every tcgen05 instruction costs its issuing thread a few hundred cycles whatever its size (measured: ~300 per
+// kind::i8 MMA, ~200 per tcgen05.ld, ~450 per wait::ld), so the epilogue reads 128 accumulator columns -- 128/NT
+// consecutive groups, laid out back to back in TMEM -- per round trip.
+constexpr int Q8I_THREADS = 256;
 
 struct Q8iP {
   int M[3]; int tiles[3]; int out_off[3];
@@ -618,6 +622,9 @@ struct Q8iP {
   int slots_total, slots_per_split;  // ring slots of 128 values
   float* out; long long ldo; long long zstride;
   int* error_flag;
+  int dbg;
+  long long* trace;
+  int nring;                         // shared-memory ring slots in use
 };
 
 template <int NT>
@@ -625,10 +632,20 @@ struct Q8iSmem {
   static constexpr int W_BYTES = TC_BM * 128, X_BYTES = NT * 128, SLOT = W_BYTES + X_BYTES;
   static constexpr int NSLOT_RAW = (TC_SMEM_LIMIT - 3072) / SLOT;
   static constexpr int NSLOT = NSLOT_RAW > 10 ? 10 : NSLOT_RAW;
-  static constexpr int NBUF = (512 / NT) > 8 ? 8 : (512 / NT);
-  static constexpr int TMEM_COLS = NBUF * NT < 32 ? 32 : NBUF * NT;   // 128, 256, 512, 512: powers of two
-  static constexpr int TOTAL = NSLOT * SLOT + 1024 + (2 * NSLOT + 2 * NBUF) * 8 + 64;
+  // One tcgen05.commit per STAGE of SPC slots (a commit costs the issuing thread a few hundred cycles; the same
+  // barrier releases the stage's shared-memory slots to the producer and hands its accumulators to the epilogue).
+  static constexpr int SPC = 1;
+  // MMA-issuing warps: a tcgen05.mma.kind::i8 costs its issuing thread ~300 cycles whatever its size (measured), so
+  // the slots are dealt round-robin to two issuers (each owns whole groups: accumulation order is untouched).  The number
+  // of accumulator stages is a multiple of the issuers, so a stage is always refilled by the same thread (a waiter
+  // that skipped a phase of the release barrier would read its parity wrongly).
+  static constexpr int NISS = 2;
+  static constexpr int TMEM_COLS = 512;
+  static constexpr int NMD = 64;                  // commit barriers (more than the slots that can be in flight)
+  static constexpr int NACC_MAX = 32;
+  static constexpr int TOTAL = NSLOT * SLOT + 1024 + (NSLOT + NMD + NACC_MAX) * 8 + 64;
   static_assert(TOTAL <= TC_SMEM_LIMIT, "shared memory overflow");
+  static_assert(NSLOT + NACC_MAX + 1 <= NMD, "commit barrier ring too short");
 };
 
 __host__ __device__ constexpr uint32_t q8i_idesc(int nt) {   // kind::i8: D = S32 (2), A = B = signed 8-bit (1), K-major, M = 128
@@ -646,6 +663,11 @@ __device__ __forceinline__ void tc_tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "r"(taddr));
 }
 
+__device__ __forceinline__ void tc_tmem_ld64(uint32_t taddr, uint32_t* v) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x64.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47, %48, %49, %50, %51, %52, %53, %54, %55, %56, %57, %58, %59, %60, %61, %62, %63}, [%64];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31]), "=r"(v[32]), "=r"(v[33]), "=r"(v[34]), "=r"(v[35]), "=r"(v[36]), "=r"(v[37]), "=r"(v[38]), "=r"(v[39]), "=r"(v[40]), "=r"(v[41]), "=r"(v[42]), "=r"(v[43]), "=r"(v[44]), "=r"(v[45]), "=r"(v[46]), "=r"(v[47]), "=r"(v[48]), "=r"(v[49]), "=r"(v[50]), "=r"(v[51]), "=r"(v[52]), "=r"(v[53]), "=r"(v[54]), "=r"(v[55]), "=r"(v[56]), "=r"(v[57]), "=r"(v[58]), "=r"(v[59]), "=r"(v[60]), "=r"(v[61]), "=r"(v[62]), "=r"(v[63]) : "r"(taddr));
+}
+
 template <int NT>
 __global__ void __launch_bounds__(Q8I_THREADS, 1)
 gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__ CUtensorMap mw1,
@@ -654,12 +676,13 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
   constexpr int CH = NT / 2;   // accumulator columns per epilogue thread
   extern __shared__ unsigned char tc_smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int nring = p.nring;             // ring slots actually used (the activation scales take the rest)
+  float* xs_sm = reinterpret_cast<float*>(smem + nring * S::SLOT);   // [groups of this split][NT]
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::NSLOT * S::SLOT);
   uint64_t* full = bars;                 // slot landed (W + X bytes)
-  uint64_t* empty = full + S::NSLOT;     // the MMAs that read the slot have completed
-  uint64_t* afull = empty + S::NSLOT;    // group accumulator complete
-  uint64_t* aempty = afull + S::NBUF;    // group accumulator read out by the 8 epilogue warps
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aempty + S::NBUF);
+  uint64_t* mdone = full + S::NSLOT;     // the MMAs of a stage have completed: slots reusable, accumulators readable
+  uint64_t* aempty = mdone + S::NMD;     // a stage's accumulators have been read out by the 8 epilogue warps
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aempty + S::NACC_MAX);
   int* abort_flag = reinterpret_cast<int*>(tmem_slot + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -674,11 +697,16 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
   int nsub = p.K / 32 - slot0 * 4;               // K = 32 sub-blocks (one MMA each) of this split
   if (nsub > nslots * 4) nsub = nslots * 4;
   const int mpg = p.gs >> 5;                     // MMAs per group
-  const int ng = nsub / mpg;                     // groups of this split
+  const int ng = (p.dbg & 8) ? 0 : nsub / mpg;   // groups of this split
+  const int gps = 128 / p.gs;                    // groups per slot
+  const int gpc = gps * S::SPC;                  // groups per stage (one commit)
+  const int nacc = S::TMEM_COLS / (gpc * NT);    // accumulator stages (slots) in TMEM: 4 .. 32, a power of two
+  const int nstage = (nslots + S::SPC - 1) / S::SPC;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < S::NSLOT; s++) { tc_mbar_init(&full[s], 1); tc_mbar_init(&empty[s], 1); }
-    for (int b = 0; b < S::NBUF; b++) { tc_mbar_init(&afull[b], 1); tc_mbar_init(&aempty[b], 8); }
+    for (int s = 0; s < S::NSLOT; s++) tc_mbar_init(&full[s], 1);
+    for (int b = 0; b < S::NMD; b++) tc_mbar_init(&mdone[b], 1);
+    for (int b = 0; b < S::NACC_MAX; b++) tc_mbar_init(&aempty[b], 4);
     *abort_flag = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -702,100 +730,150 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
       asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
       // the first ring of weight tiles goes out before the dependency wait (transaction bytes may land before the
       // matching expect_tx: the phase cannot complete until the arrival below)
-      const int pre = nslots < S::NSLOT ? nslots : S::NSLOT;
+      const int pre = nslots < nring ? nslots : nring;
       for (int j = 0; j < pre; j++)
-        tc_tma_2d_hint(smem + j * S::SLOT, mw, (slot0 + j) * 128, row0, &full[j], pol_w);
+        tc_tma_2d_hint(smem + j * S::SLOT, mw, (slot0 + j) * 32, row0, &full[j], pol_w);
       pdl_wait();
       for (int j = 0; j < pre; j++) {
         tc_mbar_expect_tx(&full[j], S::SLOT);
-        tc_tma_2d(smem + j * S::SLOT + S::W_BYTES, &mx, (slot0 + j) * 128, n0, &full[j]);
+        tc_tma_2d(smem + j * S::SLOT + S::W_BYTES, &mx, (slot0 + j) * 32, n0, &full[j]);
       }
       for (int j = pre; j < nslots; j++) {
-        const int s = j % S::NSLOT;
-        if (!tc_mbar_wait(&empty[s], ((j / S::NSLOT) & 1u) ^ 1u, abort_flag)) break;
+        const int s = j % nring;
+        if (p.dbg & 8) { if (!tc_mbar_wait(&full[s], ((j / nring) & 1u) ^ 1u, abort_flag)) break; }   // TMA alone
+        else {
+          const int st = j - nring;                    // the slot use whose MMAs must have completed
+          if (!tc_mbar_wait(&mdone[st % S::NMD], (st / S::NMD) & 1u, abort_flag)) break;
+        }
+        TC_TRACE(5, j);
         tc_mbar_expect_tx(&full[s], S::SLOT);
-        tc_tma_2d_hint(smem + s * S::SLOT, mw, (slot0 + j) * 128, row0, &full[s], pol_w);
-        tc_tma_2d(smem + s * S::SLOT + S::W_BYTES, &mx, (slot0 + j) * 128, n0, &full[s]);
+        TC_TRACE(0, j);
+        tc_tma_2d_hint(smem + s * S::SLOT, mw, (slot0 + j) * 32, row0, &full[s], pol_w);
+        tc_tma_2d(smem + s * S::SLOT + S::W_BYTES, &mx, (slot0 + j) * 32, n0, &full[s]);
       }
     }
-  } else if (warp == 1) {
-    if (lane == 0) {
+  } else if (warp == 1 || warp == 3) {
+    // ===== MMA issuers (warps 1 and 3): issuer i takes the slots j = i, i + 2, ...
+    if (lane == 0 && !(p.dbg & 8)) {
       constexpr uint32_t idesc = q8i_idesc(NT);
-      int gsub = 0, gi = 0;                       // sub-block index within the split, group index
+      const int mpg_sh = 31 - __clz(mpg), gps_sh = 31 - __clz(gps), nacc_mask = nacc - 1;   // all powers of two
       bool ok = true;
-      for (int j = 0; j < nslots && ok; j++) {
-        const int s = j % S::NSLOT;
-        if (!tc_mbar_wait(&full[s], (j / S::NSLOT) & 1u, abort_flag)) break;
+      for (int j = warp >> 1; j < nslots && ok; j += S::NISS) {
+        const int s = j % nring;
+        if (j >= nacc) {                          // the accumulator stage must have been drained
+          ok = tc_mbar_wait(&aempty[j & nacc_mask], ((j / nacc) & 1u) ^ 1u, abort_flag);
+          if (!ok) break;
+        }
+        if (!tc_mbar_wait(&full[s], (j / nring) & 1u, abort_flag)) break;
+        if (warp == 1) TC_TRACE(1, j);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint64_t adesc = tc_smem_desc(tc_smem_u32(smem + s * S::SLOT));
         const uint64_t bdesc = tc_smem_desc(tc_smem_u32(smem + s * S::SLOT + S::W_BYTES));
-        for (int sub = 0; sub < 4 && gsub < nsub; sub++, gsub++) {
-          const int in_g = gsub % mpg;
-          const int buf = gi % S::NBUF;
-          if (in_g == 0 && gi >= S::NBUF) {
-            ok = tc_mbar_wait(&aempty[buf], ((gi / S::NBUF) & 1u) ^ 1u, abort_flag);
-            if (!ok) break;
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          }
-          q8i_mma(tmem_base + buf * NT, adesc + (uint64_t)(sub * 2), bdesc + (uint64_t)(sub * 2), idesc, (uint32_t)(in_g != 0));
-          if (in_g == mpg - 1) { tc_commit(&afull[buf]); gi++; }
+        const uint32_t acc0 = tmem_base + (uint32_t)(((j & nacc_mask) << gps_sh) * NT);
+        const int nsub_j = (nsub - 4 * j) < 4 ? (nsub - 4 * j) : 4;
+#pragma unroll
+        for (int sub = 0; sub < 4; sub++) {
+          if (sub < nsub_j && !(p.dbg & 1))
+            q8i_mma(acc0 + (uint32_t)((sub >> mpg_sh) * NT), adesc + (uint64_t)(sub * 2), bdesc + (uint64_t)(sub * 2), idesc,
+                    (uint32_t)((sub & (mpg - 1)) != 0));
         }
-        tc_commit(&empty[s]);
+        tc_commit(&mdone[j % S::NMD]);
+        if (warp == 1) TC_TRACE(2, j);
       }
     }
   } else if (warp >= 4) {
-    const int q = warp & 3, chalf = (warp - 4) >> 2;
+    // ===== epilogue: thread = weight row (TMEM lane), all NT columns
+    const int q = warp & 3;
     const int r = q * 32 + lane;
     const int row = row0 + r;
     const bool row_ok = row < p.M[mat];
     const int g0 = (slot0 * 128) / p.gs;
     const float* srow = p.S[mat] + (size_t)(row_ok ? row : p.M[mat] - 1) * p.ngrp + g0;
-    float acc[CH];
+    float acc[NT];
 #pragma unroll
-    for (int c = 0; c < CH; c++) acc[c] = 0.0f;
-    float ws_next = ng > 0 ? __ldg(srow) : 0.0f;
+    for (int c = 0; c < NT; c++) acc[c] = 0.0f;
+    // Weight scales: this thread's row, four groups per 128-bit load, requested two to three chunks (8-12 groups,
+    // well over a thousand cycles) before their use -- with ~200 KB of the SM's memory carved out as shared, L1 keeps
+    // next to nothing and every one of these loads is an L2 round trip.
+    const bool ws_vec = ((reinterpret_cast<uintptr_t>(srow) & 15u) == 0) && (p.ngrp % 4 == 0);
+    auto load_ws4 = [&](int chunk) -> float4 {
+      const int g = 4 * chunk;
+      float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (g + 3 < ng && ws_vec) return __ldg(reinterpret_cast<const float4*>(srow + g));
+      if (g < ng) r4.x = __ldg(srow + g);
+      if (g + 1 < ng) r4.y = __ldg(srow + g + 1);
+      if (g + 2 < ng) r4.z = __ldg(srow + g + 2);
+      if (g + 3 < ng) r4.w = __ldg(srow + g + 3);
+      return r4;
+    };
+    float4 ws_cur = load_ws4(0), ws_n1 = load_ws4(1), ws_n2 = load_ws4(2);
     pdl_trigger();
     pdl_wait();                                   // the activation scales come from the previous kernel
-    const float* xs0 = p.xsT + (size_t)g0 * p.ldxs + n0 + chalf * CH;
+    {  // all activation scales of this CTA's K range -> shared memory (NT floats per group), once
+      const float* src = p.xsT + (size_t)g0 * p.ldxs + n0;
+      const int t = threadIdx.x - 128;            // 0..127
+      for (int i = t; i < ng * (NT / 4); i += 128) {
+        const int g = i / (NT / 4), c4 = i - g * (NT / 4);
+        reinterpret_cast<float4*>(xs_sm)[i] = __ldg(reinterpret_cast<const float4*>(src + (size_t)g * p.ldxs) + c4);
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");   // the 4 epilogue warps only
+    }
+    constexpr int LG = 128 / NT;                  // groups per TMEM read (128 columns)
+    const int sb_sh = 31 - __clz(LG) - (31 - __clz(gps));   // log2(slots per batch)
+    const int nb_mask = (nacc >> sb_sh) - 1;      // batches in the TMEM ring - 1
+    const uint32_t tq = tmem_base + ((uint32_t)(q * 32) << 16);
     bool ok = true;
-    for (int gi = 0; gi < ng && ok; gi++) {
-      const float ws = ws_next;
-      if (gi + 1 < ng) ws_next = __ldg(srow + gi + 1);
-      float xs[CH];
-#pragma unroll
-      for (int c = 0; c < CH; c += 4) {
-        const float4 t = __ldg(reinterpret_cast<const float4*>(xs0 + (size_t)gi * p.ldxs + c));
-        xs[c] = t.x; xs[c + 1] = t.y; xs[c + 2] = t.z; xs[c + 3] = t.w;
+    uint32_t v[128];
+    for (int bi = 0; bi * LG < ng && ok; bi++) {
+      // the batch's slots: the last slot of each issuer covers the earlier ones (an issuer's commits complete in order)
+      const int s_first = bi << sb_sh;
+      int s_last = s_first + (1 << sb_sh) - 1;
+      if (s_last > nslots - 1) s_last = nslots - 1;
+      int w = 1;
+      if (lane == 0) {
+        w = tc_mbar_wait(&mdone[s_last % S::NMD], (s_last / S::NMD) & 1u, abort_flag) ? 1 : 0;
+        if (w && s_last > s_first) w = tc_mbar_wait(&mdone[(s_last - 1) % S::NMD], ((s_last - 1) / S::NMD) & 1u, abort_flag) ? 1 : 0;
       }
-      const int buf = gi % S::NBUF;
-      ok = tc_mbar_wait(&afull[buf], (gi / S::NBUF) & 1u, abort_flag);
+      ok = __shfl_sync(THA_FULL_MASK, w, 0) != 0;
       if (!ok) break;
+      if (threadIdx.x == 128) TC_TRACE(3, bi);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      uint32_t v[CH];
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * NT + chalf * CH);
-      if constexpr (CH == 8) {
-        tc_tmem_ld8(taddr, *reinterpret_cast<uint32_t(*)[8]>(&v[0]));
-      } else {
-#pragma unroll
-        for (int c = 0; c < CH; c += 16) tc_tmem_ld16(taddr + c, *reinterpret_cast<uint32_t(*)[16]>(&v[c]));
-      }
+      const uint32_t ta = tq + (uint32_t)((bi & nb_mask) * 128);
+      tc_tmem_ld64(ta, v);
+      tc_tmem_ld64(ta + 64, v + 64);
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
-      if (lane == 0) tc_mbar_arrive(&aempty[buf]);
+      if (lane == 0)
+        for (int sl = s_first; sl <= s_last; sl++) tc_mbar_arrive(&aempty[sl & (nacc - 1)]);
+      if (threadIdx.x == 128) TC_TRACE(4, bi);
 #pragma unroll
-      for (int c = 0; c < CH; c++) {
-        // |group sum| <= 128 * 127 * 127 < 2^22: 1.5 * 2^23 + i is exact in fp32, so this IS (float)i -- two full-rate
-        // instructions instead of a quarter-rate I2F
-        const float f = __int_as_float(0x4B400000 + (int)v[c]) - 12582912.0f;
-        acc[c] = __fadd_rn(acc[c], __fmul_rn(__fmul_rn(f, ws), xs[c]));   // runq.c:334, no contraction
+      for (int b = 0; b < LG; b++) {
+        const int gi = bi * LG + b;
+        if (gi < ng) {
+          if ((gi & 3) == 0 && gi > 0) { ws_cur = ws_n1; ws_n1 = ws_n2; ws_n2 = load_ws4((gi >> 2) + 2); }
+          const int wi = gi & 3;
+          const float ws = wi == 0 ? ws_cur.x : (wi == 1 ? ws_cur.y : (wi == 2 ? ws_cur.z : ws_cur.w));
+#pragma unroll
+          for (int c = 0; c < NT; c += 4) {
+            const float4 t = *reinterpret_cast<const float4*>(xs_sm + gi * NT + c);   // same address in every lane: a broadcast
+            const float xs[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+              // |group sum| <= 128 * 127 * 127 < 2^22: 1.5 * 2^23 + i is exact in fp32, so this IS (float)i -- two
+              // full-rate instructions instead of a quarter-rate I2F
+              const float f = __int_as_float(0x4B400000 + (int)v[b * NT + c + e]) - 12582912.0f;
+              acc[c + e] = __fadd_rn(acc[c + e], __fmul_rn(__fmul_rn(f, ws), xs[e]));   // runq.c:334, no contraction
+            }
+          }
+        }
       }
     }
     float* outz = p.out + (size_t)blockIdx.z * p.zstride + p.out_off[mat] + row;
     if (ok && row_ok) {
 #pragma unroll
-      for (int c = 0; c < CH; c++) {
-        const int n = n0 + chalf * CH + c;
+      for (int c = 0; c < NT; c++) {
+        const int n = n0 + c;
         if (n < p.N) outz[(size_t)n * p.ldo] = acc[c];
       }
     }
@@ -807,6 +885,7 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(S::TMEM_COLS));
   }
   if (threadIdx.x == 0 && *abort_flag && p.error_flag) atomicExch(p.error_flag, 1);
+  (void)nstage;
 }
 
 bool gemm_q8i_ok(const Q8iArgs& a) {
@@ -818,7 +897,10 @@ bool gemm_q8i_ok(const Q8iArgs& a) {
   return true;
 }
 
-int gemm_q8i_pick_nt(int N) { return N <= 16 ? 16 : (N <= 32 ? 32 : 64); }
+int gemm_q8i_pick_nt(int N, int gs) {   // a slot's groups must fit one 128-column TMEM read: NT <= gs
+  const int nt = N <= 16 ? 16 : (N <= 32 ? 32 : 64);
+  return nt > gs ? gs : nt;
+}
 
 template <int NT>
 static int q8i_launch_nt(cudaStream_t st, const CUtensorMap* mw, const CUtensorMap& mx, const Q8iP& p, dim3 grid, bool pdl) {
@@ -831,7 +913,7 @@ static int q8i_launch_nt(cudaStream_t st, const CUtensorMap* mw, const CUtensorM
 
 int gemm_q8i_launch(cudaStream_t st, const Q8iArgs& a, bool pdl) {
   if (!gemm_q8i_ok(a)) return THA_STATUS_INVALID_ARG;
-  const int NT = gemm_q8i_pick_nt(a.N);
+  const int NT = gemm_q8i_pick_nt(a.N, a.gs);
   if (a.ldxs < ceil_div(a.N, NT) * NT) return THA_STATUS_INVALID_ARG;   // a column tile reads NT scales per group
   CUtensorMap mw[3], mx;
   Q8iP p = {};
@@ -853,6 +935,15 @@ int gemm_q8i_launch(cudaStream_t st, const Q8iArgs& a, bool pdl) {
   if (ceil_div(p.slots_total, p.slots_per_split) != splits) return THA_STATUS_INVALID_ARG;
   p.out = a.out; p.ldo = a.ldo; p.zstride = a.zstride;
   THA_TRY_RC(gemm_tc_init(&p.error_flag));
+  p.dbg = tc_env("THA_Q8I_DBG", 0);
+  p.trace = g_trace;
+  {  // the activation scales of one split sit behind the ring: [groups per split][NT] floats
+    const int slot_bytes = TC_BM * 128 + NT * 128;
+    const int nslot_max = (TC_SMEM_LIMIT - 3072) / slot_bytes > 10 ? 10 : (TC_SMEM_LIMIT - 3072) / slot_bytes;
+    const int xs_bytes = p.slots_per_split * (128 / a.gs) * NT * 4;
+    p.nring = nslot_max - ceil_div(xs_bytes, slot_bytes);
+    if (p.nring < 3) return THA_STATUS_NOT_SUPPORTED;
+  }
   p.ny = ceil_div(a.N, NT);
   dim3 grid(tiles * p.ny, 1, splits);
   switch (NT) {

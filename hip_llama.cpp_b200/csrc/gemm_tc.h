@@ -38,7 +38,7 @@ struct Q8iArgs {
   float* out; long long ldo; long long zstride; int splits;   // split over 128-value slots
 };
 bool gemm_q8i_ok(const Q8iArgs& a);
-int gemm_q8i_pick_nt(int N);
+int gemm_q8i_pick_nt(int N, int gs);
 int gemm_q8i_launch(cudaStream_t st, const Q8iArgs& a, bool pdl);
 
 bool gemm_tc_ok(const TcArgs& a);
