@@ -161,21 +161,20 @@ __global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __res
 // ---- Q8_0 rows (runq.c:344-481 on the tensor cores) ---------------------------------------------------------------
 // The activation that enters a matmul is quantised exactly as runq.c:145-171 does (scale = max|x| / 127 per group,
 // round half away from zero) -- the int8 values and scales are bit-identical to q8_prep_kernel's for the same input --
-// and handed to the matmul as its dequantised fp32 value q * scale split into tf32 hi/lo.
+// and handed to the int8 tensor-core matmul (gemm_q8i_kernel) as int8 rows + transposed group scales.
 
-__device__ __forceinline__ void q8_group_split(const float* v, int n_per_lane, float* __restrict__ oh, float* __restrict__ ol,
-                                               int base, int lane) {
+// One group of one row: int8 values -> xq[row, base + ...], scale -> xsT[g * ldxs + row] (transposed: the matmul's
+// epilogue wants the NT scales of a group side by side).
+__device__ __forceinline__ void q8_group_quant(const float* v, int n_per_lane, int8_t* __restrict__ xq_row, float* __restrict__ xsT,
+                                               int ldxs, int row, int g, int gs, int lane) {
   float amax = 0.0f;
   for (int j = 0; j < n_per_lane; j++) amax = fmaxf(amax, fabsf(v[j]));
   amax = warp_max(amax);
   const float scale = __fdiv_rn(amax, 127.0f);
+  if (lane == 0) xsT[(size_t)g * ldxs + row] = scale;
   for (int j = 0; j < n_per_lane; j++) {
     const float r = __fdiv_rn(v[j], scale);
-    const int q = (r != r) ? 0 : __float2int_rn(roundf(r));
-    const float deq = (float)(int8_t)q * scale;
-    const float hi = st_tf32(deq);
-    oh[base + lane + 32 * j] = hi;
-    ol[base + lane + 32 * j] = deq - hi;
+    xq_row[g * gs + lane + 32 * j] = (r != r) ? (int8_t)0 : (int8_t)__float2int_rn(roundf(r));
   }
 }
 
@@ -185,7 +184,7 @@ __global__ void __launch_bounds__(256) tc_prep_q8_kernel(float* __restrict__ x, 
                                                          long long zstride, const float* __restrict__ emb,
                                                          const int* __restrict__ token, const int* __restrict__ pos,
                                                          const float* __restrict__ gain, int d, int gs,
-                                                         float* __restrict__ xh, float* __restrict__ xl,
+                                                         int8_t* __restrict__ xq, float* __restrict__ xsT, int ldxs,
                                                          const int* __restrict__ gather) {
   __shared__ float red[33];
   pdl_wait();
@@ -194,10 +193,10 @@ __global__ void __launch_bounds__(256) tc_prep_q8_kernel(float* __restrict__ x, 
   const int b = gather ? gather[ob] : ob;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float* xr = x + (size_t)b * d;
-  float* hr = xh + (size_t)ob * d;
-  float* lr = xl + (size_t)ob * d;
-  if (pos[b] < 0) {
-    for (int i = threadIdx.x; i < d; i += blockDim.x) { hr[i] = 0.0f; lr[i] = 0.0f; }
+  int8_t* qr = xq + (size_t)ob * d;
+  if (pos[b] < 0) {   // idle slot: zeros in, zeros out
+    for (int i = threadIdx.x; i < d; i += blockDim.x) qr[i] = 0;
+    for (int g = threadIdx.x; g < d / gs; g += blockDim.x) xsT[(size_t)g * ldxs + ob] = 0.0f;
     return;
   }
   const float* er = emb ? emb + (size_t)token[b] * d : nullptr;
@@ -232,15 +231,15 @@ __global__ void __launch_bounds__(256) tc_prep_q8_kernel(float* __restrict__ x, 
       }
       v[j] = gain[i] * (ssn * t);
     }
-    q8_group_split(v, npl, hr, lr, g * gs, lane);
+    q8_group_quant(v, npl, qr, xsT, ldxs, ob, g, gs, lane);
   }
 }
 
 // Warp per group: src row (attention output), or with h > 0 the SwiGLU of the w1|w3 partials (run.cc:344-347 order),
-// quantised per group and written as dequantised hi/lo.  grid (ceil(K / gs / 8), rows)
+// quantised per group (int8 row + transposed scales).  grid (ceil(K / gs / 8), rows)
 __global__ void __launch_bounds__(256) tc_quant_split_kernel(const float* __restrict__ src, long long ld, int nz,
                                                              long long zstride, int h, const int* __restrict__ pos, int K,
-                                                             int gs, float* __restrict__ oh, float* __restrict__ ol) {
+                                                             int gs, int8_t* __restrict__ oq, float* __restrict__ osT, int ldxs) {
   pdl_wait();
   pdl_trigger();
   const int b = blockIdx.y, lane = threadIdx.x & 31;
@@ -269,7 +268,7 @@ __global__ void __launch_bounds__(256) tc_quant_split_kernel(const float* __rest
     }
     v[j] = r;
   }
-  q8_group_split(v, npl, oh + (size_t)b * K, ol + (size_t)b * K, g * gs, lane);
+  q8_group_quant(v, npl, oq + (size_t)b * K, osT, ldxs, b, g, gs, lane);
 }
 
 // ---- scratch ----------------------------------------------------------------------------
@@ -277,6 +276,9 @@ struct TcScratch {
   float *xh = nullptr, *xl = nullptr, *hh = nullptr, *hl = nullptr, *scale = nullptr, *part = nullptr;
   float *xr = nullptr, *qr = nullptr, *xbr = nullptr;   // row-major activations of a prefill chunk (decode uses RunState's)
   int* tab = nullptr;                                   // prefill row / tile tables
+  int8_t *xq = nullptr, *hq = nullptr;                  // Q8_0: quantised matmul inputs [R, d], [R, hidden]
+  float *xsT = nullptr, *hsT = nullptr;                 // their group scales, transposed [groups, ldxs]
+  size_t n_xq = 0, n_hq = 0, n_xsT = 0, n_hsT = 0;
   size_t n_x = 0, n_xl = 0, n_h = 0, n_hl = 0, n_part = 0, n_xr = 0, n_qr = 0, n_xbr = 0, n_tab = 0; int n_b = 0;
 };
 static std::map<int, TcScratch> g_tc_scratch;
@@ -354,10 +356,18 @@ static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefil
   std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
   TcScratch& s = g_tc_scratch[ws->device];
   const TcPlan pl = make_plan(*c, R, q8);
-  THA_TRY_RC(grow(&s.xh, &s.n_x, (size_t)R * c->dim, ws));
-  THA_TRY_RC(grow(&s.xl, &s.n_xl, (size_t)R * c->dim, ws));
-  THA_TRY_RC(grow(&s.hh, &s.n_h, (size_t)R * c->hidden_dim, ws));
-  THA_TRY_RC(grow(&s.hl, &s.n_hl, (size_t)R * c->hidden_dim, ws));
+  if (q8) {   // int8 rows (sized in floats: bytes / 4) and transposed scales (rows padded to the widest column tile)
+    const size_t ldxs = (size_t)ceil_div(R, 64) * 64;
+    THA_TRY_RC(grow(reinterpret_cast<float**>(&s.xq), &s.n_xq, ((size_t)R * c->dim + 3) / 4, ws));
+    THA_TRY_RC(grow(reinterpret_cast<float**>(&s.hq), &s.n_hq, ((size_t)R * c->hidden_dim + 3) / 4, ws));
+    THA_TRY_RC(grow(&s.xsT, &s.n_xsT, ldxs * (c->dim / 32), ws));
+    THA_TRY_RC(grow(&s.hsT, &s.n_hsT, ldxs * (c->hidden_dim / 32), ws));
+  } else {
+    THA_TRY_RC(grow(&s.xh, &s.n_x, (size_t)R * c->dim, ws));
+    THA_TRY_RC(grow(&s.xl, &s.n_xl, (size_t)R * c->dim, ws));
+    THA_TRY_RC(grow(&s.hh, &s.n_h, (size_t)R * c->hidden_dim, ws));
+    THA_TRY_RC(grow(&s.hl, &s.n_hl, (size_t)R * c->hidden_dim, ws));
+  }
   THA_TRY_RC(grow(&s.part, &s.n_part, pl.part_floats, ws));
   if (R > s.n_b) {
     if (s.scale) cudaFree(s.scale);
@@ -407,13 +417,13 @@ static int gemm(cudaStream_t st, bool pdl, int n_mats, const float* const* W, co
 }
 
 static int gemm_q8(cudaStream_t st, bool pdl, int n_mats, const int8_t* const* Wq, const float* const* Ws, int gs, const int* M,
-                   const int* off, int K, const float* xh, const float* xl, int N, float* out, long long ldo, long long zstride,
-                   int splits) {
-  TcArgs a = {};
+                   const int* off, int K, const int8_t* xq, const float* xsT, int ldxs, int N, float* out, long long ldo,
+                   long long zstride, int splits) {
+  Q8iArgs a = {};
   a.n_mats = n_mats;
   for (int i = 0; i < n_mats; i++) { a.Wq[i] = Wq[i]; a.Ws[i] = Ws[i]; a.M[i] = M[i]; a.out_off[i] = off[i]; }
-  a.gs = gs; a.K = K; a.Xhi = xh; a.Xlo = xl; a.N = N; a.ldx = K; a.out = out; a.ldo = ldo; a.zstride = zstride; a.splits = splits;
-  return gemm_tc_launch(st, a, pdl);
+  a.gs = gs; a.K = K; a.Xq = xq; a.xsT = xsT; a.ldxs = ldxs; a.N = N; a.out = out; a.ldo = ldo; a.zstride = zstride; a.splits = splits;
+  return gemm_q8i_launch(st, a, pdl);
 }
 
 // What differs between a decode step and a prefill chunk.
@@ -442,17 +452,19 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
   const int ld_qkv = d + 2 * kvd, ld_h = 2 * hd;
   const int* nogather = nullptr;
   const int gs = wq ? wq->group_size : 0;
+  const int ldxs = ceil_div(R, 64) * 64;
   // the (fused RMSNorm +) split that feeds a matmul whose input is the residual stream
   auto prep = [&](int rows, int nz, long long zs, const float* emb, const float* gain, const int* gather) -> int {
     if (wq) {
       THA_CUDA_OK(launch(tc_prep_q8_kernel, dim3(rows), dim3(256), 0, st, pdl, io.x, (const float*)sc.part, nz, zs, emb, io.token,
-                         io.pos, gain, d, gs, sc.xh, sc.xl, gather));
+                         io.pos, gain, d, gs, sc.xq, sc.xsT, ldxs, gather));
     } else {
       THA_CUDA_OK(launch(tc_prep_kernel, dim3(rows), dim3(256), 0, st, pdl, io.x, (const float*)sc.part, nz, zs, emb, io.token,
                          io.pos, gain, d, sc.xh, sc.xl, sc.scale, gather));
     }
     return THA_STATUS_SUCCESS;
   };
+  bool mm_hidden = false;   // Q8_0: the next matmul reads the quantised hidden activations (w2) instead of the dim-wide ones
   // n stacked matrices of layer l: fp32 pointers or (int8, scales) pairs
   auto mm = [&](int n, const float* const* W, const tha_qtensor_t* const* Q, size_t per_layer, int l, const int* M, const int* off,
                 int K, const float* xh, const float* xl, int N, float* out, long long ldo, long long zs, int z,
@@ -465,7 +477,8 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
       q[i] = Q[i]->q + (size_t)l * elems;
       sc3[i] = Q[i]->s + (size_t)l * (elems / gs);
     }
-    return gemm_q8(st, pdl, n, q, sc3, gs, M, off, K, xh, xl, N, out, ldo, zs, z);
+    const bool hidden_in = mm_hidden;       // which quantised buffer feeds this matmul
+    return gemm_q8(st, pdl, n, q, sc3, gs, M, off, K, hidden_in ? sc.hq : sc.xq, hidden_in ? sc.hsT : sc.xsT, ldxs, N, out, ldo, zs, z);
   };
   int prev_z = 0;                 // partials waiting to be added into x
   long long prev_zs = 0;
@@ -494,7 +507,7 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
     }
     if (wq)   // runq.c:437: the attention output is quantised before wo
       THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(d / gs, 8), R), dim3(256), 0, st, pdl, (const float*)io.xb, (long long)d,
-                         0, 0LL, 0, io.pos, d, gs, sc.xh, sc.xl));
+                         0, 0LL, 0, io.pos, d, gs, sc.xq, sc.xsT, ldxs));
     {
       const float* W[1] = {wq ? nullptr : w.wo + (size_t)l * d * d};
       const tha_qtensor_t* Q[1] = {wq ? &wq->wo : nullptr};
@@ -510,7 +523,7 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
     }
     if (wq)   // runq.c:457-465: SwiGLU, then quantise hb
       THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(hd / gs, 8), R), dim3(256), 0, st, pdl, (const float*)sc.part,
-                         (long long)ld_h, pl.z_w13, (long long)R * ld_h, hd, io.pos, hd, gs, sc.hh, sc.hl));
+                         (long long)ld_h, pl.z_w13, (long long)R * ld_h, hd, io.pos, hd, gs, sc.hq, sc.hsT, ldxs));
     else
       THA_CUDA_OK(launch(tc_swiglu_split_kernel, dim3(ceil_div(hd, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part, pl.z_w13,
                          (long long)R * ld_h, ld_h, io.pos, hd, sc.hh, sc.hl));
@@ -518,7 +531,10 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
       const float* W[1] = {wq ? nullptr : w.w2 + (size_t)l * d * hd};
       const tha_qtensor_t* Q[1] = {wq ? &wq->w2 : nullptr};
       const int M[1] = {d}, off[1] = {0};
-      THA_TRY_RC(mm(1, W, Q, 0, l, M, off, hd, sc.hh, sc.hl, R, sc.part, d, (long long)R * d, pl.z_w2, nullptr));
+      mm_hidden = true;
+      const int rc_w2 = mm(1, W, Q, 0, l, M, off, hd, sc.hh, sc.hl, R, sc.part, d, (long long)R * d, pl.z_w2, nullptr);
+      mm_hidden = false;
+      THA_TRY_RC(rc_w2);
     }
     prev_z = pl.z_w2;
     prev_zs = (long long)R * d;
