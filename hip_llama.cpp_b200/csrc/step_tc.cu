@@ -48,7 +48,7 @@ __device__ __forceinline__ float st_tf32(float v) { return __uint_as_float((__fl
 // One block per output row.  x row: embedding row (emb != nullptr) or x + sum of nz partials.  With `gather`
 // output row r is computed from source row gather[r] (the classifier input of a prefill chunk: the last
 // row of every sequence) and x is left untouched.
-__global__ void __launch_bounds__(256) tc_prep_kernel(float* __restrict__ x, const float* __restrict__ part, int nz,
+__global__ void __launch_bounds__(1024) tc_prep_kernel(float* __restrict__ x, const float* __restrict__ part, int nz,
                                                       long long zstride, const float* __restrict__ emb,
                                                       const int* __restrict__ token, const int* __restrict__ pos,
                                                       const float* __restrict__ gain, int d, float* __restrict__ xh,
@@ -163,112 +163,122 @@ __global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __res
 // round half away from zero) -- the int8 values and scales are bit-identical to q8_prep_kernel's for the same input --
 // and handed to the int8 tensor-core matmul (gemm_q8i_kernel) as int8 rows + transposed group scales.
 
-// One group of one row: int8 values -> xq[row, base + ...], scale -> xsT[g * ldxs + row] (transposed: the matmul's
-// epilogue wants the NT scales of a group side by side).
-__device__ __forceinline__ void q8_group_quant(const float* v, int n_per_lane, int8_t* __restrict__ xq_row, float* __restrict__ xsT,
-                                               int ldxs, int row, int g, int gs, int lane) {
-  float amax = 0.0f;
-  for (int j = 0; j < n_per_lane; j++) amax = fmaxf(amax, fabsf(v[j]));
-  amax = warp_max(amax);
+// Four consecutive values per thread, a group = gs/4 consecutive lanes (8, 16 or 32): the group maximum is a
+// segmented shuffle reduction, the four int8 results leave as one 32-bit store.  v = the thread's values (index i4 in
+// units of float4 within the row).  scale -> xsT[g * ldxs + row] (transposed: the matmul's epilogue wants the NT scales
+// of a group side by side).
+// Called by whole warps (lanes past the row pass valid = false and zeros).
+__device__ __forceinline__ void q8_quant4(float4 v, int gs, int i4, int8_t* __restrict__ xq_row, float* __restrict__ xsT,
+                                          int ldxs, int row, bool valid) {
+  float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+  for (int o = gs >> 3; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(THA_FULL_MASK, amax, o));
   const float scale = __fdiv_rn(amax, 127.0f);
-  if (lane == 0) xsT[(size_t)g * ldxs + row] = scale;
-  for (int j = 0; j < n_per_lane; j++) {
-    const float r = __fdiv_rn(v[j], scale);
-    xq_row[g * gs + lane + 32 * j] = (r != r) ? (int8_t)0 : (int8_t)__float2int_rn(roundf(r));
+  if (!valid) return;
+  const int g = (4 * i4) / gs;
+  if (((4 * i4) % gs) == 0) xsT[(size_t)g * ldxs + row] = scale;
+  const float in[4] = {v.x, v.y, v.z, v.w};
+  unsigned int packed = 0;
+#pragma unroll
+  for (int e = 0; e < 4; e++) {
+    const float r = __fdiv_rn(in[e], scale);
+    const int q = (r != r) ? 0 : __float2int_rn(roundf(r));
+    packed |= ((unsigned int)q & 0xFFu) << (8 * e);
   }
+  *reinterpret_cast<unsigned int*>(xq_row + 4 * i4) = packed;
 }
 
-// One block per output row: x row = embedding row or x + sum of partials (written back), RMSNorm in the reference's
-// order w * (ss * x) (run.cc:196-209), group quantisation, dequantised hi/lo out.  gs in {32, 64, 128}.
-__global__ void __launch_bounds__(256) tc_prep_q8_kernel(float* __restrict__ x, const float* __restrict__ part, int nz,
-                                                         long long zstride, const float* __restrict__ emb,
-                                                         const int* __restrict__ token, const int* __restrict__ pos,
-                                                         const float* __restrict__ gain, int d, int gs,
-                                                         int8_t* __restrict__ xq, float* __restrict__ xsT, int ldxs,
-                                                         const int* __restrict__ gather) {
+// One block per output row (up to 1024 threads, one or more float4 per thread, all loads of a thread independent):
+// x row = embedding row or x + sum of partials (written back), RMSNorm in the reference's order w * (ss * x)
+// (run.cc:196-209), group quantisation.  gs in {32, 64, 128}; d % gs == 0.
+constexpr int PREP_MAX_V = 4;   // float4 per thread kept in registers: d <= 4 * 1024 * 4
+__global__ void __launch_bounds__(1024) tc_prep_q8_kernel(float* __restrict__ x, const float* __restrict__ part, int nz,
+                                                          long long zstride, const float* __restrict__ emb,
+                                                          const int* __restrict__ token, const int* __restrict__ pos,
+                                                          const float* __restrict__ gain, int d, int gs,
+                                                          int8_t* __restrict__ xq, float* __restrict__ xsT, int ldxs,
+                                                          const int* __restrict__ gather) {
   __shared__ float red[33];
   pdl_wait();
   pdl_trigger();
   const int ob = blockIdx.x;
   const int b = gather ? gather[ob] : ob;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int d4 = d >> 2;
   float* xr = x + (size_t)b * d;
   int8_t* qr = xq + (size_t)ob * d;
   if (pos[b] < 0) {   // idle slot: zeros in, zeros out
-    for (int i = threadIdx.x; i < d; i += blockDim.x) qr[i] = 0;
+    for (int i = threadIdx.x; i < d4; i += blockDim.x) reinterpret_cast<unsigned int*>(qr)[i] = 0u;
     for (int g = threadIdx.x; g < d / gs; g += blockDim.x) xsT[(size_t)g * ldxs + ob] = 0.0f;
     return;
   }
   const float* er = emb ? emb + (size_t)token[b] * d : nullptr;
+  float4 v[PREP_MAX_V];
   float ss = 0.0f;
-  for (int i = threadIdx.x; i < d; i += blockDim.x) {   // same thread/element mapping as q8_prep_kernel: same sum order
-    float v;
-    if (er) v = er[i];
-    else {
-      v = xr[i];
-#pragma unroll 4
-      for (int z = 0; z < nz; z++) v += part[(size_t)z * zstride + (size_t)b * d + i];
+#pragma unroll
+  for (int k = 0; k < PREP_MAX_V; k++) {
+    const int i = threadIdx.x + k * blockDim.x;
+    v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < d4) {
+      if (er) v[k] = reinterpret_cast<const float4*>(er)[i];
+      else {
+        v[k] = reinterpret_cast<const float4*>(xr)[i];
+#pragma unroll 8
+        for (int z = 0; z < nz; z++) {   // fixed order
+          const float4 pz = *reinterpret_cast<const float4*>(part + (size_t)z * zstride + (size_t)b * d + 4 * i);
+          v[k].x += pz.x; v[k].y += pz.y; v[k].z += pz.z; v[k].w += pz.w;
+        }
+      }
+      if ((er || nz) && !gather) reinterpret_cast<float4*>(xr)[i] = v[k];
+      ss = dot4(v[k], v[k], ss);
     }
-    if ((er || nz) && !gather) xr[i] = v;
-    ss = fmaf(v, v, ss);
   }
   ss = block_sum(ss, red);
   ss /= d; ss += 1e-5f;
   const float ssn = 1.0f / sqrtf(ss);
-  const int npl = gs >> 5;
-  for (int g = warp; g < d / gs; g += 8) {
-    float v[4];
-    for (int j = 0; j < npl; j++) {
-      const int i = g * gs + lane + 32 * j;
-      float t;
-      if (er) t = er[i];
-      else {
-        t = xr[i];
-        if (gather || !(er || nz)) {   // x was not rewritten: redo the sum (same order, same value)
-#pragma unroll 4
-          for (int z = 0; z < nz; z++) t += part[(size_t)z * zstride + (size_t)b * d + i];
-        }
+#pragma unroll
+  for (int k = 0; k < PREP_MAX_V; k++) {
+    const int i = threadIdx.x + k * blockDim.x;
+    if (k * (int)blockDim.x < d4) {               // block-uniform: whole warps take part in the group reductions
+      const bool in = i < d4;
+      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (in) {
+        const float4 g4 = reinterpret_cast<const float4*>(gain)[i];
+        t.x = g4.x * (ssn * v[k].x); t.y = g4.y * (ssn * v[k].y); t.z = g4.z * (ssn * v[k].z); t.w = g4.w * (ssn * v[k].w);
       }
-      v[j] = gain[i] * (ssn * t);
+      q8_quant4(t, gs, i, qr, xsT, ldxs, ob, in);
     }
-    q8_group_quant(v, npl, qr, xsT, ldxs, ob, g, gs, lane);
   }
 }
 
-// Warp per group: src row (attention output), or with h > 0 the SwiGLU of the w1|w3 partials (run.cc:344-347 order),
-// quantised per group (int8 row + transposed scales).  grid (ceil(K / gs / 8), rows)
+// One float4 per thread: src row (attention output), or with h > 0 the SwiGLU of the w1|w3 partials (run.cc:344-347
+// order), quantised per group (int8 row + transposed scales).  grid (ceil(K / 4 / 256), rows)
 __global__ void __launch_bounds__(256) tc_quant_split_kernel(const float* __restrict__ src, long long ld, int nz,
                                                              long long zstride, int h, const int* __restrict__ pos, int K,
                                                              int gs, int8_t* __restrict__ oq, float* __restrict__ osT, int ldxs) {
   pdl_wait();
   pdl_trigger();
-  const int b = blockIdx.y, lane = threadIdx.x & 31;
-  const int g = blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (g >= K / gs) return;
-  const int npl = gs >> 5;
-  float v[4];
-  const bool live = pos[b] >= 0;
-  for (int j = 0; j < npl; j++) {
-    const int i = g * gs + lane + 32 * j;
-    float r = 0.0f;
-    if (live) {
-      if (h > 0) {
-        float a = 0.0f, c = 0.0f;
-#pragma unroll 4
-        for (int z = 0; z < nz; z++) {
-          a += src[(size_t)z * zstride + (size_t)b * ld + i];
-          c += src[(size_t)z * zstride + (size_t)b * ld + h + i];
-        }
-        r = a;
-        r *= (1.0f / (1.0f + expf(-r)));
-        r *= c;
-      } else {
-        r = src[(size_t)b * ld + i];
+  const int b = blockIdx.y;
+  const int i4 = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool in = 4 * i4 < K;   // K % gs == 0: a group is never cut, but a warp may be
+  float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (in && pos[b] >= 0) {
+    if (h > 0) {
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), c = a;
+#pragma unroll 8
+      for (int z = 0; z < nz; z++) {
+        const float4 pa = *reinterpret_cast<const float4*>(src + (size_t)z * zstride + (size_t)b * ld + 4 * i4);
+        const float4 pc = *reinterpret_cast<const float4*>(src + (size_t)z * zstride + (size_t)b * ld + h + 4 * i4);
+        a.x += pa.x; a.y += pa.y; a.z += pa.z; a.w += pa.w;
+        c.x += pc.x; c.y += pc.y; c.z += pc.z; c.w += pc.w;
       }
+      r.x = a.x * (1.0f / (1.0f + expf(-a.x))); r.x *= c.x;
+      r.y = a.y * (1.0f / (1.0f + expf(-a.y))); r.y *= c.y;
+      r.z = a.z * (1.0f / (1.0f + expf(-a.z))); r.z *= c.z;
+      r.w = a.w * (1.0f / (1.0f + expf(-a.w))); r.w *= c.w;
+    } else {
+      r = *reinterpret_cast<const float4*>(src + (size_t)b * ld + 4 * i4);
     }
-    v[j] = r;
   }
-  q8_group_quant(v, npl, oq + (size_t)b * K, osT, ldxs, b, g, gs, lane);
+  q8_quant4(r, gs, i4, oq + (size_t)b * K, osT, ldxs, b, in);
 }
 
 // ---- scratch ----------------------------------------------------------------------------
@@ -402,7 +412,7 @@ int step_tc_q8_prepare(Workspace* ws, const tha_config_t* c, int B) { return pre
 bool step_tc_q8_supported(const tha_config_t* c, int B, int gs) {
   if (!step_tc_supported(c, B)) return false;
   if (gs != 32 && gs != 64 && gs != 128) return false;
-  return c->dim % gs == 0 && c->hidden_dim % gs == 0 && c->dim >= 128 && c->hidden_dim >= 128;
+  return c->dim % gs == 0 && c->hidden_dim % gs == 0 && c->dim >= 128 && c->hidden_dim >= 128 && c->dim <= 16384;
 }
 
 static int gemm(cudaStream_t st, bool pdl, int n_mats, const float* const* W, const int* M, const int* off, int K,
@@ -453,13 +463,16 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
   const int* nogather = nullptr;
   const int gs = wq ? wq->group_size : 0;
   const int ldxs = ceil_div(R, 64) * 64;
+  int prep_threads = ceil_div(d / 4, 32) * 32;   // one float4 per thread where the row allows it
+  if (prep_threads > 1024) prep_threads = 1024;
+  if (prep_threads < 128) prep_threads = 128;
   // the (fused RMSNorm +) split that feeds a matmul whose input is the residual stream
   auto prep = [&](int rows, int nz, long long zs, const float* emb, const float* gain, const int* gather) -> int {
     if (wq) {
-      THA_CUDA_OK(launch(tc_prep_q8_kernel, dim3(rows), dim3(256), 0, st, pdl, io.x, (const float*)sc.part, nz, zs, emb, io.token,
+      THA_CUDA_OK(launch(tc_prep_q8_kernel, dim3(rows), dim3(prep_threads), 0, st, pdl, io.x, (const float*)sc.part, nz, zs, emb, io.token,
                          io.pos, gain, d, gs, sc.xq, sc.xsT, ldxs, gather));
     } else {
-      THA_CUDA_OK(launch(tc_prep_kernel, dim3(rows), dim3(256), 0, st, pdl, io.x, (const float*)sc.part, nz, zs, emb, io.token,
+      THA_CUDA_OK(launch(tc_prep_kernel, dim3(rows), dim3(prep_threads), 0, st, pdl, io.x, (const float*)sc.part, nz, zs, emb, io.token,
                          io.pos, gain, d, sc.xh, sc.xl, sc.scale, gather));
     }
     return THA_STATUS_SUCCESS;
@@ -506,7 +519,7 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
                                    s.value_cache + loff, kv_bs, hs, c.seq_len, pdl, wq ? nullptr : sc.xh, wq ? nullptr : sc.xl));
     }
     if (wq)   // runq.c:437: the attention output is quantised before wo
-      THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(d / gs, 8), R), dim3(256), 0, st, pdl, (const float*)io.xb, (long long)d,
+      THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(d / 4, 256), R), dim3(256), 0, st, pdl, (const float*)io.xb, (long long)d,
                          0, 0LL, 0, io.pos, d, gs, sc.xq, sc.xsT, ldxs));
     {
       const float* W[1] = {wq ? nullptr : w.wo + (size_t)l * d * d};
@@ -522,7 +535,7 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
       THA_TRY_RC(mm(2, W, Q, 0, l, M, off, d, sc.xh, sc.xl, R, sc.part, ld_h, (long long)R * ld_h, pl.z_w13, sc.scale));
     }
     if (wq)   // runq.c:457-465: SwiGLU, then quantise hb
-      THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(hd / gs, 8), R), dim3(256), 0, st, pdl, (const float*)sc.part,
+      THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(hd / 4, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part,
                          (long long)ld_h, pl.z_w13, (long long)R * ld_h, hd, io.pos, hd, gs, sc.hq, sc.hsT, ldxs));
     else
       THA_CUDA_OK(launch(tc_swiglu_split_kernel, dim3(ceil_div(hd, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part, pl.z_w13,

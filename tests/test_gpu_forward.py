@@ -193,11 +193,19 @@ def test_fp32_prefill_vs_oracle(oracle, tmp_path, name):
 
 @pytest.mark.parametrize("name", list(MODELS))
 @pytest.mark.parametrize("B", [1, 4, 9])
-def test_q8_batched_ragged_vs_oracle(oracle, tmp_path, name, B):
+@pytest.mark.parametrize("tc", [-1, 0])
+def test_q8_batched_ragged_vs_oracle(oracle, tmp_path, name, B, tc):
+    """tc = -1: the default path (int8 tensor-core matmuls); tc = 0: the dp4a GEMV step."""
+    lib = load_pkg("cabi").lib()
     cfg, w, v0, v2 = small_model_files(str(tmp_path), name, MODELS[name])
-    e = engine_from_v2(v2, B)
-    m = oracle.open(v2, quantized=True)
-    run_ragged(e, m, min(cfg.seq_len, 16), B, np.random.default_rng(B), Q8_E2E_EPS, q8=True)
+    lib.c.tha_set_option(b"tc", tc)
+    try:
+        e = engine_from_v2(v2, B)
+        m = oracle.open(v2, quantized=True)
+        run_ragged(e, m, min(cfg.seq_len, 16), B, np.random.default_rng(B), Q8_E2E_EPS, q8=True)
+        assert lib.c.tha_gemm_check_error() == 0
+    finally:
+        lib.c.tha_set_option(b"tc", -1)
 
 
 @pytest.mark.parametrize("name", list(MODELS))
