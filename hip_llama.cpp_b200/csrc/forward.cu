@@ -48,7 +48,7 @@ int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const
                     const tha_weights_q8_t* wq, const tha_state_t& s, int n_seqs, const int* slot, const int* pos0,
                     const int* len, const int* tokens, float* logits, int* next_d, const float* rc, const float* rs);
 bool step_tc_q8_supported(const tha_config_t* c, int B, int gs);
-int step_tc_q8_prepare(Workspace* ws, const tha_config_t* c, int B);
+int step_tc_q8_prepare(Workspace* ws, const tha_config_t* c, int B, int gs);
 int step_tc_q8_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_q8_t& wq,
                      const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
                      const float* rc, const float* rs, bool pdl);
@@ -335,7 +335,7 @@ int decode_step_q8(cudaStream_t st, int B, const tha_config_t* cfg, const tha_we
   // Option "tc" = 0 keeps the GEMV step.
   const int tcm = tc_mode();
   if (tcm != 0 && step_tc_q8_supported(cfg, B, gs)) {
-    THA_TRY(step_tc_q8_prepare(ws, cfg, B));
+    THA_TRY(step_tc_q8_prepare(ws, cfg, B, gs));
     a.tc = 1;   // part of the graph key
     float* lg = logits_d ? logits_d : s->logits;
     if (!lg) return THA_STATUS_INVALID_ARG;

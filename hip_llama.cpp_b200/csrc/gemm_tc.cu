@@ -622,9 +622,8 @@ struct Q8iP {
   int slots_total, slots_per_split;  // ring slots of 128 values
   float* out; long long ldo; long long zstride;
   int* error_flag;
-  int dbg;
-  long long* trace;
   int nring;                         // shared-memory ring slots in use
+  int splits, n_items;               // work items = (tiles of all matrices) x column tiles x splits
 };
 
 template <int NT>
@@ -668,40 +667,56 @@ __device__ __forceinline__ void tc_tmem_ld64(uint32_t taddr, uint32_t* v) {
                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31]), "=r"(v[32]), "=r"(v[33]), "=r"(v[34]), "=r"(v[35]), "=r"(v[36]), "=r"(v[37]), "=r"(v[38]), "=r"(v[39]), "=r"(v[40]), "=r"(v[41]), "=r"(v[42]), "=r"(v[43]), "=r"(v[44]), "=r"(v[45]), "=r"(v[46]), "=r"(v[47]), "=r"(v[48]), "=r"(v[49]), "=r"(v[50]), "=r"(v[51]), "=r"(v[52]), "=r"(v[53]), "=r"(v[54]), "=r"(v[55]), "=r"(v[56]), "=r"(v[57]), "=r"(v[58]), "=r"(v[59]), "=r"(v[60]), "=r"(v[61]), "=r"(v[62]), "=r"(v[63]) : "r"(taddr));
 }
 
+// Persistent: a CTA walks the work items (weight tile, column tile, K split) blockIdx.x, blockIdx.x + gridDim.x, ...
+// with ONE running slot counter, so the TMA ring, the MMA issuers and the epilogue flow from one item into the next
+// without draining (a fresh CTA per item paid ~3 us of ramp for ~6 us of streaming).  Every item is padded to a whole
+// number of TMEM read batches with slots past the end of K: TMA zero-fills them, their integer sums are 0 and the
+// epilogue skips their groups.
 template <int NT>
 __global__ void __launch_bounds__(Q8I_THREADS, 1)
 gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__ CUtensorMap mw1,
                 const __grid_constant__ CUtensorMap mw2, const __grid_constant__ CUtensorMap mx, const Q8iP p) {
   using S = Q8iSmem<NT>;
-  constexpr int CH = NT / 2;   // accumulator columns per epilogue thread
   extern __shared__ unsigned char tc_smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~(uintptr_t)1023);
   const int nring = p.nring;             // ring slots actually used (the activation scales take the rest)
-  float* xs_sm = reinterpret_cast<float*>(smem + nring * S::SLOT);   // [groups of this split][NT]
+  float* xs_sm = reinterpret_cast<float*>(smem + nring * S::SLOT);   // [groups of one item][NT]
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::NSLOT * S::SLOT);
   uint64_t* full = bars;                 // slot landed (W + X bytes)
-  uint64_t* mdone = full + S::NSLOT;     // the MMAs of a stage have completed: slots reusable, accumulators readable
-  uint64_t* aempty = mdone + S::NMD;     // a stage's accumulators have been read out by the 8 epilogue warps
+  uint64_t* mdone = full + S::NSLOT;     // the MMAs of a slot have completed: slot reusable, accumulators readable
+  uint64_t* aempty = mdone + S::NMD;     // a slot's accumulators have been read out by the 4 epilogue warps
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aempty + S::NACC_MAX);
   int* abort_flag = reinterpret_cast<int*>(tmem_slot + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int tile = blockIdx.x / p.ny, mat = 0;
-  if (tile >= p.tiles[0]) { tile -= p.tiles[0]; mat = 1; if (tile >= p.tiles[1]) { tile -= p.tiles[1]; mat = 2; } }
-  const CUtensorMap* mw = (mat == 0) ? &mw0 : (mat == 1 ? &mw1 : &mw2);
-  const int row0 = tile * TC_BM;
-  const int n0 = (blockIdx.x % p.ny) * NT;
-  const int slot0 = blockIdx.z * p.slots_per_split;
-  int nslots = p.slots_total - slot0;
-  if (nslots > p.slots_per_split) nslots = p.slots_per_split;
-  int nsub = p.K / 32 - slot0 * 4;               // K = 32 sub-blocks (one MMA each) of this split
-  if (nsub > nslots * 4) nsub = nslots * 4;
   const int mpg = p.gs >> 5;                     // MMAs per group
-  const int ng = (p.dbg & 8) ? 0 : nsub / mpg;   // groups of this split
   const int gps = 128 / p.gs;                    // groups per slot
-  const int gpc = gps * S::SPC;                  // groups per stage (one commit)
-  const int nacc = S::TMEM_COLS / (gpc * NT);    // accumulator stages (slots) in TMEM: 4 .. 32, a power of two
-  const int nstage = (nslots + S::SPC - 1) / S::SPC;
+  const int nacc = S::TMEM_COLS / (gps * NT);    // accumulator stages (slots) in TMEM: 4 .. 32, a power of two
+  const int nacc_sh = 31 - __clz(nacc);
+  constexpr int LG = 128 / NT;                   // groups per TMEM read (128 columns)
+  const int sb = LG / gps;                       // slots per TMEM read batch (NT <= gs: at least 1)
+  const int tiles01 = p.tiles[0] + p.tiles[1];
+
+  // work item -> (matrix, row0, n0, first slot, real slots, padded slots, real groups)
+  struct Item { int mat, row0, n0, slot0, nslots, npad, ng; };
+  auto item_of = [&](int it) -> Item {
+    Item w;
+    const int z = it % p.splits;
+    const int t = it / p.splits;
+    int tile = t / p.ny;
+    w.n0 = (t - tile * p.ny) * NT;
+    w.mat = 0;
+    if (tile >= p.tiles[0]) { w.mat = 1; if (tile >= tiles01) { w.mat = 2; tile -= tiles01; } else tile -= p.tiles[0]; }
+    w.row0 = tile * TC_BM;
+    w.slot0 = z * p.slots_per_split;
+    w.nslots = p.slots_total - w.slot0;
+    if (w.nslots > p.slots_per_split) w.nslots = p.slots_per_split;
+    w.npad = ((w.nslots + sb - 1) / sb) * sb;
+    const int g0 = w.slot0 * gps;
+    w.ng = p.ngrp - g0;
+    if (w.ng > w.nslots * gps) w.ng = w.nslots * gps;
+    return w;
+  };
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S::NSLOT; s++) tc_mbar_init(&full[s], 1);
@@ -712,7 +727,9 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   if (warp == 0 && lane == 0) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(mw) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mw0) : "memory");
+    if (p.tiles[1]) asm volatile("prefetch.tensormap [%0];" ::"l"(&mw1) : "memory");
+    if (p.tiles[2]) asm volatile("prefetch.tensormap [%0];" ::"l"(&mw2) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mx) : "memory");
   }
   if (warp == 2) {
@@ -725,157 +742,165 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
+    // ===== TMA producer
     if (lane == 0) {
       uint64_t pol_w;
       asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
-      // the first ring of weight tiles goes out before the dependency wait (transaction bytes may land before the
-      // matching expect_tx: the phase cannot complete until the arrival below)
-      const int pre = nslots < nring ? nslots : nring;
-      for (int j = 0; j < pre; j++)
-        tc_tma_2d_hint(smem + j * S::SLOT, mw, (slot0 + j) * 32, row0, &full[j], pol_w);
-      pdl_wait();
-      for (int j = 0; j < pre; j++) {
-        tc_mbar_expect_tx(&full[j], S::SLOT);
-        tc_tma_2d(smem + j * S::SLOT + S::W_BYTES, &mx, (slot0 + j) * 32, n0, &full[j]);
-      }
-      for (int j = pre; j < nslots; j++) {
-        const int s = j % nring;
-        if (p.dbg & 8) { if (!tc_mbar_wait(&full[s], ((j / nring) & 1u) ^ 1u, abort_flag)) break; }   // TMA alone
-        else {
-          const int st = j - nring;                    // the slot use whose MMAs must have completed
-          if (!tc_mbar_wait(&mdone[st % S::NMD], (st / S::NMD) & 1u, abort_flag)) break;
+      int jb = 0;                                   // running slot counter at the start of the item
+      bool ok = true;
+      for (int it = blockIdx.x; it < p.n_items && ok; it += gridDim.x) {
+        const Item w = item_of(it);
+        const CUtensorMap* mw = (w.mat == 0) ? &mw0 : (w.mat == 1 ? &mw1 : &mw2);
+        int j = 0;
+        if (jb == 0) {
+          // the first ring of weight tiles goes out before the dependency wait (transaction bytes may land before
+          // the matching expect_tx: the phase cannot complete until the arrival below)
+          const int pre = w.npad < nring ? w.npad : nring;
+          for (; j < pre; j++) tc_tma_2d_hint(smem + j * S::SLOT, mw, (w.slot0 + j) * 32, w.row0, &full[j], pol_w);
+          pdl_wait();
+          for (j = 0; j < pre; j++) {
+            tc_mbar_expect_tx(&full[j], S::SLOT);
+            tc_tma_2d(smem + j * S::SLOT + S::W_BYTES, &mx, (w.slot0 + j) * 32, w.n0, &full[j]);
+          }
         }
-        TC_TRACE(5, j);
-        tc_mbar_expect_tx(&full[s], S::SLOT);
-        TC_TRACE(0, j);
-        tc_tma_2d_hint(smem + s * S::SLOT, mw, (slot0 + j) * 32, row0, &full[s], pol_w);
-        tc_tma_2d(smem + s * S::SLOT + S::W_BYTES, &mx, (slot0 + j) * 32, n0, &full[s]);
+        for (; j < w.npad; j++) {
+          const int jg = jb + j, s = jg % nring;
+          if (jg >= nring) {
+            const int st = jg - nring;              // the slot use whose MMAs must have completed
+            if (!tc_mbar_wait(&mdone[st % S::NMD], (st / S::NMD) & 1u, abort_flag)) { ok = false; break; }
+          }
+          tc_mbar_expect_tx(&full[s], S::SLOT);
+          tc_tma_2d_hint(smem + s * S::SLOT, mw, (w.slot0 + j) * 32, w.row0, &full[s], pol_w);
+          tc_tma_2d(smem + s * S::SLOT + S::W_BYTES, &mx, (w.slot0 + j) * 32, w.n0, &full[s]);
+        }
+        jb += w.npad;
       }
     }
   } else if (warp == 1 || warp == 3) {
-    // ===== MMA issuers (warps 1 and 3): issuer i takes the slots j = i, i + 2, ...
-    if (lane == 0 && !(p.dbg & 8)) {
+    // ===== MMA issuers (warps 1 and 3): issuer i takes the slots with running index = i (mod 2)
+    if (lane == 0) {
       constexpr uint32_t idesc = q8i_idesc(NT);
       const int mpg_sh = 31 - __clz(mpg), gps_sh = 31 - __clz(gps), nacc_mask = nacc - 1;   // all powers of two
+      const int me = warp >> 1;
+      int jb = 0;
       bool ok = true;
-      for (int j = warp >> 1; j < nslots && ok; j += S::NISS) {
-        const int s = j % nring;
-        if (j >= nacc) {                          // the accumulator stage must have been drained
-          ok = tc_mbar_wait(&aempty[j & nacc_mask], ((j / nacc) & 1u) ^ 1u, abort_flag);
-          if (!ok) break;
-        }
-        if (!tc_mbar_wait(&full[s], (j / nring) & 1u, abort_flag)) break;
-        if (warp == 1) TC_TRACE(1, j);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint64_t adesc = tc_smem_desc(tc_smem_u32(smem + s * S::SLOT));
-        const uint64_t bdesc = tc_smem_desc(tc_smem_u32(smem + s * S::SLOT + S::W_BYTES));
-        const uint32_t acc0 = tmem_base + (uint32_t)(((j & nacc_mask) << gps_sh) * NT);
-        const int nsub_j = (nsub - 4 * j) < 4 ? (nsub - 4 * j) : 4;
+      for (int it = blockIdx.x; it < p.n_items && ok; it += gridDim.x) {
+        const Item w = item_of(it);
+        for (int j = (jb + me) & 1; j < w.npad; j += 2) {
+          const int jg = jb + j, s = jg % nring;
+          if (jg >= nacc) {                         // the accumulator stage must have been drained
+            if (!tc_mbar_wait(&aempty[jg & nacc_mask], ((jg >> nacc_sh) & 1u) ^ 1u, abort_flag)) { ok = false; break; }
+          }
+          if (!tc_mbar_wait(&full[s], (jg / nring) & 1u, abort_flag)) { ok = false; break; }
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint64_t adesc = tc_smem_desc(tc_smem_u32(smem + s * S::SLOT));
+          const uint64_t bdesc = tc_smem_desc(tc_smem_u32(smem + s * S::SLOT + S::W_BYTES));
+          const uint32_t acc0 = tmem_base + (uint32_t)(((jg & nacc_mask) << gps_sh) * NT);
 #pragma unroll
-        for (int sub = 0; sub < 4; sub++) {
-          if (sub < nsub_j && !(p.dbg & 1))
+          for (int sub = 0; sub < 4; sub++)       // past the end of K the tiles are zero-filled: always four MMAs
             q8i_mma(acc0 + (uint32_t)((sub >> mpg_sh) * NT), adesc + (uint64_t)(sub * 2), bdesc + (uint64_t)(sub * 2), idesc,
                     (uint32_t)((sub & (mpg - 1)) != 0));
+          tc_commit(&mdone[jg % S::NMD]);
         }
-        tc_commit(&mdone[j % S::NMD]);
-        if (warp == 1) TC_TRACE(2, j);
+        jb += w.npad;
       }
     }
   } else if (warp >= 4) {
     // ===== epilogue: thread = weight row (TMEM lane), all NT columns
     const int q = warp & 3;
     const int r = q * 32 + lane;
-    const int row = row0 + r;
-    const bool row_ok = row < p.M[mat];
-    const int g0 = (slot0 * 128) / p.gs;
-    const float* srow = p.S[mat] + (size_t)(row_ok ? row : p.M[mat] - 1) * p.ngrp + g0;
-    float acc[NT];
-#pragma unroll
-    for (int c = 0; c < NT; c++) acc[c] = 0.0f;
-    // Weight scales: this thread's row, four groups per 128-bit load, requested two to three chunks (8-12 groups,
-    // well over a thousand cycles) before their use -- with ~200 KB of the SM's memory carved out as shared, L1 keeps
-    // next to nothing and every one of these loads is an L2 round trip.
-    const bool ws_vec = ((reinterpret_cast<uintptr_t>(srow) & 15u) == 0) && (p.ngrp % 4 == 0);
-    auto load_ws4 = [&](int chunk) -> float4 {
-      const int g = 4 * chunk;
-      float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (g + 3 < ng && ws_vec) return __ldg(reinterpret_cast<const float4*>(srow + g));
-      if (g < ng) r4.x = __ldg(srow + g);
-      if (g + 1 < ng) r4.y = __ldg(srow + g + 1);
-      if (g + 2 < ng) r4.z = __ldg(srow + g + 2);
-      if (g + 3 < ng) r4.w = __ldg(srow + g + 3);
-      return r4;
-    };
-    float4 ws_cur = load_ws4(0), ws_n1 = load_ws4(1), ws_n2 = load_ws4(2);
-    pdl_trigger();
-    pdl_wait();                                   // the activation scales come from the previous kernel
-    {  // all activation scales of this CTA's K range -> shared memory (NT floats per group), once
-      const float* src = p.xsT + (size_t)g0 * p.ldxs + n0;
-      const int t = threadIdx.x - 128;            // 0..127
-      for (int i = t; i < ng * (NT / 4); i += 128) {
-        const int g = i / (NT / 4), c4 = i - g * (NT / 4);
-        reinterpret_cast<float4*>(xs_sm)[i] = __ldg(reinterpret_cast<const float4*>(src + (size_t)g * p.ldxs) + c4);
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");   // the 4 epilogue warps only
-    }
-    constexpr int LG = 128 / NT;                  // groups per TMEM read (128 columns)
-    const int sb_sh = 31 - __clz(LG) - (31 - __clz(gps));   // log2(slots per batch)
-    const int nb_mask = (nacc >> sb_sh) - 1;      // batches in the TMEM ring - 1
     const uint32_t tq = tmem_base + ((uint32_t)(q * 32) << 16);
+    const int gps_sh = 31 - __clz(gps);
+    pdl_trigger();
+    pdl_wait();                                     // the activation scales come from the previous kernel
+    int jb = 0;
     bool ok = true;
     uint32_t v[128];
-    for (int bi = 0; bi * LG < ng && ok; bi++) {
-      // the batch's slots: the last slot of each issuer covers the earlier ones (an issuer's commits complete in order)
-      const int s_first = bi << sb_sh;
-      int s_last = s_first + (1 << sb_sh) - 1;
-      if (s_last > nslots - 1) s_last = nslots - 1;
-      int w = 1;
-      if (lane == 0) {
-        w = tc_mbar_wait(&mdone[s_last % S::NMD], (s_last / S::NMD) & 1u, abort_flag) ? 1 : 0;
-        if (w && s_last > s_first) w = tc_mbar_wait(&mdone[(s_last - 1) % S::NMD], ((s_last - 1) / S::NMD) & 1u, abort_flag) ? 1 : 0;
+    for (int it = blockIdx.x; it < p.n_items && ok; it += gridDim.x) {
+      const Item w = item_of(it);
+      const int ng = w.ng;
+      const int row = w.row0 + r;
+      const bool row_ok = row < p.M[w.mat];
+      const int g0 = w.slot0 * gps;
+      const float* srow = p.S[w.mat] + (size_t)(row_ok ? row : p.M[w.mat] - 1) * p.ngrp + g0;
+      float acc[NT];
+#pragma unroll
+      for (int c = 0; c < NT; c++) acc[c] = 0.0f;
+      // Weight scales: this thread's row, four groups per 128-bit load, requested two to three chunks (8-12 groups,
+      // well over a thousand cycles) before their use -- with ~200 KB of the SM's memory carved out as shared, L1
+      // keeps next to nothing and every one of these loads is an L2 round trip.
+      const bool ws_vec = ((reinterpret_cast<uintptr_t>(srow) & 15u) == 0) && (p.ngrp % 4 == 0);
+      auto load_ws4 = [&](int chunk) -> float4 {
+        const int g = 4 * chunk;
+        float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (g + 3 < ng && ws_vec) return __ldg(reinterpret_cast<const float4*>(srow + g));
+        if (g < ng) r4.x = __ldg(srow + g);
+        if (g + 1 < ng) r4.y = __ldg(srow + g + 1);
+        if (g + 2 < ng) r4.z = __ldg(srow + g + 2);
+        if (g + 3 < ng) r4.w = __ldg(srow + g + 3);
+        return r4;
+      };
+      float4 ws_cur = load_ws4(0), ws_n1 = load_ws4(1), ws_n2 = load_ws4(2);
+      {  // the activation scales of this item's K range -> shared memory (NT floats per group)
+        asm volatile("bar.sync 1, 128;" ::: "memory");   // the 4 epilogue warps: everybody is done with the previous item's
+        const float* src = p.xsT + (size_t)g0 * p.ldxs + w.n0;
+        const int t = threadIdx.x - 128;            // 0..127
+        for (int i = t; i < ng * (NT / 4); i += 128) {
+          const int g = i / (NT / 4), c4 = i - g * (NT / 4);
+          reinterpret_cast<float4*>(xs_sm)[i] = __ldg(reinterpret_cast<const float4*>(src + (size_t)g * p.ldxs) + c4);
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
       }
-      ok = __shfl_sync(THA_FULL_MASK, w, 0) != 0;
-      if (!ok) break;
-      if (threadIdx.x == 128) TC_TRACE(3, bi);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint32_t ta = tq + (uint32_t)((bi & nb_mask) * 128);
-      tc_tmem_ld64(ta, v);
-      tc_tmem_ld64(ta + 64, v + 64);
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-      __syncwarp();
-      if (lane == 0)
-        for (int sl = s_first; sl <= s_last; sl++) tc_mbar_arrive(&aempty[sl & (nacc - 1)]);
-      if (threadIdx.x == 128) TC_TRACE(4, bi);
+      for (int bi = 0; bi * sb < w.npad && ok; bi++) {
+        // the batch's slots: the last slot of each issuer covers the earlier ones (an issuer's commits complete in order)
+        const int s_first = jb + bi * sb, s_last = s_first + sb - 1;
+        int wok = 1;
+        if (lane == 0) {
+          wok = tc_mbar_wait(&mdone[s_last % S::NMD], (s_last / S::NMD) & 1u, abort_flag) ? 1 : 0;
+          if (wok && sb > 1) wok = tc_mbar_wait(&mdone[(s_last - 1) % S::NMD], ((s_last - 1) / S::NMD) & 1u, abort_flag) ? 1 : 0;
+        }
+        ok = __shfl_sync(THA_FULL_MASK, wok, 0) != 0;
+        if (!ok) break;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t ta = tq + (uint32_t)(((s_first & (nacc - 1)) << gps_sh) * NT);
+        tc_tmem_ld64(ta, v);
+        tc_tmem_ld64(ta + 64, v + 64);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0)
+          for (int sl = s_first; sl <= s_last; sl++) tc_mbar_arrive(&aempty[sl & (nacc - 1)]);
 #pragma unroll
-      for (int b = 0; b < LG; b++) {
-        const int gi = bi * LG + b;
-        if (gi < ng) {
-          if ((gi & 3) == 0 && gi > 0) { ws_cur = ws_n1; ws_n1 = ws_n2; ws_n2 = load_ws4((gi >> 2) + 2); }
-          const int wi = gi & 3;
-          const float ws = wi == 0 ? ws_cur.x : (wi == 1 ? ws_cur.y : (wi == 2 ? ws_cur.z : ws_cur.w));
+        for (int b = 0; b < LG; b++) {
+          const int gi = bi * LG + b;
+          if (gi < ng) {
+            if ((gi & 3) == 0 && gi > 0) { ws_cur = ws_n1; ws_n1 = ws_n2; ws_n2 = load_ws4((gi >> 2) + 2); }
+            const int wi = gi & 3;
+            const float ws = wi == 0 ? ws_cur.x : (wi == 1 ? ws_cur.y : (wi == 2 ? ws_cur.z : ws_cur.w));
 #pragma unroll
-          for (int c = 0; c < NT; c += 4) {
-            const float4 t = *reinterpret_cast<const float4*>(xs_sm + gi * NT + c);   // same address in every lane: a broadcast
-            const float xs[4] = {t.x, t.y, t.z, t.w};
+            for (int c = 0; c < NT; c += 4) {
+              const float4 t = *reinterpret_cast<const float4*>(xs_sm + gi * NT + c);   // same address in every lane: a broadcast
+              const float xs[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
-            for (int e = 0; e < 4; e++) {
-              // |group sum| <= 128 * 127 * 127 < 2^22: 1.5 * 2^23 + i is exact in fp32, so this IS (float)i -- two
-              // full-rate instructions instead of a quarter-rate I2F
-              const float f = __int_as_float(0x4B400000 + (int)v[b * NT + c + e]) - 12582912.0f;
-              acc[c + e] = __fadd_rn(acc[c + e], __fmul_rn(__fmul_rn(f, ws), xs[e]));   // runq.c:334, no contraction
+              for (int e = 0; e < 4; e++) {
+                // |group sum| <= 128 * 127 * 127 < 2^22: 1.5 * 2^23 + i is exact in fp32, so this IS (float)i -- two
+                // full-rate instructions instead of a quarter-rate I2F
+                const float f = __int_as_float(0x4B400000 + (int)v[b * NT + c + e]) - 12582912.0f;
+                acc[c + e] = __fadd_rn(acc[c + e], __fmul_rn(__fmul_rn(f, ws), xs[e]));   // runq.c:334, no contraction
+              }
             }
           }
         }
       }
-    }
-    float* outz = p.out + (size_t)blockIdx.z * p.zstride + p.out_off[mat] + row;
-    if (ok && row_ok) {
+      float* outz = p.out + (size_t)(it % p.splits) * p.zstride + p.out_off[w.mat] + row;
+      if (ok && row_ok) {
 #pragma unroll
-      for (int c = 0; c < NT; c++) {
-        const int n = n0 + c;
-        if (n < p.N) outz[(size_t)n * p.ldo] = acc[c];
+        for (int c = 0; c < NT; c++) {
+          const int n = w.n0 + c;
+          if (n < p.N) outz[(size_t)n * p.ldo] = acc[c];
+        }
       }
+      jb += w.npad;
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }
@@ -885,7 +910,6 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(S::TMEM_COLS));
   }
   if (threadIdx.x == 0 && *abort_flag && p.error_flag) atomicExch(p.error_flag, 1);
-  (void)nstage;
 }
 
 bool gemm_q8i_ok(const Q8iArgs& a) {
@@ -935,17 +959,23 @@ int gemm_q8i_launch(cudaStream_t st, const Q8iArgs& a, bool pdl) {
   if (ceil_div(p.slots_total, p.slots_per_split) != splits) return THA_STATUS_INVALID_ARG;
   p.out = a.out; p.ldo = a.ldo; p.zstride = a.zstride;
   THA_TRY_RC(gemm_tc_init(&p.error_flag));
-  p.dbg = tc_env("THA_Q8I_DBG", 0);
-  p.trace = g_trace;
-  {  // the activation scales of one split sit behind the ring: [groups per split][NT] floats
+  {  // the activation scales of one item sit behind the ring: [groups per (padded) split][NT] floats
     const int slot_bytes = TC_BM * 128 + NT * 128;
     const int nslot_max = (TC_SMEM_LIMIT - 3072) / slot_bytes > 10 ? 10 : (TC_SMEM_LIMIT - 3072) / slot_bytes;
-    const int xs_bytes = p.slots_per_split * (128 / a.gs) * NT * 4;
+    const int sb = a.gs / NT;
+    const int xs_bytes = ceil_div(p.slots_per_split, sb) * sb * (128 / a.gs) * NT * 4;
     p.nring = nslot_max - ceil_div(xs_bytes, slot_bytes);
     if (p.nring < 3) return THA_STATUS_NOT_SUPPORTED;
   }
   p.ny = ceil_div(a.N, NT);
-  dim3 grid(tiles * p.ny, 1, splits);
+  p.splits = splits;
+  p.n_items = tiles * p.ny * splits;
+  int sms = 148;
+  {
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  dim3 grid(p.n_items < sms ? p.n_items : sms, 1, 1);
   switch (NT) {
     case 16: return q8i_launch_nt<16>(st, mw, mx, p, grid, pdl);
     case 32: return q8i_launch_nt<32>(st, mw, mx, p, grid, pdl);

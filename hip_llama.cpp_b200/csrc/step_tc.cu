@@ -328,8 +328,40 @@ static int pick_splits(int tiles, int K, int N, int align) {
   return best;
 }
 
-static TcPlan make_plan(const tha_config_t& c, int R, bool q8) {
-  const int al = q8 ? 4 : 1;
+// Split count for the persistent int8 matmul: 148 CTAs walk `items` = tiles x splits work items round-robin, an item
+// costs its (padded) slots plus a few slot-times of flush / restart, every extra split a little for the partial sums.
+static int pick_splits_q8(int tiles, int K, int N, int gs) {
+  const int slots = ceil_div(K, 128);
+  const int nt = gemm_q8i_pick_nt(N, gs), sb = gs / nt, ny = ceil_div(N, nt);
+  int best = 1;
+  float best_cost = 1e30f;
+  for (int z = 1; z <= 16 && z <= slots; z++) {
+    const int per = ceil_div(slots, z);
+    if (ceil_div(slots, per) != z) continue;
+    const int per_pad = ceil_div(per, sb) * sb;
+    const int items = tiles * ny * z;
+    const float cost = (float)ceil_div(items, 148) * (per_pad + 3.0f) + 0.5f * (z - 1);
+    if (cost < best_cost) { best_cost = cost; best = z; }
+  }
+  return best;
+}
+
+static TcPlan make_plan(const tha_config_t& c, int R, bool q8, int gs = 64) {
+  const int al = 1;
+  if (q8) {
+    const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads;
+    TcPlan p;
+    p.z_qkv = pick_splits_q8(ceil_div(d, 128) + 2 * ceil_div(kvd, 128), d, R, gs);
+    p.z_wo = pick_splits_q8(ceil_div(d, 128), d, R, gs);
+    p.z_w13 = pick_splits_q8(2 * ceil_div(hd, 128), d, R, gs);
+    p.z_w2 = pick_splits_q8(ceil_div(d, 128), hd, R, gs);
+    size_t m = (size_t)p.z_qkv * (d + 2 * kvd);
+    if ((size_t)p.z_wo * d > m) m = (size_t)p.z_wo * d;
+    if ((size_t)p.z_w13 * 2 * hd > m) m = (size_t)p.z_w13 * 2 * hd;
+    if ((size_t)p.z_w2 * d > m) m = (size_t)p.z_w2 * d;
+    p.part_floats = m * R;
+    return p;
+  }
   const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads;
   const int ny = ceil_div(R, gemm_tc_pick_nt(R));
   TcPlan p;
@@ -361,11 +393,11 @@ bool prefill_tc_supported(const tha_config_t* c) {
 }
 
 // Allocate / grow everything R rows need (never inside a stream capture).
-static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefill, int n_tab, bool q8) {
+static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefill, int n_tab, bool q8, int gs = 64) {
   THA_TRY_RC(gemm_tc_init(nullptr));
   std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
   TcScratch& s = g_tc_scratch[ws->device];
-  const TcPlan pl = make_plan(*c, R, q8);
+  const TcPlan pl = make_plan(*c, R, q8, gs);
   if (q8) {   // int8 rows (sized in floats: bytes / 4) and transposed scales (rows padded to the widest column tile)
     const size_t ldxs = (size_t)ceil_div(R, 64) * 64;
     THA_TRY_RC(grow(reinterpret_cast<float**>(&s.xq), &s.n_xq, ((size_t)R * c->dim + 3) / 4, ws));
@@ -406,7 +438,7 @@ static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefil
 }
 
 int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B) { return prepare_rows(ws, c, B, false, 0, false); }
-int step_tc_q8_prepare(Workspace* ws, const tha_config_t* c, int B) { return prepare_rows(ws, c, B, false, 0, true); }
+int step_tc_q8_prepare(Workspace* ws, const tha_config_t* c, int B, int gs) { return prepare_rows(ws, c, B, false, 0, true, gs); }
 
 // Q8_0 on the tensor cores: group size a multiple of the 32-value k-block (32 / 64 / 128), dims a multiple of it and >= 128.
 bool step_tc_q8_supported(const tha_config_t* c, int B, int gs) {
@@ -456,7 +488,7 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
     sc = g_tc_scratch[ws->device];
   }
   const int R = io.R;
-  const TcPlan pl = make_plan(c, R, wq != nullptr);
+  const TcPlan pl = make_plan(c, R, wq != nullptr, wq ? wq->group_size : 64);
   const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads, L = c.n_layers;
   const long long kv_bs = (long long)L * c.seq_len * kvd;
   const int ld_qkv = d + 2 * kvd, ld_h = 2 * hd;
@@ -616,7 +648,7 @@ int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const
     }
     h_last[i] = r - 1;
   }
-  THA_TRY_RC(prepare_rows(ws, &c, (int)R, true, (int)tab.size(), wq != nullptr));
+  THA_TRY_RC(prepare_rows(ws, &c, (int)R, true, (int)tab.size(), wq != nullptr, wq ? wq->group_size : 64));
   TcScratch sc;
   {
     std::lock_guard<std::mutex> lk(g_tc_scratch_mu);

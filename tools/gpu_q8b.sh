@@ -10,11 +10,11 @@ for l in sys.stdin:
     print('$1 $2 B=$3 tc=$THA_TC', round(j['value'],1),'tok/s', round(j['ms_per_step'],3),'ms frac',round(j['roofline']['frac'],3),'launches/step',j['gpu_launches']//j['steps'])
 "
 }
-for cfgs in "7b q8 1" "7b q8 8" "s110m q8 8"; do
+for cfgs in "7b q8 1" "7b q8 8" "s110m q8 1" "s110m q8 8"; do
   set -- $cfgs
   THA_TC=1 run $1 $2 $3
 done
-for cfgs in "7b q8 16" "7b q8 64" "s110m q8 64" "7b f32 64"; do
+for cfgs in "7b q8 16" "7b q8 32" "7b q8 64" "s110m q8 64" "s110m q8 256"; do
   set -- $cfgs
   THA_TC=-1 run $1 $2 $3
 done
