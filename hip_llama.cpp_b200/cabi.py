@@ -99,7 +99,6 @@ class Lib:
             "tha_prefill_supported": [C.POINTER(Config)],
             "tha_prefill_q8": [vp, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), I, vp, vp, vp, vp, vp, vp],
             "tha_matmul_q8_tc": [vp, vp, C.c_longlong, vp, vp, I, I, I, vp, vp, I, I],
-            "tha_gemm_q8_tf32x3": [vp, vp, C.c_longlong, vp, vp, I, I, I, vp, I, C.c_longlong],
             "tha_argmax_batch_f32": [vp, I, vp, I, vp],
             "tha_advance_slots": [vp, I, vp, vp, vp, I],
             "tha_malloc": [C.POINTER(vp), C.c_size_t],

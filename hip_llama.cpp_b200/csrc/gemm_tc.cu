@@ -165,7 +165,7 @@ struct TcSmem {
   static constexpr int SX = SA;
   static constexpr int SW_RAW = (TC_SMEM_LIMIT - 2048 - SX * XS_STAGE) / W_STAGE;
   static constexpr int SW = SW_RAW >= 12 ? 12 : (SW_RAW / TC_CGROUPS) * TC_CGROUPS;
-  static constexpr int NBARS = 2 * SW + 2 * SA + 1;
+  static constexpr int NBARS = 2 * SW + 2 * SA + 2;
   static constexpr int TOTAL = SW * W_STAGE + SX * XS_STAGE + 1024 /*alignment slack*/ + NBARS * 8 + 64;
   static constexpr int TMEM_COLS = 512;
   static_assert(SW >= TC_CGROUPS && SW % TC_CGROUPS == 0 && SA % TC_CGROUPS == 0, "ring / group mismatch");
@@ -173,10 +173,9 @@ struct TcSmem {
   static_assert(TOTAL <= TC_SMEM_LIMIT, "shared memory overflow");
 };
 
-// Q8 = true: the weight tile arrives as int8 ([128 rows x 128 values] per 16 KB ring slot = four k-blocks, runq.c
-// format) and the converters dequantise (value * group scale, fp32) before the same hi/lo split -- the weights cross
-// HBM at 1.0625 bytes each while the activations (already the dequantised int8 rows) and the accumulation stay fp32.
-template <int NT, bool Q8>
+// Persistent: a CTA walks the work items (weight tile, column tile, K split) blockIdx.x, blockIdx.x + gridDim.x, ...
+// with running stage counters, so the weight ring keeps streaming while the previous item's accumulator is read out.
+template <int NT>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__ CUtensorMap mw1,
                    const __grid_constant__ CUtensorMap mw2, const __grid_constant__ CUtensorMap mxh,
@@ -187,38 +186,48 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
   unsigned char* wring = smem;
   unsigned char* xring = smem + S::SW * S::W_STAGE;
   uint64_t* bars = reinterpret_cast<uint64_t*>(xring + S::SX * S::XS_STAGE);
-  uint64_t* wfull = bars;                     // W k-block landed
+  uint64_t* wfull = bars;                     // W stage landed
   uint64_t* wfree = wfull + S::SW;            // its rows are in registers: the slot may be refilled
   uint64_t* ready = wfree + S::SW;            // operand slot full: W hi/lo in TMEM (4 warps) + X hi/lo landed (TMA bytes)
   uint64_t* aempty = ready + S::SA;           // MMAs that read the operand slot have completed
-  uint64_t* accum = aempty + S::SA;           // accumulator complete
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum + 1);
+  uint64_t* accum = aempty + S::SA;           // accumulator of the current item complete
+  uint64_t* accfree = accum + 1;              // ... and read out by the 12 epilogue warps: the next item may overwrite it
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accfree + 1);
   int* abort_flag = reinterpret_cast<int*>(tmem_slot + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-  // ---- which tile
-  // blockIdx.x = tile * ny + column tile: the CTAs that share a weight tile are neighbours in launch order, so the
-  // tile comes from HBM once and from L2 for the others (activations stay L2-resident across weight tiles)
-  int tile = blockIdx.x / p.ny, mat = 0;
-  if (tile >= p.tiles[0]) { tile -= p.tiles[0]; mat = 1; if (tile >= p.tiles[1]) { tile -= p.tiles[1]; mat = 2; } }
-  const CUtensorMap* mw = (mat == 0) ? &mw0 : (mat == 1 ? &mw1 : &mw2);
-  const int row0 = tile * TC_BM;
-  const int n0 = (blockIdx.x % p.ny) * NT;
-  const int kb0 = blockIdx.z * p.kblocks_per_split;
-  int nkb = p.kblocks_total - kb0;
-  if (nkb > p.kblocks_per_split) nkb = p.kblocks_per_split;
-  const int nst = (nkb + S::KG - 1) / S::KG;   // pipeline stages of KG k-blocks (the last one may be short)
+  const int tiles01 = p.tiles[0] + p.tiles[1];
+  struct Item { int mat, row0, n0, kb0, nkb, nst; };
+  auto item_of = [&](int it) -> Item {
+    Item w;
+    const int z = it % p.splits;
+    const int t = it / p.splits;
+    int tile = t / p.ny;
+    w.n0 = (t - tile * p.ny) * NT;
+    w.mat = 0;
+    if (tile >= p.tiles[0]) { w.mat = 1; if (tile >= tiles01) { w.mat = 2; tile -= tiles01; } else tile -= p.tiles[0]; }
+    w.row0 = tile * TC_BM;
+    w.kb0 = z * p.kblocks_per_split;
+    w.nkb = p.kblocks_total - w.kb0;
+    if (w.nkb > p.kblocks_per_split) w.nkb = p.kblocks_per_split;
+    w.nst = (w.nkb + S::KG - 1) / S::KG;       // pipeline stages of KG k-blocks (the last one may be short)
+    return w;
+  };
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < S::SW; s++) { tc_mbar_init(&wfull[s], 1); tc_mbar_init(&wfree[s], Q8 ? 4 * (4 / S::KG) : 4); }
+    for (int s = 0; s < S::SW; s++) { tc_mbar_init(&wfull[s], 1); tc_mbar_init(&wfree[s], 4); }
     for (int s = 0; s < S::SA; s++) { tc_mbar_init(&ready[s], 5); tc_mbar_init(&aempty[s], 1); }
     tc_mbar_init(accum, 1);
+    tc_mbar_init(accfree, 4 * TC_CGROUPS);
     *abort_flag = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
-  if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(mw) : "memory");
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mw0) : "memory");
+    if (p.tiles[1]) asm volatile("prefetch.tensormap [%0];" ::"l"(&mw1) : "memory");
+    if (p.tiles[2]) asm volatile("prefetch.tensormap [%0];" ::"l"(&mw2) : "memory");
+  }
   if (warp == 3 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mxh) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mxl) : "memory");
@@ -241,76 +250,90 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
     if (lane == 0) {
       uint64_t pol_w;
       asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
-      if (Q8) {
-        const int nslots = (nkb + 3) >> 2;               // ring slot = 128 int8 per row = four k-blocks
-        for (int j = 0; j < nslots; j++) {
-          const int s = j % S::SW;
-          if (j >= S::SW && !tc_mbar_wait(&wfree[s], ((j / S::SW) & 1u) ^ 1u, abort_flag)) break;
-          tc_mbar_expect_tx(&wfull[s], S::W_BYTES);      // the box is always delivered whole (zero-filled past K)
-          tc_tma_2d_hint(wring + s * S::W_BYTES, mw, (kb0 + 4 * j) * (TC_BK / 4), row0, &wfull[s], pol_w);
+      int gb = 0;                                 // running stage counter at the start of the item
+      bool ok = true;
+      for (int it = blockIdx.x; it < p.n_items && ok; it += gridDim.x) {
+        const Item w = item_of(it);
+        const CUtensorMap* mw = (w.mat == 0) ? &mw0 : (w.mat == 1 ? &mw1 : &mw2);
+        for (int i = 0; i < w.nst; i++) {
+          const int g = gb + i, s = g % S::SW;
+          if (g >= S::SW && !tc_mbar_wait(&wfree[s], ((g / S::SW) & 1u) ^ 1u, abort_flag)) { ok = false; break; }
+          const int nk = (w.nkb - i * S::KG) < S::KG ? (w.nkb - i * S::KG) : S::KG;
+          tc_mbar_expect_tx(&wfull[s], nk * S::W_BYTES);
+          TC_TRACE(0, i);
+          for (int kk = 0; kk < nk; kk++)
+            tc_tma_2d_hint(wring + s * S::W_STAGE + kk * S::W_BYTES, mw, (w.kb0 + i * S::KG + kk) * TC_BK, w.row0, &wfull[s], pol_w);
         }
-      } else
-      for (int i = 0; i < nst; i++) {
-        const int s = i % S::SW;
-        if (i >= S::SW && !tc_mbar_wait(&wfree[s], ((i / S::SW) & 1u) ^ 1u, abort_flag)) break;
-        const int nk = (nkb - i * S::KG) < S::KG ? (nkb - i * S::KG) : S::KG;
-        tc_mbar_expect_tx(&wfull[s], nk * S::W_BYTES);
-        TC_TRACE(0, i);
-        for (int kk = 0; kk < nk; kk++)
-          tc_tma_2d_hint(wring + s * S::W_STAGE + kk * S::W_BYTES, mw, (kb0 + i * S::KG + kk) * TC_BK, row0, &wfull[s], pol_w);
+        gb += w.nst;
       }
     }
   } else if (warp == 3) {
     // ===== X producer (activations: written by the previous kernel)
     if (lane == 0) {
       pdl_wait();
-      for (int i = 0; i < nst; i++) {
-        const int s = i % S::SX;
-        if (i >= S::SX && !tc_mbar_wait(&aempty[s], ((i / S::SX) & 1u) ^ 1u, abort_flag)) break;
-        const int nk = (nkb - i * S::KG) < S::KG ? (nkb - i * S::KG) : S::KG;
-        TC_TRACE(1, i);
-        tc_mbar_expect_tx(&ready[s], nk * S::XS_BYTES);
-        for (int kk = 0; kk < nk; kk++) {
-          unsigned char* st = xring + s * S::XS_STAGE + kk * S::XS_BYTES;
-          tc_tma_2d(st, &mxh, (kb0 + i * S::KG + kk) * TC_BK, n0, &ready[s]);
-          tc_tma_2d(st + S::X_BYTES, &mxl, (kb0 + i * S::KG + kk) * TC_BK, n0, &ready[s]);
+      int gb = 0;
+      bool ok = true;
+      for (int it = blockIdx.x; it < p.n_items && ok; it += gridDim.x) {
+        const Item w = item_of(it);
+        for (int i = 0; i < w.nst; i++) {
+          const int g = gb + i, s = g % S::SX;
+          if (g >= S::SX && !tc_mbar_wait(&aempty[s], ((g / S::SX) & 1u) ^ 1u, abort_flag)) { ok = false; break; }
+          const int nk = (w.nkb - i * S::KG) < S::KG ? (w.nkb - i * S::KG) : S::KG;
+          TC_TRACE(1, i);
+          tc_mbar_expect_tx(&ready[s], nk * S::XS_BYTES);
+          for (int kk = 0; kk < nk; kk++) {
+            unsigned char* st = xring + s * S::XS_STAGE + kk * S::XS_BYTES;
+            tc_tma_2d(st, &mxh, (w.kb0 + i * S::KG + kk) * TC_BK, w.n0, &ready[s]);
+            tc_tma_2d(st + S::X_BYTES, &mxl, (w.kb0 + i * S::KG + kk) * TC_BK, w.n0, &ready[s]);
+          }
         }
+        gb += w.nst;
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer: A (weights, hi / lo) from TMEM, B (activations, hi / lo) from shared memory
     if (lane == 0) {
       constexpr uint32_t idesc = tc_idesc(NT), idesc2 = tc_idesc(2 * NT);
-      for (int i = 0; i < nst; i++) {
-        const int sa = i % S::SA;
-        TC_TRACE(8, i);
-        if (!tc_mbar_wait(&ready[sa], (i / S::SA) & 1u, abort_flag)) break;
-        TC_TRACE(9, i);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        TC_TRACE(5, i);
-        const int nk = (nkb - i * S::KG) < S::KG ? (nkb - i * S::KG) : S::KG;
-        // Per K = 8 step TWO MMAs instead of three: the X tile is stored [Xhi rows | Xlo rows], so one
-        // descriptor over 2*NT rows gives D[:, 0:NT] += Whi.Xhi and D[:, NT:2NT] += Whi.Xlo in a single
-        // instruction (an MMA of this shape costs ~60 cycles for any N <= 128); Wlo.Xhi then adds into the
-        // second half.  Columns [NT, 2NT) hold the small correction terms, [0, NT) the main sum.
+      int gb = 0, n_it = 0;
+      bool ok = true;
+      for (int it = blockIdx.x; it < p.n_items && ok; it += gridDim.x, n_it++) {
+        const Item w = item_of(it);
+        if (n_it > 0) {                           // the previous item's accumulator must have been read out
+          if (!tc_mbar_wait(accfree, (n_it - 1) & 1u, abort_flag)) break;
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        }
+        for (int i = 0; i < w.nst; i++) {
+          const int g = gb + i, sa = g % S::SA;
+          TC_TRACE(8, i);
+          if (!tc_mbar_wait(&ready[sa], (g / S::SA) & 1u, abort_flag)) { ok = false; break; }
+          TC_TRACE(9, i);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          TC_TRACE(5, i);
+          const int nk = (w.nkb - i * S::KG) < S::KG ? (w.nkb - i * S::KG) : S::KG;
+          // Per K = 8 step TWO MMAs instead of three: the X tile is stored [Xhi rows | Xlo rows], so one
+          // descriptor over 2*NT rows gives D[:, 0:NT] += Whi.Xhi and D[:, NT:2NT] += Whi.Xlo in a single
+          // instruction (an MMA of this shape costs ~60 cycles for any N <= 128); Wlo.Xhi then adds into the
+          // second half.  Columns [NT, 2NT) hold the small correction terms, [0, NT) the main sum.
 #pragma unroll
-        for (int kk = 0; kk < S::KG; kk++) {
-          if (kk < nk) {
-            const uint64_t xhi = tc_smem_desc(tc_smem_u32(xring + sa * S::XS_STAGE + kk * S::XS_BYTES));
-            const uint32_t ahi = tmem_a + sa * S::A_STAGE + kk * S::A_COLS, alo = ahi + TC_BK;
+          for (int kk = 0; kk < S::KG; kk++) {
+            if (kk < nk) {
+              const uint64_t xhi = tc_smem_desc(tc_smem_u32(xring + sa * S::XS_STAGE + kk * S::XS_BYTES));
+              const uint32_t ahi = tmem_a + sa * S::A_STAGE + kk * S::A_COLS, alo = ahi + TC_BK;
 #pragma unroll
-            for (int k = 0; k < TC_BK / 8; k++) {       // UMMA K = 8 tf32: 8 TMEM columns of A, 32 bytes (2 descriptor units) of B
-              const uint64_t adv = (uint64_t)(k * 2);
-              tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xhi + adv, idesc2, (uint32_t)((i | kk | k) != 0));
-              tc_mma_tf32_ts(tmem_dl, alo + 8 * k, xhi + adv, idesc, 1u);
+              for (int k = 0; k < TC_BK / 8; k++) {       // UMMA K = 8 tf32: 8 TMEM columns of A, 32 bytes (2 descriptor units) of B
+                const uint64_t adv = (uint64_t)(k * 2);
+                tc_mma_tf32_ts(tmem_d, ahi + 8 * k, xhi + adv, idesc2, (uint32_t)((i | kk | k) != 0));
+                tc_mma_tf32_ts(tmem_dl, alo + 8 * k, xhi + adv, idesc, 1u);
+              }
             }
           }
+          TC_TRACE(6, i);
+          tc_commit(&aempty[sa]);
+          TC_TRACE(7, i);
         }
-        TC_TRACE(6, i);
-        tc_commit(&aempty[sa]);
-        TC_TRACE(7, i);
+        if (ok) tc_commit(accum);
+        gb += w.nst;
       }
-      tc_commit(accum);
     }
   } else if (warp >= 4) {
     // ===== converters (shared -> hi/lo -> TMEM), then epilogue.  Thread = weight row of the tile.
@@ -318,58 +341,19 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
     const int r = q * 32 + lane;
     const int grp = (warp >> 2) - 1;                    // converter group 0..TC_CGROUPS-1
     bool ok = true;
-    // Q8: this thread's row of group scales (rows past M are zero-filled by TMA: any valid scale will do)
-    const float* srow = nullptr;
-    float sc_next[S::KG];
-    if (Q8) {
-      const int rr = (row0 + r < p.M[mat]) ? row0 + r : p.M[mat] - 1;
-      srow = p.S[mat] + (size_t)rr * p.ngrp;
-#pragma unroll
-      for (int kk = 0; kk < S::KG; kk++) {
-        const int kb = grp * S::KG + kk;
-        sc_next[kk] = (kb < nkb) ? __ldg(srow + ((kb0 + kb) * TC_BK) / p.gs) : 0.0f;
-      }
-    }
-    for (int i = grp; i < nst && ok; i += TC_CGROUPS) {
-      const int sw = Q8 ? ((i * S::KG) >> 2) % S::SW : i % S::SW, sa = i % S::SA;
-      const unsigned wpar = Q8 ? ((((i * S::KG) >> 2) / S::SW) & 1u) : ((i / S::SW) & 1u);
-      const int nk = (nkb - i * S::KG) < S::KG ? (nkb - i * S::KG) : S::KG;
-      float sc[S::KG];
-      if (Q8) {
+    int gb = 0, n_it = 0;
+    for (int it = blockIdx.x; it < p.n_items && ok; it += gridDim.x, n_it++) {
+      const Item w = item_of(it);
+      int i0 = (grp - gb % TC_CGROUPS + TC_CGROUPS) % TC_CGROUPS;   // first stage of this item with running index = grp (mod groups)
+      for (int i = i0; i < w.nst && ok; i += TC_CGROUPS) {
+        const int g = gb + i, sw = g % S::SW, sa = g % S::SA;
+        const int nk = (w.nkb - i * S::KG) < S::KG ? (w.nkb - i * S::KG) : S::KG;
+        ok = tc_mbar_wait(&wfull[sw], (g / S::SW) & 1u, abort_flag);
+        if (threadIdx.x == 128 + 128 * grp) TC_TRACE(2, i);
 #pragma unroll
         for (int kk = 0; kk < S::KG; kk++) {
-          sc[kk] = sc_next[kk];
-          const int kb = (i + TC_CGROUPS) * S::KG + kk;   // this group's next stage: the load has a whole stage to land
-          sc_next[kk] = (kb < nkb) ? __ldg(srow + ((kb0 + kb) * TC_BK) / p.gs) : 0.0f;
-        }
-      }
-      ok = tc_mbar_wait(&wfull[sw], wpar, abort_flag);
-      if (threadIdx.x == 128 + 128 * grp) TC_TRACE(2, i);
-#pragma unroll
-      for (int kk = 0; kk < S::KG; kk++) {
-        if (kk < nk) {
-          uint32_t hi[32], lo[32];
-          if (Q8) {
-            const int sub = (i * S::KG + kk) & 3;          // k-block within the slot: logical 16-byte chunks 2*sub, 2*sub+1
-            const unsigned char* wrow = wring + sw * S::W_BYTES + r * 128;
-#pragma unroll
-            for (int j = 0; j < 2; j++) {
-              const int4 v = *reinterpret_cast<const int4*>(wrow + (((2 * sub + j) ^ (r & 7)) << 4));
-              const int wv[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-              for (int e = 0; e < 4; e++) {
-                const uint32_t u = (uint32_t)wv[e] ^ 0x80808080u;   // int8 -> biased byte; 0x4B0000uu = 2^23 + uu exactly
-#pragma unroll
-                for (int b = 0; b < 4; b++) {
-                  const float f = __uint_as_float(__byte_perm(u, 0x4B000000u, 0x7650 + b)) - 8388736.0f;   // = (float)int8
-                  const float w = f * sc[kk];                       // the dequantised weight (runq.c:139-143)
-                  const float h = tc_tf32(w);
-                  hi[16 * j + 4 * e + b] = __float_as_uint(h);
-                  lo[16 * j + 4 * e + b] = __float_as_uint(w - h);
-                }
-              }
-            }
-          } else {
+          if (kk < nk) {
+            uint32_t hi[32], lo[32];
             const unsigned char* wrow = wring + sw * S::W_STAGE + kk * S::W_BYTES + r * 128;
 #pragma unroll
             for (int j = 0; j < 8; j++) {                  // logical 16-byte chunk j lives at j ^ (row & 7) (SWIZZLE_128B)
@@ -380,51 +364,56 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
               lo[4 * j + 0] = __float_as_uint(v.x - h0); lo[4 * j + 1] = __float_as_uint(v.y - h1);
               lo[4 * j + 2] = __float_as_uint(v.z - h2); lo[4 * j + 3] = __float_as_uint(v.w - h3);
             }
+            if (kk == 0 && g >= S::SA && ok) ok = tc_mbar_wait(&aempty[sa], ((g / S::SA) & 1u) ^ 1u, abort_flag);
+            if (kk == 0 && threadIdx.x == 128 + 128 * grp) TC_TRACE(3, i);
+            const uint32_t ta = tmem_a + sa * S::A_STAGE + kk * S::A_COLS + ((uint32_t)(q * 32) << 16);
+            tc_tmem_st32(ta, hi);                          // consumes every loaded value: the shared-memory reads are complete
+            tc_tmem_st32(ta + TC_BK, lo);
           }
-          if (kk == 0 && i >= S::SA && ok) ok = tc_mbar_wait(&aempty[sa], ((i / S::SA) & 1u) ^ 1u, abort_flag);
-          if (kk == 0 && threadIdx.x == 128 + 128 * grp) TC_TRACE(3, i);
-          const uint32_t ta = tmem_a + sa * S::A_STAGE + kk * S::A_COLS + ((uint32_t)(q * 32) << 16);
-          tc_tmem_st32(ta, hi);                          // consumes every loaded value: the shared-memory reads are complete
-          tc_tmem_st32(ta + TC_BK, lo);
+        }
+        __syncwarp();
+        if (lane == 0) tc_mbar_arrive(&wfree[sw]);         // the W slot can be refilled while the stores drain
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (threadIdx.x == 128 + 128 * grp) TC_TRACE(4, i);
+        if (lane == 0) tc_mbar_arrive(&ready[sa]);
+      }
+      // ---- epilogue of the item: lane = weight row within this warp's 32-lane TMEM quarter
+      if (n_it == 0) {
+        pdl_trigger();
+        pdl_wait();   // returns at once (the X producer already waited); makes the predecessor's writes visible to these threads
+      }
+      if (ok) ok = tc_mbar_wait(accum, n_it & 1u, abort_flag);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const int row = w.row0 + r;
+      const bool row_ok = row < p.M[w.mat];
+      float* outz = p.out + (size_t)(it % p.splits) * p.zstride + p.out_off[w.mat] + row;
+      if (ok) {
+#pragma unroll 1
+        for (int c = 16 * grp; c < NT; c += 16 * TC_CGROUPS) {
+          uint32_t v[16], w2[16];
+          const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c;
+          tc_tmem_ld16(taddr, v);
+          if (S::SPLIT_ACC) tc_tmem_ld16(taddr + NT, w2);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int j = 0; j < 16; j++) {
+            const int n = w.n0 + c + j;
+            if (n < p.N && row_ok) {
+              float x = __uint_as_float(v[j]);
+              if (S::SPLIT_ACC) x += __uint_as_float(w2[j]);
+              if (p.colscale) x *= p.colscale[n];
+              outz[(size_t)n * p.ldo] = x;
+            }
+          }
         }
       }
-      __syncwarp();
-      if (lane == 0) tc_mbar_arrive(&wfree[sw]);         // the W slot can be refilled while the stores drain
-      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
-      if (threadIdx.x == 128 + 128 * grp) TC_TRACE(4, i);
-      if (lane == 0) tc_mbar_arrive(&ready[sa]);
+      if (lane == 0) tc_mbar_arrive(accfree);
+      gb += w.nst;
     }
-    // ---- epilogue: lane = weight row within this warp's 32-lane TMEM quarter
-    pdl_trigger();
-    pdl_wait();   // returns at once (the X producer already waited); makes the predecessor's writes visible to these threads
-    if (ok) ok = tc_mbar_wait(accum, 0, abort_flag);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const int row = row0 + r;
-    const bool row_ok = row < p.M[mat];
-    float* outz = p.out + (size_t)blockIdx.z * p.zstride + p.out_off[mat] + row;
-    if (ok) {
-#pragma unroll 1
-      for (int c = 16 * grp; c < NT; c += 16 * TC_CGROUPS) {
-        uint32_t v[16], w[16];
-        const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c;
-        tc_tmem_ld16(taddr, v);
-        if (S::SPLIT_ACC) tc_tmem_ld16(taddr + NT, w);
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-          const int n = n0 + c + j;
-          if (n < p.N && row_ok) {
-            float x = __uint_as_float(v[j]);
-            if (S::SPLIT_ACC) x += __uint_as_float(w[j]);
-            if (p.colscale) x *= p.colscale[n];
-            outz[(size_t)n * p.ldo] = x;
-          }
-        }
-      }
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }
   __syncthreads();
   if (warp == 2) {
@@ -434,7 +423,6 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
   if (threadIdx.x == 0 && *abort_flag && p.error_flag) atomicExch(p.error_flag, 1);
 }
 
-// x -> hi = tf32(x), lo = x - hi (the activation side of the 3xTF32 split) for callers that hand in plain fp32 rows
 __global__ void split_hilo_kernel(const float* __restrict__ x, long long ldx, float* __restrict__ hi, float* __restrict__ lo, int K) {
   const int n = blockIdx.y;
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < K; k += gridDim.x * blockDim.x) {
@@ -511,28 +499,26 @@ int gemm_tc_init(int** flag_out) {
 
 bool gemm_tc_ok(const TcArgs& a) {
   if (a.K % 4 || a.ldx % 4 || a.K < TC_BK || a.N < 1) return false;
-  const bool q8 = a.Wq[0] != nullptr;
-  if (q8 && (a.gs < TC_BK || a.gs % TC_BK || a.K % a.gs || a.K < 128)) return false;   // a k-block lies inside one group
-  for (int i = 0; i < a.n_mats; i++) {
-    const void* wp = q8 ? (const void*)a.Wq[i] : (const void*)a.W[i];
-    if (!wp || (reinterpret_cast<uintptr_t>(wp) & 15u) || a.M[i] < 1 || (q8 && !a.Ws[i])) return false;
-  }
+  for (int i = 0; i < a.n_mats; i++)
+    if (!a.W[i] || (reinterpret_cast<uintptr_t>(a.W[i]) & 15u) || a.M[i] < 1) return false;
   return a.Xhi && a.Xlo && (reinterpret_cast<uintptr_t>(a.Xhi) & 15u) == 0 && (reinterpret_cast<uintptr_t>(a.Xlo) & 15u) == 0;
 }
 
-int gemm_tc_pick_nt(int N) { return N <= 16 ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128)); }   // wider N: more column tiles (grid.y)
+int gemm_tc_pick_nt(int N) { return N <= 16 ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128)); }   // wider N: more column tiles
 
-template <int NT, bool Q8>
-static int tc_launch_ntq(cudaStream_t st, const CUtensorMap* mw, const CUtensorMap& mxh, const CUtensorMap& mxl, const TcP& p, dim3 grid, bool pdl) {
+static int tc_sm_count() {
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return sms;
+}
+
+template <int NT>
+static int tc_launch_nt(cudaStream_t st, const CUtensorMap* mw, const CUtensorMap& mxh, const CUtensorMap& mxl, const TcP& p, dim3 grid, bool pdl) {
   using S = TcSmem<NT>;
-  auto k = gemm_tf32x3_kernel<NT, Q8>;
+  auto k = gemm_tf32x3_kernel<NT>;
   THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
   THA_CUDA_OK(launch(k, grid, dim3(TC_THREADS), (size_t)S::TOTAL, st, pdl, mw[0], mw[1], mw[2], mxh, mxl, p));
   return THA_STATUS_SUCCESS;
-}
-template <int NT>
-static int tc_launch_nt(cudaStream_t st, const TcArgs& a, const CUtensorMap* mw, const CUtensorMap& mxh, const CUtensorMap& mxl, const TcP& p, dim3 grid, bool pdl) {
-  return a.Wq[0] ? tc_launch_ntq<NT, true>(st, mw, mxh, mxl, p, grid, pdl) : tc_launch_ntq<NT, false>(st, mw, mxh, mxl, p, grid, pdl);
 }
 
 int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl) {
@@ -541,12 +527,9 @@ int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl) {
   CUtensorMap mw[3], mxh, mxl;
   TcP p = {};
   int tiles = 0;
-  const bool q8 = a.Wq[0] != nullptr;
-  if (q8) { p.gs = a.gs; p.ngrp = a.K / a.gs; }
   for (int i = 0; i < 3; i++) {
     if (i < a.n_mats) {
-      if (q8) { THA_TRY_RC(tc_map(a.Wq[i], a.M[i], a.K, a.K, TC_BM, &mw[i], 1)); p.S[i] = a.Ws[i]; }
-      else THA_TRY_RC(tc_map(a.W[i], a.M[i], a.K, a.K, TC_BM, &mw[i]));
+      THA_TRY_RC(tc_map(a.W[i], a.M[i], a.K, a.K, TC_BM, &mw[i]));
       p.M[i] = a.M[i]; p.tiles[i] = ceil_div(a.M[i], TC_BM); p.out_off[i] = a.out_off[i];
     } else {
       mw[i] = mw[0]; p.M[i] = 0; p.tiles[i] = 0; p.out_off[i] = 0;
@@ -559,21 +542,20 @@ int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl) {
   p.kblocks_total = ceil_div(a.K, TC_BK);
   const int splits = a.splits < 1 ? 1 : a.splits;
   p.kblocks_per_split = ceil_div(p.kblocks_total, splits);
-  if (q8) p.kblocks_per_split = (p.kblocks_per_split + 3) & ~3;   // a split starts on a ring-slot boundary (128 int8 per row)
-  const int zdim = ceil_div(p.kblocks_total, p.kblocks_per_split);
-  if (zdim != splits) return THA_STATUS_INVALID_ARG;   // caller sizes its partial buffers by `splits`
+  if (ceil_div(p.kblocks_total, p.kblocks_per_split) != splits) return THA_STATUS_INVALID_ARG;   // caller sizes its partial buffers by `splits`
   p.out = a.out; p.ldo = a.ldo; p.zstride = a.zstride; p.colscale = a.colscale;
-  p.w_hint = tc_env("THA_TC_HINT", 1);
-  p.dbg = tc_env("THA_TC_DBG", 0);
   p.trace = g_trace;
   THA_TRY_RC(gemm_tc_init(&p.error_flag));
   p.ny = ceil_div(a.N, NT);
-  dim3 grid(tiles * p.ny, 1, zdim);
+  p.splits = splits;
+  p.n_items = tiles * p.ny * splits;
+  const int sms = tc_sm_count();
+  dim3 grid(p.n_items < sms ? p.n_items : sms, 1, 1);
   switch (NT) {
-    case 16: return tc_launch_nt<16>(st, a, mw, mxh, mxl, p, grid, pdl);
-    case 32: return tc_launch_nt<32>(st, a, mw, mxh, mxl, p, grid, pdl);
-    case 64: return tc_launch_nt<64>(st, a, mw, mxh, mxl, p, grid, pdl);
-    default: return tc_launch_nt<128>(st, a, mw, mxh, mxl, p, grid, pdl);
+    case 16: return tc_launch_nt<16>(st, mw, mxh, mxl, p, grid, pdl);
+    case 32: return tc_launch_nt<32>(st, mw, mxh, mxl, p, grid, pdl);
+    case 64: return tc_launch_nt<64>(st, mw, mxh, mxl, p, grid, pdl);
+    default: return tc_launch_nt<128>(st, mw, mxh, mxl, p, grid, pdl);
   }
 }
 
@@ -997,11 +979,10 @@ using namespace tha;
 // C-ABI: out[n*ldo + row] = sum_k W[row,k] X[n,k]   (N rows of activations against one weight matrix)
 static std::map<int, std::pair<float*, size_t>> g_split_scratch;   // per device: [hi | lo]
 
-static int gemm_any(void* stream, float* out, long long ldo, const float* W, const int8_t* Wq, const float* Ws, int gs, int M,
-                    int K, const float* X, int N, long long ldx) {
-  const void* wp = Wq ? (const void*)Wq : (const void*)W;
-  if (!out || !wp || !X || M < 1 || N < 1 || K < 1 || (Wq && (!Ws || gs < 1))) return THA_STATUS_INVALID_ARG;
-  if (K % 4 || K < 32 || (reinterpret_cast<uintptr_t>(wp) & 15u)) return THA_STATUS_NOT_SUPPORTED;
+extern "C" int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const float* W, int M, int K, const float* X, int N,
+                               long long ldx) {
+  if (!out || !W || !X || M < 1 || N < 1 || K < 1) return THA_STATUS_INVALID_ARG;
+  if (K % 4 || K < 32 || (reinterpret_cast<uintptr_t>(W) & 15u)) return THA_STATUS_NOT_SUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
   int dev = 0;
   THA_CUDA_OK(cudaGetDevice(&dev));
@@ -1023,19 +1004,10 @@ static int gemm_any(void* stream, float* out, long long ldo, const float* W, con
   count_launch();
   THA_LAUNCH_OK();
   TcArgs a = {};
-  a.n_mats = 1; a.W[0] = W; a.Wq[0] = Wq; a.Ws[0] = Ws; a.gs = gs; a.M[0] = M; a.out_off[0] = 0; a.K = K; a.Xhi = hi; a.Xlo = lo;
-  a.N = N; a.ldx = K;
+  a.n_mats = 1; a.W[0] = W; a.M[0] = M; a.out_off[0] = 0; a.K = K; a.Xhi = hi; a.Xlo = lo; a.N = N; a.ldx = K;
   a.out = out; a.ldo = ldo; a.zstride = 0; a.splits = 1; a.colscale = nullptr;
   if (!gemm_tc_ok(a)) return THA_STATUS_NOT_SUPPORTED;
   return gemm_tc_launch(st, a, false);
-}
-extern "C" int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const float* W, int M, int K, const float* X, int N,
-                               long long ldx) {
-  return gemm_any(stream, out, ldo, W, nullptr, nullptr, 0, M, K, X, N, ldx);
-}
-extern "C" int tha_gemm_q8_tf32x3(void* stream, float* out, long long ldo, const int8_t* Wq, const float* Ws, int gs, int M, int K,
-                                  const float* X, int N, long long ldx) {
-  return gemm_any(stream, out, ldo, nullptr, Wq, Ws, gs, M, K, X, N, ldx);
 }
 extern "C" int tha_matmul_q8_tc(void* stream, float* out, long long ldo, const int8_t* Wq, const float* Ws, int gs, int M, int K,
                                 const int8_t* Xq, const float* XsT, int ldxs, int N) {

@@ -10,7 +10,6 @@ namespace tha {
 struct TcArgs {
   int n_mats;                 // 1..3 stacked weight matrices with the same K
   const float* W[3]; int M[3]; int out_off[3];   // rows of matrix i land at out[n*ldo + out_off[i] + row]
-  const int8_t* Wq[3]; const float* Ws[3]; int gs;   // Q8_0 weights instead of W (Wq[0] != nullptr): int8 [M, K] + scales [M, K/gs]
   int K;
   const float* Xhi; const float* Xlo; int N; long long ldx;   // activations [N, ldx] split: hi = tf32(x), lo = x - hi
   float* out; long long ldo; long long zstride;  // split z writes out + z*zstride (partials, summed by the consumer)
@@ -23,11 +22,9 @@ struct TcP {                  // kernel parameter block
   int K, N, ny, kblocks_total, kblocks_per_split;   // ny = column tiles
   float* out; long long ldo; long long zstride;
   const float* colscale;
-  const float* S[3]; int ngrp, gs;   // Q8_0: group scales of each matrix
   int* error_flag;
-  int dbg;
+  int splits, n_items;          // work items = (tiles of all matrices) x column tiles x splits, walked by persistent CTAs
   long long* trace;           // development aid (tha_gemm_trace)
-  int w_hint;                 // weight loads carry an L2 evict-first hint
 };
 
 // Q8_0 weights x Q8_0 activations on the int8 tensor cores (gemm_q8i_kernel)

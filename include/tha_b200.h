@@ -123,16 +123,12 @@ int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const float* W, int
                     long long ldx);
 /* 1 if a tensor-core matmul on the current device gave up on a pipeline barrier since the last call */
 int tha_gemm_check_error(void);
-/* Same with Q8_0 weights (int8 Wq[M,K] + scales Ws[M, K/gs], runq.c:34-37): out = dequantize(W) . X; the int8 rows are
- * dequantised inside the kernel, so the weights cross HBM at 1.0625 bytes each.  gs in {32, 64, 128}, K % gs == 0, K >= 128. */
 /* runq.c:317-342 on the INT8 tensor cores: out[n*ldo + m] = sum_g (float)(sum_{k in g} Wq[m,k] Xq[n,k]) * Ws[m,g] * XsT[g*ldxs + n],
  * groups in ascending order, no FMA contraction -- bit-identical to the reference loop.  Xq int8 [N, K]; XsT the activation
  * group scales TRANSPOSED [K/gs, ldxs] with ldxs >= N rounded up to 16/32/64 (the column tile) and a multiple of 4.
  * gs in {32, 64, 128}, K % gs == 0, K >= 128. */
 int tha_matmul_q8_tc(void* stream, float* out, long long ldo, const int8_t* Wq, const float* Ws, int gs, int M, int K,
                      const int8_t* Xq, const float* XsT, int ldxs, int N);
-int tha_gemm_q8_tf32x3(void* stream, float* out, long long ldo, const int8_t* Wq, const float* Ws, int gs, int M, int K,
-                       const float* X, int N, long long ldx);
 
 /* ---- thaDNN ops ----------------------------------------------------------------- */
 /* thaDNN_s_rmsnorm_v2_batch, src/thaDNN/thaDNN_rmsnorm.cpp:35-83; rows `dim` apart, o may alias x */

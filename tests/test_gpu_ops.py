@@ -305,28 +305,6 @@ def test_gemm_tf32x3_vs_oracle(L, oracle, M, K, N):
     assert np.abs(got - full).max() <= 5e-5 * np.abs(full).max()
 
 
-@pytest.mark.parametrize("M,K,N,gs", [(128, 128, 1, 64), (100, 192, 5, 64), (768, 768, 9, 64), (2304, 704, 33, 64),
-                                      (768, 2048, 64, 64), (4096, 768, 128, 128), (1000, 1024, 130, 32), (512, 4096, 257, 64)])
-def test_gemm_q8_tf32x3(L, M, K, N, gs):
-    """Q8_0 weights through the tensor-core matmul: the int8 rows are dequantised (value * group scale, runq.c:139-143)
-    inside the kernel; against fp64 of the same dequantised weights, within 5e-5 of the largest output."""
-    ck = load_pkg("checkpoint")
-    rng = np.random.default_rng(M + K + N)
-    w = (rng.standard_normal((M, K)).astype(np.float32) * 0.05)
-    q, sc = ck.quantize_q80(w, gs)
-    q = q.reshape(M, K); sc = sc.reshape(M, K // gs)
-    x = (rng.random((N, K), dtype=np.float32) - 0.5)
-    Q, S, X, O = tdev(q), tdev(sc), tdev(x), tdev(np.full((N, M), np.nan, np.float32))
-    sync()
-    L.check(L.c.tha_gemm_q8_tf32x3(stream_ptr(), P(O), M, P(Q), P(S), gs, M, K, P(X), N, K), "tha_gemm_q8_tf32x3")
-    sync()
-    assert L.c.tha_gemm_check_error() == 0
-    deq = q.astype(np.float64) * np.repeat(sc.astype(np.float64), gs, axis=1)
-    full = x.astype(np.float64) @ deq.T
-    got = O.cpu().numpy()
-    assert np.abs(got - full).max() <= 5e-5 * np.abs(full).max()
-
-
 @pytest.mark.parametrize("M,K,N,gs", [(128, 128, 1, 64), (100, 192, 5, 64), (768, 768, 9, 64), (2304, 704, 33, 64), (768, 2048, 64, 64),
                                       (4096, 768, 100, 128), (1000, 1024, 130, 32), (512, 4096, 70, 64), (4096, 11008, 3, 64)])
 def test_matmul_q8_int8_tensor_cores_bit_exact(L, oracle, M, K, N, gs):

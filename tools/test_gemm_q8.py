@@ -8,12 +8,7 @@ st = torch.cuda.Stream()
 def run(M, K, N, q8, reps=20):
     X = torch.randn(N, K, device="cuda")
     out = torch.zeros(N, M, device="cuda")
-    if q8:
-        Wq = torch.randint(-127, 128, (M, K), dtype=torch.int8, device="cuda")
-        Ws = torch.rand(M, K // 64, device="cuda") * 0.01
-        call = lambda: lib.tha_gemm_q8_tf32x3(st.cuda_stream, out.data_ptr(), M, Wq.data_ptr(), Ws.data_ptr(), 64, M, K, X.data_ptr(), N, K)
-        wbytes = M * K * 1.0625
-    else:
+    if True:
         W = torch.randn(M, K, device="cuda") * 0.05
         call = lambda: lib.tha_gemm_tf32x3(st.cuda_stream, out.data_ptr(), M, W.data_ptr(), M, K, X.data_ptr(), N, K)
         wbytes = M * K * 4
@@ -30,8 +25,7 @@ def run(M, K, N, q8, reps=20):
           f"{2*M*K*N/us/1e6:7.1f} TFLOP/s  {us*1e-6*1.965e9*148/nkb:7.0f} SM-cycles per tile-kblock", flush=True)
 if not os.environ.get("Q8I_SHORT"):
     for shape in [(4096, 4096, 64), (11008, 4096, 64), (4096, 11008, 64), (32000, 4096, 64), (22016, 4096, 16), (22016, 4096, 128), (22016, 4096, 2048)]:
-        for q8 in (False, True):
-            run(*shape, q8)
+        run(*shape, False)
 
 print("---- int8 tensor cores (tha_matmul_q8_tc)")
 def run_i8(M, K, N, reps=20):
