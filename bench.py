@@ -52,6 +52,8 @@ def parse_args():
     ap.add_argument("--model", default="s110m", choices=["s110m", "s15m", "7b"])
     ap.add_argument("--quant", default="f32", choices=["f32", "q8"])
     ap.add_argument("--seq-len", type=int, default=0, help="override the context length (KV slab size) of the architecture")
+    ap.add_argument("--tp", type=int, default=1, help="tensor-parallel width (= WORLD_SIZE under torchrun): ONE replica split "
+                    "over the GPUs, all-reduce fused into its consumer over NVLink peer memory (strong scaling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
@@ -175,6 +177,43 @@ def build_weights(args, device):
     return cfg, eng.DeviceWeights(cfg, w, device=device), w
 
 
+def build_tp_rank(args, device, rank, tp):
+    """This rank's shard of ONE replica split `tp` ways (hip_llama.cpp_b200/tp.py)."""
+    from pkgload import load_pkg
+    import dataclasses
+    cfg, ck = model_config(args.model)
+    eng, tpm = load_pkg("engine"), load_pkg("tp")
+    if args.seq_len:
+        cfg = dataclasses.replace(cfg, seq_len=args.seq_len)
+    q8 = args.quant == "q8"
+    host_w = None
+    if args.model == "7b":
+        dw = tpm.device_random_shard(cfg, tp, rank, q8, seed=1337, device=device)
+    else:
+        host_w = ck.random_weights(cfg, seed=1337, std=0.02)
+        if q8:
+            gs = ck.v2_group_size(cfg)
+            qt = {}
+            for n in ck.V2_QORDER:
+                t = host_w[n]
+                if n == "tok_emb":
+                    q, s = ck.quantize_q80(t, gs)
+                    qt[n] = (q.reshape(t.shape), s)
+                else:
+                    qs, ss = zip(*[ck.quantize_q80(t[l], gs) for l in range(cfg.n_layers)])
+                    qt[n] = (np.stack(qs).reshape(t.shape), np.stack(ss))
+            qt["wcls"] = qt["tok_emb"]
+            lcfg, lqt = tpm.shard_q8(cfg, gs, qt, tp, rank)
+            dw = eng.DeviceWeightsQ8(lcfg, gs, {k: host_w[k] for k in ("rms_att", "rms_ffn", "rms_final")}, lqt, device=device)
+        else:
+            lcfg, lw = tpm.shard_f32(cfg, host_w, tp, rank)
+            dw = eng.DeviceWeights(lcfg, lw, device=device)
+    e = tpm.TpRank(cfg, dw, tp, rank, args.batch, device=device)
+    # for the byte count: a config whose kv_dim is this rank's share
+    e.cfg_bytes = dataclasses.replace(cfg, n_kv_heads=cfg.n_kv_heads // tp)
+    return cfg, dw, host_w, e
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -183,12 +222,22 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     device = f"cuda:{local_rank}"
     eng = load_pkg("engine")
-    cfg, dw, host_w = build_weights(args, device)
     B, K, W = args.batch, args.steps, args.warmup
+    tp = args.tp
+    if tp > 1:
+        if world != tp:
+            raise SystemExit(f"--tp {tp} needs WORLD_SIZE == {tp} (torchrun --nproc-per-node {tp})")
+        cfg, dw, host_w, e = build_tp_rank(args, device, rank, tp)
+        e.connect_distributed()
+    else:
+        cfg, dw, host_w = build_weights(args, device)
     if W + K + 1 > cfg.seq_len:
         raise SystemExit(f"warmup+steps must stay below seq_len={cfg.seq_len}")
-    e = eng.Engine(dw, B, device=device, with_att=False)
+    if tp == 1:
+        e = eng.Engine(dw, B, device=device, with_att=False)
     wbytes = dw.nbytes()
+    if tp > 1 and not e.q8:
+        wbytes = sum(t.numel() * 4 for n, t in dw.t.items() if n not in ("wcls",))   # classifier == embedding table
     rng = np.random.default_rng(1234 + rank)
     tok0 = rng.integers(3, cfg.vocab_size, size=B).astype(np.int32)
 
@@ -206,12 +255,15 @@ def run_ours(args, rank, world, local_rank):
         logits = torch.zeros(B, cfg.vocab_size, dtype=torch.float32, device=device)
 
         def step():
-            e.decode_greedy(tok, pos, nxt, logits, stream=stream)
+            if tp > 1:
+                e.decode_step(tok, pos, logits, nxt, advance=True, stream=stream)
+            else:
+                e.decode_greedy(tok, pos, nxt, logits, stream=stream)
 
         for _ in range(W):
             step()
         stream.synchronize()
-        launches_per_step = e.last_step_launches() + (1 if e.q8 else 0)
+        launches_per_step = e.last_step_launches() + (1 if (e.q8 and tp == 1) else 0)
         sampler = ClockSampler(local_rank)
         barrier()
         if rank == 0:
@@ -226,15 +278,19 @@ def run_ours(args, rank, world, local_rank):
         clocks = sampler.stop() if rank == 0 else None
         ms = ev0.elapsed_time(ev1)
     ms_max = load_pkg("dp").max_over_ranks(ms, device)   # the job runs at the pace of its slowest rank
-    value = world * B * K / (ms_max * 1e-3)
-    # algorithmic bytes of the timed steps on this rank (positions W .. W+K-1)
-    total_bytes = sum(step_bytes(cfg, wbytes, p, B) for p in range(W, W + K))
+    value = (1 if tp > 1 else world) * B * K / (ms_max * 1e-3)
+    if tp > 1 and e.check_error():
+        raise SystemExit("tensor-parallel exchange: a wait on a peer timed out")
+    # algorithmic bytes of the timed steps on this rank (positions W .. W+K-1); under --tp: this rank's shard
+    # (its weights, the KV rows of its heads; embedding row, logits and classifier are replicated)
+    cfg_b = e.cfg_bytes if tp > 1 else cfg
+    total_bytes = sum(step_bytes(cfg_b, wbytes, p, B) for p in range(W, W + K))
     achieved = total_bytes / (ms * 1e-3) / 1e9
     peak, peak_src = measured_peak()
 
     # ---------------- e2e: the reference-facing call with HOST buffers ----------------
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and tp == 1:
         lg_host = torch.empty(B, cfg.vocab_size, dtype=torch.float32).pin_memory()
         tok_h = tok0.copy()
         pos_h = np.zeros(B, np.int32)
@@ -328,9 +384,10 @@ def base_line(args, cfg, world):
         "dtype": "f32" if args.quant == "f32" else "int8+f32", "data": "synthetic",
         "config": {
             "workload": f"{model_label(args.model)} {'fp32' if args.quant == 'f32' else 'Q8_0'} batched greedy decode, "
-                        f"{B} slots per GPU, positions {args.warmup}..{args.warmup + args.steps - 1}, "
-                        "sequences sharded over GPUs (replicated weights, no collective)",
-            "batch_per_gpu": B, "global_batch": B * world, "vocab": cfg.vocab_size, "seq_len": cfg.seq_len,
+                        f"{B} slots per {'replica' if args.tp > 1 else 'GPU'}, positions {args.warmup}..{args.warmup + args.steps - 1}, "
+                        + (f"ONE replica tensor-parallel over {args.tp} GPUs (all-reduce after wo / w2 fused into its consumer over "
+                           "NVLink peer memory)" if args.tp > 1 else "sequences sharded over GPUs (replicated weights, no collective)"),
+            "batch_per_gpu": B, "global_batch": B * (1 if args.tp > 1 else world), "parallelism": (f"tp{args.tp}" if args.tp > 1 else f"dp{world}"), "vocab": cfg.vocab_size, "seq_len": cfg.seq_len,
             "weights": "seeded random-init N(0,0.02) of the named architecture",
             "l2": "inputs larger than L2 (weights read once per step: %d MB > 126 MB L2); no flush" %
                   (0,),
@@ -374,6 +431,8 @@ def main():
     if rank == 0:
         cfg = r["cfg"]
         line = base_line(args, cfg, world)
+        if args.tp > 1:
+            line["scaling"] = "strong"
         line["config"]["l2"] = ("inputs larger than L2: %.0f MB of weights streamed once per step vs 126 MB L2; no flush"
                                 % (r["wbytes"] / 1e6)) if r["wbytes"] > 126e6 else \
             "weights (%.0f MB) fit the 126 MB L2: number is L2-assisted, not an HBM figure" % (r["wbytes"] / 1e6)

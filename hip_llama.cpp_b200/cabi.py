@@ -101,6 +101,17 @@ class Lib:
             "tha_matmul_q8_tc": [vp, vp, C.c_longlong, vp, vp, I, I, I, vp, vp, I, I],
             "tha_argmax_batch_f32": [vp, I, vp, I, vp],
             "tha_advance_slots": [vp, I, vp, vp, vp, I],
+            "tha_tp_create": [C.POINTER(vp), I, I, I, C.POINTER(C.c_int), C.c_size_t],
+            "tha_tp_export": [vp, vp],
+            "tha_tp_local_ptr": [vp, C.POINTER(vp)],
+            "tha_tp_connect_ipc": [vp, C.c_char_p],
+            "tha_tp_connect_ptr": [vp, C.POINTER(vp)],
+            "tha_tp_check_error": [vp],
+            "tha_tp_destroy": [vp],
+            "tha_tp_decode_step_f32": [vp, vp, I, C.POINTER(Config), C.POINTER(WeightsF32), C.POINTER(State), vp, vp, vp, vp, I],
+            "tha_tp_decode_step_q8": [vp, vp, I, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), vp, vp, vp, vp, I],
+            "tha_tp_prefill_f32": [vp, vp, C.POINTER(Config), C.POINTER(WeightsF32), C.POINTER(State), I, vp, vp, vp, vp, vp, vp],
+            "tha_tp_prefill_q8": [vp, vp, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), I, vp, vp, vp, vp, vp, vp],
             "tha_malloc": [C.POINTER(vp), C.c_size_t],
             "tha_free": [vp],
             "tha_stream_create": [C.POINTER(vp)],

@@ -16,6 +16,7 @@
 // dependent-launch attribute: its weight prefetch overlaps its predecessor's tail.
 #include "common.cuh"
 #include "gemv.cuh"
+#include "tp.h"
 #include "workspace.h"
 
 namespace tha {
@@ -39,19 +40,22 @@ int mega_step_launch(cudaStream_t st, Workspace* ws, int B, const tha_config_t* 
 int mega_check_abort(int dev);
 // step_tc.cu: the step with tensor-core weight matmuls (more than 8 slots)
 bool step_tc_supported(const tha_config_t* c, int B);
-int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B);
+int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B, const TpCtx* tp = nullptr);
 int step_tc_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_f32_t& w,
                   const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
-                  const float* rc, const float* rs, bool pdl);
-bool prefill_tc_supported(const tha_config_t* c);
+                  const float* rc, const float* rs, bool pdl, const TpCtx* tp = nullptr);
+bool prefill_tc_supported(const tha_config_t* c, const TpCtx* tp = nullptr);
 int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_f32_t* w32,
                     const tha_weights_q8_t* wq, const tha_state_t& s, int n_seqs, const int* slot, const int* pos0,
-                    const int* len, const int* tokens, float* logits, int* next_d, const float* rc, const float* rs);
-bool step_tc_q8_supported(const tha_config_t* c, int B, int gs);
-int step_tc_q8_prepare(Workspace* ws, const tha_config_t* c, int B, int gs);
+                    const int* len, const int* tokens, float* logits, int* next_d, const float* rc, const float* rs,
+                    const TpCtx* tp = nullptr);
+bool step_tc_q8_supported(const tha_config_t* c, int B, int gs, const TpCtx* tp = nullptr);
+bool step_tc_tp_supported(const tha_config_t* c, int B, const TpCtx* tp);
+int step_tc_q8_prepare(Workspace* ws, const tha_config_t* c, int B, int gs, const TpCtx* tp = nullptr);
 int step_tc_q8_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_q8_t& wq,
                      const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
-                     const float* rc, const float* rs, bool pdl);
+                     const float* rc, const float* rs, bool pdl, const TpCtx* tp = nullptr);
+TpCtx* tp_ctx(tha_tp_t* t);
 int gemm_tc_check_error();
 int tc_mode();   // -1 auto (B > 8), 0 never, 1 whenever the shape allows
 int advance_launch(cudaStream_t st, int B, int* token, int* pos, const int* next, int seq_len, bool pdl);
@@ -519,4 +523,87 @@ extern "C" int tha_forward_batch_q8(void* stream, int n_batches, const tha_confi
                       [&](const int* tok_d, const int* pos_d, float* target) {
                         return decode_step_q8(st, n_batches, cfg, w, s, tok_d, pos_d, target, nullptr);
                       });
+}
+
+// ---------------------------------------------------------------------------- tensor parallel ----
+// One rank's share of the decode step / prompt ingestion of a model split tp ways (tp.h).  cfg is the
+// LOCAL config (n_heads, n_kv_heads, hidden_dim = this rank's share; dim = full width), w / s hold the local shards:
+// wq [L, da, dim], wk/wv [L, kvd, dim], wo [L, dim, da], w1/w3 [L, hd, dim], w2 [L, dim, hd]; embedding, norms and
+// classifier replicated; KV cache [B][L][S][kvd] of the local heads.  Every rank must make the same sequence of calls.
+namespace tha {
+struct StepArgsTp { int B; tha_config_t cfg; tha_weights_f32_t w; tha_weights_q8_t wq; tha_state_t s;
+                    const int* token_d; const int* pos_d; float* logits_d; int* next_d; int pdl; int q8; int advance; const void* tp; };
+
+static int tp_decode(cudaStream_t st, TpCtx* tp, int B, const tha_config_t* cfg, const tha_weights_f32_t* w,
+                     const tha_weights_q8_t* wq, const tha_state_t* s, int* token_d, int* pos_d, float* logits_d,
+                     int* next_d, int advance) {
+  if (!tp || B <= 0 || !cfg || (!w && !wq) || !s || !token_d || !pos_d || (!logits_d && !s->logits)) return THA_STATUS_INVALID_ARG;
+  if (advance && !next_d) return THA_STATUS_INVALID_ARG;
+  if (!s->x || !s->xb || !s->q || !s->key_cache || !s->value_cache) return THA_STATUS_INVALID_ARG;
+  if (wq ? !step_tc_q8_supported(cfg, B, wq->group_size, tp) : !step_tc_tp_supported(cfg, B, tp)) return THA_STATUS_NOT_SUPPORTED;
+  int dev = -1;
+  THA_CUDA_OK(cudaGetDevice(&dev));
+  if (dev != tp->device) return THA_STATUS_INVALID_ARG;
+  Workspace* ws = &tp->ws;
+  const float *rc, *rs;
+  THA_TRY(ws_rope(ws, tp->head_size, cfg->seq_len, &rc, &rs));
+  if (wq) THA_TRY(step_tc_q8_prepare(ws, cfg, B, wq->group_size, tp));
+  else THA_TRY(step_tc_prepare(ws, cfg, B, tp));
+  StepArgsTp a;
+  memset(&a, 0, sizeof(a));
+  a.B = B; a.cfg = *cfg; if (w) a.w = *w; if (wq) a.wq = *wq; a.s = *s; a.token_d = token_d; a.pos_d = pos_d;
+  a.logits_d = logits_d; a.next_d = next_d; a.pdl = pdl_enabled(); a.q8 = wq != nullptr; a.advance = advance; a.tp = tp;
+  float* lg = logits_d ? logits_d : s->logits;
+  return run_step(st, ws, &a, sizeof(a), [&]() {
+    if (wq) THA_TRY(step_tc_q8_issue(st, ws, B, *cfg, *wq, *s, token_d, pos_d, lg, next_d, rc, rs, a.pdl != 0, tp));
+    else THA_TRY(step_tc_issue(st, ws, B, *cfg, *w, *s, token_d, pos_d, lg, next_d, rc, rs, a.pdl != 0, tp));
+    if (advance) THA_TRY(advance_launch(st, B, token_d, pos_d, next_d, cfg->seq_len, a.pdl != 0));
+    return (int)THA_STATUS_SUCCESS;
+  });
+}
+}  // namespace tha
+
+extern "C" int tha_tp_decode_step_f32(void* stream, tha_tp_t* tp, int n_batches, const tha_config_t* cfg_local,
+                                      const tha_weights_f32_t* w_local, const tha_state_t* s_local, int* token_d, int* pos_d,
+                                      float* logits_d, int* next_d, int advance) {
+  return tp_decode((cudaStream_t)stream, tp_ctx(tp), n_batches, cfg_local, w_local, nullptr, s_local, token_d, pos_d, logits_d,
+                   next_d, advance);
+}
+
+extern "C" int tha_tp_decode_step_q8(void* stream, tha_tp_t* tp, int n_batches, const tha_config_t* cfg_local,
+                                     const tha_weights_q8_t* w_local, const tha_state_t* s_local, int* token_d, int* pos_d,
+                                     float* logits_d, int* next_d, int advance) {
+  return tp_decode((cudaStream_t)stream, tp_ctx(tp), n_batches, cfg_local, nullptr, w_local, s_local, token_d, pos_d, logits_d,
+                   next_d, advance);
+}
+
+static int tp_prefill(cudaStream_t st, TpCtx* tp, const tha_config_t* cfg, const tha_weights_f32_t* w, const tha_weights_q8_t* wq,
+                      const tha_state_t* s, int n_seqs, const int* slot_host, const int* pos0_host, const int* len_host,
+                      const int* tokens_host, float* logits_d, int* next_d) {
+  if (!tp || !cfg || (!w && !wq) || !s || n_seqs < 1 || !slot_host || !pos0_host || !len_host || !tokens_host ||
+      !s->key_cache || !s->value_cache)
+    return THA_STATUS_INVALID_ARG;
+  if (!prefill_tc_supported(cfg, tp)) return THA_STATUS_NOT_SUPPORTED;
+  Workspace* ws = &tp->ws;
+  const float *rc, *rs;
+  THA_TRY(ws_rope(ws, tp->head_size, cfg->seq_len, &rc, &rs));
+  launches_reset();
+  const int rcode = step_tc_prefill(st, ws, *cfg, w, wq, *s, n_seqs, slot_host, pos0_host, len_host, tokens_host, logits_d,
+                                    next_d, rc, rs, tp);
+  last_step_launches_set(launches_get());
+  return rcode;
+}
+
+extern "C" int tha_tp_prefill_f32(void* stream, tha_tp_t* tp, const tha_config_t* cfg_local, const tha_weights_f32_t* w_local,
+                                  const tha_state_t* s_local, int n_seqs, const int* slot_host, const int* pos0_host,
+                                  const int* len_host, const int* tokens_host, float* logits_d, int* next_d) {
+  return tp_prefill((cudaStream_t)stream, tp_ctx(tp), cfg_local, w_local, nullptr, s_local, n_seqs, slot_host, pos0_host,
+                    len_host, tokens_host, logits_d, next_d);
+}
+
+extern "C" int tha_tp_prefill_q8(void* stream, tha_tp_t* tp, const tha_config_t* cfg_local, const tha_weights_q8_t* w_local,
+                                 const tha_state_t* s_local, int n_seqs, const int* slot_host, const int* pos0_host,
+                                 const int* len_host, const int* tokens_host, float* logits_d, int* next_d) {
+  return tp_prefill((cudaStream_t)stream, tp_ctx(tp), cfg_local, nullptr, w_local, s_local, n_seqs, slot_host, pos0_host,
+                    len_host, tokens_host, logits_d, next_d);
 }

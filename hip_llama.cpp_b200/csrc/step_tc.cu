@@ -26,6 +26,7 @@
 
 #include "common.cuh"
 #include "gemm_tc.h"
+#include "tp.h"
 #include "workspace.h"
 
 namespace tha {
@@ -45,6 +46,53 @@ int attn_prefill_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_
 
 __device__ __forceinline__ float st_tf32(float v) { return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u); }
 
+// ---- tensor-parallel exchange (tp.h) -------------------------------------------------------------------------------
+// The consumer of a wo / w2 matmul reads every rank's partials.  Before it does, block 0 tells every rank "my partials
+// of exchange e are in place" (the matmul before this kernel has completed: pdl_wait / stream order), and every block
+// waits until all ranks have said so.  Flags only grow (e = step epoch * exchanges per step + k + 1), nothing is reset.
+// Two exchange buffers alternate (wo -> 0, w2 -> 1): a rank can only overwrite buffer 0 of layer l+1 after it passed the
+// w2 exchange of layer l, which every rank signals after it finished reading buffer 0 of layer l.
+constexpr long long TP_TIMEOUT_CYCLES = 40000000000ll;   // ~20 s: a lost peer ends in an error flag, not a hang
+__device__ __forceinline__ void tp_wait_peers(const TpPeers& t) {
+  const unsigned e = *t.epoch * (unsigned)t.nx + (unsigned)t.k + 1u;
+  if (blockIdx.x == 0 && (int)threadIdx.x < t.n) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(t.peer_flags[threadIdx.x] + t.rank), "r"(e) : "memory");
+  }
+  if ((int)threadIdx.x < t.n) {
+    const unsigned* f = t.peer_flags[t.rank] + threadIdx.x;
+    const long long t0 = clock64();
+    for (;;) {
+      unsigned v;
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+      if ((int)(v - e) >= 0) break;
+      if (clock64() - t0 > TP_TIMEOUT_CYCLES) { *t.err = 1; break; }
+    }
+  }
+  __syncthreads();
+}
+// partials may live in a peer's HBM: system-scope load, never served from a stale line
+__device__ __forceinline__ float4 ld_peer4(const float* p) {
+  float4 r;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+  return r;
+}
+// x += every rank's partials, ranks in ascending order, splits in ascending order (identical on every rank)
+__device__ __forceinline__ void tp_add_partials(float4& v, const TpPeers& t, long long zstride, size_t off) {
+  for (int r = 0; r < t.n; r++) {
+#pragma unroll 4
+    for (int z = 0; z < t.nz[r]; z++) {
+      const float4 pz = ld_peer4(t.part[r] + (size_t)z * zstride + off);
+      v.x += pz.x; v.y += pz.y; v.z += pz.z; v.w += pz.w;
+    }
+  }
+}
+__global__ void tp_epoch_kernel(unsigned* epoch) {
+  pdl_wait();
+  pdl_trigger();
+  if (threadIdx.x == 0) *epoch += 1u;
+}
+
 // One block per output row.  x row: embedding row (emb != nullptr) or x + sum of nz partials.  With `gather`
 // output row r is computed from source row gather[r] (the classifier input of a prefill chunk: the last
 // row of every sequence) and x is left untouched.
@@ -53,10 +101,11 @@ __global__ void __launch_bounds__(1024) tc_prep_kernel(float* __restrict__ x, co
                                                       const int* __restrict__ token, const int* __restrict__ pos,
                                                       const float* __restrict__ gain, int d, float* __restrict__ xh,
                                                       float* __restrict__ xl, float* __restrict__ scale,
-                                                      const int* __restrict__ gather) {
+                                                      const int* __restrict__ gather, const TpPeers tp) {
   __shared__ float red[33];
   pdl_wait();
   pdl_trigger();
+  if (tp.n && !emb) tp_wait_peers(tp);
   const int ob = blockIdx.x;
   const int b = gather ? gather[ob] : ob;
   const int d4 = d >> 2;
@@ -75,10 +124,13 @@ __global__ void __launch_bounds__(1024) tc_prep_kernel(float* __restrict__ x, co
     if (er) v = er[i];
     else {
       v = xr[i];
+      if (tp.n) tp_add_partials(v, tp, zstride, (size_t)b * d + 4 * i);
+      else {
 #pragma unroll 4
-      for (int z = 0; z < nz; z++) {   // fixed order; unrolled so the loads of several partials are in flight together
-        const float4 pz = *reinterpret_cast<const float4*>(part + (size_t)z * zstride + (size_t)b * d + 4 * i);
-        v.x += pz.x; v.y += pz.y; v.z += pz.z; v.w += pz.w;
+        for (int z = 0; z < nz; z++) {   // fixed order; unrolled so the loads of several partials are in flight together
+          const float4 pz = *reinterpret_cast<const float4*>(part + (size_t)z * zstride + (size_t)b * d + 4 * i);
+          v.x += pz.x; v.y += pz.y; v.z += pz.z; v.w += pz.w;
+        }
       }
     }
     if ((er || nz) && !gather) xr[i] = v;
@@ -196,10 +248,11 @@ __global__ void __launch_bounds__(1024) tc_prep_q8_kernel(float* __restrict__ x,
                                                           const int* __restrict__ token, const int* __restrict__ pos,
                                                           const float* __restrict__ gain, int d, int gs,
                                                           int8_t* __restrict__ xq, float* __restrict__ xsT, int ldxs,
-                                                          const int* __restrict__ gather) {
+                                                          const int* __restrict__ gather, const TpPeers tp) {
   __shared__ float red[33];
   pdl_wait();
   pdl_trigger();
+  if (tp.n && !emb) tp_wait_peers(tp);
   const int ob = blockIdx.x;
   const int b = gather ? gather[ob] : ob;
   const int d4 = d >> 2;
@@ -221,10 +274,13 @@ __global__ void __launch_bounds__(1024) tc_prep_q8_kernel(float* __restrict__ x,
       if (er) v[k] = reinterpret_cast<const float4*>(er)[i];
       else {
         v[k] = reinterpret_cast<const float4*>(xr)[i];
+        if (tp.n) tp_add_partials(v[k], tp, zstride, (size_t)b * d + 4 * i);
+        else {
 #pragma unroll 8
-        for (int z = 0; z < nz; z++) {   // fixed order
-          const float4 pz = *reinterpret_cast<const float4*>(part + (size_t)z * zstride + (size_t)b * d + 4 * i);
-          v[k].x += pz.x; v[k].y += pz.y; v[k].z += pz.z; v[k].w += pz.w;
+          for (int z = 0; z < nz; z++) {   // fixed order
+            const float4 pz = *reinterpret_cast<const float4*>(part + (size_t)z * zstride + (size_t)b * d + 4 * i);
+            v[k].x += pz.x; v[k].y += pz.y; v[k].z += pz.z; v[k].w += pz.w;
+          }
         }
       }
       if ((er || nz) && !gather) reinterpret_cast<float4*>(xr)[i] = v[k];
@@ -291,7 +347,7 @@ struct TcScratch {
   size_t n_xq = 0, n_hq = 0, n_xsT = 0, n_hsT = 0;
   size_t n_x = 0, n_xl = 0, n_h = 0, n_hl = 0, n_part = 0, n_xr = 0, n_qr = 0, n_xbr = 0, n_tab = 0; int n_b = 0;
 };
-static std::map<int, TcScratch> g_tc_scratch;
+static std::map<Workspace*, TcScratch> g_tc_scratch;   // per workspace (= per device, or per tensor-parallel rank)
 static std::mutex g_tc_scratch_mu;
 
 static int grow(float** p, size_t* cap, size_t need, Workspace* ws) {
@@ -346,58 +402,61 @@ static int pick_splits_q8(int tiles, int K, int N, int gs) {
   return best;
 }
 
-static TcPlan make_plan(const tha_config_t& c, int R, bool q8, int gs = 64) {
-  const int al = 1;
-  if (q8) {
-    const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads;
-    TcPlan p;
-    p.z_qkv = pick_splits_q8(ceil_div(d, 128) + 2 * ceil_div(kvd, 128), d, R, gs);
-    p.z_wo = pick_splits_q8(ceil_div(d, 128), d, R, gs);
-    p.z_w13 = pick_splits_q8(2 * ceil_div(hd, 128), d, R, gs);
-    p.z_w2 = pick_splits_q8(ceil_div(d, 128), hd, R, gs);
-    size_t m = (size_t)p.z_qkv * (d + 2 * kvd);
-    if ((size_t)p.z_wo * d > m) m = (size_t)p.z_wo * d;
-    if ((size_t)p.z_w13 * 2 * hd > m) m = (size_t)p.z_w13 * 2 * hd;
-    if ((size_t)p.z_w2 * d > m) m = (size_t)p.z_w2 * d;
-    p.part_floats = m * R;
-    return p;
-  }
-  const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads;
-  const int ny = ceil_div(R, gemm_tc_pick_nt(R));
+// Local shapes of the pipeline: d = residual width; da = attention width (heads on this rank x head size), kvd, hd =
+// this rank's share under tensor parallelism (da == d, hd == hidden_dim without it).
+struct Dims { int d, da, kvd, hd, hs; };
+static Dims dims_of(const tha_config_t& c, const TpCtx* tp) {
+  Dims m;
+  m.d = c.dim; m.hs = tp ? tp->head_size : c.dim / c.n_heads;
+  m.da = m.hs * c.n_heads; m.kvd = m.hs * c.n_kv_heads; m.hd = c.hidden_dim;
+  return m;
+}
+
+static int plan_z(int tiles, int K, int R, bool q8, int gs) {
+  if (q8) return pick_splits_q8(tiles, K, R, gs);
+  return pick_splits(tiles * ceil_div(R, gemm_tc_pick_nt(R)), K, R, 1);
+}
+
+static TcPlan make_plan(const Dims& m, int R, bool q8, int gs = 64) {
+  const int d = m.d, da = m.da, hd = m.hd, kvd = m.kvd;
   TcPlan p;
-  p.z_qkv = pick_splits((ceil_div(d, 128) + 2 * ceil_div(kvd, 128)) * ny, d, R, al);
-  p.z_wo = pick_splits(ceil_div(d, 128) * ny, d, R, al);
-  p.z_w13 = pick_splits(2 * ceil_div(hd, 128) * ny, d, R, al);
-  p.z_w2 = pick_splits(ceil_div(d, 128) * ny, hd, R, al);
-  size_t m = (size_t)p.z_qkv * (d + 2 * kvd);
-  if ((size_t)p.z_wo * d > m) m = (size_t)p.z_wo * d;
-  if ((size_t)p.z_w13 * 2 * hd > m) m = (size_t)p.z_w13 * 2 * hd;
-  if ((size_t)p.z_w2 * d > m) m = (size_t)p.z_w2 * d;
-  p.part_floats = m * R;
+  p.z_qkv = plan_z(ceil_div(da, 128) + 2 * ceil_div(kvd, 128), d, R, q8, gs);
+  p.z_wo = plan_z(ceil_div(d, 128), da, R, q8, gs);
+  p.z_w13 = plan_z(2 * ceil_div(hd, 128), d, R, q8, gs);
+  p.z_w2 = plan_z(ceil_div(d, 128), hd, R, q8, gs);
+  size_t m_ = (size_t)p.z_qkv * (da + 2 * kvd);
+  if ((size_t)p.z_wo * d > m_) m_ = (size_t)p.z_wo * d;
+  if ((size_t)p.z_w13 * 2 * hd > m_) m_ = (size_t)p.z_w13 * 2 * hd;
+  if ((size_t)p.z_w2 * d > m_) m_ = (size_t)p.z_w2 * d;
+  p.part_floats = m_ * R;
   return p;
 }
 
-bool step_tc_supported(const tha_config_t* c, int B) {
+static bool rows_supported(const tha_config_t* c, int B, const TpCtx* tp) {
   if (B < 1) return false;
   const int d = c->dim, hd = c->hidden_dim;
-  if (d % c->n_heads || c->n_heads % c->n_kv_heads) return false;
-  const int hs = d / c->n_heads, kvd = hs * c->n_kv_heads;
-  if (d % 4 || hd % 4 || kvd % 4 || (hs & 1) || d < 32 || hd < 32) return false;
-  return attn_fused_supported(c->n_heads, hs, d, kvd);
+  if (c->n_heads < 1 || c->n_kv_heads < 1 || c->n_heads % c->n_kv_heads) return false;
+  if (!tp && d % c->n_heads) return false;
+  const int hs = tp ? tp->head_size : d / c->n_heads, kvd = hs * c->n_kv_heads, da = hs * c->n_heads;
+  if (d % 4 || hd % 4 || kvd % 4 || da % 4 || (hs & 1) || d < 32 || hd < 32 || da < 32) return false;
+  return attn_fused_supported(c->n_heads, hs, da, kvd);
 }
+bool step_tc_supported(const tha_config_t* c, int B) { return rows_supported(c, B, nullptr); }
 
-bool prefill_tc_supported(const tha_config_t* c) {
-  if (!step_tc_supported(c, 1)) return false;
-  const int hs = c->dim / c->n_heads;
+bool prefill_tc_supported(const tha_config_t* c, const TpCtx* tp) {
+  if (!rows_supported(c, 1, tp)) return false;
+  const int hs = tp ? tp->head_size : c->dim / c->n_heads;
   return attn_prefill_supported(hs, hs * c->n_kv_heads);
 }
 
 // Allocate / grow everything R rows need (never inside a stream capture).
-static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefill, int n_tab, bool q8, int gs = 64) {
+static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefill, int n_tab, bool q8, int gs = 64,
+                        const TpCtx* tp = nullptr) {
   THA_TRY_RC(gemm_tc_init(nullptr));
   std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
-  TcScratch& s = g_tc_scratch[ws->device];
-  const TcPlan pl = make_plan(*c, R, q8, gs);
+  TcScratch& s = g_tc_scratch[ws];
+  const Dims dm = dims_of(*c, tp);
+  const TcPlan pl = make_plan(dm, R, q8, gs);
   if (q8) {   // int8 rows (sized in floats: bytes / 4) and transposed scales (rows padded to the widest column tile)
     const size_t ldxs = (size_t)ceil_div(R, 64) * 64;
     THA_TRY_RC(grow(reinterpret_cast<float**>(&s.xq), &s.n_xq, ((size_t)R * c->dim + 3) / 4, ws));
@@ -428,24 +487,27 @@ static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefil
     }
     return THA_STATUS_SUCCESS;
   }
-  const int hs = c->dim / c->n_heads;
+  const int hs = dm.hs;
   int J = 8;
-  for (; J >= 1; J--) if ((128 * J) % hs == 0 && c->dim % (128 * J) == 0) break;
-  const int nseg = c->dim / (128 * J);
+  for (; J >= 1; J--) if ((128 * J) % hs == 0 && dm.da % (128 * J) == 0) break;
+  const int nseg = dm.da / (128 * J);
   const int nsplit = attn_fused_nsplit(R, nseg, c->seq_len);
   if (nsplit > 1) THA_TRY_RC(ws_ensure_attn(ws, (size_t)R * nseg * nsplit * 32 * J, R * nseg));
   return THA_STATUS_SUCCESS;
 }
 
-int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B) { return prepare_rows(ws, c, B, false, 0, false); }
-int step_tc_q8_prepare(Workspace* ws, const tha_config_t* c, int B, int gs) { return prepare_rows(ws, c, B, false, 0, true, gs); }
+int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B, const TpCtx* tp) { return prepare_rows(ws, c, B, false, 0, false, 64, tp); }
+int step_tc_q8_prepare(Workspace* ws, const tha_config_t* c, int B, int gs, const TpCtx* tp) { return prepare_rows(ws, c, B, false, 0, true, gs, tp); }
 
 // Q8_0 on the tensor cores: group size a multiple of the 32-value k-block (32 / 64 / 128), dims a multiple of it and >= 128.
-bool step_tc_q8_supported(const tha_config_t* c, int B, int gs) {
-  if (!step_tc_supported(c, B)) return false;
+bool step_tc_q8_supported(const tha_config_t* c, int B, int gs, const TpCtx* tp) {
+  if (!rows_supported(c, B, tp)) return false;
   if (gs != 32 && gs != 64 && gs != 128) return false;
-  return c->dim % gs == 0 && c->hidden_dim % gs == 0 && c->dim >= 128 && c->hidden_dim >= 128 && c->dim <= 16384;
+  const int da = tp ? tp->head_size * c->n_heads : c->dim;
+  return c->dim % gs == 0 && c->hidden_dim % gs == 0 && da % gs == 0 && c->dim >= 128 && c->hidden_dim >= 128 && da >= 128 &&
+         c->dim <= 16384;
 }
+bool step_tc_tp_supported(const tha_config_t* c, int B, const TpCtx* tp) { return rows_supported(c, B, tp); }
 
 static int gemm(cudaStream_t st, bool pdl, int n_mats, const float* const* W, const int* M, const int* off, int K,
                 const float* xh, const float* xl, int N, float* out, long long ldo, long long zstride, int splits,
@@ -479,46 +541,77 @@ struct RowsIO {
 };
 
 // `wq` != nullptr: Q8_0 weights (then `w` only lends its embedding table and norm gains).
+// `tp` != nullptr: this rank's share of a tensor-parallel model (c = the LOCAL config: n_heads, n_kv_heads, hidden_dim
+// are this rank's; dim is the full residual width): the wo / w2 partials go to the exchange buffers and their consumer
+// sums every rank's (tp.h).
 static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_f32_t& w,
                       const tha_weights_q8_t* wq, const tha_state_t& s, const RowsIO& io, const float* rc, const float* rs,
-                      bool pdl) {
+                      bool pdl, const TpCtx* tp = nullptr) {
   TcScratch sc;
   {
     std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
-    sc = g_tc_scratch[ws->device];
+    sc = g_tc_scratch[ws];
   }
   const int R = io.R;
-  const TcPlan pl = make_plan(c, R, wq != nullptr, wq ? wq->group_size : 64);
-  const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads, L = c.n_layers;
-  const long long kv_bs = (long long)L * c.seq_len * kvd;
-  const int ld_qkv = d + 2 * kvd, ld_h = 2 * hd;
-  const int* nogather = nullptr;
+  const bool q8 = wq != nullptr;
   const int gs = wq ? wq->group_size : 0;
+  const Dims dm = dims_of(c, tp);
+  const TcPlan pl = make_plan(dm, R, q8, q8 ? gs : 64);
+  const int d = dm.d, da = dm.da, hd = dm.hd, hs = dm.hs, kvd = dm.kvd, L = c.n_layers;
+  const long long kv_bs = (long long)L * c.seq_len * kvd;
+  const int ld_qkv = da + 2 * kvd, ld_h = 2 * hd;
+  const int* nogather = nullptr;
   const int ldxs = ceil_div(R, 64) * 64;
   int prep_threads = ceil_div(d / 4, 32) * 32;   // one float4 per thread where the row allows it
   if (prep_threads > 1024) prep_threads = 1024;
   if (prep_threads < 128) prep_threads = 128;
+  // tensor parallelism: split counts of every rank's w2 (local hidden sizes may differ), exchange bookkeeping
+  int z_w2_of[TP_MAX] = {0};
+  const bool tpx = tp && tp->tp > 1;
+  if (tpx) {
+    size_t need = (size_t)pl.z_wo * R * d;
+    for (int r = 0; r < tp->tp; r++) {
+      z_w2_of[r] = plan_z(ceil_div(d, 128), tp->hidden_of[r], R, q8, q8 ? gs : 64);
+      if ((size_t)z_w2_of[r] * R * d > need) need = (size_t)z_w2_of[r] * R * d;
+    }
+    if (need > tp->xchg_floats || !tp->connected || tp->hidden_of[tp->rank] != hd) return THA_STATUS_INVALID_ARG;
+  }
+  int xk = 0;   // exchanges issued so far in this step
+  auto peers_of = [&](int which, bool w2) -> TpPeers {
+    TpPeers t = {};
+    if (!tpx) return t;
+    t.n = tp->tp; t.rank = tp->rank; t.k = xk++; t.nx = 2 * L;
+    for (int r = 0; r < tp->tp; r++) {
+      t.part[r] = tp->xchg(r, which);
+      t.nz[r] = w2 ? z_w2_of[r] : pl.z_wo;
+      t.peer_flags[r] = tp->flags(r);
+    }
+    t.epoch = tp->epoch(); t.err = tp->err();
+    return t;
+  };
+  float* out_wo = tpx ? tp->xchg(tp->rank, 0) : sc.part;
+  float* out_w2 = tpx ? tp->xchg(tp->rank, 1) : sc.part;
   // the (fused RMSNorm +) split that feeds a matmul whose input is the residual stream
-  auto prep = [&](int rows, int nz, long long zs, const float* emb, const float* gain, const int* gather) -> int {
+  auto prep = [&](int rows, const float* part, int nz, long long zs, const float* emb, const float* gain, const int* gather,
+                  const TpPeers& tpp) -> int {
     if (wq) {
-      THA_CUDA_OK(launch(tc_prep_q8_kernel, dim3(rows), dim3(prep_threads), 0, st, pdl, io.x, (const float*)sc.part, nz, zs, emb, io.token,
-                         io.pos, gain, d, gs, sc.xq, sc.xsT, ldxs, gather));
+      THA_CUDA_OK(launch(tc_prep_q8_kernel, dim3(rows), dim3(prep_threads), 0, st, pdl, io.x, part, nz, zs, emb, io.token,
+                         io.pos, gain, d, gs, sc.xq, sc.xsT, ldxs, gather, tpp));
     } else {
-      THA_CUDA_OK(launch(tc_prep_kernel, dim3(rows), dim3(prep_threads), 0, st, pdl, io.x, (const float*)sc.part, nz, zs, emb, io.token,
-                         io.pos, gain, d, sc.xh, sc.xl, sc.scale, gather));
+      THA_CUDA_OK(launch(tc_prep_kernel, dim3(rows), dim3(prep_threads), 0, st, pdl, io.x, part, nz, zs, emb, io.token,
+                         io.pos, gain, d, sc.xh, sc.xl, sc.scale, gather, tpp));
     }
     return THA_STATUS_SUCCESS;
   };
   bool mm_hidden = false;   // Q8_0: the next matmul reads the quantised hidden activations (w2) instead of the dim-wide ones
   // n stacked matrices of layer l: fp32 pointers or (int8, scales) pairs
-  auto mm = [&](int n, const float* const* W, const tha_qtensor_t* const* Q, size_t per_layer, int l, const int* M, const int* off,
+  auto mm = [&](int n, const float* const* W, const tha_qtensor_t* const* Q, int l, const int* M, const int* off,
                 int K, const float* xh, const float* xl, int N, float* out, long long ldo, long long zs, int z,
                 const float* colscale) -> int {
     if (!wq) return gemm(st, pdl, n, W, M, off, K, xh, xl, N, out, ldo, zs, z, colscale);
     const int8_t* q[3]; const float* sc3[3];
     for (int i = 0; i < n; i++) {
       const size_t elems = (size_t)M[i] * K;
-      (void)per_layer;
       q[i] = Q[i]->q + (size_t)l * elems;
       sc3[i] = Q[i]->s + (size_t)l * (elems / gs);
     }
@@ -527,21 +620,25 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
   };
   int prev_z = 0;                 // partials waiting to be added into x
   long long prev_zs = 0;
+  TpPeers none = {};
   for (int l = 0; l < L; l++) {
     const int loff = l * c.seq_len * kvd;
-    THA_TRY_RC(prep(R, prev_z, prev_zs, l == 0 ? w.token_embedding_table : (const float*)nullptr,
-                    w.rms_att_weight + (size_t)l * d, nogather));
+    THA_TRY_RC(prep(R, out_w2, prev_z, prev_zs, l == 0 ? w.token_embedding_table : (const float*)nullptr,
+                    w.rms_att_weight + (size_t)l * d, nogather, l == 0 ? none : peers_of(1, true)));
     {
       const float* W[3] = {nullptr, nullptr, nullptr};
-      if (!wq) { W[0] = w.wq + (size_t)l * d * d; W[1] = w.wk + (size_t)l * d * kvd; W[2] = w.wv + (size_t)l * d * kvd; }
+      if (!wq) { W[0] = w.wq + (size_t)l * da * d; W[1] = w.wk + (size_t)l * d * kvd; W[2] = w.wv + (size_t)l * d * kvd; }
       const tha_qtensor_t* Q[3] = {wq ? &wq->wq : nullptr, wq ? &wq->wk : nullptr, wq ? &wq->wv : nullptr};
-      const int M[3] = {d, kvd, kvd}, off[3] = {0, d, d + kvd};
-      THA_TRY_RC(mm(3, W, Q, 0, l, M, off, d, sc.xh, sc.xl, R, sc.part, ld_qkv, (long long)R * ld_qkv, pl.z_qkv, sc.scale));
+      const int M[3] = {da, kvd, kvd}, off[3] = {0, da, da + kvd};
+      THA_TRY_RC(mm(3, W, Q, l, M, off, d, sc.xh, sc.xl, R, sc.part, ld_qkv, (long long)R * ld_qkv, pl.z_qkv, sc.scale));
     }
     THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld_qkv / 2, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part,
-                       pl.z_qkv, (long long)R * ld_qkv, ld_qkv, io.pos, d, kvd, hs, rc, rs, io.q, s.key_cache, s.value_cache,
+                       pl.z_qkv, (long long)R * ld_qkv, ld_qkv, io.pos, da, kvd, hs, rc, rs, io.q, s.key_cache, s.value_cache,
                        kv_bs, loff, io.slot));
-    if (!io.logits && l == L - 1) return THA_STATUS_SUCCESS;   // cache-only ingestion: the last layer's K/V rows are in place
+    if (!io.logits && l == L - 1) {   // cache-only ingestion: the last layer's K/V rows are in place
+      if (tpx) THA_CUDA_OK(launch(tp_epoch_kernel, dim3(1), dim3(32), 0, st, pdl, tp->epoch()));
+      return THA_STATUS_SUCCESS;
+    }
     if (io.n_tiles > 0) {
       THA_TRY_RC(attn_prefill_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, wq ? nullptr : sc.xh,
                                      wq ? nullptr : sc.xl, s.key_cache + loff, s.value_cache + loff, kv_bs, io.slot, io.pos,
@@ -551,20 +648,20 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
                                    s.value_cache + loff, kv_bs, hs, c.seq_len, pdl, wq ? nullptr : sc.xh, wq ? nullptr : sc.xl));
     }
     if (wq)   // runq.c:437: the attention output is quantised before wo
-      THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(d / 4, 256), R), dim3(256), 0, st, pdl, (const float*)io.xb, (long long)d,
-                         0, 0LL, 0, io.pos, d, gs, sc.xq, sc.xsT, ldxs));
+      THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(da / 4, 256), R), dim3(256), 0, st, pdl, (const float*)io.xb, (long long)da,
+                         0, 0LL, 0, io.pos, da, gs, sc.xq, sc.xsT, ldxs));
     {
-      const float* W[1] = {wq ? nullptr : w.wo + (size_t)l * d * d};
+      const float* W[1] = {wq ? nullptr : w.wo + (size_t)l * d * da};
       const tha_qtensor_t* Q[1] = {wq ? &wq->wo : nullptr};
       const int M[1] = {d}, off[1] = {0};
-      THA_TRY_RC(mm(1, W, Q, 0, l, M, off, d, sc.xh, sc.xl, R, sc.part, d, (long long)R * d, pl.z_wo, nullptr));
+      THA_TRY_RC(mm(1, W, Q, l, M, off, da, sc.xh, sc.xl, R, out_wo, d, (long long)R * d, pl.z_wo, nullptr));
     }
-    THA_TRY_RC(prep(R, pl.z_wo, (long long)R * d, nullptr, w.rms_ffn_weight + (size_t)l * d, nogather));
+    THA_TRY_RC(prep(R, out_wo, pl.z_wo, (long long)R * d, nullptr, w.rms_ffn_weight + (size_t)l * d, nogather, peers_of(0, false)));
     {
       const float* W[2] = {wq ? nullptr : w.w1 + (size_t)l * d * hd, wq ? nullptr : w.w3 + (size_t)l * d * hd};
       const tha_qtensor_t* Q[2] = {wq ? &wq->w1 : nullptr, wq ? &wq->w3 : nullptr};
       const int M[2] = {hd, hd}, off[2] = {0, hd};
-      THA_TRY_RC(mm(2, W, Q, 0, l, M, off, d, sc.xh, sc.xl, R, sc.part, ld_h, (long long)R * ld_h, pl.z_w13, sc.scale));
+      THA_TRY_RC(mm(2, W, Q, l, M, off, d, sc.xh, sc.xl, R, sc.part, ld_h, (long long)R * ld_h, pl.z_w13, sc.scale));
     }
     if (wq)   // runq.c:457-465: SwiGLU, then quantise hb
       THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(hd / 4, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part,
@@ -577,31 +674,32 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
       const tha_qtensor_t* Q[1] = {wq ? &wq->w2 : nullptr};
       const int M[1] = {d}, off[1] = {0};
       mm_hidden = true;
-      const int rc_w2 = mm(1, W, Q, 0, l, M, off, hd, sc.hh, sc.hl, R, sc.part, d, (long long)R * d, pl.z_w2, nullptr);
+      const int rc_w2 = mm(1, W, Q, l, M, off, hd, sc.hh, sc.hl, R, out_w2, d, (long long)R * d, pl.z_w2, nullptr);
       mm_hidden = false;
       THA_TRY_RC(rc_w2);
     }
     prev_z = pl.z_w2;
     prev_zs = (long long)R * d;
   }
-  THA_TRY_RC(prep(io.n_out, prev_z, prev_zs, nullptr, w.rms_final_weight, io.out_rows));
+  THA_TRY_RC(prep(io.n_out, out_w2, prev_z, prev_zs, nullptr, w.rms_final_weight, io.out_rows, peers_of(1, true)));
   {
     const float* W[1] = {wq ? nullptr : w.wcls};
     const tha_qtensor_t* Q[1] = {wq ? &wq->wcls : nullptr};
     const int M[1] = {c.vocab_size}, off[1] = {0};
-    THA_TRY_RC(mm(1, W, Q, 0, 0, M, off, d, sc.xh, sc.xl, io.n_out, io.logits, c.vocab_size, 0, 1, sc.scale));
+    THA_TRY_RC(mm(1, W, Q, 0, M, off, d, sc.xh, sc.xl, io.n_out, io.logits, c.vocab_size, 0, 1, sc.scale));
   }
   if (io.next) THA_TRY_RC(argmax_launch(st, io.n_out, io.logits, c.vocab_size, io.next, pdl));
+  if (tpx) THA_CUDA_OK(launch(tp_epoch_kernel, dim3(1), dim3(32), 0, st, pdl, tp->epoch()));
   return THA_STATUS_SUCCESS;
 }
 
 int step_tc_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_f32_t& w,
                   const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
-                  const float* rc, const float* rs, bool pdl) {
+                  const float* rc, const float* rs, bool pdl, const TpCtx* tp) {
   RowsIO io = {};
   io.R = B; io.x = s.x; io.q = s.q; io.xb = s.xb; io.token = token_d; io.pos = pos_d; io.slot = nullptr;
   io.n_tiles = 0; io.n_out = B; io.out_rows = nullptr; io.logits = logits; io.next = next_d;
-  return issue_rows(st, ws, c, w, nullptr, s, io, rc, rs, pdl);
+  return issue_rows(st, ws, c, w, nullptr, s, io, rc, rs, pdl, tp);
 }
 
 static tha_weights_f32_t q8_norms_view(const tha_weights_q8_t& wq) {
@@ -613,11 +711,11 @@ static tha_weights_f32_t q8_norms_view(const tha_weights_q8_t& wq) {
 
 int step_tc_q8_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_q8_t& wq,
                      const tha_state_t& s, const int* token_d, const int* pos_d, float* logits, int* next_d,
-                     const float* rc, const float* rs, bool pdl) {
+                     const float* rc, const float* rs, bool pdl, const TpCtx* tp) {
   RowsIO io = {};
   io.R = B; io.x = s.x; io.q = s.q; io.xb = s.xb; io.token = token_d; io.pos = pos_d; io.slot = nullptr;
   io.n_tiles = 0; io.n_out = B; io.out_rows = nullptr; io.logits = logits; io.next = next_d;
-  return issue_rows(st, ws, c, q8_norms_view(wq), &wq, s, io, rc, rs, pdl);
+  return issue_rows(st, ws, c, q8_norms_view(wq), &wq, s, io, rc, rs, pdl, tp);
 }
 
 // Batched prompt ingestion.  Host arrays: sequence i occupies cache slab slot[i], its len[i] tokens (consecutive
@@ -625,9 +723,10 @@ int step_tc_q8_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& 
 // the classifier runs on the last row of each sequence ([n_seqs, vocab], and argmax -> next[n_seqs]).
 int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_f32_t* w32,
                     const tha_weights_q8_t* wq, const tha_state_t& s, int n_seqs, const int* slot, const int* pos0,
-                    const int* len, const int* tokens, float* logits, int* next_d, const float* rc, const float* rs) {
-  if (!prefill_tc_supported(&c)) return THA_STATUS_NOT_SUPPORTED;
-  if (wq && !step_tc_q8_supported(&c, 1, wq->group_size)) return THA_STATUS_NOT_SUPPORTED;
+                    const int* len, const int* tokens, float* logits, int* next_d, const float* rc, const float* rs,
+                    const TpCtx* tp) {
+  if (!prefill_tc_supported(&c, tp)) return THA_STATUS_NOT_SUPPORTED;
+  if (wq && !step_tc_q8_supported(&c, 1, wq->group_size, tp)) return THA_STATUS_NOT_SUPPORTED;
   const tha_weights_f32_t w = wq ? q8_norms_view(*wq) : *w32;
   long long R = 0, T = 0;
   for (int i = 0; i < n_seqs; i++) {
@@ -648,11 +747,11 @@ int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const
     }
     h_last[i] = r - 1;
   }
-  THA_TRY_RC(prepare_rows(ws, &c, (int)R, true, (int)tab.size(), wq != nullptr, wq ? wq->group_size : 64));
+  THA_TRY_RC(prepare_rows(ws, &c, (int)R, true, (int)tab.size(), wq != nullptr, wq ? wq->group_size : 64, tp));
   TcScratch sc;
   {
     std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
-    sc = g_tc_scratch[ws->device];
+    sc = g_tc_scratch[ws];
   }
   // pageable source: the copy is staged before the call returns, so `tab` may go out of scope
   THA_CUDA_OK(cudaMemcpyAsync(sc.tab, tab.data(), tab.size() * sizeof(int), cudaMemcpyHostToDevice, st));
@@ -661,7 +760,7 @@ int step_tc_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const
   io.slot = sc.tab; io.pos = sc.tab + R; io.token = sc.tab + 2 * R;
   io.n_tiles = (int)T; io.tile_row0 = sc.tab + 3 * R; io.tile_n = sc.tab + 3 * R + T;
   io.n_out = n_seqs; io.out_rows = sc.tab + 3 * R + 2 * T; io.logits = logits; io.next = logits ? next_d : nullptr;
-  return issue_rows(st, ws, c, w, wq, s, io, rc, rs, true);
+  return issue_rows(st, ws, c, w, wq, s, io, rc, rs, pdl_enabled() != 0, tp);
 }
 
 }  // namespace tha

@@ -100,7 +100,8 @@ class DeviceWeightsQ8:
         return n
 
 
-def device_random_weights(cfg: Config, q8: bool = False, seed: int = 1337, device="cuda", std: float = 0.02, gs: int = 64):
+def device_random_weights(cfg: Config, q8: bool = False, seed: int = 1337, device="cuda", std: float = 0.02, gs: int = 64,
+                          shapes: dict | None = None, shard_seed: int | None = None):
     """Random-init weights of the named architecture generated ON the device (benchmarks of models whose
     host-side generation would take minutes: Llama-2-7B is 26 GB in fp32).  Same N(0, std) law as
     checkpoint.random_weights; Q8_0 tensors are quantised on the device with the exporter's rule
@@ -108,8 +109,9 @@ def device_random_weights(cfg: Config, q8: bool = False, seed: int = 1337, devic
     g = torch.Generator(device=device)
     g.manual_seed(seed)
     L, d, h, kvd, V = cfg.n_layers, cfg.dim, cfg.hidden_dim, cfg.kv_dim, cfg.vocab_size
-    shapes = {"tok_emb": (V, d), "wq": (L, d, d), "wk": (L, kvd, d), "wv": (L, kvd, d), "wo": (L, d, d),
-              "w1": (L, h, d), "w2": (L, d, h), "w3": (L, h, d)}
+    if shapes is None:   # tensor-parallel shards pass their local shapes (tp.py); "tok_emb" stays first: it is replicated
+        shapes = {"tok_emb": (V, d), "wq": (L, d, d), "wk": (L, kvd, d), "wv": (L, kvd, d), "wo": (L, d, d),
+                  "w1": (L, h, d), "w2": (L, d, h), "w3": (L, h, d)}
     norms = {"rms_att": torch.ones(L, d, device=device), "rms_ffn": torch.ones(L, d, device=device),
              "rms_final": torch.ones(d, device=device)}
 
@@ -118,10 +120,17 @@ def device_random_weights(cfg: Config, q8: bool = False, seed: int = 1337, devic
         t.normal_(0.0, std, generator=g)
         return t
 
+    def reseed(n):   # everything after the replicated embedding table differs per shard
+        if n == "tok_emb" and shard_seed is not None:
+            g.manual_seed(shard_seed)
+
     if not q8:
         w = DeviceWeights.__new__(DeviceWeights)
         w.cfg = cfg
-        w.t = {n: gen(sh) for n, sh in shapes.items()}
+        w.t = {}
+        for n, sh in shapes.items():
+            w.t[n] = gen(sh)
+            reseed(n)
         w.t.update(norms)
         w.t["wcls"] = w.t["tok_emb"]
         t = w.t
@@ -145,6 +154,7 @@ def device_random_weights(cfg: Config, q8: bool = False, seed: int = 1337, devic
             q[l] = torch.round(x / scale[:, None]).to(torch.int8).reshape(-1)
             del x
         w.t[n + ".q"], w.t[n + ".s"] = q.reshape(sh), sc
+        reseed(n)
     w.t["wcls.q"], w.t["wcls.s"] = w.t["tok_emb.q"], w.t["tok_emb.s"]
     w.t["tok_emb"] = (w.t["tok_emb.q"].reshape(-1, gs).float() * w.t["tok_emb.s"].reshape(-1, 1)).reshape(V, d).contiguous()
     t = w.t

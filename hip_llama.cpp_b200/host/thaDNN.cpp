@@ -133,3 +133,42 @@ thablasStatus_t thaDNN_s_decode_greedy_batch(thablasHandle_t* handle, int n_batc
   return st(tha_decode_step_f32(calc(handle), n_batches, (const tha_config_t*)p, (const tha_weights_f32_t*)w,
                                 (const tha_state_t*)s_batch, token_d, pos_d, logits_d, next_d));
 }
+
+// ---- tensor parallelism (include/tha_b200.h: tha_tp_*) ------------------------------------------------
+thablasStatus_t thaTPCreate(thaTP_t* tp, int tp_size, int rank, int head_size, const int hidden_of_rank[], size_t xchg_floats) {
+  return st(tha_tp_create(tp, tp_size, rank, head_size, hidden_of_rank, xchg_floats));
+}
+thablasStatus_t thaTPConnectLocal(thaTP_t ranks[], int tp_size) {
+  if (!ranks || tp_size < 1 || tp_size > 8) return THABLAS_STATUS_ALLOC_FAILED;
+  void* bases[8];
+  for (int r = 0; r < tp_size; r++) {
+    const int rc = tha_tp_local_ptr(ranks[r], &bases[r]);
+    if (rc) return st(rc);
+  }
+  // tha_tp_connect_ptr enables peer access FROM the current device: the caller selects each rank's device in turn,
+  // exactly as the reference's per-device threads do (src/llama.cpp:927); here we query the owner of each block.
+  int prev = 0;
+  tha_get_device(&prev);
+  for (int r = 0; r < tp_size; r++) {
+    int rc = tha_tp_select_device(ranks[r]);
+    if (!rc) rc = tha_tp_connect_ptr(ranks[r], bases);
+    if (rc) { tha_set_device(prev); return st(rc); }
+  }
+  tha_set_device(prev);
+  return THABLAS_STATUS_SUCCESS;
+}
+thablasStatus_t thaTPDestroy(thaTP_t tp) { return st(tha_tp_destroy(tp)); }
+thablasStatus_t thaDNN_s_forward_batch_tp(thablasHandle_t* handle, thaTP_t tp, int n_batches, Config* p_local,
+                                          TransformerWeights* w_local, RunState* s_local, int* token_d, int* pos_d,
+                                          float* logits_d, int* next_d, int advance) {
+  if (!handle) return THABLAS_STATUS_HANDLE_IS_NULLPTR;
+  return st(tha_tp_decode_step_f32(calc(handle), tp, n_batches, (const tha_config_t*)p_local, (const tha_weights_f32_t*)w_local,
+                                   (const tha_state_t*)s_local, token_d, pos_d, logits_d, next_d, advance));
+}
+thablasStatus_t thaDNN_q8_forward_batch_tp(thablasHandle_t* handle, thaTP_t tp, int n_batches, Config* p_local,
+                                           TransformerWeightsQ8* w_local, RunState* s_local, int* token_d, int* pos_d,
+                                           float* logits_d, int* next_d, int advance) {
+  if (!handle) return THABLAS_STATUS_HANDLE_IS_NULLPTR;
+  return st(tha_tp_decode_step_q8(calc(handle), tp, n_batches, (const tha_config_t*)p_local, (const tha_weights_q8_t*)w_local,
+                                  (const tha_state_t*)s_local, token_d, pos_d, logits_d, next_d, advance));
+}

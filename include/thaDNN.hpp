@@ -53,3 +53,21 @@ thablasStatus_t thaDNN_s_prefill_batch(thablasHandle_t* handle, Config* p, Trans
 thablasStatus_t thaDNN_s_decode_greedy_batch(thablasHandle_t* handle, int n_batches, Config* p, TransformerWeights* w,
                                              RunState* s_batch, int* token_d, int* pos_d, int* next_d,
                                              float* logits_d, int advance);
+
+// Tensor-parallel step (additive; SURVEY.md 8e "Optional TP"): ONE replica of a model split over the GPUs of a box,
+// one rank per GPU (one host thread per device as in src/llama.cpp:913, or one process per device).  p / w / s_batch
+// are the rank's LOCAL config, weight shards and state (include/tha_b200.h, "tensor parallelism"); the all-reduce after
+// the wo and w2 matmuls is fused into the kernel that consumes it, over NVLink peer memory.  Every rank makes the same
+// calls.  token_d / pos_d / next_d / logits_d are DEVICE arrays (next_d, logits_d nullable); advance != 0 moves every
+// active slot on (token = next, pos += 1).  Asynchronous on handle->calc_stream.
+struct tha_tp;
+typedef struct tha_tp* thaTP_t;
+thablasStatus_t thaTPCreate(thaTP_t* tp, int tp_size, int rank, int head_size, const int hidden_of_rank[], size_t xchg_floats);
+thablasStatus_t thaTPConnectLocal(thaTP_t ranks[], int tp_size);   // all ranks in this process: enables peer access, wires pointers
+thablasStatus_t thaTPDestroy(thaTP_t tp);
+thablasStatus_t thaDNN_s_forward_batch_tp(thablasHandle_t* handle, thaTP_t tp, int n_batches, Config* p_local,
+                                          TransformerWeights* w_local, RunState* s_local, int* token_d, int* pos_d,
+                                          float* logits_d, int* next_d, int advance);
+thablasStatus_t thaDNN_q8_forward_batch_tp(thablasHandle_t* handle, thaTP_t tp, int n_batches, Config* p_local,
+                                           TransformerWeightsQ8* w_local, RunState* s_local, int* token_d, int* pos_d,
+                                           float* logits_d, int* next_d, int advance);

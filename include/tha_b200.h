@@ -230,6 +230,46 @@ int tha_prefill_q8(void* stream, const tha_config_t* cfg, const tha_weights_q8_t
                    float* logits_d, int* next_d);
 int tha_prefill_supported(const tha_config_t* cfg); /* 1 when tha_prefill_f32 handles this architecture */
 
+/* ---- tensor parallelism (Llama-2-7B split 2/4/8 ways over NVLink; SURVEY.md 8e "Optional TP") ------------------
+ * One tha_tp_t per rank (= per GPU; one process per GPU, or one host thread per GPU in one process as the reference's
+ * driver runs, src/llama.cpp:913).  wq/wk/wv/w1/w3 are split by output rows (heads, hidden units), wo/w2 by input
+ * columns (the reference has no TP; its closest relative is the pipeline split of src/thaDNN.cpp:83-427).  The
+ * all-reduce after wo and w2 is FUSED into its consumer: each rank's matmul leaves its partial sums in an exchange
+ * buffer in its own HBM, mapped by its peers (cudaIpc across processes, peer access inside one), and the residual-add
+ * + RMSNorm kernel of every rank reads all ranks' partials over NVLink in a fixed order after a flag handshake -- no
+ * separate collective kernel, bit-identical residual stream on every rank.
+ *   create:  hidden_of_rank[tp] = every rank's local hidden_dim (a multiple of the Q8_0 group size; may differ between
+ *            ranks: 11008 / 8 is not a multiple of 64); xchg_floats = capacity of each of the two exchange buffers,
+ *            >= max over ranks of (split-K factor <= 16) * rows * dim.
+ *   connect: across processes, gather every rank's 64-byte handle (tha_tp_export) and pass the [tp][64] array to
+ *            tha_tp_connect_ipc; inside one process pass the tp block pointers (tha_tp_local_ptr) to tha_tp_connect_ptr.
+ *   step:    cfg_local has n_heads / n_kv_heads / hidden_dim of THIS rank and the full dim; weights / state are the
+ *            local shards (wq [L,da,dim], wk,wv [L,kvd,dim], wo [L,dim,da], w1,w3 [L,hd,dim], w2 [L,dim,hd]; embedding,
+ *            norms, classifier replicated; KV cache [B][L][S][kvd] of the local heads; q, xb >= [B, da]).  Every rank
+ *            makes the same sequence of calls; advance != 0 adds the greedy slot bookkeeping (tha_advance_slots).
+ *   A peer that never shows up ends in tha_tp_check_error() == 1 after ~20 s, not in a hang. */
+typedef struct tha_tp tha_tp_t;
+int tha_tp_create(tha_tp_t** out, int tp, int rank, int head_size, const int* hidden_of_rank, size_t xchg_floats);
+int tha_tp_export(tha_tp_t* t, void* handle64_out);
+int tha_tp_local_ptr(tha_tp_t* t, void** base);
+int tha_tp_connect_ipc(tha_tp_t* t, const void* handles);
+int tha_tp_connect_ptr(tha_tp_t* t, void* const* bases);
+int tha_tp_check_error(tha_tp_t* t);
+int tha_tp_select_device(tha_tp_t* t);   /* cudaSetDevice(the rank's device) */
+int tha_tp_destroy(tha_tp_t* t);
+int tha_tp_decode_step_f32(void* stream, tha_tp_t* tp, int n_batches, const tha_config_t* cfg_local,
+                           const tha_weights_f32_t* w_local, const tha_state_t* s_local, int* token_d, int* pos_d,
+                           float* logits_d, int* next_d, int advance);
+int tha_tp_decode_step_q8(void* stream, tha_tp_t* tp, int n_batches, const tha_config_t* cfg_local,
+                          const tha_weights_q8_t* w_local, const tha_state_t* s_local, int* token_d, int* pos_d,
+                          float* logits_d, int* next_d, int advance);
+int tha_tp_prefill_f32(void* stream, tha_tp_t* tp, const tha_config_t* cfg_local, const tha_weights_f32_t* w_local,
+                       const tha_state_t* s_local, int n_seqs, const int* slot_host, const int* pos0_host,
+                       const int* len_host, const int* tokens_host, float* logits_d, int* next_d);
+int tha_tp_prefill_q8(void* stream, tha_tp_t* tp, const tha_config_t* cfg_local, const tha_weights_q8_t* w_local,
+                      const tha_state_t* s_local, int n_seqs, const int* slot_host, const int* pos0_host,
+                      const int* len_host, const int* tokens_host, float* logits_d, int* next_d);
+
 int tha_step_needs_att_scratch(const tha_config_t* cfg);
 /* number of kernels the last tha_decode_step_* call on this thread launched */
 int tha_last_step_launches(void);
