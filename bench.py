@@ -54,6 +54,8 @@ def parse_args():
     ap.add_argument("--seq-len", type=int, default=0, help="override the context length (KV slab size) of the architecture")
     ap.add_argument("--tp", type=int, default=1, help="tensor-parallel width (= WORLD_SIZE under torchrun): ONE replica split "
                     "over the GPUs, all-reduce fused into its consumer over NVLink peer memory (strong scaling)")
+    ap.add_argument("--pos0", type=int, default=0, help="profiling aid: slots start at this position over a zero-filled KV cache "
+                    "(same bytes and time per step as a real context of that length); the default 0 is the benchmark")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
@@ -231,8 +233,8 @@ def run_ours(args, rank, world, local_rank):
         e.connect_distributed()
     else:
         cfg, dw, host_w = build_weights(args, device)
-    if W + K + 1 > cfg.seq_len:
-        raise SystemExit(f"warmup+steps must stay below seq_len={cfg.seq_len}")
+    if args.pos0 + W + K + 1 > cfg.seq_len:
+        raise SystemExit(f"pos0+warmup+steps must stay below seq_len={cfg.seq_len}")
     if tp == 1:
         e = eng.Engine(dw, B, device=device, with_att=False)
     wbytes = dw.nbytes()
@@ -250,7 +252,7 @@ def run_ours(args, rank, world, local_rank):
     stream = torch.cuda.Stream()
     with torch.cuda.stream(stream):
         tok = torch.from_numpy(tok0).to(device)
-        pos = torch.zeros(B, dtype=torch.int32, device=device)
+        pos = torch.full((B,), args.pos0, dtype=torch.int32, device=device)
         nxt = torch.zeros(B, dtype=torch.int32, device=device)
         logits = torch.zeros(B, cfg.vocab_size, dtype=torch.float32, device=device)
 
@@ -284,7 +286,7 @@ def run_ours(args, rank, world, local_rank):
     # algorithmic bytes of the timed steps on this rank (positions W .. W+K-1); under --tp: this rank's shard
     # (its weights, the KV rows of its heads; embedding row, logits and classifier are replicated)
     cfg_b = e.cfg_bytes if tp > 1 else cfg
-    total_bytes = sum(step_bytes(cfg_b, wbytes, p, B) for p in range(W, W + K))
+    total_bytes = sum(step_bytes(cfg_b, wbytes, p, B) for p in range(args.pos0 + W, args.pos0 + W + K))
     achieved = total_bytes / (ms * 1e-3) / 1e9
     peak, peak_src = measured_peak()
 
@@ -384,7 +386,7 @@ def base_line(args, cfg, world):
         "dtype": "f32" if args.quant == "f32" else "int8+f32", "data": "synthetic",
         "config": {
             "workload": f"{model_label(args.model)} {'fp32' if args.quant == 'f32' else 'Q8_0'} batched greedy decode, "
-                        f"{B} slots per {'replica' if args.tp > 1 else 'GPU'}, positions {args.warmup}..{args.warmup + args.steps - 1}, "
+                        f"{B} slots per {'replica' if args.tp > 1 else 'GPU'}, positions {args.pos0 + args.warmup}..{args.pos0 + args.warmup + args.steps - 1}, "
                         + (f"ONE replica tensor-parallel over {args.tp} GPUs (all-reduce after wo / w2 fused into its consumer over "
                            "NVLink peer memory)" if args.tp > 1 else "sequences sharded over GPUs (replicated weights, no collective)"),
             "batch_per_gpu": B, "global_batch": B * (1 if args.tp > 1 else world), "parallelism": (f"tp{args.tp}" if args.tp > 1 else f"dp{world}"), "vocab": cfg.vocab_size, "seq_len": cfg.seq_len,

@@ -108,6 +108,8 @@ class Lib:
             "tha_tp_connect_ptr": [vp, C.POINTER(vp)],
             "tha_tp_check_error": [vp],
             "tha_tp_destroy": [vp],
+            "tha_tp_set_mode": [vp, I],
+            "tha_tp_select_device": [vp],
             "tha_tp_decode_step_f32": [vp, vp, I, C.POINTER(Config), C.POINTER(WeightsF32), C.POINTER(State), vp, vp, vp, vp, I],
             "tha_tp_decode_step_q8": [vp, vp, I, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), vp, vp, vp, vp, I],
             "tha_tp_prefill_f32": [vp, vp, C.POINTER(Config), C.POINTER(WeightsF32), C.POINTER(State), I, vp, vp, vp, vp, vp, vp],

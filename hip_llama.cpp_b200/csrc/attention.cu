@@ -9,6 +9,8 @@
 //     still fills the GPU; the last CTA of a (slot, segment) merges the splits.
 //     K/V rows are read once, fully coalesced (a warp reads whole contiguous row
 //     segments with 128-bit loads); scores never touch HBM.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "workspace.h"
 
@@ -241,19 +243,45 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
 // ------------------------------------------------------------------ launchers -------
 namespace tha {
 
-// Segment choice for the fused kernel: G whole heads with G*hs = 128*J floats, J in 1..8.
-// Returns J (0 = shape not supported by the fused kernel).
-static int fused_J(int n_heads, int head_size, int dim) {
+int attn_fused_nsplit(int B, int nseg, int seq_len);
+
+// Segment choice for the fused kernel: a CTA covers G whole heads with G*hs = 128*J floats, J in 1..8.
+// Returns J (0 = shape not supported by the fused kernel).  The NARROWEST segment wins: J = 1 needs 48 registers per
+// thread (five CTAs per SM whose load and math phases interleave) where J = 6 needs 188 (one CTA per SM, its 8 warps in
+// lock step): measured on stories110M at 256 slots, position 128: 140 k -> 172 k tok/s; 64 slots: 63 k -> 79 k;
+// Llama-2-7B Q8_0 at 64 slots, position 256: 5.0 k (J = 8) -> 6.4 k tok/s (tools/attn_sweep.sh).  A warp still reads
+// 512 contiguous bytes of each K / V row.  THA_ATTN_J forces a width (development aid).
+// Grouped-query models: a segment covers whole groups of query heads that share a K/V head where one fits (each K/V
+// row is then read by one CTA, not by kv_mul of them).
+static int fused_J(int n_heads, int head_size, int dim, int kv_mul = 1) {
+  (void)n_heads;
   if (head_size < 4 || head_size > 128 || (head_size & (head_size - 1))) return 0;  // power of two, <= 128
-  for (int J = 8; J >= 1; J--) {
+  static int forced = -1;
+  if (forced < 0) { const char* v = getenv("THA_ATTN_J"); forced = (v && *v) ? atoi(v) : 0; }
+  int best = 0;
+  for (int J = 1; J <= 8; J++) {
     const int seg = 128 * J;
-    if (seg % head_size == 0 && dim % seg == 0) return J;
+    if (seg % head_size || dim % seg) continue;
+    if (forced > 0 && J == forced) return J;
+    if (!best) best = J;
+    if (kv_mul > 1 && seg % (kv_mul * head_size) == 0) return J;
   }
-  return 0;
+  return best;
 }
 
 bool attn_fused_supported(int n_heads, int head_size, int dim, int kv_dim) {
   return fused_J(n_heads, head_size, dim) != 0 && (kv_dim % 4 == 0);
+}
+
+// Segment width and time split of the launch for B slots; grows the split scratch (never inside a stream capture).
+int attn_fused_prepare(Workspace* ws, int B, int n_heads, int n_kv_heads, int head_size, int seq_len) {
+  const int dim = n_heads * head_size;
+  const int J = fused_J(n_heads, head_size, dim, n_heads / n_kv_heads);
+  if (!J) return THA_STATUS_NOT_SUPPORTED;
+  const int nseg = dim / (128 * J);
+  const int nsplit = attn_fused_nsplit(B, nseg, seq_len);
+  if (nsplit > 1) return ws_ensure_attn(ws, (size_t)B * nseg * nsplit * 32 * J, B * nseg);
+  return THA_STATUS_SUCCESS;
 }
 
 int attn_fused_nsplit(int B, int nseg, int seq_len) {
@@ -270,7 +298,7 @@ int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
                       int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo) {
   const int dim = n_heads * head_size, kv_dim = n_kv_heads * head_size;
-  const int J = fused_J(n_heads, head_size, dim);
+  const int J = fused_J(n_heads, head_size, dim, n_heads / n_kv_heads);
   if (!J || kv_dim % 4) return THA_STATUS_NOT_SUPPORTED;
   AttnP p;
   p.pos = pos_d; p.q = q; p.out = out; p.kc = kc; p.vc = vc; p.out_hi = out_hi; p.out_lo = out_lo;

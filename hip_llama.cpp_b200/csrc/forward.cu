@@ -24,7 +24,7 @@ namespace tha {
 int embed_launch(cudaStream_t st, int B, float* x, const float* table, const int* token, const int* pos, int dim, bool pdl);
 int argmax_launch(cudaStream_t st, int B, const float* logits, int vocab, int* next, bool pdl);
 bool attn_fused_supported(int n_heads, int head_size, int dim, int kv_dim);
-int attn_fused_nsplit(int B, int nseg, int seq_len);
+int attn_fused_prepare(Workspace* ws, int B, int n_heads, int n_kv_heads, int head_size, int seq_len);
 int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
                       int head_size, int seq_len, bool pdl, float* out_hi = nullptr, float* out_lo = nullptr);
@@ -78,10 +78,11 @@ static unsigned long long fnv1a(const void* data, size_t n, unsigned long long h
 // Issue the step directly, or (default) capture it once per distinct argument set into a
 // CUDA graph and replay it.  `key`/`key_len`: every value the launches depend on.
 template <typename IssueFn>
-static int run_step(cudaStream_t st, Workspace* ws, const void* key_data, size_t key_len, IssueFn issue) {
+static int run_step(cudaStream_t st, Workspace* ws, const void* key_data, size_t key_len, IssueFn issue, bool do_launch = true) {
   launches_reset();
   const bool use_graph = graph_enabled() && st != nullptr && st != cudaStreamLegacy;
   if (!use_graph) {
+    if (!do_launch) return THA_STATUS_SUCCESS;
     int rc2 = issue();
     g_last_step_launches = launches_get();
     return rc2;
@@ -102,7 +103,8 @@ static int run_step(cudaStream_t st, Workspace* ws, const void* key_data, size_t
     if (e != cudaSuccess) { set_last_error("cudaGraphInstantiate", e); return THA_STATUS_EXECUTION_FAILED; }
     it = ws->graphs.emplace(key, sg).first;
   }
-  THA_CUDA_OK(cudaGraphLaunch(it->second.exec, st));
+  if (do_launch) THA_CUDA_OK(cudaGraphLaunch(it->second.exec, st));
+  else THA_CUDA_OK(cudaGraphUpload(it->second.exec, st));   // prepare only: the executable graph is resident, nothing runs
   g_last_step_launches = it->second.launches;
   return THA_STATUS_SUCCESS;
 }
@@ -217,13 +219,7 @@ int decode_step_f32(cudaStream_t st, int B, const tha_config_t* cfg, const tha_w
   }
   const bool fused = attn_fused_supported(cfg->n_heads, hs, cfg->dim, kvd);
   if (!fused && !s->att) return THA_STATUS_INVALID_ARG;
-  if (fused) {  // grow the split scratch now: no allocation may happen inside a capture
-    int J = 8;
-    for (; J >= 1; J--) if ((128 * J) % hs == 0 && cfg->dim % (128 * J) == 0) break;
-    const int nseg = cfg->dim / (128 * J);
-    const int nsplit = attn_fused_nsplit(B, nseg, cfg->seq_len);
-    if (nsplit > 1) THA_TRY(ws_ensure_attn(ws, (size_t)B * nseg * nsplit * 32 * J, B * nseg));
-  }
+  if (fused) THA_TRY(attn_fused_prepare(ws, B, cfg->n_heads, cfg->n_kv_heads, hs, cfg->seq_len));   // grow the split scratch now: no allocation may happen inside a capture
   return run_step(st, ws, &a, sizeof(a), [&]() {
     THA_TRY(issue_step_f32(st, ws, a, rc, rs));
     if (advance) THA_TRY(advance_launch(st, B, const_cast<int*>(token_d), const_cast<int*>(pos_d), next_d, cfg->seq_len, a.pdl != 0));
@@ -349,13 +345,7 @@ int decode_step_q8(cudaStream_t st, int B, const tha_config_t* cfg, const tha_we
   }
   const bool fused = attn_fused_supported(cfg->n_heads, hs, cfg->dim, kvd);
   if (!fused && !s->att) return THA_STATUS_INVALID_ARG;
-  if (fused) {
-    int J = 8;
-    for (; J >= 1; J--) if ((128 * J) % hs == 0 && cfg->dim % (128 * J) == 0) break;
-    const int nseg = cfg->dim / (128 * J);
-    const int nsplit = attn_fused_nsplit(B, nseg, cfg->seq_len);
-    if (nsplit > 1) THA_TRY(ws_ensure_attn(ws, (size_t)B * nseg * nsplit * 32 * J, B * nseg));
-  }
+  if (fused) THA_TRY(attn_fused_prepare(ws, B, cfg->n_heads, cfg->n_kv_heads, hs, cfg->seq_len));
   THA_TRY(ws_ensure_q8(ws, B, cfg->dim > cfg->hidden_dim ? cfg->dim : cfg->hidden_dim, gs));
   return run_step(st, ws, &a, sizeof(a), [&]() { return issue_step_q8(st, ws, a, rc, rs); });
 }
@@ -559,7 +549,7 @@ static int tp_decode(cudaStream_t st, TpCtx* tp, int B, const tha_config_t* cfg,
     else THA_TRY(step_tc_issue(st, ws, B, *cfg, *w, *s, token_d, pos_d, lg, next_d, rc, rs, a.pdl != 0, tp));
     if (advance) THA_TRY(advance_launch(st, B, token_d, pos_d, next_d, cfg->seq_len, a.pdl != 0));
     return (int)THA_STATUS_SUCCESS;
-  });
+  }, tp->mode != 1);
 }
 }  // namespace tha
 
@@ -588,8 +578,13 @@ static int tp_prefill(cudaStream_t st, TpCtx* tp, const tha_config_t* cfg, const
   const float *rc, *rs;
   THA_TRY(ws_rope(ws, tp->head_size, cfg->seq_len, &rc, &rs));
   launches_reset();
+  TpCtx solo;   // prepare only: the same launches without the exchange
+  if (tp->mode == 1) {
+    solo.tp = 1; solo.rank = 0; solo.head_size = tp->head_size; solo.hidden_of[0] = cfg->hidden_dim; solo.device = tp->device;
+    solo.connected = true;
+  }
   const int rcode = step_tc_prefill(st, ws, *cfg, w, wq, *s, n_seqs, slot_host, pos0_host, len_host, tokens_host, logits_d,
-                                    next_d, rc, rs, tp);
+                                    next_d, rc, rs, tp->mode == 1 ? &solo : tp);
   last_step_launches_set(launches_get());
   return rcode;
 }

@@ -33,7 +33,7 @@ namespace tha {
 
 int argmax_launch(cudaStream_t st, int B, const float* logits, int vocab, int* next, bool pdl);
 bool attn_fused_supported(int n_heads, int head_size, int dim, int kv_dim);
-int attn_fused_nsplit(int B, int nseg, int seq_len);
+int attn_fused_prepare(Workspace* ws, int B, int n_heads, int n_kv_heads, int head_size, int seq_len);
 int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
                       int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo);
@@ -487,13 +487,7 @@ static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefil
     }
     return THA_STATUS_SUCCESS;
   }
-  const int hs = dm.hs;
-  int J = 8;
-  for (; J >= 1; J--) if ((128 * J) % hs == 0 && dm.da % (128 * J) == 0) break;
-  const int nseg = dm.da / (128 * J);
-  const int nsplit = attn_fused_nsplit(R, nseg, c->seq_len);
-  if (nsplit > 1) THA_TRY_RC(ws_ensure_attn(ws, (size_t)R * nseg * nsplit * 32 * J, R * nseg));
-  return THA_STATUS_SUCCESS;
+  return attn_fused_prepare(ws, R, c->n_heads, c->n_kv_heads, dm.hs, c->seq_len);
 }
 
 int step_tc_prepare(Workspace* ws, const tha_config_t* c, int B, const TpCtx* tp) { return prepare_rows(ws, c, B, false, 0, false, 64, tp); }

@@ -87,6 +87,17 @@ extern "C" int tha_tp_connect_ptr(tha_tp_t* t, void* const* bases) {
   return THA_STATUS_SUCCESS;
 }
 
+// mode 1 = PREPARE ONLY: the next tha_tp_decode_step_* call allocates its scratch, captures and instantiates its CUDA
+// graph and caches it, but launches nothing; the next tha_tp_prefill_* call runs once without the exchange (garbage
+// results; every buffer grown, every kernel loaded).  A host that drives several ranks of ONE device from one thread
+// (tests/test_gpu_tp.py) prepares all ranks first: nothing that may synchronise with the device (cudaMalloc / cudaFree,
+// lazy module loading, graph instantiation) then happens while a peer's kernels are already waiting for this rank.
+extern "C" int tha_tp_set_mode(tha_tp_t* t, int mode) {
+  if (!t || mode < 0 || mode > 1) return THA_STATUS_INVALID_ARG;
+  t->c.mode = mode;
+  return THA_STATUS_SUCCESS;
+}
+
 // make the rank's device current (host threads that drive several ranks)
 extern "C" int tha_tp_select_device(tha_tp_t* t) {
   if (!t) return THA_STATUS_INVALID_ARG;

@@ -35,6 +35,7 @@ struct TpCtx {
   unsigned char* peer[TP_MAX] = {nullptr};   // every rank's block as mapped here (peer[rank] == base)
   bool ipc_opened[TP_MAX] = {false};
   bool connected = false;
+  int mode = 0;                           // 1: prepare only (tha_tp_set_mode)
   int device = -1;
   Workspace ws;                           // this rank's own scratch (two ranks may share a device in tests)
   size_t block_bytes() const { return TP_HDR_BYTES + 2 * xchg_floats * sizeof(float); }

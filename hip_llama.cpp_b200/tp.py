@@ -173,6 +173,11 @@ class TpRank:
         self.connect_ipc(hs)
 
     # ---- the steps ------------------------------------------------------------------------------------
+    def set_mode(self, prepare_only: bool) -> None:
+        """prepare_only: the next step / prefill call grows scratch, loads kernels and builds its CUDA graph but does
+        not take part in an exchange (tha_tp_set_mode) -- for hosts that drive several ranks of one device."""
+        self.lib.check(self.lib.c.tha_tp_set_mode(self.ctx, 1 if prepare_only else 0), "tha_tp_set_mode")
+
     def decode_step(self, token_d, pos_d, logits_d=None, next_d=None, advance=False, stream=None):
         import torch
         s = stream if stream is not None else torch.cuda.current_stream()

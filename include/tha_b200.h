@@ -255,6 +255,7 @@ int tha_tp_local_ptr(tha_tp_t* t, void** base);
 int tha_tp_connect_ipc(tha_tp_t* t, const void* handles);
 int tha_tp_connect_ptr(tha_tp_t* t, void* const* bases);
 int tha_tp_check_error(tha_tp_t* t);
+int tha_tp_set_mode(tha_tp_t* t, int mode); /* 1: the next step / prefill call only prepares (scratch, graph, module loads) */
 int tha_tp_select_device(tha_tp_t* t);   /* cudaSetDevice(the rank's device) */
 int tha_tp_destroy(tha_tp_t* t);
 int tha_tp_decode_step_f32(void* stream, tha_tp_t* tp, int n_batches, const tha_config_t* cfg_local,

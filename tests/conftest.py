@@ -9,6 +9,12 @@ sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
+# tests/test_gpu_tp.py runs the ranks of a tensor-parallel replica as concurrent streams of ONE device; they hand-shake
+# inside their kernels, so two ranks' streams must never share a hardware work queue (the default 8 queues are dealt to
+# streams round-robin, and an aliased pair serialises: the first rank then waits for a peer queued behind it).  Must be
+# set before the CUDA context exists.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")

@@ -51,6 +51,34 @@ def make_ranks(cfg, w, tp, B, q8, max_rows=None):
     return ranks
 
 
+_STREAMS = []
+
+
+def rank_streams(tp):
+    """One stream per rank, created once (back to back: distinct hardware queues, see conftest.py) and reused."""
+    import torch
+    while len(_STREAMS) < tp:
+        _STREAMS.append(torch.cuda.Stream())
+    return _STREAMS[:tp]
+
+
+def step_all(ranks, streams, call):
+    """One call on every rank of a replica whose ranks share this process (and here: one device).  First every rank
+    PREPARES (scratch, module loads, graph instantiation -- anything that may synchronise with the device), then the
+    real calls go out back to back: while a rank's kernels wait for a peer, the host does nothing but enqueue."""
+    import torch
+    for r, rk in enumerate(ranks):
+        rk.set_mode(True)
+        call(r, streams[r])
+        rk.set_mode(False)
+    torch.cuda.synchronize()
+    for r in range(len(ranks)):
+        call(r, streams[r])
+    torch.cuda.synchronize()
+    for r, rk in enumerate(ranks):
+        assert not rk.check_error(), f"rank {r}: a wait on a peer timed out"
+
+
 @pytest.fixture
 def no_pdl():
     lib = load_pkg("cabi").lib()
@@ -67,7 +95,7 @@ def test_tp_decode_vs_oracle(oracle, tmp_path, no_pdl, name, tp, q8, B):
     cfg, w, v0, v2 = small_model_files(str(tmp_path), name, TP_MODELS[name])
     m = oracle.open(v2 if q8 else v0, quantized=q8)
     ranks = make_ranks(cfg, w, tp, B, q8)
-    streams = [torch.cuda.Stream() for _ in range(tp)]
+    streams = rank_streams(tp)
     seqs = [m.new_seq() for _ in range(B)]
     rng = np.random.default_rng(B + tp)
     n_steps = 10
@@ -80,12 +108,7 @@ def test_tp_decode_vs_oracle(oracle, tmp_path, no_pdl, name, tp, q8, B):
             pos[pos < 0] = -1
             tok_d = [torch.from_numpy(tok).cuda() for _ in range(tp)]
             pos_d = [torch.from_numpy(pos).cuda() for _ in range(tp)]
-            torch.cuda.synchronize()
-            for r in range(tp):
-                ranks[r].decode_step(tok_d[r], pos_d[r], logits[r], nxt[r], stream=streams[r])
-            torch.cuda.synchronize()
-            for r in range(tp):
-                assert not ranks[r].check_error(), f"rank {r}: a wait on a peer timed out"
+            step_all(ranks, streams, lambda r, st: ranks[r].decode_step(tok_d[r], pos_d[r], logits[r], nxt[r], stream=st))
             got = [l.cpu().numpy() for l in logits]
             for r in range(1, tp):   # every rank sums the same partials in the same order
                 act = pos >= 0
@@ -123,7 +146,7 @@ def test_tp_prefill_then_decode(oracle, tmp_path, no_pdl, q8):
     cfg, w, v0, v2 = small_model_files(str(tmp_path), name, TP_MODELS[name])
     m = oracle.open(v2 if q8 else v0, quantized=q8)
     ranks = make_ranks(cfg, w, tp, B, q8, max_rows=64)
-    streams = [torch.cuda.Stream() for _ in range(tp)]
+    streams = rank_streams(tp)
     rng = np.random.default_rng(5)
     lens = [5, 17, 30]
     prompts = [rng.integers(0, cfg.vocab_size, size=n).astype(np.int32) for n in lens]
@@ -136,12 +159,7 @@ def test_tp_prefill_then_decode(oracle, tmp_path, no_pdl, q8):
     logits = [torch.zeros(B, cfg.vocab_size, device="cuda") for _ in range(tp)]
     nxt = [torch.zeros(B, dtype=torch.int32, device="cuda") for _ in range(tp)]
     try:
-        torch.cuda.synchronize()
-        for r in range(tp):
-            ranks[r].prefill([(b, 0, prompts[b]) for b in range(B)], logits[r], nxt[r], stream=streams[r])
-        torch.cuda.synchronize()
-        for r in range(tp):
-            assert not ranks[r].check_error()
+        step_all(ranks, streams, lambda r, st: ranks[r].prefill([(b, 0, prompts[b]) for b in range(B)], logits[r], nxt[r], stream=st))
         got = logits[0].cpu().numpy()
         assert np.array_equal(got, logits[1].cpu().numpy())
         for b in range(B):
@@ -156,10 +174,7 @@ def test_tp_prefill_then_decode(oracle, tmp_path, no_pdl, q8):
             assert tok_d[0].cpu().tolist() == want_tok
             for b in range(B):
                 want_last[b] = seqs[b].forward(want_tok[b], lens[b] + step).copy()
-            torch.cuda.synchronize()
-            for r in range(tp):
-                ranks[r].decode_step(tok_d[r], pos_d[r], logits[r], nxt[r], advance=True, stream=streams[r])
-            torch.cuda.synchronize()
+            step_all(ranks, streams, lambda r, st: ranks[r].decode_step(tok_d[r], pos_d[r], logits[r], nxt[r], advance=True, stream=st))
             for b in range(B):
                 assert_close(logits[0][b].cpu().numpy(), want_last[b], 1e-4, f"decode after prefill step {step} slot {b}")
         assert pos_d[1].cpu().tolist() == [n + 4 for n in lens]
