@@ -137,43 +137,55 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
 
   const float* kb = p.kc + (size_t)b * p.kv_batch_stride;
   const float* vb = p.vc + (size_t)b * p.kv_batch_stride;
-  for (int t = t0 + warp; t < t1; t += 16) {
-    const bool two = (t + 8) < t1;
-    const float* ka = kb + (size_t)t * p.kv_dim;
-    const float* va = vb + (size_t)t * p.kv_dim;
-    const float* kb2 = two ? ka + (size_t)8 * p.kv_dim : ka;
-    const float* vb2 = two ? va + (size_t)8 * p.kv_dim : va;
-    float4 k_a[J], v_a[J], k_b[J], v_b[J];
+  // A warp takes rows t, t+8, .., t+8(RW-1) per iteration (RW x 2 x J independent 128-bit loads in flight per lane)
+  // and folds them into the running softmax with ONE rescale: exp(m_old - m_new) once per RW rows.  Scores are scaled
+  // by 1/sqrt(hs) (exact for head sizes 16 and 64; 1 ulp from the reference's division otherwise) and exponentials
+  // are ex2.approx-based (__expf, 2 ulp): both far inside the 1e-4 tolerance, and a third of the instructions of the
+  // previous form (this kernel was issue- as well as latency-limited: sm__throughput 50 % at 4.3 TB/s).
+  constexpr int RW = (J <= 2) ? 4 : 2;
+  const float inv_sqrt_hs = 1.0f / sqrt_hs;
+  for (int t = t0 + warp; t < t1; t += 8 * RW) {
+    float4 kr[RW][J], vr[RW][J];
+    bool live[RW];
 #pragma unroll
-    for (int j = 0; j < J; j++) {
-      k_a[j] = ldg_stream(reinterpret_cast<const float4*>(ka + koff[j]));
-      k_b[j] = ldg_stream(reinterpret_cast<const float4*>(kb2 + koff[j]));
+    for (int r = 0; r < RW; r++) {
+      live[r] = (t + 8 * r) < t1;
+      const float* ka = kb + (size_t)(live[r] ? t + 8 * r : t) * p.kv_dim;
+#pragma unroll
+      for (int j = 0; j < J; j++) kr[r][j] = ldg_stream(reinterpret_cast<const float4*>(ka + koff[j]));
+    }
+#pragma unroll
+    for (int r = 0; r < RW; r++) {
+      const float* va = vb + (size_t)(live[r] ? t + 8 * r : t) * p.kv_dim;
+#pragma unroll
+      for (int j = 0; j < J; j++) vr[r][j] = ldg_stream(reinterpret_cast<const float4*>(va + koff[j]));
     }
 #pragma unroll
     for (int j = 0; j < J; j++) {
-      v_a[j] = ldg_stream(reinterpret_cast<const float4*>(va + koff[j]));
-      v_b[j] = ldg_stream(reinterpret_cast<const float4*>(vb2 + koff[j]));
-    }
+      float sc[RW];
 #pragma unroll
-    for (int j = 0; j < J; j++) {
-      float sa = dot4(qv[j], k_a[j], 0.0f);
-      float sb = dot4(qv[j], k_b[j], 0.0f);
+      for (int r = 0; r < RW; r++) sc[r] = dot4(qv[j], kr[r][j], 0.0f);
       for (int o = LH >> 1; o > 0; o >>= 1) {
-        sa += __shfl_xor_sync(THA_FULL_MASK, sa, o);
-        sb += __shfl_xor_sync(THA_FULL_MASK, sb, o);
+#pragma unroll
+        for (int r = 0; r < RW; r++) sc[r] += __shfl_xor_sync(THA_FULL_MASK, sc[r], o);
       }
-      sa /= sqrt_hs;
-      sb = two ? sb / sqrt_hs : -INFINITY;
-      const float mn = fmaxf(m[j], fmaxf(sa, sb));
-      const float corr = expf(m[j] - mn);   // exp(-inf) = 0 on the first step
-      const float pa = expf(sa - mn);
-      const float pb2 = two ? expf(sb - mn) : 0.0f;
-      l[j] = l[j] * corr + pa + pb2;
-      acc[j].x = acc[j].x * corr + pa * v_a[j].x + pb2 * v_b[j].x;
-      acc[j].y = acc[j].y * corr + pa * v_a[j].y + pb2 * v_b[j].y;
-      acc[j].z = acc[j].z * corr + pa * v_a[j].z + pb2 * v_b[j].z;
-      acc[j].w = acc[j].w * corr + pa * v_a[j].w + pb2 * v_b[j].w;
-      m[j] = mn;
+      float mn = m[j];
+#pragma unroll
+      for (int r = 0; r < RW; r++) {
+        sc[r] = live[r] ? sc[r] * inv_sqrt_hs : -INFINITY;
+        mn = fmaxf(mn, sc[r]);
+      }
+      const float corr = __expf(m[j] - mn);   // exp(-inf) = 0 on the first step
+      float ls = l[j] * corr;
+      float4 a = make_float4(acc[j].x * corr, acc[j].y * corr, acc[j].z * corr, acc[j].w * corr);
+#pragma unroll
+      for (int r = 0; r < RW; r++) {
+        const float pr = __expf(sc[r] - mn);  // dead rows: exp(-inf) = 0
+        ls += pr;
+        a.x = fmaf(pr, vr[r][j].x, a.x); a.y = fmaf(pr, vr[r][j].y, a.y);
+        a.z = fmaf(pr, vr[r][j].z, a.z); a.w = fmaf(pr, vr[r][j].w, a.w);
+      }
+      l[j] = ls; acc[j] = a; m[j] = mn;
     }
   }
 

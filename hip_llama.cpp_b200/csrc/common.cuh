@@ -36,6 +36,9 @@ int graph_enabled();   // capture the decode step into a CUDA graph
 
 // Thread-local count of kernels launched (reported by tha_last_step_launches()).
 void count_launch(int n = 1);
+// Development aid (THA_TRACE=1, graphs off): an event after every launch; tha_trace_dump() prints the time between
+// consecutive events per kernel (= its live duration including the gap before it).
+void trace_launch(const void* fn, cudaStream_t st);
 
 // Launch with optional programmatic-dependent-launch attribute.  Kernels launched
 // this way call pdl_wait() before touching anything a previous kernel wrote and
@@ -54,7 +57,9 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
   count_launch();
-  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+  trace_launch(reinterpret_cast<const void*>(kernel), stream);
+  return e;
 }
 
 // ---- device helpers ------------------------------------------------------------------

@@ -61,6 +61,30 @@ int tc_mode();   // -1 auto (B > 8), 0 never, 1 whenever the shape allows
 int advance_launch(cudaStream_t st, int B, int* token, int* pos, const int* next, int seq_len, bool pdl);
 
 static thread_local int g_last_step_launches = 0;
+#define THA_TRY_RC2(expr) do { int _st = (expr); if (_st != THA_STATUS_SUCCESS) return _st; } while (0)
+
+// A step of R >= dual_min_rows() rows is issued as TWO concurrent branches of half the rows each (fork / join inside the
+// captured graph).  Every kernel of the row pipeline costs ~5-10 us of dependent latency whatever its size (launch ->
+// griddepcontrol.wait -> load -> compute -> flush), 9-10 kernels per layer; two independent chains overlap each other's
+// latency and the attention kernel of one (HBM-bound) runs under the matmuls of the other.  The weights are read by
+// both branches; they run a layer apart at most, so the second read is an L2 hit (28 MB per layer of stories110M).
+struct DualPlan { bool on; int B0, B1; Workspace* ws2; cudaStream_t st2; };
+static int dual_plan(Workspace* ws, int B, DualPlan* d) {
+  d->on = false; d->B0 = B; d->B1 = 0; d->ws2 = nullptr; d->st2 = nullptr;
+  const int m = dual_min_rows();
+  if (m <= 0 || B < m || B < 2) return THA_STATUS_SUCCESS;
+  THA_TRY_RC2(ws_ensure_dual(ws));
+  d->on = true; d->B0 = (B + 1) / 2; d->B1 = B - d->B0; d->ws2 = ws->sibling; d->st2 = ws->side_stream;
+  return THA_STATUS_SUCCESS;
+}
+static tha_state_t state_rows(const tha_state_t& s, const tha_config_t& c, int row0) {
+  const int hs = c.dim / c.n_heads, kvd = hs * c.n_kv_heads;
+  const size_t kv_bs = (size_t)c.n_layers * c.seq_len * kvd;
+  tha_state_t t = s;
+  t.x = s.x + (size_t)row0 * c.dim; t.q = s.q + (size_t)row0 * c.dim; t.xb = s.xb + (size_t)row0 * c.dim;
+  t.key_cache = s.key_cache + row0 * kv_bs; t.value_cache = s.value_cache + row0 * kv_bs;
+  return t;
+}
 
 struct StepArgs {
   int B; tha_config_t cfg; tha_weights_f32_t w; tha_state_t s;
@@ -74,6 +98,7 @@ static unsigned long long fnv1a(const void* data, size_t n, unsigned long long h
 }
 
 #define THA_TRY(expr) do { int _st = (expr); if (_st != THA_STATUS_SUCCESS) return _st; } while (0)
+
 
 // Issue the step directly, or (default) capture it once per distinct argument set into a
 // CUDA graph and replay it.  `key`/`key_len`: every value the launches depend on.
@@ -208,12 +233,27 @@ int decode_step_f32(cudaStream_t st, int B, const tha_config_t* cfg, const tha_w
     });
   }
   if (use_tc) {
-    THA_TRY(step_tc_prepare(ws, cfg, B));
-    a.mega = 2;   // part of the graph key
+    DualPlan dp;
+    THA_TRY(dual_plan(ws, B, &dp));
+    THA_TRY(step_tc_prepare(ws, cfg, dp.B0));
+    if (dp.on) THA_TRY(step_tc_prepare(dp.ws2, cfg, dp.B1));
+    a.mega = dp.on ? 3 : 2;   // part of the graph key
     float* lg = logits_d ? logits_d : s->logits;
     return run_step(st, ws, &a, sizeof(a), [&]() {
-      THA_TRY(step_tc_issue(st, ws, B, *cfg, *w, *s, token_d, pos_d, lg, next_d, rc, rs, a.pdl != 0));
-      if (advance) THA_TRY(advance_launch(st, B, const_cast<int*>(token_d), const_cast<int*>(pos_d), next_d, cfg->seq_len, a.pdl != 0));
+      const bool pdl = a.pdl != 0;
+      if (dp.on) {   // the second half of the slots: a concurrent branch
+        THA_CUDA_OK(cudaEventRecord(ws->ev_fork, st));
+        THA_CUDA_OK(cudaStreamWaitEvent(dp.st2, ws->ev_fork, 0));
+        const tha_state_t s2 = state_rows(*s, *cfg, dp.B0);
+        int* nx2 = next_d ? next_d + dp.B0 : nullptr;
+        THA_TRY(step_tc_issue(dp.st2, dp.ws2, dp.B1, *cfg, *w, s2, token_d + dp.B0, pos_d + dp.B0,
+                              lg + (size_t)dp.B0 * cfg->vocab_size, nx2, rc, rs, pdl));
+        if (advance) THA_TRY(advance_launch(dp.st2, dp.B1, const_cast<int*>(token_d) + dp.B0, const_cast<int*>(pos_d) + dp.B0, nx2, cfg->seq_len, pdl));
+        THA_CUDA_OK(cudaEventRecord(ws->ev_join, dp.st2));
+      }
+      THA_TRY(step_tc_issue(st, ws, dp.B0, *cfg, *w, *s, token_d, pos_d, lg, next_d, rc, rs, pdl));
+      if (advance) THA_TRY(advance_launch(st, dp.B0, const_cast<int*>(token_d), const_cast<int*>(pos_d), next_d, cfg->seq_len, pdl));
+      if (dp.on) THA_CUDA_OK(cudaStreamWaitEvent(st, ws->ev_join, 0));
       return (int)THA_STATUS_SUCCESS;
     });
   }
@@ -335,12 +375,26 @@ int decode_step_q8(cudaStream_t st, int B, const tha_config_t* cfg, const tha_we
   // Option "tc" = 0 keeps the GEMV step.
   const int tcm = tc_mode();
   if (tcm != 0 && step_tc_q8_supported(cfg, B, gs)) {
-    THA_TRY(step_tc_q8_prepare(ws, cfg, B, gs));
-    a.tc = 1;   // part of the graph key
+    DualPlan dp;
+    THA_TRY(dual_plan(ws, B, &dp));
+    THA_TRY(step_tc_q8_prepare(ws, cfg, dp.B0, gs));
+    if (dp.on) THA_TRY(step_tc_q8_prepare(dp.ws2, cfg, dp.B1, gs));
+    a.tc = dp.on ? 2 : 1;   // part of the graph key
     float* lg = logits_d ? logits_d : s->logits;
     if (!lg) return THA_STATUS_INVALID_ARG;
     return run_step(st, ws, &a, sizeof(a), [&]() {
-      return step_tc_q8_issue(st, ws, B, *cfg, *w, *s, token_d, pos_d, lg, next_d, rc, rs, a.pdl != 0);
+      const bool pdl = a.pdl != 0;
+      if (dp.on) {
+        THA_CUDA_OK(cudaEventRecord(ws->ev_fork, st));
+        THA_CUDA_OK(cudaStreamWaitEvent(dp.st2, ws->ev_fork, 0));
+        const tha_state_t s2 = state_rows(*s, *cfg, dp.B0);
+        THA_TRY(step_tc_q8_issue(dp.st2, dp.ws2, dp.B1, *cfg, *w, s2, token_d + dp.B0, pos_d + dp.B0,
+                                 lg + (size_t)dp.B0 * cfg->vocab_size, next_d ? next_d + dp.B0 : nullptr, rc, rs, pdl));
+        THA_CUDA_OK(cudaEventRecord(ws->ev_join, dp.st2));
+      }
+      THA_TRY(step_tc_q8_issue(st, ws, dp.B0, *cfg, *w, *s, token_d, pos_d, lg, next_d, rc, rs, pdl));
+      if (dp.on) THA_CUDA_OK(cudaStreamWaitEvent(st, ws->ev_join, 0));
+      return (int)THA_STATUS_SUCCESS;
     });
   }
   const bool fused = attn_fused_supported(cfg->n_heads, hs, cfg->dim, kvd);

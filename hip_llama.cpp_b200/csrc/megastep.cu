@@ -804,7 +804,7 @@ int mega_step_launch(cudaStream_t st, Workspace* ws, int B, const tha_config_t* 
     THA_CUDA_OK(cudaMalloc(&sc.att_cnt, sc.cnt_cap * sizeof(int)));
     THA_CUDA_OK(cudaMemset(sc.att_cnt, 0, sc.cnt_cap * sizeof(int)));
     THA_CUDA_OK(cudaDeviceSynchronize());
-    ws->graphs.clear();
+    ws_drop_graphs(ws);
   }
   if (prepare_only) return THA_STATUS_SUCCESS;
 

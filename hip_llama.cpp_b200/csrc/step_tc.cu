@@ -355,7 +355,7 @@ static int grow(float** p, size_t* cap, size_t need, Workspace* ws) {
   if (*p) THA_CUDA_OK(cudaFree(*p));
   THA_CUDA_OK(cudaMalloc(p, need * sizeof(float)));
   *cap = need;
-  ws->graphs.clear();   // cached graphs captured the old pointers
+  ws_drop_graphs(ws);   // cached graphs captured the old pointers
   gemm_tc_forget();
   return THA_STATUS_SUCCESS;
 }
@@ -474,7 +474,7 @@ static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefil
     if (s.scale) cudaFree(s.scale);
     THA_CUDA_OK(cudaMalloc(&s.scale, (size_t)R * sizeof(float)));
     s.n_b = R;
-    ws->graphs.clear();
+    ws_drop_graphs(ws);
   }
   if (prefill) {
     THA_TRY_RC(grow(&s.xr, &s.n_xr, (size_t)R * c->dim, ws));
@@ -524,6 +524,15 @@ static int gemm_q8(cudaStream_t st, bool pdl, int n_mats, const int8_t* const* W
   return gemm_q8i_launch(st, a, pdl);
 }
 
+// Development aid (THA_SKIP bit mask): leave a class of kernels out of the step to read its LIVE share of the step time off
+// the difference (results are garbage): 1 layer matmuls, 2 attention, 4 prep, 8 RoPE/scatter, 16 SwiGLU / quantise,
+// 32 classifier, 64 argmax.
+static int skip_mask() {
+  static int m = -1;
+  if (m < 0) { const char* v = getenv("THA_SKIP"); m = (v && *v) ? atoi(v) : 0; }
+  return m;
+}
+
 // What differs between a decode step and a prefill chunk.
 struct RowsIO {
   int R;                                   // rows
@@ -570,6 +579,7 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
     }
     if (need > tp->xchg_floats || !tp->connected || tp->hidden_of[tp->rank] != hd) return THA_STATUS_INVALID_ARG;
   }
+  const int skip = skip_mask();
   int xk = 0;   // exchanges issued so far in this step
   auto peers_of = [&](int which, bool w2) -> TpPeers {
     TpPeers t = {};
@@ -588,6 +598,7 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
   // the (fused RMSNorm +) split that feeds a matmul whose input is the residual stream
   auto prep = [&](int rows, const float* part, int nz, long long zs, const float* emb, const float* gain, const int* gather,
                   const TpPeers& tpp) -> int {
+    if (skip & 4) return THA_STATUS_SUCCESS;
     if (wq) {
       THA_CUDA_OK(launch(tc_prep_q8_kernel, dim3(rows), dim3(prep_threads), 0, st, pdl, io.x, part, nz, zs, emb, io.token,
                          io.pos, gain, d, gs, sc.xq, sc.xsT, ldxs, gather, tpp));
@@ -602,6 +613,8 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
   auto mm = [&](int n, const float* const* W, const tha_qtensor_t* const* Q, int l, const int* M, const int* off,
                 int K, const float* xh, const float* xl, int N, float* out, long long ldo, long long zs, int z,
                 const float* colscale) -> int {
+    if ((skip & 1) && out != io.logits) return THA_STATUS_SUCCESS;
+    if ((skip & 32) && out == io.logits) return THA_STATUS_SUCCESS;
     if (!wq) return gemm(st, pdl, n, W, M, off, K, xh, xl, N, out, ldo, zs, z, colscale);
     const int8_t* q[3]; const float* sc3[3];
     for (int i = 0; i < n; i++) {
@@ -626,6 +639,7 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
       const int M[3] = {da, kvd, kvd}, off[3] = {0, da, da + kvd};
       THA_TRY_RC(mm(3, W, Q, l, M, off, d, sc.xh, sc.xl, R, sc.part, ld_qkv, (long long)R * ld_qkv, pl.z_qkv, sc.scale));
     }
+    if (!(skip & 8))
     THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld_qkv / 2, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part,
                        pl.z_qkv, (long long)R * ld_qkv, ld_qkv, io.pos, da, kvd, hs, rc, rs, io.q, s.key_cache, s.value_cache,
                        kv_bs, loff, io.slot));
@@ -633,7 +647,8 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
       if (tpx) THA_CUDA_OK(launch(tp_epoch_kernel, dim3(1), dim3(32), 0, st, pdl, tp->epoch()));
       return THA_STATUS_SUCCESS;
     }
-    if (io.n_tiles > 0) {
+    if (skip & 2) {
+    } else if (io.n_tiles > 0) {
       THA_TRY_RC(attn_prefill_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, wq ? nullptr : sc.xh,
                                      wq ? nullptr : sc.xl, s.key_cache + loff, s.value_cache + loff, kv_bs, io.slot, io.pos,
                                      io.tile_row0, io.tile_n, pdl));
@@ -641,7 +656,8 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
       THA_TRY_RC(attn_fused_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, s.key_cache + loff,
                                    s.value_cache + loff, kv_bs, hs, c.seq_len, pdl, wq ? nullptr : sc.xh, wq ? nullptr : sc.xl));
     }
-    if (wq)   // runq.c:437: the attention output is quantised before wo
+    if (skip & 16) {
+    } else if (wq)   // runq.c:437: the attention output is quantised before wo
       THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(da / 4, 256), R), dim3(256), 0, st, pdl, (const float*)io.xb, (long long)da,
                          0, 0LL, 0, io.pos, da, gs, sc.xq, sc.xsT, ldxs));
     {
@@ -657,7 +673,8 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
       const int M[2] = {hd, hd}, off[2] = {0, hd};
       THA_TRY_RC(mm(2, W, Q, l, M, off, d, sc.xh, sc.xl, R, sc.part, ld_h, (long long)R * ld_h, pl.z_w13, sc.scale));
     }
-    if (wq)   // runq.c:457-465: SwiGLU, then quantise hb
+    if (skip & 16) {
+    } else if (wq)   // runq.c:457-465: SwiGLU, then quantise hb
       THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(hd / 4, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part,
                          (long long)ld_h, pl.z_w13, (long long)R * ld_h, hd, io.pos, hd, gs, sc.hq, sc.hsT, ldxs));
     else
@@ -682,7 +699,7 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
     const int M[1] = {c.vocab_size}, off[1] = {0};
     THA_TRY_RC(mm(1, W, Q, 0, M, off, d, sc.xh, sc.xl, io.n_out, io.logits, c.vocab_size, 0, 1, sc.scale));
   }
-  if (io.next) THA_TRY_RC(argmax_launch(st, io.n_out, io.logits, c.vocab_size, io.next, pdl));
+  if (io.next && !(skip & 64)) THA_TRY_RC(argmax_launch(st, io.n_out, io.logits, c.vocab_size, io.next, pdl));
   if (tpx) THA_CUDA_OK(launch(tp_epoch_kernel, dim3(1), dim3(32), 0, st, pdl, tp->epoch()));
   return THA_STATUS_SUCCESS;
 }

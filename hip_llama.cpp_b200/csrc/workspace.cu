@@ -4,6 +4,8 @@
 #include <string.h>
 
 #include <mutex>
+#include <string>
+#include <vector>
 
 #include "common.cuh"
 #include "workspace.h"
@@ -41,9 +43,31 @@ int tc_mode() {
   return g_tc;
 }
 int* opt_tc() { return &g_tc; }
+static int g_dual = -2;
+int dual_min_rows() {
+  // off by default: measured slower (tools/dual_sweep.sh) -- the matmuls are persistent full-GPU kernels, two branches
+  // only serialise smaller ones
+  if (g_dual == -2) { const char* v = getenv("THA_DUAL"); g_dual = (v && *v) ? atoi(v) : 0; }
+  return g_dual;
+}
+int* opt_dual() { return &g_dual; }
 void count_launch(int n) { g_launches += n; }
 int launches_reset() { int v = g_launches; g_launches = 0; return v; }
 int launches_get() { return g_launches; }
+
+static int g_trace = -1;
+static std::vector<std::pair<const void*, cudaEvent_t>> g_trace_ev;
+void trace_launch(const void* fn, cudaStream_t st) {
+  if (g_trace < 0) g_trace = env_flag("THA_TRACE", 0);
+  if (!g_trace) return;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) { cudaGetLastError(); return; }
+  cudaEvent_t ev;
+  if (cudaEventCreate(&ev) != cudaSuccess) return;
+  cudaEventRecord(ev, st);
+  std::lock_guard<std::mutex> lk(g_mu);
+  g_trace_ev.emplace_back(fn, ev);
+}
 
 Workspace* workspace() {
   int dev = -1;
@@ -57,6 +81,18 @@ Workspace* workspace() {
   return ws;
 }
 
+int ws_ensure_dual(Workspace* ws) {
+  if (ws->sibling) return THA_STATUS_SUCCESS;
+  Workspace* sib = new Workspace();
+  sib->device = ws->device;
+  sib->parent = ws;
+  THA_CUDA_OK(cudaStreamCreateWithFlags(&ws->side_stream, cudaStreamNonBlocking));
+  THA_CUDA_OK(cudaEventCreateWithFlags(&ws->ev_fork, cudaEventDisableTiming));
+  THA_CUDA_OK(cudaEventCreateWithFlags(&ws->ev_join, cudaEventDisableTiming));
+  ws->sibling = sib;
+  return THA_STATUS_SUCCESS;
+}
+
 int ws_ensure_attn(Workspace* ws, size_t part_slots, int n_counters) {
   if (part_slots > ws->part_cap) {
     if (ws->part_acc) { cudaFree(ws->part_acc); cudaFree(ws->part_ml); }
@@ -64,7 +100,7 @@ int ws_ensure_attn(Workspace* ws, size_t part_slots, int n_counters) {
     THA_CUDA_OK(cudaMalloc(&ws->part_acc, cap * sizeof(float4)));
     THA_CUDA_OK(cudaMalloc(&ws->part_ml, cap * sizeof(float2)));
     ws->part_cap = cap;
-    ws->graphs.clear();  // cached graphs captured the old pointers
+    ws_drop_graphs(ws);  // cached graphs captured the old pointers
   }
   if (n_counters > ws->counters_cap) {
     if (ws->counters) cudaFree(ws->counters);
@@ -72,7 +108,7 @@ int ws_ensure_attn(Workspace* ws, size_t part_slots, int n_counters) {
     THA_CUDA_OK(cudaMalloc(&ws->counters, cap * sizeof(int)));
     THA_CUDA_OK(cudaMemset(ws->counters, 0, cap * sizeof(int)));
     ws->counters_cap = cap;
-    ws->graphs.clear();
+    ws_drop_graphs(ws);
   }
   return THA_STATUS_SUCCESS;
 }
@@ -87,7 +123,7 @@ int ws_ensure_tokpos(Workspace* ws, int n_batches) {
   THA_CUDA_OK(cudaMallocHost(&ws->tokpos_h, 3 * cap * sizeof(int)));
   ws->next_h = ws->tokpos_h + 2 * cap;
   ws->tokpos_cap = cap;
-  ws->graphs.clear();
+  ws_drop_graphs(ws);
   return THA_STATUS_SUCCESS;
 }
 
@@ -99,7 +135,7 @@ int ws_ensure_q8(Workspace* ws, int n_batches, int kmax, int gs) {
   (void)gs;   // groups are at least 16 values (the kernel's requirement): need / 16 scales always suffice
   THA_CUDA_OK(cudaMalloc(&ws->q8_xs, (need / 16 + 1) * sizeof(float)));
   ws->q8_cap = need;
-  ws->graphs.clear();
+  ws_drop_graphs(ws);
   return THA_STATUS_SUCCESS;
 }
 
@@ -146,6 +182,34 @@ extern "C" int tha_set_option(const char* name, int value) {
   if (!strcmp(name, "pdl")) { *tha::opt_pdl() = value != 0; return THA_STATUS_SUCCESS; }
   if (!strcmp(name, "graph")) { *tha::opt_graph() = value != 0; return THA_STATUS_SUCCESS; }
   if (!strcmp(name, "tc")) { *tha::opt_tc() = value; return THA_STATUS_SUCCESS; }
+  if (!strcmp(name, "dual")) { tha::dual_min_rows(); *tha::opt_dual() = value; return THA_STATUS_SUCCESS; }
   if (!strcmp(name, "mega")) { tha::mega_set_enabled(value); return THA_STATUS_SUCCESS; }
   return THA_STATUS_INVALID_ARG;
+}
+
+// Development aid: per-kernel live time (event to event) of everything launched since the last dump; skips the first
+// `skip` launches.  Prints "name  count  avg_us  total_us" lines to stdout.
+extern "C" int tha_trace_dump(int skip) {
+  cudaDeviceSynchronize();
+  std::map<std::string, std::pair<int, double>> agg;
+  double total = 0.0;
+  {
+    std::lock_guard<std::mutex> lk(tha::g_mu);
+    auto& v = tha::g_trace_ev;
+    for (size_t i = 1; i < v.size(); i++) {
+      if ((int)i < skip) continue;
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, v[i - 1].second, v[i].second) != cudaSuccess) { cudaGetLastError(); continue; }
+      const char* name = nullptr;
+      if (cudaFuncGetName(&name, v[i].first) != cudaSuccess || !name) { cudaGetLastError(); name = "?"; }
+      auto& a = agg[std::string(name).substr(0, 60)];
+      a.first++; a.second += ms * 1e3; total += ms * 1e3;
+    }
+    for (auto& e : v) cudaEventDestroy(e.second);
+    v.clear();
+  }
+  for (auto& kv : agg) printf("%-62s n=%5d avg %8.2f us total %10.1f us (%.1f%%)\n", kv.first.c_str(), kv.second.first, kv.second.second / kv.second.first, kv.second.second, 100.0 * kv.second.second / total);
+  printf("total %.1f us\n", total);
+  fflush(stdout);
+  return 0;
 }

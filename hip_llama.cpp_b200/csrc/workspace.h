@@ -33,12 +33,22 @@ struct Workspace {
   std::map<std::pair<int, int>, RopeTable> rope;
   // cached graphs of the decode step keyed by a hash of every launch argument
   std::map<unsigned long long, StepGraph> graphs;
+  // two half-batches of a step as two concurrent branches of the graph (forward.cu, "dual"): the second branch's
+  // scratch owner, its stream and the fork / join events
+  Workspace* sibling = nullptr;
+  Workspace* parent = nullptr;            // set on a sibling: graphs that captured its pointers live in the parent
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
 Workspace* workspace();   // for the current device (thread-safe)
 int ws_ensure_attn(Workspace* ws, size_t part_slots, int n_counters);
 int ws_ensure_tokpos(Workspace* ws, int n_batches);
 int ws_ensure_q8(Workspace* ws, int n_batches, int kmax, int gs);
+int ws_ensure_dual(Workspace* ws);
+// cached graphs captured pointers that are about to change
+inline void ws_drop_graphs(Workspace* ws) { ws->graphs.clear(); if (ws->parent) ws->parent->graphs.clear(); }
+int dual_min_rows();   // rows from which a step is issued as two concurrent half-batches (0 = never)
 int ws_rope(Workspace* ws, int head_size, int seq_len, const float** cos_d, const float** sin_d);
 
 }  // namespace tha

@@ -271,6 +271,7 @@ int tha_tp_prefill_q8(void* stream, tha_tp_t* tp, const tha_config_t* cfg_local,
                       const tha_state_t* s_local, int n_seqs, const int* slot_host, const int* pos0_host,
                       const int* len_host, const int* tokens_host, float* logits_d, int* next_d);
 
+int tha_trace_dump(int skip);   /* development aid: THA_TRACE=1 + graphs off -> live per-kernel times (event to event) */
 int tha_step_needs_att_scratch(const tha_config_t* cfg);
 /* number of kernels the last tha_decode_step_* call on this thread launched */
 int tha_last_step_launches(void);
