@@ -293,6 +293,8 @@ def run_ours(args, rank, world, local_rank):
     # ---------------- e2e: the reference-facing call with HOST buffers ----------------
     e2e = None
     if not args.no_e2e and tp == 1:
+        # the host-side greedy sampler gets this rank's share of the box's cores (torchrun pins OMP_NUM_THREADS to 1)
+        torch.set_num_threads(max(1, host_cores() // max(world, 1)))
         lg_host = torch.empty(B, cfg.vocab_size, dtype=torch.float32).pin_memory()
         tok_h = tok0.copy()
         pos_h = np.zeros(B, np.int32)
