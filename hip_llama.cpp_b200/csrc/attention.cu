@@ -87,11 +87,17 @@ struct AttnP {
   int nseg, nsplit;
   float4* part_acc; float2* part_ml; int* counters;
   float* out_hi; float* out_lo;             // nullable: the tf32 hi/lo split of `out` for the tensor-core wo matmul
+  int8_t* out_q; float* out_sT; int ldxs, gs;   // nullable: `out` quantised per group (runq.c:145-171) for the int8 wo matmul
 };
 
 __device__ __forceinline__ float attn_tf32(float v) { return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u); }
-__device__ __forceinline__ void attn_store(const AttnP& p, float* outp, float4 r) {
+// called by whole warps (the group maxima of the quantiser are shuffles)
+__device__ __forceinline__ void attn_store(const AttnP& p, float* outp, float4 r, int b) {
   *reinterpret_cast<float4*>(outp) = r;
+  if (p.out_q) {
+    const int i4 = (int)((outp - p.out) - (size_t)b * p.dim) >> 2;
+    q8_quant4(r, p.gs, i4, p.out_q + (size_t)b * p.dim, p.out_sT, p.ldxs, b, true);
+  }
   if (p.out_hi) {
     const size_t off = outp - p.out;
     const float4 h = make_float4(attn_tf32(r.x), attn_tf32(r.y), attn_tf32(r.z), attn_tf32(r.w));
@@ -112,7 +118,12 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   pdl_trigger();
   const int b = blockIdx.x, seg = blockIdx.y, split = blockIdx.z;
   const int pb = p.pos[b];
-  if (pb < 0) return;
+  if (pb < 0) {   // idle slot: the int8 matmul that follows gets zeros (as the stand-alone quantiser gave it)
+    if (p.out_q && split == 0 && threadIdx.x < F)
+      q8_quant4(make_float4(0.f, 0.f, 0.f, 0.f), p.gs, (seg * (128 * J) >> 2) + threadIdx.x, p.out_q + (size_t)b * p.dim, p.out_sT,
+                p.ldxs, b, true);
+    return;
+  }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int hs = p.head_size, LH = hs >> 2;  // lanes per head
   const float sqrt_hs = sqrtf((float)hs);
@@ -214,7 +225,7 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   }
   float* outp = p.out + (size_t)b * p.dim + seg * (128 * J) + 4 * f;
   if (p.nsplit == 1) {
-    if (f < F) attn_store(p, outp, make_float4(A.x / L, A.y / L, A.z / L, A.w / L));
+    if (f < F) attn_store(p, outp, make_float4(A.x / L, A.y / L, A.z / L, A.w / L), b);
     return;
   }
 
@@ -245,7 +256,7 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
       GL += ml.y * e;
       GA.x += a.x * e; GA.y += a.y * e; GA.z += a.z * e; GA.w += a.w * e;
     }
-    attn_store(p, outp, make_float4(GA.x / GL, GA.y / GL, GA.z / GL, GA.w / GL));
+    attn_store(p, outp, make_float4(GA.x / GL, GA.y / GL, GA.z / GL, GA.w / GL), b);
   }
   if (threadIdx.x == 0) p.counters[b * p.nseg + seg] = 0;  // self-reset for the next launch
 }
@@ -308,12 +319,15 @@ int attn_fused_nsplit(int B, int nseg, int seq_len) {
 // kc / vc are the caches already offset to the layer (base + loff).
 int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
-                      int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo) {
+                      int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo, int8_t* out_q, float* out_sT,
+                      int ldxs, int gs) {
   const int dim = n_heads * head_size, kv_dim = n_kv_heads * head_size;
   const int J = fused_J(n_heads, head_size, dim, n_heads / n_kv_heads);
   if (!J || kv_dim % 4) return THA_STATUS_NOT_SUPPORTED;
   AttnP p;
   p.pos = pos_d; p.q = q; p.out = out; p.kc = kc; p.vc = vc; p.out_hi = out_hi; p.out_lo = out_lo;
+  p.out_q = out_q; p.out_sT = out_sT; p.ldxs = ldxs; p.gs = gs;
+  if (out_q && (gs < 32 || gs > 128 || (gs & (gs - 1)) || 128 % gs)) return THA_STATUS_NOT_SUPPORTED;
   p.kv_batch_stride = kv_batch_stride; p.kv_dim = kv_dim; p.head_size = head_size;
   p.kv_mul = n_heads / n_kv_heads; p.dim = dim;
   p.nseg = dim / (128 * J);
@@ -407,5 +421,5 @@ extern "C" int tha_mha_fused_v1_f32(void* stream, int n_batches, const int* pos_
   if (!ws) return THA_STATUS_EXECUTION_FAILED;
   const int kv_dim = n_kv_heads * head_size;
   return attn_fused_launch((cudaStream_t)stream, ws, n_batches, pos_d, n_heads, n_kv_heads, q, xb, key_cache + loff,
-                           value_cache + loff, (long long)n_layers * seq_len * kv_dim, head_size, seq_len, false, nullptr, nullptr);
+                           value_cache + loff, (long long)n_layers * seq_len * kv_dim, head_size, seq_len, false, nullptr, nullptr, nullptr, nullptr, 0, 0);
 }

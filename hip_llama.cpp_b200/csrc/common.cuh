@@ -138,6 +138,31 @@ __device__ __forceinline__ float dot4(const float4& a, const float4& b, float ac
   return acc;
 }
 
+// The runq.c:145-171 quantiser on float4 lanes (scale = max|x| / 127 per group, round half away from zero; bit-exact).
+// Four consecutive values per thread, a group = gs/4 consecutive lanes (8, 16 or 32): the group maximum is a
+// segmented shuffle reduction, the four int8 results leave as one 32-bit store.  v = the thread's values (index i4 in
+// units of float4 within the row).  scale -> xsT[g * ldxs + row] (transposed: the matmul's epilogue wants the NT scales
+// of a group side by side).
+// Called by whole warps (lanes past the row pass valid = false and zeros).
+__device__ __forceinline__ void q8_quant4(float4 v, int gs, int i4, int8_t* __restrict__ xq_row, float* __restrict__ xsT,
+                                          int ldxs, int row, bool valid) {
+  float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+  for (int o = gs >> 3; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(THA_FULL_MASK, amax, o));
+  const float scale = __fdiv_rn(amax, 127.0f);
+  if (!valid) return;
+  const int g = (4 * i4) / gs;
+  if (((4 * i4) % gs) == 0) xsT[(size_t)g * ldxs + row] = scale;
+  const float in[4] = {v.x, v.y, v.z, v.w};
+  unsigned int packed = 0;
+#pragma unroll
+  for (int e = 0; e < 4; e++) {
+    const float r = __fdiv_rn(in[e], scale);
+    const int q = (r != r) ? 0 : __float2int_rn(roundf(r));
+    packed |= ((unsigned int)q & 0xFFu) << (8 * e);
+  }
+  *reinterpret_cast<unsigned int*>(xq_row + 4 * i4) = packed;
+}
+
 #endif  // __CUDACC__
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

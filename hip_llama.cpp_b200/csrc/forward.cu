@@ -27,7 +27,8 @@ bool attn_fused_supported(int n_heads, int head_size, int dim, int kv_dim);
 int attn_fused_prepare(Workspace* ws, int B, int n_heads, int n_kv_heads, int head_size, int seq_len);
 int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
-                      int head_size, int seq_len, bool pdl, float* out_hi = nullptr, float* out_lo = nullptr);
+                      int head_size, int seq_len, bool pdl, float* out_hi = nullptr, float* out_lo = nullptr,
+                      int8_t* out_q = nullptr, float* out_sT = nullptr, int ldxs = 0, int gs = 0);
 int launches_reset();
 int launches_get();
 // megastep.cu: the whole step as one persistent kernel (small models, B <= 8)

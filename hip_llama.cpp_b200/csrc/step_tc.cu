@@ -36,7 +36,8 @@ bool attn_fused_supported(int n_heads, int head_size, int dim, int kv_dim);
 int attn_fused_prepare(Workspace* ws, int B, int n_heads, int n_kv_heads, int head_size, int seq_len);
 int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
-                      int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo);
+                      int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo, int8_t* out_q = nullptr,
+                      float* out_sT = nullptr, int ldxs = 0, int gs = 0);
 
 bool attn_prefill_supported(int head_size, int kv_dim);
 int attn_prefill_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_heads, int head_size, const float* q,
@@ -215,30 +216,7 @@ __global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __res
 // round half away from zero) -- the int8 values and scales are bit-identical to q8_prep_kernel's for the same input --
 // and handed to the int8 tensor-core matmul (gemm_q8i_kernel) as int8 rows + transposed group scales.
 
-// Four consecutive values per thread, a group = gs/4 consecutive lanes (8, 16 or 32): the group maximum is a
-// segmented shuffle reduction, the four int8 results leave as one 32-bit store.  v = the thread's values (index i4 in
-// units of float4 within the row).  scale -> xsT[g * ldxs + row] (transposed: the matmul's epilogue wants the NT scales
-// of a group side by side).
-// Called by whole warps (lanes past the row pass valid = false and zeros).
-__device__ __forceinline__ void q8_quant4(float4 v, int gs, int i4, int8_t* __restrict__ xq_row, float* __restrict__ xsT,
-                                          int ldxs, int row, bool valid) {
-  float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
-  for (int o = gs >> 3; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(THA_FULL_MASK, amax, o));
-  const float scale = __fdiv_rn(amax, 127.0f);
-  if (!valid) return;
-  const int g = (4 * i4) / gs;
-  if (((4 * i4) % gs) == 0) xsT[(size_t)g * ldxs + row] = scale;
-  const float in[4] = {v.x, v.y, v.z, v.w};
-  unsigned int packed = 0;
-#pragma unroll
-  for (int e = 0; e < 4; e++) {
-    const float r = __fdiv_rn(in[e], scale);
-    const int q = (r != r) ? 0 : __float2int_rn(roundf(r));
-    packed |= ((unsigned int)q & 0xFFu) << (8 * e);
-  }
-  *reinterpret_cast<unsigned int*>(xq_row + 4 * i4) = packed;
-}
-
+// q8_quant4 (common.cuh): four consecutive values per thread, a group = gs/4 consecutive lanes.
 // One block per output row (up to 1024 threads, one or more float4 per thread, all loads of a thread independent):
 // x row = embedding row or x + sum of partials (written back), RMSNorm in the reference's order w * (ss * x)
 // (run.cc:196-209), group quantisation.  gs in {32, 64, 128}; d % gs == 0.
@@ -653,11 +631,13 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
                                      wq ? nullptr : sc.xl, s.key_cache + loff, s.value_cache + loff, kv_bs, io.slot, io.pos,
                                      io.tile_row0, io.tile_n, pdl));
     } else {
+      // Q8_0: the quantiser of the attention output (runq.c:437) runs in the attention kernel's final store
       THA_TRY_RC(attn_fused_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, s.key_cache + loff,
-                                   s.value_cache + loff, kv_bs, hs, c.seq_len, pdl, wq ? nullptr : sc.xh, wq ? nullptr : sc.xl));
+                                   s.value_cache + loff, kv_bs, hs, c.seq_len, pdl, wq ? nullptr : sc.xh, wq ? nullptr : sc.xl,
+                                   wq ? sc.xq : nullptr, wq ? sc.xsT : nullptr, ldxs, gs));
     }
-    if (skip & 16) {
-    } else if (wq)   // runq.c:437: the attention output is quantised before wo
+    if ((skip & 16) || (wq && io.n_tiles == 0 && !(skip & 2))) {
+    } else if (wq)   // prompt rows: runq.c:437 as its own launch
       THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(da / 4, 256), R), dim3(256), 0, st, pdl, (const float*)io.xb, (long long)da,
                          0, 0LL, 0, io.pos, da, gs, sc.xq, sc.xsT, ldxs));
     {
