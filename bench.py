@@ -290,6 +290,45 @@ def run_ours(args, rank, world, local_rank):
     achieved = total_bytes / (ms * 1e-3) / 1e9
     peak, peak_src = measured_peak()
 
+    # ---------------- the dominant kernel of a long-context step, alone: decode attention ----------------
+    # (tha_mha_fused_v1_f32 = attn_fused_kernel over the KV cache this run just filled; one launch per layer so every
+    #  launch streams a different layer's rows: no L2 reuse between launches when a layer's rows exceed the L2)
+    attn = None
+    if tp == 1:
+        try:
+            import ctypes as C
+            lib = e.lib
+            hs = cfg.dim // cfg.n_heads
+            kvd = hs * cfg.n_kv_heads
+            pos_last = args.pos0 + W + K - 1
+            with torch.cuda.stream(stream):
+                posk = torch.full((B,), pos_last, dtype=torch.int32, device=device)
+                vp = lambda t: C.c_void_p(t.data_ptr())
+                lib.c.tha_mha_fused_v1_f32.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                                       C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]
+                def attn_layer(l):
+                    lib.check(lib.c.tha_mha_fused_v1_f32(C.c_void_p(stream.cuda_stream), B, vp(posk), cfg.n_heads, cfg.n_kv_heads,
+                                                         cfg.n_layers, vp(e.state.q), vp(e.state.xb), vp(e.state.key_cache),
+                                                         vp(e.state.value_cache), hs, cfg.seq_len, l * cfg.seq_len * kvd), "tha_mha_fused_v1_f32")
+                reps = 4
+                for l in range(cfg.n_layers):
+                    attn_layer(l)
+                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a0.record(stream)
+                for _ in range(reps):
+                    for l in range(cfg.n_layers):
+                        attn_layer(l)
+                a1.record(stream)
+                stream.synchronize()
+            us = a0.elapsed_time(a1) * 1e3 / (reps * cfg.n_layers)
+            nbytes = B * 2 * kvd * 4 * (pos_last + 1)
+            attn = {"kernel": "attn_fused_kernel (decode attention of one layer, all slots at position %d)" % pos_last,
+                    "bytes_per_launch": nbytes, "us_per_launch": us, "achieved": nbytes / us / 1e3, "unit": "GB/s",
+                    "frac": nbytes / us / 1e3 / peak,
+                    "l2": "a layer's rows: %.0f MB vs 126 MB L2; launches cycle over the %d layers" % (nbytes / 1e6, cfg.n_layers)}
+        except Exception as ex:   # a diagnostic, never the reason a bench line is missing
+            attn = {"kernel": "attn_fused_kernel", "error": str(ex)}
+
     # ---------------- e2e: the reference-facing call with HOST buffers ----------------
     e2e = None
     if not args.no_e2e and tp == 1:
@@ -319,7 +358,7 @@ def run_ours(args, rank, world, local_rank):
                "api": "tha_forward_batch_%s (thaDNN_s_forward_batch)" % args.quant}
     return dict(cfg=cfg, value=value, ms_per_step=ms_max / K, achieved=achieved, peak=peak, peak_src=peak_src,
                 bytes_per_step=total_bytes / K, wbytes=wbytes, clocks=clocks, e2e=e2e,
-                launches=launches_per_step * K, launches_per_step=launches_per_step, host_w=host_w)
+                launches=launches_per_step * K, launches_per_step=launches_per_step, host_w=host_w, attn=attn)
 
 
 # ------------------------------------------------------------------ the reference's CPU path ----
@@ -447,7 +486,8 @@ def main():
                             "kernel": ("mega_step_kernel (whole decode step, 1 persistent launch)" if r["launches_per_step"] == 1 else
                                        "decode step (%d kernels per step, CUDA-graph replay)" % r["launches_per_step"]),
                             "bytes_per_step": r["bytes_per_step"], "peak_source": r["peak_src"],
-                            "frac_of_nominal_8TBs": r["achieved"] / 8000.0}
+                            "frac_of_nominal_8TBs": r["achieved"] / 8000.0,
+                            "dominant_kernel_alone": r["attn"]}
         if not args.no_cpu_baseline:
             try:
                 if args.model == "7b":
