@@ -356,6 +356,26 @@ def run_ours(args, rank, world, local_rank):
         e2e = {"value": world * B * Ke / dt, "unit": UNIT, "h2d_bytes_per_step": int(2 * 4 * B),
                "d2h_bytes_per_step": int(B * cfg.vocab_size * 4), "steps": Ke,
                "api": "tha_forward_batch_%s (thaDNN_s_forward_batch)" % args.quant}
+        # the additive greedy form of the same call (argmax on the device, B ints back): what the shipped driver uses at -t 0
+        tok_h[:] = tok0
+        pos_h[:] = 0
+        nx_h = np.zeros(B, np.int32)
+
+        def gstep():
+            e.forward_greedy(tok_h, pos_h, nx_h, stream=stream)
+            tok_h[:] = nx_h
+            pos_h[:] += 1
+
+        for _ in range(W):
+            gstep()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(Ke):
+            gstep()
+        torch.cuda.synchronize()
+        dtg = load_pkg("dp").max_over_ranks(time.perf_counter() - t0, device)
+        e2e["greedy_call"] = {"value": world * B * Ke / dtg, "unit": UNIT, "h2d_bytes_per_step": int(2 * 4 * B),
+                              "d2h_bytes_per_step": int(4 * B), "api": "tha_forward_greedy_%s (additive: forward + sample_argmax)" % args.quant}
     return dict(cfg=cfg, value=value, ms_per_step=ms_max / K, achieved=achieved, peak=peak, peak_src=peak_src,
                 bytes_per_step=total_bytes / K, wbytes=wbytes, clocks=clocks, e2e=e2e,
                 launches=launches_per_step * K, launches_per_step=launches_per_step, host_w=host_w, attn=attn)

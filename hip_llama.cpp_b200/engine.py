@@ -209,6 +209,19 @@ class Engine:
         self.lib.check(st, "tha_forward_batch")
         return logits_host
 
+    def forward_greedy(self, tokens, pos, next_host=None, stream=None):
+        """thaDNN_s_forward_batch + sample_argmax (src/llama.cpp:275-286) in one call: HOST token/pos in, HOST next
+        token per slot out (argmax on the device; B ints cross PCIe instead of B*vocab floats)."""
+        tok = np.ascontiguousarray(tokens, dtype=np.int32)
+        ps = np.ascontiguousarray(pos, dtype=np.int32)
+        if next_host is None:
+            next_host = np.zeros(self.B, np.int32)
+        fn = self.lib.c.tha_forward_greedy_q8 if self.q8 else self.lib.c.tha_forward_greedy_f32
+        st = fn(_stream_ptr(stream), self.B, C.byref(self.ccfg), C.byref(self.w.c), C.byref(self.state.c),
+                tok.ctypes.data_as(C.c_void_p), ps.ctypes.data_as(C.c_void_p), next_host.ctypes.data_as(C.c_void_p))
+        self.lib.check(st, "tha_forward_greedy")
+        return next_host
+
     def decode_step(self, token_d, pos_d, logits_d=None, next_d=None, stream=None):
         """Resident step: device token/pos, optional device logits and greedy next tokens."""
         fn = self.lib.c.tha_decode_step_q8 if self.q8 else self.lib.c.tha_decode_step_f32
