@@ -328,6 +328,16 @@ struct TcScratch {
 static std::map<Workspace*, TcScratch> g_tc_scratch;   // per workspace (= per device, or per tensor-parallel rank)
 static std::mutex g_tc_scratch_mu;
 
+void step_tc_release(Workspace* ws) {
+  std::lock_guard<std::mutex> lk(g_tc_scratch_mu);
+  auto it = g_tc_scratch.find(ws);
+  if (it == g_tc_scratch.end()) return;
+  TcScratch& s = it->second;
+  void* ptrs[] = {s.xh, s.xl, s.hh, s.hl, s.scale, s.part, s.xr, s.qr, s.xbr, s.tab, s.xq, s.hq, s.xsT, s.hsT};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  g_tc_scratch.erase(it);
+}
+
 static int grow(float** p, size_t* cap, size_t need, Workspace* ws) {
   if (need <= *cap) return THA_STATUS_SUCCESS;
   if (*p) THA_CUDA_OK(cudaFree(*p));
@@ -402,6 +412,18 @@ static TcPlan make_plan(const Dims& m, int R, bool q8, int gs = 64) {
   p.z_wo = plan_z(ceil_div(d, 128), da, R, q8, gs);
   p.z_w13 = plan_z(2 * ceil_div(hd, 128), d, R, q8, gs);
   p.z_w2 = plan_z(ceil_div(d, 128), hd, R, q8, gs);
+  {   // development aid: THA_TC_Z="qkv,wo,w13,w2" overrides the planner (0 keeps its choice)
+    static int ov[4] = {-1, 0, 0, 0};
+    if (ov[0] < 0) {
+      ov[0] = 0;
+      const char* v = getenv("THA_TC_Z");
+      if (v && *v) sscanf(v, "%d,%d,%d,%d", &ov[0], &ov[1], &ov[2], &ov[3]);
+    }
+    if (ov[0] > 0) p.z_qkv = ov[0];
+    if (ov[1] > 0) p.z_wo = ov[1];
+    if (ov[2] > 0) p.z_w13 = ov[2];
+    if (ov[3] > 0) p.z_w2 = ov[3];
+  }
   size_t m_ = (size_t)p.z_qkv * (da + 2 * kvd);
   if ((size_t)p.z_wo * d > m_) m_ = (size_t)p.z_wo * d;
   if ((size_t)p.z_w13 * 2 * hd > m_) m_ = (size_t)p.z_w13 * 2 * hd;

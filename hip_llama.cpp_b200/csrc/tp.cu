@@ -118,7 +118,7 @@ extern "C" int tha_tp_destroy(tha_tp_t* t) {
   if (!t) return THA_STATUS_SUCCESS;
   TpCtx& c = t->c;
   cudaDeviceSynchronize();
-  for (auto& g : c.ws.graphs) if (g.second.exec) cudaGraphExecDestroy(g.second.exec);
+  ws_release(&c.ws);
   for (int r = 0; r < c.tp; r++) if (c.ipc_opened[r]) cudaIpcCloseMemHandle(c.peer[r]);
   if (c.base) cudaFree(c.base);
   delete t;

@@ -81,6 +81,17 @@ Workspace* workspace() {
   return ws;
 }
 
+void ws_release(Workspace* ws) {
+  ws_drop_graphs(ws);
+  step_tc_release(ws);
+  if (ws->part_acc) { cudaFree(ws->part_acc); cudaFree(ws->part_ml); ws->part_acc = nullptr; ws->part_ml = nullptr; ws->part_cap = 0; }
+  if (ws->counters) { cudaFree(ws->counters); ws->counters = nullptr; ws->counters_cap = 0; }
+  if (ws->tok_d) { cudaFree(ws->tok_d); cudaFreeHost(ws->tokpos_h); ws->tok_d = nullptr; ws->tokpos_cap = 0; }
+  if (ws->q8_xq) { cudaFree(ws->q8_xq); cudaFree(ws->q8_xs); ws->q8_xq = nullptr; ws->q8_cap = 0; }
+  for (auto& r : ws->rope) { cudaFree(r.second.cos_d); cudaFree(r.second.sin_d); }
+  ws->rope.clear();
+}
+
 int ws_ensure_dual(Workspace* ws) {
   if (ws->sibling) return THA_STATUS_SUCCESS;
   Workspace* sib = new Workspace();

@@ -47,7 +47,14 @@ int ws_ensure_tokpos(Workspace* ws, int n_batches);
 int ws_ensure_q8(Workspace* ws, int n_batches, int kmax, int gs);
 int ws_ensure_dual(Workspace* ws);
 // cached graphs captured pointers that are about to change
-inline void ws_drop_graphs(Workspace* ws) { ws->graphs.clear(); if (ws->parent) ws->parent->graphs.clear(); }
+inline void ws_drop_graphs(Workspace* ws) {
+  for (Workspace* w = ws; w; w = w->parent) {
+    for (auto& g : w->graphs) if (g.second.exec) cudaGraphExecDestroy(g.second.exec);
+    w->graphs.clear();
+  }
+}
+void ws_release(Workspace* ws);        // free everything a (tensor-parallel rank's) workspace owns
+void step_tc_release(Workspace* ws);   // ... and the row pipeline's scratch keyed by it
 int dual_min_rows();   // rows from which a step is issued as two concurrent half-batches (0 = never)
 int ws_rope(Workspace* ws, int head_size, int seq_len, const float** cos_d, const float** sin_d);
 
