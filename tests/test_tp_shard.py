@@ -65,3 +65,79 @@ def test_q8_shards_keep_groups():
         got = np.concatenate([deq(*sh[r][1][name]) for r in range(tp)], axis=axis)
         assert np.array_equal(got, full), name
     assert [s[0].hidden_dim for s in sh] == [384, 320]
+
+
+def _tp_forward_numpy(cfg, shards, tokens):
+    """The arithmetic of the tensor-parallel step in numpy float64: every rank works on its
+    shard with the LOCAL config, the wo / w2 partial products of all ranks are summed into one residual stream.
+    Returns the logits after each token (run.cc:244-374 semantics)."""
+    tp = len(shards)
+    d, L, S = cfg.dim, cfg.n_layers, cfg.seq_len
+    hs = cfg.dim // cfg.n_heads
+    w0 = shards[0][1]
+    kc = [np.zeros((L, S, hs * sh[0].n_kv_heads)) for sh in shards]
+    vc = [np.zeros((L, S, hs * sh[0].n_kv_heads)) for sh in shards]
+    out = []
+
+    def rms(x, g):
+        return g * (x / np.sqrt((x * x).mean() + 1e-5))
+
+    def rope(v, pos):
+        v = v.copy()
+        for i in range(0, v.size, 2):
+            f = 1.0 / (10000.0 ** ((i % hs) / hs))
+            c, s = np.cos(pos * f), np.sin(pos * f)
+            v[i], v[i + 1] = v[i] * c - v[i + 1] * s, v[i] * s + v[i + 1] * c
+        return v
+
+    for pos, tok in enumerate(tokens):
+        x = w0["tok_emb"][tok].astype(np.float64)
+        for l in range(L):
+            xb = rms(x, w0["rms_att"][l])
+            part = np.zeros(d)
+            for r, (lc, lw) in enumerate(shards):
+                q = rope(lw["wq"][l].astype(np.float64) @ xb, pos)
+                kc[r][l, pos] = rope(lw["wk"][l].astype(np.float64) @ xb, pos)
+                vc[r][l, pos] = lw["wv"][l].astype(np.float64) @ xb
+                kv_mul = lc.n_heads // lc.n_kv_heads
+                att_out = np.zeros(hs * lc.n_heads)
+                for h in range(lc.n_heads):
+                    kh = kc[r][l, :pos + 1, (h // kv_mul) * hs:(h // kv_mul + 1) * hs]
+                    vh = vc[r][l, :pos + 1, (h // kv_mul) * hs:(h // kv_mul + 1) * hs]
+                    sc = kh @ q[h * hs:(h + 1) * hs] / np.sqrt(hs)
+                    p = np.exp(sc - sc.max()); p /= p.sum()
+                    att_out[h * hs:(h + 1) * hs] = p @ vh
+                part += lw["wo"][l].astype(np.float64) @ att_out        # this rank's partial of the residual update
+            x = x + part                                                # the exchange: every rank adds all partials
+            xb = rms(x, w0["rms_ffn"][l])
+            part = np.zeros(d)
+            for lc, lw in shards:
+                a = lw["w1"][l].astype(np.float64) @ xb
+                c = lw["w3"][l].astype(np.float64) @ xb
+                part += lw["w2"][l].astype(np.float64) @ (a / (1.0 + np.exp(-a)) * c)
+            x = x + part
+        out.append(w0["tok_emb"].astype(np.float64) @ rms(x, w0["rms_final"]))
+    return out
+
+
+@pytest.mark.parametrize("tp,kv", [(2, 8), (2, 4), (4, 4)])
+def test_tp_arithmetic_matches_unsplit_oracle(oracle, tmp_path, tp, kv):
+    """The split itself (which rows / columns / heads / hidden units go where, grouped-query heads, uneven hidden
+    widths) pinned on the CPU: the sharded arithmetic reproduces the oracle's logits of the UNSPLIT model."""
+    import os
+    ck, tpm = load_pkg("checkpoint"), load_pkg("tp")
+    cfg = ck.Config(dim=128, hidden_dim=448, n_layers=2, n_heads=8, n_kv_heads=kv, vocab_size=96, seq_len=12)
+    w = ck.random_weights(cfg, seed=11, std=0.1)
+    rng = np.random.default_rng(3)
+    for k in ("rms_att", "rms_ffn", "rms_final"):
+        w[k] = (1.0 + 0.1 * rng.standard_normal(w[k].shape)).astype(np.float32)
+    path = os.path.join(str(tmp_path), "m.bin")
+    ck.write_v0(path, cfg, w)
+    seq = oracle.open(path).new_seq()
+    shards = [tpm.shard_f32(cfg, w, tp, r) for r in range(tp)]
+    assert sum(s[0].hidden_dim for s in shards) == cfg.hidden_dim       # 448 = 7 groups of 64: uneven at tp = 2 and 4
+    tokens = rng.integers(0, cfg.vocab_size, size=6)
+    got = _tp_forward_numpy(cfg, shards, tokens)
+    for pos, tok in enumerate(tokens):
+        want = seq.forward(int(tok), pos)
+        assert np.allclose(got[pos], want, rtol=2e-4, atol=2e-4), f"tp={tp} kv={kv} pos {pos}: {np.abs(got[pos] - want).max()}"
