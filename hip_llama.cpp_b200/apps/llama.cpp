@@ -32,6 +32,7 @@ static void error_usage() {
   fprintf(stderr, "  -o <string> (only for test mode) output filename\n");
   fprintf(stderr, "  -b <int>    batch size (slots per GPU)\n");
   fprintf(stderr, "  -g <int>    number of GPUs (default: all)\n");
+  fprintf(stderr, "  -w <int>    tensor-parallel width: ONE replica split over this many ranks (rank r on GPU r %% n_gpus), greedy only (-t 0)\n");
   fprintf(stderr, "  -k <string> also write the generated token ids to this file\n");
   fprintf(stderr, "  -x <0|1>    ignore stop tokens (fixed-length timing runs)\n");
   fprintf(stderr, "  -r <0|1>    fp32 models: ingest prompts in one tensor-core pass (default 1); 0 = one decode step per prompt token\n");
@@ -43,7 +44,7 @@ int main(int argc, char* argv[]) {
   char* checkpoint_path = nullptr;
   const char* tokenizer_path = "./assets/tokenizer.bin";
   float temperature = 1.0f, topp = 0.9f;
-  int steps = 256, batch = 1, n_gpus = 0, ignore_stop = 0, prefill = 1;
+  int steps = 256, batch = 1, n_gpus = 0, ignore_stop = 0, prefill = 1, tp = 1;
   const char* prompt = nullptr;
   unsigned long long rng_seed = 0;
   const char* mode = "generate";
@@ -70,6 +71,7 @@ int main(int argc, char* argv[]) {
     else if (f == 'k') token_filename = v;
     else if (f == 'x') ignore_stop = atoi(v);
     else if (f == 'r') prefill = atoi(v);
+    else if (f == 'w') tp = atoi(v);
     else error_usage();
   }
   if (rng_seed == 0) rng_seed = (unsigned int)time(nullptr);
@@ -92,6 +94,10 @@ int main(int argc, char* argv[]) {
   opt.n_devices = n_gpus;
   opt.ignore_stop = ignore_stop;
   opt.prefill = prefill;
+  opt.tp = tp < 1 ? 1 : tp;
+  // ranks of one replica that share a GPU hand-shake between concurrent kernels: every rank's stream needs its own
+  // hardware queue (set before the CUDA context exists)
+  if (opt.tp > 1) setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
 
   if (strcmp(mode, "generate") == 0) {
     // one request through the same driver (the reference's generate() is the single-sequence loop, :1087-1147 of run.cc)
@@ -101,7 +107,7 @@ int main(int argc, char* argv[]) {
     requests.str_gens.assign(1, "");
     requests.tok_gens.assign(1, std::vector<int>());
     opt.batch_size = 1;
-    opt.n_devices = 1;
+    opt.n_devices = opt.tp > 1 ? n_gpus : 1;
     opt.temperature = temperature; opt.topp = topp; opt.seed = rng_seed;
     DriverStats st;
     const long start = time_in_ms();

@@ -115,7 +115,8 @@ static int run_step(cudaStream_t st, Workspace* ws, const void* key_data, size_t
   }
   const unsigned long long key = fnv1a(key_data, key_len);
   auto it = ws->graphs.find(key);
-  if (it == ws->graphs.end()) {
+  const bool fresh = it == ws->graphs.end();
+  if (fresh) {
     cudaGraph_t graph = nullptr;
     THA_CUDA_OK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
     int rc2 = issue();
@@ -130,7 +131,7 @@ static int run_step(cudaStream_t st, Workspace* ws, const void* key_data, size_t
     it = ws->graphs.emplace(key, sg).first;
   }
   if (do_launch) THA_CUDA_OK(cudaGraphLaunch(it->second.exec, st));
-  else THA_CUDA_OK(cudaGraphUpload(it->second.exec, st));   // prepare only: the executable graph is resident, nothing runs
+  else if (fresh) THA_CUDA_OK(cudaGraphUpload(it->second.exec, st));   // prepare only: the executable graph is resident, nothing runs
   g_last_step_launches = it->second.launches;
   return THA_STATUS_SUCCESS;
 }
@@ -656,4 +657,63 @@ extern "C" int tha_tp_prefill_q8(void* stream, tha_tp_t* tp, const tha_config_t*
                                  const int* len_host, const int* tokens_host, float* logits_d, int* next_d) {
   return tp_prefill((cudaStream_t)stream, tp_ctx(tp), cfg_local, nullptr, w_local, s_local, n_seqs, slot_host, pos0_host,
                     len_host, tokens_host, logits_d, next_d);
+}
+
+// One greedy decode step of a tensor-parallel replica whose ranks are all driven by THIS host thread (the shipped
+// driver with -p N; ranks may share a device): HOST token / pos in, HOST next token per slot out (rank 0's; every rank
+// computes the same).  Order of business: stage the inputs on every rank, PREPARE every rank (scratch, graph -- anything
+// that may synchronise with a device), then launch all ranks back to back, then wait.
+extern "C" int tha_tp_forward_greedy(int tp, tha_tp_t* const* ranks, void* const* streams, int n_batches, int q8,
+                                     const tha_config_t* const* cfg_local, const void* const* w_local,
+                                     const tha_state_t* const* s_local, const int* token_host, const int* pos_host,
+                                     int* next_host) {
+  if (tp < 1 || tp > TP_MAX || !ranks || !streams || n_batches < 1 || !cfg_local || !w_local || !s_local || !token_host ||
+      !pos_host || !next_host)
+    return THA_STATUS_INVALID_ARG;
+  const int B = n_batches;
+  for (int r = 0; r < tp; r++) {
+    TpCtx* t = tp_ctx(ranks[r]);
+    if (!t || !cfg_local[r] || !w_local[r] || !s_local[r]) return THA_STATUS_INVALID_ARG;
+    THA_CUDA_OK(cudaSetDevice(t->device));
+    Workspace* ws = &t->ws;
+    THA_TRY(ws_ensure_tokpos(ws, B));
+    const int cap = ws->tokpos_cap;
+    memcpy(ws->tokpos_h, token_host, B * sizeof(int));
+    memcpy(ws->tokpos_h + cap, pos_host, B * sizeof(int));
+    THA_CUDA_OK(cudaMemcpyAsync(ws->tok_d, ws->tokpos_h, 2 * cap * sizeof(int), cudaMemcpyHostToDevice, (cudaStream_t)streams[r]));
+  }
+  for (int pass = 0; pass < 2; pass++) {
+    for (int r = 0; r < tp; r++) {
+      TpCtx* t = tp_ctx(ranks[r]);
+      THA_CUDA_OK(cudaSetDevice(t->device));
+      const int saved = t->mode;
+      if (pass == 0) t->mode = 1;
+      const int rc = tp_decode((cudaStream_t)streams[r], t, B, cfg_local[r], q8 ? nullptr : (const tha_weights_f32_t*)w_local[r],
+                               q8 ? (const tha_weights_q8_t*)w_local[r] : nullptr, s_local[r], t->ws.tok_d, t->ws.pos_d, nullptr,
+                               t->ws.next_d, 0);
+      t->mode = saved;
+      THA_TRY(rc);
+    }
+  }
+  {
+    TpCtx* t0 = tp_ctx(ranks[0]);
+    THA_CUDA_OK(cudaSetDevice(t0->device));
+    THA_CUDA_OK(cudaMemcpyAsync(t0->ws.next_h, t0->ws.next_d, B * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)streams[0]));
+  }
+  for (int r = 0; r < tp; r++) {
+    THA_CUDA_OK(cudaSetDevice(tp_ctx(ranks[r])->device));
+    THA_CUDA_OK(cudaStreamSynchronize((cudaStream_t)streams[r]));
+  }
+  for (int r = 0; r < tp; r++) {
+    if (tha_tp_check_error(ranks[r])) {
+      set_last_error("tensor-parallel exchange: a wait on a peer timed out", cudaErrorLaunchTimeout);
+      return THA_STATUS_EXECUTION_FAILED;
+    }
+  }
+  if (gemm_tc_check_error()) {
+    set_last_error("tensor-core matmul: a pipeline barrier wait timed out", cudaErrorLaunchTimeout);
+    return THA_STATUS_EXECUTION_FAILED;
+  }
+  memcpy(next_host, tp_ctx(ranks[0])->ws.next_h, B * sizeof(int));
+  return THA_STATUS_SUCCESS;
 }

@@ -75,6 +75,7 @@ struct Slot {
 
 int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenizer_path, Requests* requests,
                       const DriverOptions& opt, DriverStats* stats) {
+  if (opt.tp > 1) return run_tensor_parallel(t32, tq8, tokenizer_path, requests, opt, stats);
   const Config cfg = t32 ? t32->config : tq8->config;
   const int vocab = cfg.vocab_size, B = opt.batch_size;
   int n_devices = 0;
@@ -230,6 +231,151 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
 
   for (auto& s : samplers) free_sampler(&s);
   if (stats) { stats->gen_tokens = gen_cnt; stats->steps = n_steps; stats->prefill_rows = n_prefill_rows; stats->load_seconds = load_s; stats->loop_seconds = loop_s; }
+  return (int)gen_cnt;
+}
+
+// ---- one replica, tensor parallel -------------------------------------------------------------
+// The slot state machine of run_data_parallel with ONE set of slots; the model is split over opt.tp ranks (rank r on
+// device r % n_devices: with fewer devices than ranks several ranks share a device, which is how the single-GPU tests
+// run it), all driven by this thread through tha_tp_forward_greedy.  Greedy decode; prompts are fed token by token as in
+// the reference (src/llama.cpp:1029-1030).
+int run_tensor_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenizer_path, Requests* requests,
+                        const DriverOptions& opt, DriverStats* stats) {
+  const Config cfg = t32 ? t32->config : tq8->config;
+  const int vocab = cfg.vocab_size, B = opt.batch_size, tp = opt.tp;
+  if (opt.temperature != 0.0f) { fprintf(stderr, "tensor parallel (-w): greedy decode only, use -t 0\n"); exit(EXIT_FAILURE); }
+  if (tp > 8) { fprintf(stderr, "tensor parallel (-w): at most 8 ranks\n"); exit(EXIT_FAILURE); }
+  int n_devices = 0;
+  CHECK_THA(tha_device_count(&n_devices));
+  if (opt.n_devices > 0 && opt.n_devices < n_devices) n_devices = opt.n_devices;
+  if (n_devices < 1) { fprintf(stderr, "no CUDA device\n"); exit(EXIT_FAILURE); }
+  const int unit = t32 ? 64 : tq8->weights.group_size;
+  int hidden_of[8];
+  Config cfg_local[8];
+  for (int r = 0; r < tp; r++)
+    if (tp_local_config(&cfg, tp, r, unit, &cfg_local[r])) {
+      fprintf(stderr, "tensor parallel (-w %d): heads %d / kv heads %d / hidden %d cannot be split\n", tp, cfg.n_heads, cfg.n_kv_heads, cfg.hidden_dim);
+      exit(EXIT_FAILURE);
+    }
+  tp_split_hidden(cfg.hidden_dim, tp, unit, hidden_of);
+  fprintf(stderr, "\n TENSOR PARALLELISM \n\n Ranks %d on %d device(s)\n\n Batch Size %d\n", tp, n_devices, B);
+  // ranks sharing a device hand-shake between concurrent kernels of that device: an early-launched (PDL) persistent
+  // matmul of one rank must not hold the SMs its peer needs
+  if (n_devices < tp) tha_set_option("pdl", 0);
+
+  Tokenizer tok;
+  build_tokenizer(&tok, tokenizer_path, vocab);
+  thablasHandle_t handle[8];
+  thaTP_t ctx[8] = {nullptr};
+  TransformerWeights* w_d[8] = {nullptr};
+  TransformerWeightsQ8* wq_d[8] = {nullptr};
+  RunState* s_d[8] = {nullptr};
+  const int head_size = cfg.dim / cfg.n_heads;
+  const long t_load0 = time_in_ms();
+  for (int r = 0; r < tp; r++) {
+    CHECK_THA(tha_set_device(r % n_devices));
+    thablasCreate(&handle[r]);
+    if (t32) copy_weight_shard_to_device(t32, tp, r, w_d[r]);
+    else copy_weight_shard_to_device_q8(tq8, tp, r, wq_d[r]);
+    alloc_state_to_device_batch_tp(&cfg, &cfg_local[r], s_d[r], B);
+    if (thaTPCreate(&ctx[r], tp, r, head_size, hidden_of, (size_t)16 * B * cfg.dim) != THABLAS_STATUS_SUCCESS) {
+      fprintf(stderr, "thaTPCreate failed: %s\n", tha_last_error());
+      exit(EXIT_FAILURE);
+    }
+    CHECK_THA(tha_device_sync());
+  }
+  if (thaTPConnectLocal(ctx, tp) != THABLAS_STATUS_SUCCESS) {
+    fprintf(stderr, "thaTPConnectLocal failed (no peer access between the devices?): %s\n", tha_last_error());
+    exit(EXIT_FAILURE);
+  }
+  const double load_s = (time_in_ms() - t_load0) / 1000.0;
+  fprintf(stdout, "\nLoad model time (%d shards): %f\n", tp, load_s);
+
+  void* streams[8];
+  const tha_config_t* cfgs[8];
+  const void* ws[8];
+  const tha_state_t* ss[8];
+  for (int r = 0; r < tp; r++) {
+    streams[r] = (void*)handle[r].calc_stream;
+    cfgs[r] = (const tha_config_t*)&cfg_local[r];
+    ws[r] = t32 ? (const void*)w_d[r] : (const void*)wq_d[r];
+    ss[r] = (const tha_state_t*)s_d[r];
+  }
+
+  const int kvd = cfg.dim * cfg.n_kv_heads / cfg.n_heads;
+  BatchManager bm(B, cfg.seq_len, cfg.n_layers, kvd);   // slot table only: the KV slabs are the ranks' own
+  std::vector<Slot> slots(B);
+  std::vector<int> token(B, 0), pos(B, -1), next(B, 0);
+  int next_idx = opt.device_offset;
+  long long gen_cnt = 0, n_steps = 0;
+  const long t_loop0 = time_in_ms();
+  for (;;) {
+    for (int s = 0; s < B; s++) {   // refill free slots
+      if (bm.request_of(s) >= 0) continue;
+      const int req = next_idx;
+      if (req >= requests->num_reqs) break;
+      next_idx += opt.device_stride;
+      const int got = bm.acquire_slot(req);
+      Slot& sl = slots[got];
+      const std::string& prompt = requests->str_reqs[req];
+      sl.prompt.assign(prompt.size() + 3, 0);
+      int n_prompt = 0;
+      encode(&tok, prompt.c_str(), 1, 0, sl.prompt.data(), &n_prompt);
+      if (n_prompt < 1) { fprintf(stderr, "something is wrong, expected at least 1 prompt token\n"); exit(EXIT_FAILURE); }
+      sl.prompt.resize(n_prompt);
+      sl.text.clear();
+      sl.ids.assign(1, sl.prompt[0]);
+      sl.steps = requests->max_seq_len;
+      if (opt.max_new_positions > 0 && opt.max_new_positions < sl.steps) sl.steps = opt.max_new_positions;
+      token[got] = sl.prompt[0];
+      pos[got] = 0;
+    }
+    if (bm.active_slots() == 0) break;
+    const int rc = tha_tp_forward_greedy(tp, ctx, streams, B, t32 ? 0 : 1, cfgs, ws, ss, token.data(), pos.data(), next.data());
+    if (rc) { fprintf(stderr, "tha_tp_forward_greedy failed (%d): %s\n", rc, tha_last_error()); exit(EXIT_FAILURE); }
+    n_steps++;
+    for (int s = 0; s < B; s++) {   // src/llama.cpp:1025-1050
+      const int req = bm.request_of(s);
+      if (req < 0) continue;
+      Slot& sl = slots[s];
+      const int nx = (pos[s] < (int)sl.prompt.size() - 1) ? sl.prompt[pos[s] + 1] : next[s];
+      bm.advance(s);
+      pos[s] += 1;
+      bool done = false;
+      if ((nx == 1 || nx == 2) && !opt.ignore_stop) {
+        done = true;
+      } else {
+        append_str(decode(&tok, token[s], nx), sl.text);
+        sl.ids.push_back(nx);
+        token[s] = nx;
+        if (pos[s] >= sl.steps) done = true;
+      }
+      if (done) {
+        requests->str_gens[req] = sl.text + "\n";
+        requests->tok_gens[req] = sl.ids;
+        gen_cnt += pos[s] - 1;
+        bm.release_slot(s);
+        pos[s] = -1;
+        token[s] = 0;
+      }
+    }
+  }
+  const double loop_s = (time_in_ms() - t_loop0) / 1000.0;
+
+  for (int r = 0; r < tp; r++) {
+    CHECK_THA(tha_set_device(r % n_devices));
+    CHECK_THA(tha_device_sync());
+  }
+  for (int r = 0; r < tp; r++) {
+    CHECK_THA(tha_set_device(r % n_devices));
+    thaTPDestroy(ctx[r]);
+    free_state_on_device(s_d[r]);
+    if (w_d[r]) free_weight_on_device(w_d[r], w_d[r]->wcls == w_d[r]->token_embedding_table);
+    if (wq_d[r]) free_weight_on_device_q8(wq_d[r], 1);
+    thablasDestroy(handle[r]);
+  }
+  free_tokenizer(&tok);
+  if (stats) { stats->gen_tokens = gen_cnt; stats->steps = n_steps; stats->prefill_rows = 0; stats->load_seconds = load_s; stats->loop_seconds = loop_s; }
   return (int)gen_cnt;
 }
 

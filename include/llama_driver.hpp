@@ -74,6 +74,8 @@ struct DriverOptions {
   int device_offset = 0, device_stride = 1;  // request sharding across processes: this process serves requests r with r % stride == offset
   int prefill = 1;             // fp32 models: ingest a new request's prompt in one tensor-core pass (tha_prefill_f32) instead of
                                // one forced-prompt decode step per token (src/llama.cpp:1029-1030); 0 = the reference's scheme
+  int tp = 1;                  // > 1: ONE replica split tensor-parallel over `tp` ranks (app flag -w); rank r runs on device r % n_devices,
+                               // all ranks are driven by one host thread; greedy decode only (temperature 0), prompts fed token by token
   int verbose = 0;
 };
 struct DriverStats {
@@ -89,4 +91,7 @@ int test_data_parallelism(Transformer* transformer, Tokenizer* tokenizer, const 
                           int batch_size);
 int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenizer_path, Requests* requests,
                       const DriverOptions& opt, DriverStats* stats);
+// One replica, tensor parallel: same slot state machine, the step is tha_tp_forward_greedy.
+int run_tensor_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenizer_path, Requests* requests,
+                        const DriverOptions& opt, DriverStats* stats);
 long time_in_ms();

@@ -264,6 +264,12 @@ int tha_tp_decode_step_f32(void* stream, tha_tp_t* tp, int n_batches, const tha_
 int tha_tp_decode_step_q8(void* stream, tha_tp_t* tp, int n_batches, const tha_config_t* cfg_local,
                           const tha_weights_q8_t* w_local, const tha_state_t* s_local, int* token_d, int* pos_d,
                           float* logits_d, int* next_d, int advance);
+/* One greedy step of a replica whose `tp` ranks are all driven by the calling host thread (ranks may share a device):
+ * HOST token / pos in, HOST next token per slot out.  streams[r], cfg_local[r], w_local[r] (tha_weights_f32_t* or
+ * tha_weights_q8_t* by `q8`), s_local[r] belong to rank r.  Prepares every rank before the first launch. */
+int tha_tp_forward_greedy(int tp, tha_tp_t* const* ranks, void* const* streams, int n_batches, int q8,
+                          const tha_config_t* const* cfg_local, const void* const* w_local,
+                          const tha_state_t* const* s_local, const int* token_host, const int* pos_host, int* next_host);
 int tha_tp_prefill_f32(void* stream, tha_tp_t* tp, const tha_config_t* cfg_local, const tha_weights_f32_t* w_local,
                        const tha_state_t* s_local, int n_seqs, const int* slot_host, const int* pos0_host,
                        const int* len_host, const int* tokens_host, float* logits_d, int* next_d);
