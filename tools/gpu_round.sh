@@ -1,12 +1,12 @@
 #!/bin/bash
-# One gpurun call: tests, default bench, per-step DRAM-byte pass, one full capture of the tcgen05 matmul.
-set -x
+# Everything round 1 measured on ONE GPU, in one gpurun call (about 6 minutes of box time):
+#   gpurun --timeout 1500 -- 'bash tools/gpu_round.sh'
+# tests + smoke + default bench + the configuration table of BASELINE.md section 4 (gpu_verify.sh), then the launch lists
+# and the full capture of the dominant kernel (gpu_prof_r01k.sh).  Multi-GPU: tools/gpu_scale.sh N (gpurun --gpus N),
+# tools/tp_check.py and tools/bench_prefill_tp.py under torchrun.  Sweeps that led to the current defaults:
+# tools/attn_sweep.sh (attention segment width), tools/z_sweep.sh (split-K planner), tools/skip_sweep.sh (live share of
+# each kernel class), tools/dual_sweep.sh (two concurrent half-batch branches: slower, off).
 cd "$GRAFT_REPO_ROOT" || exit 1
-python -m pytest tests -x -q -m gpu > gpurun_out/r1e_tests.log 2>&1; echo "tests rc=$?"; tail -3 gpurun_out/r1e_tests.log
-python bench.py > gpurun_out/r1e_bench_default.json 2> gpurun_out/r1e_bench_default.err; echo "bench rc=$?"
-CMD="python bench.py --steps 6 --warmup 4 --no-cpu-baseline --no-e2e"
-$CMD > gpurun_out/r1e_plain.log 2>&1 || exit 1
-ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -s 560 -c 224 --csv \
-    --log-file gpurun_out/r1e_launches_tc_B256.csv $CMD > gpurun_out/r1e_ncu1.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:gemm_tf32x3 -s 40 -c 5 -o gpurun_out/r1e_gemm_tf32x3_B256 -f $CMD > gpurun_out/r1e_ncu2.log 2>&1
-ls -la gpurun_out/
+bash tools/gpu_verify.sh round
+bash tools/gpu_prof_r01k.sh
+ls -la gpurun_out/ | tail -30
