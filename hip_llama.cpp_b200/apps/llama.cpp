@@ -49,7 +49,7 @@ int main(int argc, char* argv[]) {
   unsigned long long rng_seed = 0;
   const char* mode = "generate";
   const char *input_filename = nullptr, *output_filename = nullptr, *token_filename = nullptr;
-  bool t_given = false, s_given = false;
+  bool t_given = false, s_given = false, n_given = false;
 
   if (argc >= 2) checkpoint_path = argv[1]; else error_usage();
   for (int i = 2; i < argc; i += 2) {
@@ -59,7 +59,7 @@ int main(int argc, char* argv[]) {
     if (f == 't') { temperature = atof(v); t_given = true; }
     else if (f == 'p') topp = atof(v);
     else if (f == 's') { rng_seed = strtoull(v, nullptr, 10); s_given = true; }
-    else if (f == 'n') steps = atoi(v);
+    else if (f == 'n') { steps = atoi(v); n_given = true; }
     else if (f == 'i') prompt = v;
     else if (f == 'z') tokenizer_path = v;
     else if (f == 'm') mode = v;
@@ -119,7 +119,8 @@ int main(int argc, char* argv[]) {
     if (input_filename == nullptr || output_filename == nullptr) error_usage();
     Tokenizer probe;   // max_token_length sizes the request buffers in the reference (:1590)
     build_tokenizer(&probe, tokenizer_path, cfg.vocab_size);
-    read_inputfile(input_filename, probe.max_token_length, cfg.seq_len, &requests);
+    // the reference always runs a request to seq_len; an explicit -n caps the positions per request (short test runs)
+    read_inputfile(input_filename, probe.max_token_length, n_given ? steps : cfg.seq_len, &requests);
     free_tokenizer(&probe);
     if (t_given) { opt.temperature = temperature; opt.topp = topp; }
     if (s_given) opt.seed = rng_seed;

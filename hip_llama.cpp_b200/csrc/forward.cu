@@ -409,11 +409,25 @@ int decode_step_q8(cudaStream_t st, int B, const tha_config_t* cfg, const tha_we
 int last_step_launches_get() { return g_last_step_launches; }
 void last_step_launches_set(int v) { g_last_step_launches = v; }
 
+// Host-side range check of a step's inputs: an idle slot carries pos < 0; anything else must index the RoPE tables,
+// the slot's KV slab and the embedding table.
+static int check_tokpos(int B, int vocab, int seq_len, const int* token_host, const int* pos_host) {
+  for (int b = 0; b < B; b++) {
+    if (pos_host[b] < 0) continue;
+    if (pos_host[b] >= seq_len || token_host[b] < 0 || token_host[b] >= vocab) {
+      set_last_error("token / pos out of range", cudaErrorInvalidValue);
+      return THA_STATUS_INVALID_ARG;
+    }
+  }
+  return THA_STATUS_SUCCESS;
+}
+
 // H2D of token/pos through the pinned staging block, step, D2H of the logits, sync.
 template <typename StepFn>
-static int forward_host(cudaStream_t st, int B, int vocab, float* state_logits, const int* token_host,
+static int forward_host(cudaStream_t st, int B, int vocab, int seq_len, float* state_logits, const int* token_host,
                         const int* pos_host, float* logits_out, StepFn step) {
   if (B <= 0 || !token_host || !pos_host || !logits_out) return THA_STATUS_INVALID_ARG;
+  THA_TRY(check_tokpos(B, vocab, seq_len, token_host, pos_host));
   Workspace* ws = workspace();
   if (!ws) return THA_STATUS_EXECUTION_FAILED;
   THA_TRY(ws_ensure_tokpos(ws, B));
@@ -457,7 +471,7 @@ extern "C" int tha_forward_batch_f32(void* stream, int n_batches, const tha_conf
                                      float* logits_out) {
   if (!cfg || !s) return THA_STATUS_INVALID_ARG;
   cudaStream_t st = (cudaStream_t)stream;
-  return forward_host(st, n_batches, cfg->vocab_size, s->logits, token_host, pos_host, logits_out,
+  return forward_host(st, n_batches, cfg->vocab_size, cfg->seq_len, s->logits, token_host, pos_host, logits_out,
                       [&](const int* tok_d, const int* pos_d, float* target) {
                         return decode_step_f32(st, n_batches, cfg, w, s, tok_d, pos_d, target, nullptr, 0);
                       });
@@ -465,9 +479,10 @@ extern "C" int tha_forward_batch_f32(void* stream, int n_batches, const tha_conf
 
 // Greedy variant of the host-facing step: argmax on the device, B ints back instead of B*vocab floats.
 template <typename StepFn>
-static int forward_host_greedy(cudaStream_t st, int B, const int* token_host, const int* pos_host, int* next_host,
-                               StepFn step) {
-  if (B <= 0 || !token_host || !pos_host || !next_host) return THA_STATUS_INVALID_ARG;
+static int forward_host_greedy(cudaStream_t st, int B, const tha_config_t* cfg, const int* token_host, const int* pos_host,
+                               int* next_host, StepFn step) {
+  if (B <= 0 || !cfg || !token_host || !pos_host || !next_host) return THA_STATUS_INVALID_ARG;
+  THA_TRY(check_tokpos(B, cfg->vocab_size, cfg->seq_len, token_host, pos_host));
   Workspace* ws = workspace();
   if (!ws) return THA_STATUS_EXECUTION_FAILED;
   THA_TRY(ws_ensure_tokpos(ws, B));
@@ -482,6 +497,10 @@ static int forward_host_greedy(cudaStream_t st, int B, const int* token_host, co
     set_last_error("persistent step kernel: a barrier wait timed out", cudaErrorLaunchTimeout);
     return THA_STATUS_EXECUTION_FAILED;
   }
+  if (gemm_tc_check_error()) {
+    set_last_error("tensor-core matmul: a pipeline barrier wait timed out", cudaErrorLaunchTimeout);
+    return THA_STATUS_EXECUTION_FAILED;
+  }
   memcpy(next_host, ws->next_h, B * sizeof(int));
   return THA_STATUS_SUCCESS;
 }
@@ -489,7 +508,7 @@ static int forward_host_greedy(cudaStream_t st, int B, const int* token_host, co
 extern "C" int tha_forward_greedy_f32(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_f32_t* w,
                                       const tha_state_t* s, const int* token_host, const int* pos_host, int* next_host) {
   cudaStream_t st = (cudaStream_t)stream;
-  return forward_host_greedy(st, n_batches, token_host, pos_host, next_host,
+  return forward_host_greedy(st, n_batches, cfg, token_host, pos_host, next_host,
                              [&](const int* tok_d, const int* pos_d, int* next_d) {
                                return decode_step_f32(st, n_batches, cfg, w, s, tok_d, pos_d, nullptr, next_d, 0);
                              });
@@ -498,7 +517,7 @@ extern "C" int tha_forward_greedy_f32(void* stream, int n_batches, const tha_con
 extern "C" int tha_forward_greedy_q8(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_q8_t* w,
                                      const tha_state_t* s, const int* token_host, const int* pos_host, int* next_host) {
   cudaStream_t st = (cudaStream_t)stream;
-  return forward_host_greedy(st, n_batches, token_host, pos_host, next_host,
+  return forward_host_greedy(st, n_batches, cfg, token_host, pos_host, next_host,
                              [&](const int* tok_d, const int* pos_d, int* next_d) {
                                return decode_step_q8(st, n_batches, cfg, w, s, tok_d, pos_d, nullptr, next_d);
                              });
@@ -565,7 +584,7 @@ extern "C" int tha_forward_batch_q8(void* stream, int n_batches, const tha_confi
                                     float* logits_out) {
   if (!cfg || !s) return THA_STATUS_INVALID_ARG;
   cudaStream_t st = (cudaStream_t)stream;
-  return forward_host(st, n_batches, cfg->vocab_size, s->logits, token_host, pos_host, logits_out,
+  return forward_host(st, n_batches, cfg->vocab_size, cfg->seq_len, s->logits, token_host, pos_host, logits_out,
                       [&](const int* tok_d, const int* pos_d, float* target) {
                         return decode_step_q8(st, n_batches, cfg, w, s, tok_d, pos_d, target, nullptr);
                       });
@@ -671,6 +690,8 @@ extern "C" int tha_tp_forward_greedy(int tp, tha_tp_t* const* ranks, void* const
       !pos_host || !next_host)
     return THA_STATUS_INVALID_ARG;
   const int B = n_batches;
+  if (!cfg_local[0]) return THA_STATUS_INVALID_ARG;
+  THA_TRY(check_tokpos(B, cfg_local[0]->vocab_size, cfg_local[0]->seq_len, token_host, pos_host));
   for (int r = 0; r < tp; r++) {
     TpCtx* t = tp_ctx(ranks[r]);
     if (!t || !cfg_local[r] || !w_local[r] || !s_local[r]) return THA_STATUS_INVALID_ARG;
@@ -700,9 +721,11 @@ extern "C" int tha_tp_forward_greedy(int tp, tha_tp_t* const* ranks, void* const
     THA_CUDA_OK(cudaSetDevice(t0->device));
     THA_CUDA_OK(cudaMemcpyAsync(t0->ws.next_h, t0->ws.next_d, B * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)streams[0]));
   }
+  bool tc_err = false;
   for (int r = 0; r < tp; r++) {
     THA_CUDA_OK(cudaSetDevice(tp_ctx(ranks[r])->device));
     THA_CUDA_OK(cudaStreamSynchronize((cudaStream_t)streams[r]));
+    if (gemm_tc_check_error()) tc_err = true;   // this rank's device
   }
   for (int r = 0; r < tp; r++) {
     if (tha_tp_check_error(ranks[r])) {
@@ -710,7 +733,7 @@ extern "C" int tha_tp_forward_greedy(int tp, tha_tp_t* const* ranks, void* const
       return THA_STATUS_EXECUTION_FAILED;
     }
   }
-  if (gemm_tc_check_error()) {
+  if (tc_err) {
     set_last_error("tensor-core matmul: a pipeline barrier wait timed out", cudaErrorLaunchTimeout);
     return THA_STATUS_EXECUTION_FAILED;
   }

@@ -420,7 +420,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(S::TMEM_COLS));
   }
-  if (threadIdx.x == 0 && *abort_flag && p.error_flag) atomicExch(p.error_flag, 1);
+  if (threadIdx.x == 0 && *abort_flag && p.error_flag) *((volatile int*)p.error_flag) = 1;
 }
 
 __global__ void split_hilo_kernel(const float* __restrict__ x, long long ldx, float* __restrict__ hi, float* __restrict__ lo, int K) {
@@ -442,7 +442,8 @@ static long long* g_trace = nullptr;   // development aid: tha_gemm_trace()
 static int tc_env(const char* n, int d) { const char* v = getenv(n); return (v && *v) ? atoi(v) : d; }
 static std::mutex g_tc_mu;
 static std::map<std::tuple<const void*, long long, int, long long, int, int>, CUtensorMap> g_maps;
-static std::map<int, int*> g_err_flags;   // per device
+struct TcErrFlag { int* host; int* dev; };   // one mapped pinned word per device: kernels store to it, the host reads it without a copy
+static std::map<int, TcErrFlag> g_err_flags;
 
 static int tc_get_encode() {
   if (g_encode) return THA_STATUS_SUCCESS;
@@ -487,13 +488,13 @@ int gemm_tc_init(int** flag_out) {
   std::lock_guard<std::mutex> lk(g_tc_mu);
   auto it = g_err_flags.find(dev);
   if (it == g_err_flags.end()) {
-    int* f = nullptr;
-    THA_CUDA_OK(cudaMalloc(&f, sizeof(int)));
-    THA_CUDA_OK(cudaMemset(f, 0, sizeof(int)));
-    THA_CUDA_OK(cudaDeviceSynchronize());
+    TcErrFlag f = {nullptr, nullptr};
+    THA_CUDA_OK(cudaHostAlloc((void**)&f.host, sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable));
+    *f.host = 0;
+    THA_CUDA_OK(cudaHostGetDevicePointer((void**)&f.dev, f.host, 0));
     it = g_err_flags.emplace(dev, f).first;
   }
-  if (flag_out) *flag_out = it->second;
+  if (flag_out) *flag_out = it->second.dev;
   return THA_STATUS_SUCCESS;
 }
 
@@ -563,16 +564,15 @@ int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl) {
 int gemm_tc_check_error() {
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return 1;
-  int* f = nullptr;
+  volatile int* f = nullptr;
   {
     std::lock_guard<std::mutex> lk(g_tc_mu);
     auto it = g_err_flags.find(dev);
     if (it == g_err_flags.end()) return 0;
-    f = it->second;
+    f = it->second.host;
   }
-  int h = 0;
-  if (cudaMemcpy(&h, f, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) return 1;
-  if (h) cudaMemset(f, 0, sizeof(int));
+  const int h = *f;   // written by a kernel that gave up (a plain store to the mapped word); callers sync their stream first
+  if (h) *f = 0;
   return h;
 }
 
@@ -891,7 +891,7 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(S::TMEM_COLS));
   }
-  if (threadIdx.x == 0 && *abort_flag && p.error_flag) atomicExch(p.error_flag, 1);
+  if (threadIdx.x == 0 && *abort_flag && p.error_flag) *((volatile int*)p.error_flag) = 1;
 }
 
 bool gemm_q8i_ok(const Q8iArgs& a) {
