@@ -24,6 +24,7 @@
 #include <mutex>
 #include <vector>
 
+#include "chain_tc.h"
 #include "common.cuh"
 #include "gemm_tc.h"
 #include "tp.h"
@@ -323,6 +324,9 @@ struct TcScratch {
   int8_t *xq = nullptr, *hq = nullptr;                  // Q8_0: quantised matmul inputs [R, d], [R, hidden]
   float *xsT = nullptr, *hsT = nullptr;                 // their group scales, transposed [groups, ldxs]
   size_t n_xq = 0, n_hq = 0, n_xsT = 0, n_hsT = 0;
+  // chained matmuls (chain_tc.cu): attention output hi/lo, sums of squares per row tile, counter blocks (one per launch of a step)
+  float *ah = nullptr, *al = nullptr, *ss = nullptr; int* ctr = nullptr;
+  size_t n_ah = 0, n_al = 0, n_ss = 0; int ctr_stride = 0, n_ctr_blocks = 0;
   size_t n_x = 0, n_xl = 0, n_h = 0, n_hl = 0, n_part = 0, n_xr = 0, n_qr = 0, n_xbr = 0, n_tab = 0; int n_b = 0;
 };
 static std::map<Workspace*, TcScratch> g_tc_scratch;   // per workspace (= per device, or per tensor-parallel rank)
@@ -333,7 +337,7 @@ void step_tc_release(Workspace* ws) {
   auto it = g_tc_scratch.find(ws);
   if (it == g_tc_scratch.end()) return;
   TcScratch& s = it->second;
-  void* ptrs[] = {s.xh, s.xl, s.hh, s.hl, s.scale, s.part, s.xr, s.qr, s.xbr, s.tab, s.xq, s.hq, s.xsT, s.hsT};
+  void* ptrs[] = {s.xh, s.xl, s.hh, s.hl, s.scale, s.part, s.xr, s.qr, s.xbr, s.tab, s.xq, s.hq, s.xsT, s.hsT, s.ah, s.al, s.ss, s.ctr};
   for (void* p : ptrs) if (p) cudaFree(p);
   g_tc_scratch.erase(it);
 }
@@ -449,6 +453,8 @@ bool prefill_tc_supported(const tha_config_t* c, const TpCtx* tp) {
   return attn_prefill_supported(hs, hs * c->n_kv_heads);
 }
 
+static void chain_needs(const tha_config_t& c, int R, size_t* part_floats, size_t* ss_floats, int* ctr_ints);
+
 // Allocate / grow everything R rows need (never inside a stream capture).
 static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefill, int n_tab, bool q8, int gs = 64,
                         const TpCtx* tp = nullptr) {
@@ -469,7 +475,26 @@ static int prepare_rows(Workspace* ws, const tha_config_t* c, int R, bool prefil
     THA_TRY_RC(grow(&s.hh, &s.n_h, (size_t)R * c->hidden_dim, ws));
     THA_TRY_RC(grow(&s.hl, &s.n_hl, (size_t)R * c->hidden_dim, ws));
   }
-  THA_TRY_RC(grow(&s.part, &s.n_part, pl.part_floats, ws));
+  size_t part_need = pl.part_floats;
+  if (!q8 && !prefill && !tp && chain_mode() != 0) {   // the chained step (chain_tc.cu)
+    size_t pf = 0, sf = 0;
+    int ci = 0;
+    chain_needs(*c, R, &pf, &sf, &ci);
+    if (pf > part_need) part_need = pf;
+    THA_TRY_RC(grow(&s.ah, &s.n_ah, (size_t)R * dm.da, ws));
+    THA_TRY_RC(grow(&s.al, &s.n_al, (size_t)R * dm.da, ws));
+    THA_TRY_RC(grow(&s.ss, &s.n_ss, sf, ws));
+    const int stride = ceil_div(ci, 32) * 32, blocks = c->n_layers + 1;
+    if (stride > s.ctr_stride || blocks > s.n_ctr_blocks) {
+      if (s.ctr) THA_CUDA_OK(cudaFree(s.ctr));
+      s.ctr_stride = stride > s.ctr_stride ? stride : s.ctr_stride;
+      s.n_ctr_blocks = blocks > s.n_ctr_blocks ? blocks : s.n_ctr_blocks;
+      THA_CUDA_OK(cudaMalloc(&s.ctr, (size_t)s.ctr_stride * s.n_ctr_blocks * sizeof(int)));
+      THA_CUDA_OK(cudaMemset(s.ctr, 0, (size_t)s.ctr_stride * s.n_ctr_blocks * sizeof(int)));   // every launch leaves its block zero again
+      ws_drop_graphs(ws);
+    }
+  }
+  THA_TRY_RC(grow(&s.part, &s.n_part, part_need, ws));
   if (R > s.n_b) {
     if (s.scale) cudaFree(s.scale);
     THA_CUDA_OK(cudaMalloc(&s.scale, (size_t)R * sizeof(float)));
@@ -543,6 +568,128 @@ struct RowsIO {
   float* logits; int* next;                // [n_out, vocab] (nullable: skip the classifier), [n_out] (nullable)
 };
 
+// ---- chained matmuls (chain_tc.cu) ---------------------------------------------------------------------------------
+// Launch k of a decode step: k = 0: wq|wk|wv of layer 0 (its input comes from the embedding prep); k = 1..L: wo, w1|w3,
+// w2 of layer k-1 and then wq|wk|wv of layer k, or the classifier after the last layer.  Attention sits between two
+// launches.  fp32 weights, one GPU (the tensor-parallel exchange and the Q8_0 rows keep one launch per matmul).
+static void chain_splits_override(int which, int* z) {   // development aid: THA_CHAIN_Z="wo,w13,w2,qkv,cls" (0 keeps the planner's)
+  static int ov[5] = {-1, 0, 0, 0, 0};
+  if (ov[0] < 0) {
+    ov[0] = 0;
+    const char* v = getenv("THA_CHAIN_Z");
+    if (v && *v) sscanf(v, "%d,%d,%d,%d,%d", &ov[0], &ov[1], &ov[2], &ov[3], &ov[4]);
+  }
+  if (ov[which] > 0) *z = ov[which];
+}
+
+static ChainArgs chain_of_launch(int k, const tha_config_t& c, const tha_weights_f32_t& w, const tha_state_t& s, const TcScratch& sc,
+                                 const RowsIO& io, const float* rc, const float* rs) {
+  const Dims dm = dims_of(c, nullptr);
+  const int d = dm.d, da = dm.da, hd = dm.hd, hs = dm.hs, kvd = dm.kvd, L = c.n_layers;
+  ChainArgs a = {};
+  a.N = io.R; a.pos = io.pos; a.slot = io.slot;
+  auto qkv = [&](int l) {
+    ChainMatmul m = {};
+    m.mode = CH_ROPE; m.n_mats = 3;
+    m.W[0] = w.wq + (size_t)l * da * d; m.W[1] = w.wk + (size_t)l * d * kvd; m.W[2] = w.wv + (size_t)l * d * kvd;
+    m.M[0] = da; m.M[1] = kvd; m.M[2] = kvd; m.K = d; m.Xhi = sc.xh; m.Xlo = sc.xl; m.colscale = sc.scale;
+    m.out = io.q; m.ldo = da; m.kc = s.key_cache; m.vc = s.value_cache; m.kv_bs = (long long)L * c.seq_len * kvd;
+    m.loff = (long long)l * c.seq_len * kvd; m.kvd = kvd; m.hs = hs; m.rc = rc; m.rs = rs;
+    chain_splits_override(3, &m.splits);
+    return m;
+  };
+  if (k == 0) { a.n = 1; a.mm[0] = qkv(0); return a; }
+  const int l = k - 1;
+  {
+    ChainMatmul& m = a.mm[0];   // wo: x += wo . attention output; next input x * rms_ffn
+    m.mode = CH_RESID; m.n_mats = 1; m.W[0] = w.wo + (size_t)l * d * da; m.M[0] = d; m.K = da; m.Xhi = sc.ah; m.Xlo = sc.al;
+    m.out = io.x; m.ldo = d; m.oh = sc.xh; m.ol = sc.xl; m.gain = w.rms_ffn_weight + (size_t)l * d; m.scale_out = sc.scale;
+    chain_splits_override(0, &m.splits);
+  }
+  {
+    ChainMatmul& m = a.mm[1];   // w1 | w3 + SwiGLU
+    m.mode = CH_SWIGLU; m.n_mats = 2; m.W[0] = w.w1 + (size_t)l * d * hd; m.W[1] = w.w3 + (size_t)l * d * hd; m.M[0] = hd; m.M[1] = hd;
+    m.K = d; m.Xhi = sc.xh; m.Xlo = sc.xl; m.colscale = sc.scale; m.oh = sc.hh; m.ol = sc.hl;
+    chain_splits_override(1, &m.splits);
+  }
+  {
+    ChainMatmul& m = a.mm[2];   // w2: x += w2 . hb; next input x * (rms_att of the next layer | rms_final)
+    m.mode = CH_RESID; m.n_mats = 1; m.W[0] = w.w2 + (size_t)l * d * hd; m.M[0] = d; m.K = hd; m.Xhi = sc.hh; m.Xlo = sc.hl;
+    m.out = io.x; m.ldo = d; m.oh = sc.xh; m.ol = sc.xl;
+    m.gain = k < L ? w.rms_att_weight + (size_t)k * d : w.rms_final_weight; m.scale_out = sc.scale;
+    chain_splits_override(2, &m.splits);
+  }
+  a.n = 3;
+  if (k < L) { a.mm[3] = qkv(k); a.n = 4; }
+  else if (io.logits) {
+    ChainMatmul& m = a.mm[3];
+    m.mode = CH_PLAIN; m.n_mats = 1; m.W[0] = w.wcls; m.M[0] = c.vocab_size; m.K = d; m.Xhi = sc.xh; m.Xlo = sc.xl; m.colscale = sc.scale;
+    m.out = io.logits; m.ldo = c.vocab_size;
+    chain_splits_override(4, &m.splits);
+    a.n = 4;
+  }
+  return a;
+}
+
+// Shapes the chained step covers: fp32, one GPU, a decode step (one row per slot, every row gets logits).
+static bool chain_supported(const tha_config_t& c, int R, const TcScratch& sc, const tha_weights_f32_t& w, const tha_state_t& s) {
+  if (chain_mode() == 0) return false;
+  const Dims dm = dims_of(c, nullptr);
+  if (dm.hd % 16 || dm.d % 4 || dm.da != dm.d) return false;
+  (void)R; (void)sc; (void)w; (void)s;
+  return true;
+}
+
+static void chain_needs(const tha_config_t& c, int R, size_t* part_floats, size_t* ss_floats, int* ctr_ints) {
+  const tha_weights_f32_t w0 = {};
+  const tha_state_t s0 = {};
+  const TcScratch sc0;
+  RowsIO io = {};
+  io.R = R;
+  float dummy = 0.0f;
+  io.logits = &dummy;   // shapes only: nothing is dereferenced
+  *part_floats = 0; *ss_floats = 0; *ctr_ints = 0;
+  const int ks[3] = {0, 1, c.n_layers};
+  for (int i = 0; i < 3; i++) {
+    const ChainArgs a = chain_of_launch(ks[i], c, w0, s0, sc0, io, nullptr, nullptr);
+    size_t pf, sf; int ci;
+    chain_tc_need(a, &pf, &sf, &ci);
+    if (pf > *part_floats) *part_floats = pf;
+    if (sf > *ss_floats) *ss_floats = sf;
+    if (ci > *ctr_ints) *ctr_ints = ci;
+  }
+}
+
+// The decode step as L + 1 matmul chains with attention in between (28 launches for 12 layers instead of 112).
+static int issue_rows_chain(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_f32_t& w, const tha_state_t& s,
+                            const TcScratch& sc, const RowsIO& io, const float* rc, const float* rs, bool pdl) {
+  const Dims dm = dims_of(c, nullptr);
+  const int R = io.R, d = dm.d, L = c.n_layers, kvd = dm.kvd, hs = dm.hs;
+  const long long kv_bs = (long long)L * c.seq_len * kvd;
+  int prep_threads = ceil_div(d / 4, 32) * 32;
+  if (prep_threads > 1024) prep_threads = 1024;
+  if (prep_threads < 128) prep_threads = 128;
+  const int skip = skip_mask();
+  const TpPeers none = {};
+  const int* nogather = nullptr;
+  // embedding gather + RMSNorm(att, layer 0) folded + split (src/thaDNN.cpp:31-36, run.cc:196-209)
+  THA_CUDA_OK(launch(tc_prep_kernel, dim3(R), dim3(prep_threads), 0, st, pdl, io.x, (const float*)nullptr, 0, 0LL,
+                     w.token_embedding_table, io.token, io.pos, w.rms_att_weight, d, sc.xh, sc.xl, sc.scale, nogather, none));
+  for (int k = 0; k <= L; k++) {
+    ChainArgs a = chain_of_launch(k, c, w, s, sc, io, rc, rs);
+    a.part = sc.part; a.part_floats = sc.n_part; a.ss_part = sc.ss; a.ss_floats = sc.n_ss;
+    a.ctr = sc.ctr + (size_t)k * sc.ctr_stride; a.ctr_ints = sc.ctr_stride;
+    if (!(skip & 1)) THA_TRY_RC(chain_tc_launch(st, a, pdl));
+    if (k == L) break;
+    const int loff = k * c.seq_len * kvd;
+    if (!(skip & 2))
+      THA_TRY_RC(attn_fused_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, s.key_cache + loff, s.value_cache + loff,
+                                   kv_bs, hs, c.seq_len, pdl, sc.ah, sc.al));
+  }
+  if (io.next && !(skip & 64)) THA_TRY_RC(argmax_launch(st, io.n_out, io.logits, c.vocab_size, io.next, pdl));
+  return THA_STATUS_SUCCESS;
+}
+
 // `wq` != nullptr: Q8_0 weights (then `w` only lends its embedding table and norm gains).
 // `tp` != nullptr: this rank's share of a tensor-parallel model (c = the LOCAL config: n_heads, n_kv_heads, hidden_dim
 // are this rank's; dim is the full residual width): the wo / w2 partials go to the exchange buffers and their consumer
@@ -557,6 +704,8 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
   }
   const int R = io.R;
   const bool q8 = wq != nullptr;
+  if (!q8 && !tp && io.n_tiles == 0 && !io.out_rows && io.n_out == R && io.logits && sc.ctr && chain_supported(c, R, sc, w, s))
+    return issue_rows_chain(st, ws, c, w, s, sc, io, rc, rs, pdl);
   const int gs = wq ? wq->group_size : 0;
   const Dims dm = dims_of(c, tp);
   const TcPlan pl = make_plan(dm, R, q8, q8 ? gs : 64);

@@ -51,6 +51,14 @@ int dual_min_rows() {
   return g_dual;
 }
 int* opt_dual() { return &g_dual; }
+static int g_chain = -2;
+int chain_mode() {   // 1: matmul chains with fused epilogues (chain_tc.cu) where the shape allows; 0 (default): one launch per matmul
+  // Off by default: measured on stories110M fp32 at 256 slots the chained step takes 1.29 ms against 0.99 ms -- a phase
+  // costs ~20 us whether its synchronisation points are kernel boundaries or counters in L2 (profiles/r02_chain_trace.txt).
+  if (g_chain == -2) { const char* v = getenv("THA_CHAIN"); g_chain = (v && *v) ? atoi(v) : 0; }
+  return g_chain;
+}
+int* opt_chain() { chain_mode(); return &g_chain; }
 void count_launch(int n) { g_launches += n; }
 int launches_reset() { int v = g_launches; g_launches = 0; return v; }
 int launches_get() { return g_launches; }
@@ -194,6 +202,7 @@ extern "C" int tha_set_option(const char* name, int value) {
   if (!strcmp(name, "graph")) { *tha::opt_graph() = value != 0; return THA_STATUS_SUCCESS; }
   if (!strcmp(name, "tc")) { *tha::opt_tc() = value; return THA_STATUS_SUCCESS; }
   if (!strcmp(name, "dual")) { tha::dual_min_rows(); *tha::opt_dual() = value; return THA_STATUS_SUCCESS; }
+  if (!strcmp(name, "chain")) { *tha::opt_chain() = value; return THA_STATUS_SUCCESS; }
   if (!strcmp(name, "mega")) { tha::mega_set_enabled(value); return THA_STATUS_SUCCESS; }
   return THA_STATUS_INVALID_ARG;
 }

@@ -55,6 +55,7 @@ inline void ws_drop_graphs(Workspace* ws) {
 }
 void ws_release(Workspace* ws);        // free everything a (tensor-parallel rank's) workspace owns
 void step_tc_release(Workspace* ws);   // ... and the row pipeline's scratch keyed by it
+int chain_mode();      // 1: matmul chains with fused epilogues (chain_tc.cu), 0: one launch per matmul (the round-1 pipeline)
 int dual_min_rows();   // rows from which a step is issued as two concurrent half-batches (0 = never)
 int ws_rope(Workspace* ws, int head_size, int seq_len, const float** cos_d, const float** sin_d);
 

@@ -127,6 +127,23 @@ def test_fp32_tensor_core_step_vs_oracle(oracle, tmp_path, name, B):
     assert flips == 0
 
 
+@pytest.mark.parametrize("name,B", [("fusedA", 16), ("fusedGQA", 70), ("fusedA", 130)])
+def test_fp32_chained_matmuls_vs_oracle(oracle, tmp_path, name, B):
+    """tha_set_option("chain", 1): wo -> w1|w3 -> w2 -> next wq|wk|wv as ONE persistent launch per layer with residual /
+    RMSNorm / SwiGLU / RoPE fused into the matmul epilogues (chain_tc.cu); same comparison, same 1e-4."""
+    lib = load_pkg("cabi").lib()
+    cfg, w, v0, v2 = small_model_files(str(tmp_path), name, MODELS[name])
+    lib.check(lib.c.tha_set_option(b"chain", 1))
+    try:
+        e = engine_from_v0(v0, B)
+        flips = run_ragged(e, oracle.open(v0), min(cfg.seq_len, 12), B, np.random.default_rng(B), FP32_EPS)
+        assert e.last_step_launches() == 2 * cfg.n_layers + 2     # embedding prep, L + 1 chains, L attentions
+        assert lib.c.tha_gemm_check_error() == 0
+    finally:
+        lib.check(lib.c.tha_set_option(b"chain", 0))
+    assert flips == 0
+
+
 def test_fp32_tensor_core_step_forced_small_batch(oracle, tmp_path):
     """tha_set_option("tc", 1): the tensor-core step for 3 slots agrees with the oracle too."""
     lib = load_pkg("cabi").lib()
