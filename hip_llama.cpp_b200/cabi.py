@@ -100,6 +100,9 @@ class Lib:
             "tha_prefill_q8": [vp, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), I, vp, vp, vp, vp, vp, vp],
             "tha_matmul_q8_tc": [vp, vp, C.c_longlong, vp, vp, I, I, I, vp, vp, I, I],
             "tha_argmax_batch_f32": [vp, I, vp, I, vp],
+            "tha_sample": [vp, I, vp, I, F, F, vp, vp, vp, vp, vp],
+            "tha_forward_sample_f32": [vp, I, C.POINTER(Config), C.POINTER(WeightsF32), C.POINTER(State), vp, vp, vp, vp, F, F, vp],
+            "tha_forward_sample_q8": [vp, I, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), vp, vp, vp, vp, F, F, vp],
             "tha_advance_slots": [vp, I, vp, vp, vp, I],
             "tha_tp_create": [C.POINTER(vp), I, I, I, C.POINTER(C.c_int), C.c_size_t],
             "tha_tp_export": [vp, vp],

@@ -60,6 +60,8 @@ TpCtx* tp_ctx(tha_tp_t* t);
 int gemm_tc_check_error();
 int tc_mode();   // -1 auto (B > 8), 0 never, 1 whenever the shape allows
 int advance_launch(cudaStream_t st, int B, int* token, int* pos, const int* next, int seq_len, bool pdl);
+int sample_launch(cudaStream_t st, int B, float* logits, int vocab, float temperature, float topp, unsigned long long* rng,
+                  const unsigned long long* reseed, const int* force, const int* pos, int* next, bool pdl);
 
 static thread_local int g_last_step_launches = 0;
 #define THA_TRY_RC2(expr) do { int _st = (expr); if (_st != THA_STATUS_SUCCESS) return _st; } while (0)
@@ -503,6 +505,69 @@ static int forward_host_greedy(cudaStream_t st, int B, const tha_config_t* cfg, 
   }
   memcpy(next_host, ws->next_h, B * sizeof(int));
   return THA_STATUS_SUCCESS;
+}
+
+// The driver's step in its default (sampled) mode: HOST token / pos / forced prompt token / sampler reseed in, HOST next
+// token per slot out; softmax, top-p and the coin run on the device (sampler.cu), B ints cross PCIe instead of B * vocab
+// floats (src/llama.cpp:1025-1050 around thaDNN_s_forward_batch + sample()).
+template <typename StepFn>
+static int forward_host_sample(cudaStream_t st, int B, const tha_config_t* cfg, float* logits_d, const int* token_host,
+                               const int* pos_host, const int* force_host, const unsigned long long* reseed_host,
+                               float temperature, float topp, int* next_host, StepFn step) {
+  if (B <= 0 || !cfg || !logits_d || !token_host || !pos_host || !next_host || temperature < 0.0f) return THA_STATUS_INVALID_ARG;
+  THA_TRY(check_tokpos(B, cfg->vocab_size, cfg->seq_len, token_host, pos_host));
+  Workspace* ws = workspace();
+  if (!ws) return THA_STATUS_EXECUTION_FAILED;
+  THA_TRY(ws_ensure_tokpos(ws, B));
+  const int cap = ws->tokpos_cap;
+  int* h = ws->tokpos_h;
+  memcpy(h, token_host, B * sizeof(int));
+  memcpy(h + cap, pos_host, B * sizeof(int));
+  for (int b = 0; b < B; b++) {
+    const int f = force_host ? force_host[b] : -1;
+    if (f >= cfg->vocab_size) return THA_STATUS_INVALID_ARG;
+    h[2 * cap + b] = f;
+  }
+  unsigned long long* rs = reinterpret_cast<unsigned long long*>(h + 3 * cap);
+  for (int b = 0; b < B; b++) rs[b] = reseed_host ? reseed_host[b] : 0ull;
+  THA_CUDA_OK(cudaMemcpyAsync(ws->tok_d, h, 5 * cap * sizeof(int), cudaMemcpyHostToDevice, st));
+  THA_TRY(step(ws->tok_d, ws->pos_d, logits_d));
+  THA_TRY(sample_launch(st, B, logits_d, cfg->vocab_size, temperature, topp, ws->rng_d, ws->reseed_d, ws->force_d, ws->pos_d,
+                        ws->next_d, false));
+  THA_CUDA_OK(cudaMemcpyAsync(ws->next_h, ws->next_d, B * sizeof(int), cudaMemcpyDeviceToHost, st));
+  THA_CUDA_OK(cudaStreamSynchronize(st));
+  if (mega_check_abort(ws->device)) {
+    set_last_error("persistent step kernel: a barrier wait timed out", cudaErrorLaunchTimeout);
+    return THA_STATUS_EXECUTION_FAILED;
+  }
+  if (gemm_tc_check_error()) {
+    set_last_error("tensor-core matmul: a pipeline barrier wait timed out", cudaErrorLaunchTimeout);
+    return THA_STATUS_EXECUTION_FAILED;
+  }
+  memcpy(next_host, ws->next_h, B * sizeof(int));
+  return THA_STATUS_SUCCESS;
+}
+
+extern "C" int tha_forward_sample_f32(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_f32_t* w,
+                                      const tha_state_t* s, const int* token_host, const int* pos_host, const int* force_host,
+                                      const unsigned long long* reseed_host, float temperature, float topp, int* next_host) {
+  if (!cfg || !s || !s->logits) return THA_STATUS_INVALID_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  return forward_host_sample(st, n_batches, cfg, s->logits, token_host, pos_host, force_host, reseed_host, temperature, topp,
+                             next_host, [&](const int* tok_d, const int* pos_d, float* lg) {
+                               return decode_step_f32(st, n_batches, cfg, w, s, tok_d, pos_d, lg, nullptr, 0);
+                             });
+}
+
+extern "C" int tha_forward_sample_q8(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_q8_t* w,
+                                     const tha_state_t* s, const int* token_host, const int* pos_host, const int* force_host,
+                                     const unsigned long long* reseed_host, float temperature, float topp, int* next_host) {
+  if (!cfg || !s || !s->logits) return THA_STATUS_INVALID_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  return forward_host_sample(st, n_batches, cfg, s->logits, token_host, pos_host, force_host, reseed_host, temperature, topp,
+                             next_host, [&](const int* tok_d, const int* pos_d, float* lg) {
+                               return decode_step_q8(st, n_batches, cfg, w, s, tok_d, pos_d, lg, nullptr);
+                             });
 }
 
 extern "C" int tha_forward_greedy_f32(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_f32_t* w,

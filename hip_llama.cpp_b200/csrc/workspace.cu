@@ -136,11 +136,17 @@ int ws_ensure_tokpos(Workspace* ws, int n_batches) {
   if (n_batches <= ws->tokpos_cap) return THA_STATUS_SUCCESS;
   if (ws->tok_d) { cudaFree(ws->tok_d); cudaFreeHost(ws->tokpos_h); }
   int cap = n_batches < 64 ? 64 : n_batches * 2;
-  THA_CUDA_OK(cudaMalloc(&ws->tok_d, 3 * cap * sizeof(int)));   // [tok | pos | next]
+  // device: [tok | pos | force | reseed (u64) | next | rng (u64)]; the pinned mirror has the same first five blocks, so ONE
+  // copy of 5 * cap ints stages everything a sampled step takes from the host (greedy steps copy the first two)
+  THA_CUDA_OK(cudaMalloc(&ws->tok_d, 8 * cap * sizeof(int)));
+  THA_CUDA_OK(cudaMemset(ws->tok_d, 0, 8 * cap * sizeof(int)));
   ws->pos_d = ws->tok_d + cap;
-  ws->next_d = ws->tok_d + 2 * cap;
-  THA_CUDA_OK(cudaMallocHost(&ws->tokpos_h, 3 * cap * sizeof(int)));
-  ws->next_h = ws->tokpos_h + 2 * cap;
+  ws->force_d = ws->tok_d + 2 * cap;
+  ws->reseed_d = reinterpret_cast<unsigned long long*>(ws->tok_d + 3 * cap);
+  ws->next_d = ws->tok_d + 5 * cap;
+  ws->rng_d = reinterpret_cast<unsigned long long*>(ws->tok_d + 6 * cap);
+  THA_CUDA_OK(cudaMallocHost(&ws->tokpos_h, 6 * cap * sizeof(int)));
+  ws->next_h = ws->tokpos_h + 5 * cap;
   ws->tokpos_cap = cap;
   ws_drop_graphs(ws);
   return THA_STATUS_SUCCESS;

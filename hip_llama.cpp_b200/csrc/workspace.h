@@ -25,7 +25,10 @@ struct Workspace {
   int* counters = nullptr; int counters_cap = 0;
   // device mirrors of the host token[] / pos[] arrays of thaDNN_s_forward_batch
   int* tok_d = nullptr; int* pos_d = nullptr; int* tokpos_h = nullptr; int tokpos_cap = 0;
-  int* next_d = nullptr; int* next_h = nullptr;   // greedy token per slot (device, pinned host)
+  int* next_d = nullptr; int* next_h = nullptr;   // next token per slot (device, pinned host)
+  int* force_d = nullptr;                         // sampled steps: prompt token to take instead of sampling (-1: sample)
+  unsigned long long* reseed_d = nullptr;         // ... non-zero: the slot starts a request with this sampler seed
+  unsigned long long* rng_d = nullptr;            // xorshift* state of the request in each slot (sampler.cu)
   // Q8_0: quantised activations of the current matmul input ([B, K] int8 + [B, K/gs] scales)
   int8_t* q8_xq = nullptr; float* q8_xs = nullptr; size_t q8_cap = 0;
   // RoPE cos/sin tables keyed by (head_size, seq_len); built on the host with libm so

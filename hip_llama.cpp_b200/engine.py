@@ -222,6 +222,25 @@ class Engine:
         self.lib.check(st, "tha_forward_greedy")
         return next_host
 
+    def forward_sample(self, tokens, pos, force=None, reseed=None, temperature=1.0, topp=0.9, next_host=None, stream=None):
+        """thaDNN_s_forward_batch + sample() per slot (src/llama.cpp:1025-1050) in one call: HOST token/pos, forced prompt
+        token per slot (-1 = sample) and sampler reseed per slot (0 = keep) in, HOST next token out; softmax / top-p / coin on
+        the device."""
+        tok = np.ascontiguousarray(tokens, dtype=np.int32)
+        ps = np.ascontiguousarray(pos, dtype=np.int32)
+        fc = None if force is None else np.ascontiguousarray(force, dtype=np.int32)
+        rs = None if reseed is None else np.ascontiguousarray(reseed, dtype=np.uint64)
+        if next_host is None:
+            next_host = np.zeros(self.B, np.int32)
+        fn = self.lib.c.tha_forward_sample_q8 if self.q8 else self.lib.c.tha_forward_sample_f32
+        vp = C.c_void_p
+        st = fn(_stream_ptr(stream), self.B, C.byref(self.ccfg), C.byref(self.w.c), C.byref(self.state.c),
+                tok.ctypes.data_as(vp), ps.ctypes.data_as(vp), fc.ctypes.data_as(vp) if fc is not None else None,
+                rs.ctypes.data_as(vp) if rs is not None else None, C.c_float(temperature), C.c_float(topp),
+                next_host.ctypes.data_as(vp))
+        self.lib.check(st, "tha_forward_sample")
+        return next_host
+
     def decode_step(self, token_d, pos_d, logits_d=None, next_d=None, stream=None):
         """Resident step: device token/pos, optional device logits and greedy next tokens."""
         fn = self.lib.c.tha_decode_step_q8 if self.q8 else self.lib.c.tha_decode_step_f32

@@ -112,8 +112,14 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
 
     RunState* s_d = nullptr;
     alloc_state_to_device_batch_cfg(&cfg, s_d, B, tha_step_needs_att_scratch((const tha_config_t*)&cfg));
+    // temperature != 0: softmax / top-p / coin run on the device (tha_forward_sample_*, csrc/sampler.cu), one xorshift*
+    // stream per request as in the reference (src/llama.cpp:895-900); opt.host_sampler = 1 keeps the reference's scheme
+    // (B * vocab logits to pinned host memory, sample() on the host cores)
+    const bool device_sampler = !greedy && !opt.host_sampler;
     float* logits_host = nullptr;
-    if (!greedy) CHECK_THA(tha_host_alloc((void**)&logits_host, (size_t)B * vocab * sizeof(float)));
+    if (!greedy && !device_sampler) CHECK_THA(tha_host_alloc((void**)&logits_host, (size_t)B * vocab * sizeof(float)));
+    std::vector<int> force(B, -1);
+    std::vector<unsigned long long> reseed(B, 0ull);
 
     const int kvd = cfg.dim * cfg.n_kv_heads / cfg.n_heads;
     BatchManager bm(B, cfg.seq_len, cfg.n_layers, kvd);
@@ -122,7 +128,7 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
     std::vector<int> token(B, 0), pos(B, -1), next(B, 0);
     Config cfg_local = cfg;
 
-    const bool use_prefill = opt.prefill && t32 && tha_prefill_supported((const tha_config_t*)&cfg_local);
+    const bool use_prefill = opt.prefill && tha_prefill_supported((const tha_config_t*)&cfg_local);
     std::vector<int> pf_slot, pf_pos0, pf_len, pf_tokens;
 
     const long t_loop0 = time_in_ms();
@@ -148,6 +154,7 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
         if (opt.max_new_positions > 0 && opt.max_new_positions < sl.steps) sl.steps = opt.max_new_positions;
         token[got] = sl.prompt[0];
         pos[got] = 0;
+        reseed[got] = opt.seed;   // the request's own sampler stream starts here
         // Prompt ingestion in one pass: positions 0..m-1 go through tha_prefill_f32 (cache rows only), the slot
         // then joins the step loop at position m with the prompt's token m -- the state the reference reaches
         // after m forced-prompt steps (src/llama.cpp:1029-1030), text and ids included.
@@ -168,9 +175,14 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
       }
       if (bm.active_slots() == 0) break;
       if (!pf_slot.empty()) {
-        CHECK_THA(tha_prefill_f32((void*)handle.calc_stream, (const tha_config_t*)&cfg_local, (const tha_weights_f32_t*)w_d,
-                                  (const tha_state_t*)s_d, (int)pf_slot.size(), pf_slot.data(), pf_pos0.data(), pf_len.data(),
-                                  pf_tokens.data(), nullptr, nullptr));
+        if (t32)
+          CHECK_THA(tha_prefill_f32((void*)handle.calc_stream, (const tha_config_t*)&cfg_local, (const tha_weights_f32_t*)w_d,
+                                    (const tha_state_t*)s_d, (int)pf_slot.size(), pf_slot.data(), pf_pos0.data(), pf_len.data(),
+                                    pf_tokens.data(), nullptr, nullptr));
+        else
+          CHECK_THA(tha_prefill_q8((void*)handle.calc_stream, (const tha_config_t*)&cfg_local, (const tha_weights_q8_t*)wq_d,
+                                   (const tha_state_t*)s_d, (int)pf_slot.size(), pf_slot.data(), pf_pos0.data(), pf_len.data(),
+                                   pf_tokens.data(), nullptr, nullptr));
         n_prefill_rows += (long long)pf_tokens.size();
       }
 
@@ -181,6 +193,18 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
                                           (const tha_state_t*)s_d, token.data(), pos.data(), next.data())
                  : tha_forward_greedy_q8((void*)handle.calc_stream, B, (const tha_config_t*)&cfg_local, (const tha_weights_q8_t*)wq_d,
                                          (const tha_state_t*)s_d, token.data(), pos.data(), next.data());
+      } else if (device_sampler) {
+        for (int s = 0; s < B; s++) {
+          const int req = bm.request_of(s);
+          force[s] = (req >= 0 && pos[s] < (int)slots[s].prompt.size() - 1) ? slots[s].prompt[pos[s] + 1] : -1;
+        }
+        rc = t32 ? tha_forward_sample_f32((void*)handle.calc_stream, B, (const tha_config_t*)&cfg_local, (const tha_weights_f32_t*)w_d,
+                                          (const tha_state_t*)s_d, token.data(), pos.data(), force.data(), reseed.data(),
+                                          opt.temperature, opt.topp, next.data())
+                 : tha_forward_sample_q8((void*)handle.calc_stream, B, (const tha_config_t*)&cfg_local, (const tha_weights_q8_t*)wq_d,
+                                         (const tha_state_t*)s_d, token.data(), pos.data(), force.data(), reseed.data(),
+                                         opt.temperature, opt.topp, next.data());
+        std::fill(reseed.begin(), reseed.end(), 0ull);
       } else {
         rc = t32 ? (int)thaDNN_s_forward_batch(handle, handle, handle, B, &cfg_local, w_d, s_d, token.data(), pos.data(), logits_host)
                  : (int)thaDNN_q8_forward_batch(handle, B, &cfg_local, wq_d, s_d, token.data(), pos.data(), logits_host);
@@ -195,7 +219,7 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
         Slot& sl = slots[s];
         int nx;
         if (pos[s] < (int)sl.prompt.size() - 1) nx = sl.prompt[pos[s] + 1];            // still inside the prompt
-        else if (greedy) nx = next[s];
+        else if (greedy || device_sampler) nx = next[s];
         else nx = sample(&samplers[req], logits_host + (size_t)s * vocab);
         bm.advance(s);
         pos[s] += 1;

@@ -207,6 +207,23 @@ int tha_forward_greedy_f32(void* stream, int n_batches, const tha_config_t* cfg,
                            const tha_state_t* s, const int* token_host, const int* pos_host, int* next_host);
 int tha_forward_greedy_q8(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_q8_t* w,
                           const tha_state_t* s, const int* token_host, const int* pos_host, int* next_host);
+/* The driver's sampler on the device (replaces sample() / sample_topp() / sample_mult() / random_f32() of
+ * src/llama.cpp:262-411 for B slots at once).  logits_d [B, vocab] is overwritten with the
+ * probabilities (as the reference's sample() does).  rng_d [B]: xorshift* state of the request in each slot, advanced once
+ * per SAMPLED token; reseed_d (nullable) [B]: non-zero = start the slot's stream from this seed first; force_d (nullable)
+ * [B]: >= 0 = the next token is this prompt token, no coin is drawn (src/llama.cpp:1029-1030); pos_d [B]: < 0 = idle.
+ * temperature 0 = greedy (first maximum). */
+int tha_sample(void* stream, int n_batches, float* logits_d, int vocab, float temperature, float topp,
+               unsigned long long* rng_d, const unsigned long long* reseed_d, const int* force_d, const int* pos_d, int* next_d);
+/* thaDNN_s_forward_batch + sample() per slot in one call (src/llama.cpp:1025-1050): HOST token / pos / forced prompt
+ * token (-1 = sample) / sampler reseed (0 = keep the slot's stream) in, HOST next token per slot out.  The sampler
+ * state of every slot lives on the device between calls. */
+int tha_forward_sample_f32(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_f32_t* w,
+                           const tha_state_t* s, const int* token_host, const int* pos_host, const int* force_host,
+                           const unsigned long long* reseed_host, float temperature, float topp, int* next_host);
+int tha_forward_sample_q8(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_q8_t* w,
+                          const tha_state_t* s, const int* token_host, const int* pos_host, const int* force_host,
+                          const unsigned long long* reseed_host, float temperature, float topp, int* next_host);
 /* greedy sampler on the device: next[b] = first argmax of logits[b, :] */
 int tha_argmax_batch_f32(void* stream, int n_batches, const float* logits, int vocab, int* next_d);
 /* greedy bookkeeping of the batching driver (src/llama.cpp:1027-1050) kept on the device:
