@@ -58,6 +58,8 @@ def parse_args():
                     "(same bytes and time per step as a real context of that length); the default 0 is the benchmark")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the bounded sub-records of the other BASELINE configs (extra.*)")
+    ap.add_argument("--no-shares", action="store_true", help="skip the live-share measurement (roofline.live_shares_us)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     return ap.parse_args()
 
@@ -81,12 +83,14 @@ def measured_peak():
 
 
 def measured_traffic(args):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one decode step, from the committed ncu capture of this
-    exact configuration (profiles/traffic.json, keyed model/quant/B<slots>); None when it was not captured."""
+    """dram__bytes_read.sum + dram__bytes_write.sum per decode step, from the committed ncu launch list of THIS
+    configuration and THESE positions (profiles/traffic.json, keyed model/quant/B<slots>/pos<first>-<last>); None when
+    that exact range was not captured (a capture at other positions says nothing about this step: the KV share differs)."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             t = json.load(f)
-        return t.get(f"{args.model}/{args.quant}/B{args.batch}", {}).get("bytes_per_step")
+        p0 = args.pos0 + args.warmup
+        return t.get(f"{args.model}/{args.quant}/B{args.batch}/pos{p0}-{p0 + args.steps - 1}", {}).get("bytes_per_step")
     except OSError:
         return None
 
@@ -290,95 +294,313 @@ def run_ours(args, rank, world, local_rank):
     achieved = total_bytes / (ms * 1e-3) / 1e9
     peak, peak_src = measured_peak()
 
-    # ---------------- the dominant kernel of a long-context step, alone: decode attention ----------------
-    # (tha_mha_fused_v1_f32 = attn_fused_kernel over the KV cache this run just filled; one launch per layer so every
-    #  launch streams a different layer's rows: no L2 reuse between launches when a layer's rows exceed the L2)
-    attn = None
-    if tp == 1:
+    # ---------------- where the timed step's time goes, live ----------------
+    # One kernel class at a time is left out of the step (tha_set_option("skip", mask); graph + PDL stay on) over the
+    # SAME positions; the difference to the full step is that class's live share.  The dominant class gets its own
+    # roofline figures: algorithmic bytes per launch / live time per launch, and useful flops against the tensor peak.
+    shares = None
+    dominant = None
+    if tp == 1 and not args.no_shares and launches_per_step > 1:
         try:
-            import ctypes as C
             lib = e.lib
-            hs = cfg.dim // cfg.n_heads
-            kvd = hs * cfg.n_kv_heads
-            pos_last = args.pos0 + W + K - 1
-            with torch.cuda.stream(stream):
-                posk = torch.full((B,), pos_last, dtype=torch.int32, device=device)
-                vp = lambda t: C.c_void_p(t.data_ptr())
-                lib.c.tha_mha_fused_v1_f32.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
-                                                       C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]
-                def attn_layer(l):
-                    lib.check(lib.c.tha_mha_fused_v1_f32(C.c_void_p(stream.cuda_stream), B, vp(posk), cfg.n_heads, cfg.n_kv_heads,
-                                                         cfg.n_layers, vp(e.state.q), vp(e.state.xb), vp(e.state.key_cache),
-                                                         vp(e.state.value_cache), hs, cfg.seq_len, l * cfg.seq_len * kvd), "tha_mha_fused_v1_f32")
-                reps = 4
-                for l in range(cfg.n_layers):
-                    attn_layer(l)
-                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                a0.record(stream)
-                for _ in range(reps):
-                    for l in range(cfg.n_layers):
-                        attn_layer(l)
-                a1.record(stream)
-                stream.synchronize()
-            us = a0.elapsed_time(a1) * 1e3 / (reps * cfg.n_layers)
-            nbytes = B * 2 * kvd * 4 * (pos_last + 1)
-            attn = {"kernel": "attn_fused_kernel (decode attention of one layer, all slots at position %d)" % pos_last,
-                    "bytes_per_launch": nbytes, "us_per_launch": us, "achieved": nbytes / us / 1e3, "unit": "GB/s",
-                    "frac": nbytes / us / 1e3 / peak,
-                    "l2": "a layer's rows: %.0f MB vs 126 MB L2; launches cycle over the %d layers" % (nbytes / 1e6, cfg.n_layers)}
+            def timed(mask):
+                lib.check(lib.c.tha_set_option(b"skip", mask), "skip")
+                with torch.cuda.stream(stream):
+                    pos.fill_(args.pos0); tok.copy_(torch.from_numpy(tok0).to(device))
+                    for _ in range(W):
+                        step()
+                    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a0.record(stream)
+                    for _ in range(K):
+                        step()
+                    a1.record(stream)
+                    stream.synchronize()
+                return a0.elapsed_time(a1) * 1e3 / K
+            full = timed(0)
+            classes = (("layer_matmuls", 1), ("attention", 2), ("prep", 4), ("rope_scatter", 8), ("swiglu_or_quantise", 16),
+                       ("classifier", 32), ("argmax", 64))
+            shares = {"full_step": full}
+            for name, mask in classes:
+                shares[name] = max(0.0, full - timed(mask))
+            lib.check(lib.c.tha_set_option(b"skip", 0), "skip")
+            top = max((n for n, _ in classes), key=lambda n: shares[n])
+            L, d, hd, kvd = cfg.n_layers, cfg.dim, cfg.hidden_dim, cfg.kv_dim
+            elem = 1.0 + 4.0 / dw.gs if e.q8 else 4.0          # bytes per weight (Q8_0: int8 + one fp32 scale per group)
+            layer_w = L * (2 * d * d + 2 * d * kvd + 3 * d * hd)
+            mid = args.pos0 + W + K / 2.0
+            per = {"layer_matmuls": (4 * L, layer_w * elem, 2.0 * B * layer_w),
+                   "classifier": (1, cfg.vocab_size * d * elem + B * cfg.vocab_size * 4, 2.0 * B * cfg.vocab_size * d),
+                   "attention": (L, B * 2 * kvd * 4 * (mid + 1) * L, 4.0 * B * d * (mid + 1) * L)}
+            if top in per:
+                n_launch, nbytes, flops = per[top]
+                us = shares[top]
+                try:
+                    tf_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"])
+                except Exception:
+                    tf_peak = 1381.0
+                dominant = {"class": top, "launches_per_step": n_launch, "live_us_per_step": us, "live_us_per_launch": us / n_launch,
+                            "algorithmic_bytes_per_step": nbytes, "achieved_gbs": nbytes / us / 1e3, "hbm_frac": nbytes / us / 1e3 / peak,
+                            "useful_tflops": flops / us / 1e6, "tensor_frac_of_sustained_bf16": flops / us / 1e6 / tf_peak,
+                            "note": "live = step time with this class minus step time without it, same positions, graph + PDL on"}
         except Exception as ex:   # a diagnostic, never the reason a bench line is missing
-            attn = {"kernel": "attn_fused_kernel", "error": str(ex)}
+            shares = {"error": str(ex)}
+    attn = {"live_shares_us": shares, "dominant_kernel": dominant}
 
-    # ---------------- e2e: the reference-facing call with HOST buffers ----------------
+    # ---------------- e2e: the driver's step with HOST buffers ----------------
+    # Headline: the call the shipped driver makes every step in the reference's DEFAULT mode (temperature 1.0, top-p 0.9,
+    # src/llama.cpp:897-900): tha_forward_sample_* = thaDNN_s_forward_batch + sample() per slot, HOST token / pos / forced
+    # token / reseed in, HOST next tokens out, sampler on the device.  Beside it: the greedy form (-t 0), and the reference's
+    # own signature (B * vocab logits into pinned host memory + host argmax), which is PCIe-bound by construction
+    # (32.8 MB per step at 256 slots).
     e2e = None
     if not args.no_e2e and tp == 1:
-        # the host-side greedy sampler gets this rank's share of the box's cores (torchrun pins OMP_NUM_THREADS to 1)
         torch.set_num_threads(max(1, host_cores() // max(world, 1)))
-        lg_host = torch.empty(B, cfg.vocab_size, dtype=torch.float32).pin_memory()
+        Ke = min(K, 128)
         tok_h = tok0.copy()
         pos_h = np.zeros(B, np.int32)
-        Ke = min(K, 128)
+        nx_h = np.zeros(B, np.int32)
+        force_h = np.full(B, -1, np.int32)
+        seeds = np.full(B, 314028, np.uint64)
 
-        def estep():
-            e.forward_batch(tok_h, pos_h, lg_host, stream=stream)   # H2D token/pos, step, D2H logits, sync
-            tok_h[:] = lg_host.argmax(dim=1).numpy()                # greedy sampler on the host cores, as the driver does
+        def loop(fn):
+            tok_h[:] = tok0
+            pos_h[:] = 0
+            for i in range(W):
+                fn(i)
+            barrier()
+            t0 = time.perf_counter()
+            for i in range(Ke):
+                fn(W + i)
+            torch.cuda.synchronize()
+            return load_pkg("dp").max_over_ranks(time.perf_counter() - t0, device)
+
+        def sstep(i):
+            e.forward_sample(tok_h, pos_h, force_h, seeds if i == 0 else None, 1.0, 0.9, nx_h, stream=stream)
+            tok_h[:] = nx_h
             pos_h[:] += 1
 
-        for _ in range(W):
-            estep()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(Ke):
-            estep()
-        torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        dt = load_pkg("dp").max_over_ranks(dt, device)
-        e2e = {"value": world * B * Ke / dt, "unit": UNIT, "h2d_bytes_per_step": int(2 * 4 * B),
-               "d2h_bytes_per_step": int(B * cfg.vocab_size * 4), "steps": Ke,
-               "api": "tha_forward_batch_%s (thaDNN_s_forward_batch)" % args.quant}
-        # the additive greedy form of the same call (argmax on the device, B ints back): what the shipped driver uses at -t 0
-        tok_h[:] = tok0
-        pos_h[:] = 0
-        nx_h = np.zeros(B, np.int32)
+        dts = loop(sstep)
+        e2e = {"value": world * B * Ke / dts, "unit": UNIT, "h2d_bytes_per_step": int((3 * 4 + 8) * B),
+               "d2h_bytes_per_step": int(4 * B), "steps": Ke,
+               "api": "tha_forward_sample_%s (thaDNN_s_forward_batch + sample(): temperature 1.0, top-p 0.9, one xorshift* "
+                      "stream per slot; softmax / top-p / coin on the device)" % args.quant}
 
-        def gstep():
+        def gstep(i):
             e.forward_greedy(tok_h, pos_h, nx_h, stream=stream)
             tok_h[:] = nx_h
             pos_h[:] += 1
 
-        for _ in range(W):
-            gstep()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(Ke):
-            gstep()
-        torch.cuda.synchronize()
-        dtg = load_pkg("dp").max_over_ranks(time.perf_counter() - t0, device)
+        dtg = loop(gstep)
         e2e["greedy_call"] = {"value": world * B * Ke / dtg, "unit": UNIT, "h2d_bytes_per_step": int(2 * 4 * B),
-                              "d2h_bytes_per_step": int(4 * B), "api": "tha_forward_greedy_%s (additive: forward + sample_argmax)" % args.quant}
+                              "d2h_bytes_per_step": int(4 * B), "api": "tha_forward_greedy_%s (forward + sample_argmax, -t 0)" % args.quant}
+        lg_host = torch.empty(B, cfg.vocab_size, dtype=torch.float32).pin_memory()
+
+        def estep(i):
+            e.forward_batch(tok_h, pos_h, lg_host, stream=stream)   # H2D token/pos, step, D2H logits, sync
+            tok_h[:] = lg_host.argmax(dim=1).numpy()                # greedy sampler on the host cores
+            pos_h[:] += 1
+
+        Kl, Ke = min(Ke, 32), min(Ke, 32)
+        dtl = loop(estep)
+        e2e["logits_call"] = {"value": world * B * Kl / dtl, "unit": UNIT, "h2d_bytes_per_step": int(2 * 4 * B),
+                              "d2h_bytes_per_step": int(B * cfg.vocab_size * 4), "steps": Kl,
+                              "api": "tha_forward_batch_%s (thaDNN_s_forward_batch: [B, vocab] logits to pinned host memory) + host argmax" % args.quant}
+        del lg_host
+
+    # ---------------- parity sample: the benchmarked engine against the reference's own code ----------------
+    parity = None
+    if tp == 1 and rank == 0 and host_w is not None and not args.no_cpu_baseline:
+        try:
+            parity = parity_sample(args, cfg, host_w, e, B)
+        except Exception as ex:
+            parity = {"error": str(ex)}
     return dict(cfg=cfg, value=value, ms_per_step=ms_max / K, achieved=achieved, peak=peak, peak_src=peak_src,
-                bytes_per_step=total_bytes / K, wbytes=wbytes, clocks=clocks, e2e=e2e,
+                bytes_per_step=total_bytes / K, wbytes=wbytes, clocks=clocks, e2e=e2e, parity=parity,
                 launches=launches_per_step * K, launches_per_step=launches_per_step, host_w=host_w, attn=attn)
+
+
+def parity_sample(args, cfg, host_w, e, B, n_slots=4, n_steps=8):
+    """Untimed: the engine that was just benchmarked decodes n_steps teacher-forced positions from 0 (all B slots, random
+    tokens); n_slots of them are replayed through oracle/_ref (run.cc / runq.c compiled unmodified) and compared."""
+    from oracle_lib import Ref32, RefQ8, ref_available
+    from pkgload import load_pkg
+    ck = load_pkg("checkpoint")
+    q8 = args.quant == "q8"
+    kind = "q8" if q8 else "fp32"
+    if not ref_available(kind):
+        return {"error": "oracle/_ref not built"}
+    rng = np.random.default_rng(4321)
+    toks = rng.integers(3, cfg.vocab_size, size=(n_steps, B)).astype(np.int32)
+    sample = sorted(set(int(x) for x in np.linspace(0, B - 1, n_slots)))
+    with tempfile.TemporaryDirectory() as td:
+        path = os.path.join(td, "model.bin")
+        (ck.write_v2 if q8 else ck.write_v0)(path, cfg, host_w)
+        ref = (RefQ8 if q8 else Ref32)()
+        h0, _ = ref.open(path)
+        hs = [h0] + [(ref.lib.refq8_clone if q8 else ref.lib.ref32_clone)(h0) for _ in sample[1:]]
+        worst_abs = worst_rel = 0.0
+        same_argmax = True
+        for stp in range(n_steps):
+            pos = np.full(B, stp, np.int32)
+            got = e.forward_batch(toks[stp], pos).numpy()
+            for h, b in zip(hs, sample):
+                want = ref.forward(h, int(toks[stp, b]), stp, cfg.vocab_size)
+                ad = np.abs(got[b] - want)
+                worst_abs = max(worst_abs, float(ad.max()))
+                worst_rel = max(worst_rel, float(ad.max() / max(np.abs(want).max(), 1e-30)))
+                same_argmax = same_argmax and int(got[b].argmax()) == int(want.argmax())
+    return {"slots": sample, "steps": n_steps, "max_abs_err": worst_abs, "max_err_over_max_logit": worst_rel,
+            "argmax_identical": bool(same_argmax), "tolerance": "fp32: 1e-4 abs-or-rel (tests); Q8_0: see tests/test_gpu_baseline_shapes.py",
+            "checker": "oracle/_ref (%s compiled unmodified), untimed" % ("runq.c" if q8 else "run.cc")}
+
+
+def resident_tok_s(e, cfg, B, W, K, device, pos0=0, seed=1):
+    """tokens/s of the resident greedy loop (device token / pos / argmax / advance), CUDA events on the launching stream."""
+    import torch
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        rng = np.random.default_rng(seed)
+        tok = torch.from_numpy(rng.integers(3, cfg.vocab_size, size=B).astype(np.int32)).to(device)
+        pos = torch.full((B,), pos0, dtype=torch.int32, device=device)
+        nxt = torch.zeros(B, dtype=torch.int32, device=device)
+        logits = torch.zeros(B, cfg.vocab_size, dtype=torch.float32, device=device)
+        for _ in range(W):
+            e.decode_greedy(tok, pos, nxt, logits, stream=stream)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for _ in range(K):
+            e.decode_greedy(tok, pos, nxt, logits, stream=stream)
+        ev1.record(stream)
+        stream.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    return B * K / (ms * 1e-3), ms / K
+
+
+def extra_records(args, device, peak):
+    """Bounded sub-records of the BASELINE configurations the headline line does not cover (configs[2], [3], [4]); a few
+    seconds each, rank 0 of a data-parallel run, random-init weights generated on the device."""
+    import dataclasses
+    import gc
+    import torch
+    from pkgload import load_pkg
+    eng, ck = load_pkg("engine"), load_pkg("checkpoint")
+    out = {}
+
+    def free():
+        gc.collect()
+        torch.cuda.empty_cache()
+
+    def decode_record(cfg, dw, B, W, K, label):
+        e = eng.Engine(dw, B, device=device, with_att=False)
+        v, ms = resident_tok_s(e, cfg, B, W, K, device)
+        nbytes = sum(step_bytes(cfg, dw.nbytes(), p, B) for p in range(W, W + K)) / K
+        rec = {"workload": label, "value": v, "unit": UNIT, "ms_per_step": ms, "launches_per_step": e.last_step_launches() + (1 if e.q8 else 0),
+               "bytes_per_step": nbytes, "achieved_gbs": nbytes / ms / 1e6, "hbm_frac": nbytes / ms / 1e6 / peak}
+        del e
+        free()
+        return rec
+
+    try:   # configs[2]: stories110M Q8_0
+        cfg = ck.STORIES110M
+        dw = eng.device_random_weights(cfg, q8=True, seed=1337, device=device)
+        out["s110m_q8_B256"] = decode_record(cfg, dw, 256, 5, 20, "stories110M Q8_0 batched greedy decode, 256 slots, positions 5..24")
+        out["s110m_q8_B1"] = decode_record(cfg, dw, 1, 5, 20, "stories110M Q8_0 greedy decode, 1 slot, positions 5..24")
+        del dw
+        free()
+    except Exception as ex:
+        out["s110m_q8"] = {"error": str(ex)}
+    try:   # configs[4]: Llama-2-7B Q8_0 at 1 / 8 / 64 slots
+        cfg = ck.LLAMA2_7B
+        dw = eng.device_random_weights(cfg, q8=True, seed=1337, device=device)
+        for B in (1, 8, 64):
+            c = dataclasses.replace(cfg, seq_len=512) if B == 64 else cfg   # 64 slots x 2048 positions of fp32 KV is 137 GB
+            dw.cfg = c
+            out[f"7b_q8_B{B}"] = decode_record(c, dw, B, 4, 12, f"Llama-2-7B Q8_0 batched greedy decode, {B} slots, positions 4..15, "
+                                               f"KV slab of {c.seq_len} positions")
+        del dw
+        free()
+    except Exception as ex:
+        out["7b_q8"] = {"error": str(ex)}
+    try:   # configs[3]: Llama-2-7B fp32, prompt of 2048 positions in one pass + first decode steps
+        cfg = dataclasses.replace(ck.LLAMA2_7B, seq_len=2304)   # room for decode positions behind the 2048-position prompt
+        dw = eng.device_random_weights(cfg, q8=False, seed=1337, device=device)
+        e = eng.Engine(dw, 1, device=device, with_att=False)
+        rng = np.random.default_rng(0)
+        T = 2048
+        seqs = [(0, 0, rng.integers(3, cfg.vocab_size, size=T).astype(np.int32))]
+        st = torch.cuda.Stream()
+        logits = torch.zeros(1, cfg.vocab_size, device=device)
+        nxt = torch.zeros(1, dtype=torch.int32, device=device)
+        with torch.cuda.stream(st):
+            e.prefill(seqs, logits, nxt, stream=st)
+            st.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            reps = 3
+            for _ in range(reps):
+                e.prefill(seqs, logits, nxt, stream=st)
+            e1.record(st)
+            st.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        d, h, L, kvd = cfg.dim, cfg.hidden_dim, cfg.n_layers, cfg.kv_dim
+        pmm = L * (2 * d * d + 2 * d * kvd + 3 * d * h)
+        flops = 2.0 * T * pmm + 2.0 * L * T * T * d + 2.0 * cfg.vocab_size * d
+        try:
+            tf_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"])
+        except Exception:
+            tf_peak = 1381.0
+        out["prefill_7b_f32_2048"] = {"workload": "Llama-2-7B fp32, one prompt of 2048 positions through tha_prefill_f32 (3xTF32 tensor-core matmuls)",
+                                      "ms": ms, "prompt_tok_per_s": T / ms * 1e3, "useful_tflops": flops / ms / 1e9,
+                                      "tensor_frac_of_sustained_bf16": flops / ms / 1e9 / tf_peak,
+                                      "note": "useful flops = 2 * T * weights + causal attention; 3xTF32 issues three tf32 MMAs per useful one"}
+        v, msd = resident_tok_s(e, cfg, 1, 2, 8, device, pos0=T)
+        nb = step_bytes(cfg, dw.nbytes(), T + 5, 1)
+        out["decode_7b_f32_B1_after_prefill"] = {"workload": "Llama-2-7B fp32 greedy decode, 1 slot, positions 2050..2057", "value": v, "unit": UNIT,
+                                                 "ms_per_step": msd, "achieved_gbs": nb / msd / 1e6, "hbm_frac": nb / msd / 1e6 / peak}
+        del e, dw
+        free()
+    except Exception as ex:
+        out["prefill_7b_f32_2048"] = {"error": str(ex)}
+    return out
+
+
+def tp_extra(args, rank, world, local_rank, B=64, W=3, K=10):
+    """Llama-2-7B Q8_0, ONE replica split over the `world` GPUs of this run (all-reduce after wo / w2 fused into its
+    consumer over NVLink peer memory), 64 slots, KV slab of 512 positions: tok/s (strong scaling against extra.7b_q8_B64
+    of the 1-GPU line).  Every rank takes part; rank 0 reports."""
+    import argparse as _ap
+    import gc
+    import torch
+    from pkgload import load_pkg
+    device = f"cuda:{local_rank}"
+    a2 = _ap.Namespace(model="7b", quant="q8", seq_len=512, batch=B)
+    cfg, dw, _, e = build_tp_rank(a2, device, rank, world)
+    e.connect_distributed()
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        tok = torch.full((B,), 17, dtype=torch.int32, device=device)
+        pos = torch.zeros(B, dtype=torch.int32, device=device)
+        nxt = torch.zeros(B, dtype=torch.int32, device=device)
+        logits = torch.zeros(B, cfg.vocab_size, dtype=torch.float32, device=device)
+        for _ in range(W):
+            e.decode_step(tok, pos, logits, nxt, advance=True, stream=stream)
+        stream.synchronize()
+        torch.distributed.barrier()
+        torch.cuda.synchronize()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for _ in range(K):
+            e.decode_step(tok, pos, logits, nxt, advance=True, stream=stream)
+        ev1.record(stream)
+        stream.synchronize()
+    ms = load_pkg("dp").max_over_ranks(ev0.elapsed_time(ev1), device)
+    err = e.check_error()
+    rec = {"workload": f"Llama-2-7B Q8_0, ONE replica tensor-parallel over {world} GPUs, {B} slots, positions {W}..{W + K - 1}",
+           "value": B * K / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / K, "scaling": "strong", "peer_wait_timed_out": bool(err)}
+    del e, dw
+    gc.collect()
+    torch.cuda.empty_cache()
+    return rec
 
 
 # ------------------------------------------------------------------ the reference's CPU path ----
@@ -491,6 +713,13 @@ def main():
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
     r = run_ours(args, rank, world, local_rank)
+    tp_rec = None
+    if world > 1 and args.tp == 1 and not args.no_extra and args.model == "s110m" and args.quant == "f32":
+        # the optional tensor-parallel split (north_star: Llama-2-7B 2/4/8-way), one replica over all ranks of this run
+        try:
+            tp_rec = tp_extra(args, rank, world, local_rank)
+        except Exception as ex:
+            tp_rec = {"error": str(ex)}
     if rank == 0:
         cfg = r["cfg"]
         line = base_line(args, cfg, world)
@@ -507,7 +736,9 @@ def main():
                                        "decode step (%d kernels per step, CUDA-graph replay)" % r["launches_per_step"]),
                             "bytes_per_step": r["bytes_per_step"], "peak_source": r["peak_src"],
                             "frac_of_nominal_8TBs": r["achieved"] / 8000.0,
-                            "dominant_kernel_alone": r["attn"]}
+                            "live_shares_us": r["attn"]["live_shares_us"], "dominant_kernel": r["attn"]["dominant_kernel"]}
+        if r.get("parity") is not None:
+            line["parity_sample"] = r["parity"]
         if not args.no_cpu_baseline:
             try:
                 if args.model == "7b":
@@ -520,6 +751,14 @@ def main():
                                                   f"{'-O3 -mavx2 -mfma' if fast else '-O2'}); run.cc has no OpenMP pragma"}
             except Exception as ex:  # the checker being absent must not hide the GPU number
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
+        if tp_rec is not None:
+            line.setdefault("extra", {})["tp_7b_q8_B64"] = tp_rec
+        if not args.no_extra and args.tp == 1 and world == 1 and args.model == "s110m" and args.quant == "f32":
+            try:
+                import torch
+                line.setdefault("extra", {}).update(extra_records(args, f"cuda:{local_rank}", r["peak"]))
+            except Exception as ex:
+                line.setdefault("extra", {})["error"] = str(ex)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

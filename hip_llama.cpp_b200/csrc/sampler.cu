@@ -20,7 +20,7 @@
 
 namespace tha {
 
-constexpr int SMP_THREADS = 1024;
+constexpr int SMP_THREADS = 512;
 constexpr int SMP_BINS = 4096;
 typedef unsigned long long u64;
 
@@ -50,7 +50,7 @@ __device__ __forceinline__ u64 smp_scan(u64 v, u64* s_warp, u64* total) {
   if (lane == 31) s_warp[wid] = inc;
   __syncthreads();
   if (wid == 0) {
-    u64 w = s_warp[lane];                // 32 warps
+    u64 w = lane < SMP_THREADS / 32 ? s_warp[lane] : 0ull;
     u64 winc = w;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -74,55 +74,92 @@ struct SmpShared {
   float red[33];
 };
 
+// The k-th (0-based) index i, ascending, with match(i) true.  Indices are dealt to threads round-robin (coalesced loads),
+// so index order = round by round, thread order inside a round: one counting barrier per round, then a scan inside the
+// round that holds the answer.  All threads call this; the result is broadcast through sh.idx (-1: fewer than k+1 matches).
+template <typename Match>
+__device__ int smp_kth(int n, u64 k, SmpShared& sh, Match match) {
+  u64 seen = 0;
+  int answer = -1;
+  for (int base = 0; base < n; base += SMP_THREADS) {
+    const int i = base + threadIdx.x;
+    const bool f = i < n && match(i);
+    const int cnt = __syncthreads_count(f);
+    if (seen + (u64)cnt > k) {
+      u64 total;
+      const u64 before = smp_scan(f ? 1ull : 0ull, sh.warp, &total);
+      if (f && seen + before == k) sh.idx = i;
+      __syncthreads();
+      answer = sh.idx;
+      break;
+    }
+    seen += (u64)cnt;
+  }
+  __syncthreads();
+  return answer;
+}
+
 // First element, in the order (probability descending, index ascending) over the candidates p >= cutoff, whose inclusive
 // prefix mass exceeds `target`.  Returns false when the candidates' total mass does not (then *idx is the LAST candidate
 // in that order and *incl the total).  All threads of the block call this with the same arguments.
+// Keys: candidates lie in [cutoff, 1], i.e. in at most 32 binades, so the bit pattern minus the cutoff's exponent has 28
+// significant bits: 5 of exponent + 23 of mantissa, split 12 / 8 / 8.  Seven mantissa bits in the first level spread
+// even a near-uniform distribution (random-init models) over hundreds of bins instead of two.
 __device__ bool smp_select(const float* pr, int n, float cutoff, u64 target, SmpShared& sh, int* idx, u64* incl) {
-  const int per = (n + SMP_THREADS - 1) / SMP_THREADS;
-  const int lo = threadIdx.x * per, hi = min(n, lo + per);
   unsigned pmask = 0, pval = 0;
   u64 base = 0;
-  const int shifts[3] = {20, 10, 0}, nbins[3] = {4096, 1024, 1024};
+  const unsigned e0 = __float_as_uint(cutoff) >> 23;                  // exponent of the cutoff (cutoff > 0)
+  const bool narrow = e0 > 95 && e0 <= 127;                           // [cutoff, 1] within 32 binades (always, unless topp is within 1e-5 of 1)
+  const unsigned rebase = narrow ? e0 << 23 : 0u;                      // otherwise: the plain bit pattern, 12 / 10 / 10
+  const int shifts[3] = {narrow ? 16 : 20, narrow ? 8 : 10, 0}, nbins[3] = {4096, narrow ? 256 : 1024, narrow ? 256 : 1024};
   for (int lv = 0; lv < 3; lv++) {
     const int shift = shifts[lv], nb = nbins[lv];
     for (int i = threadIdx.x; i < nb; i += SMP_THREADS) sh.bins[i] = 0;
     if (threadIdx.x == 0) sh.found = 0;
     __syncthreads();
-    {   // mass histogram of the elements that match the prefix; runs of one bin are merged before the atomic
-      int cur = -1;
-      u64 acc = 0;
-      for (int i = lo; i < hi; i++) {
+    {   // mass histogram of the elements that match the prefix; consecutive hits of one bin are merged before the atomic
+      int cur = -1, old = -1;
+      u64 acc = 0, oacc = 0;
+      for (int i = threadIdx.x; i < n; i += SMP_THREADS) {
         const float p = pr[i];
         if (!(p >= cutoff)) continue;
-        const unsigned key = __float_as_uint(p);
+        const unsigned key = __float_as_uint(p) - rebase;
         if ((key & pmask) != pval) continue;
         const int b = (int)((key >> shift) & (unsigned)(nb - 1));
         if (b != cur) {
-          if (cur >= 0) atomicAdd(&sh.bins[cur], acc);
-          cur = b; acc = 0;
+          if (b == old) {           // two-entry cache: a thread alternating between two bins issues no atomics until the end
+            const int tb = cur; cur = old; old = tb;
+            const u64 ta = acc; acc = oacc; oacc = ta;
+          } else {
+            if (old >= 0) atomicAdd(&sh.bins[old], oacc);
+            old = cur; oacc = acc;
+            cur = b; acc = 0;
+          }
         }
         acc += smp_fixed(p);
       }
       if (cur >= 0) atomicAdd(&sh.bins[cur], acc);
+      if (old >= 0) atomicAdd(&sh.bins[old], oacc);
     }
     __syncthreads();
     // descending walk over the bins: thread t owns bins nb-1 - t*bp ... (bp each)
-    const int bp = nb / SMP_THREADS > 0 ? nb / SMP_THREADS : 1;
+    const int bp = (nb + SMP_THREADS - 1) / SMP_THREADS;
     u64 local = 0;
-    if ((int)threadIdx.x * bp < nb)
-      for (int k = 0; k < bp; k++) local += sh.bins[nb - 1 - ((int)threadIdx.x * bp + k)];
+    for (int k = 0; k < bp; k++) {
+      const int bi = (int)threadIdx.x * bp + k;
+      if (bi < nb) local += sh.bins[nb - 1 - bi];
+    }
     u64 total;
     const u64 excl = smp_scan(local, sh.warp, &total);
     if (lv == 0 && base + total <= target) {
       // not enough mass: the last candidate in sorted order = lowest key, highest index among its equals
       unsigned best = 0xFFFFFFFFu; int bi = -1;
-      for (int i = lo; i < hi; i++) {
+      for (int i = threadIdx.x; i < n; i += SMP_THREADS) {
         const float p = pr[i];
         if (!(p >= cutoff)) continue;
         const unsigned key = __float_as_uint(p);
         if (key < best || (key == best && i > bi)) { best = key; bi = i; }
       }
-      // block reduction (min key, then max index)
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         const unsigned ok = __shfl_xor_sync(THA_FULL_MASK, best, o);
@@ -148,6 +185,7 @@ __device__ bool smp_select(const float* pr, int n, float cutoff, u64 target, Smp
       u64 run = base + excl;
       for (int k = 0; k < bp; k++) {
         const int b = nb - 1 - ((int)threadIdx.x * bp + k);
+        if (b < 0) break;
         const u64 m = sh.bins[b];
         if (m > 0 && run + m > target) { sh.bin = b; sh.base = run; sh.found = 1; break; }
         run += m;
@@ -161,28 +199,15 @@ __device__ bool smp_select(const float* pr, int n, float cutoff, u64 target, Smp
   }
   // every element of the class has the key `pval` (one probability, one mass q): the (k+1)-th of them in index order
   // is the first whose inclusive prefix exceeds the target
-  const u64 q = smp_fixed(__uint_as_float(pval));
+  const unsigned bits = pval + rebase;
+  const u64 q = smp_fixed(__uint_as_float(bits));
   const u64 k = q ? (target - base) / q : 0;
-  u64 cnt = 0;
-  for (int i = lo; i < hi; i++) cnt += (__float_as_uint(pr[i]) == pval && pr[i] >= cutoff) ? 1 : 0;
-  u64 total;
-  const u64 before = smp_scan(cnt, sh.warp, &total);
-  if (cnt > 0 && before <= k && k < before + cnt) {
-    u64 c = before;
-    for (int i = lo; i < hi; i++) {
-      if (__float_as_uint(pr[i]) == pval && pr[i] >= cutoff) {
-        if (c == k) { sh.idx = i; break; }
-        c++;
-      }
-    }
-  }
-  __syncthreads();
-  *idx = sh.idx;
+  *idx = smp_kth(n, k, sh, [&](int i) { return __float_as_uint(pr[i]) == bits; });
   *incl = base + (k + 1) * q;
   return true;
 }
 
-__global__ void __launch_bounds__(SMP_THREADS) sample_kernel(const SampleP P) {
+__global__ void __launch_bounds__(SMP_THREADS, 2) sample_kernel(const SampleP P) {
   __shared__ SmpShared sh;
   pdl_wait();
   pdl_trigger();
@@ -239,19 +264,22 @@ __global__ void __launch_bounds__(SMP_THREADS) sample_kernel(const SampleP P) {
   const u64 coin24 = sh.key;                  // coin = coin24 / 2^24
   int tok = n - 1;
   if (P.topp <= 0.0f || P.topp >= 1.0f) {
-    // ---- multinomial in index order (src/llama.cpp:288-307): first i with coin < cdf(i)
-    const int per = (n + SMP_THREADS - 1) / SMP_THREADS;
-    const int lo = threadIdx.x * per, hi = min(n, lo + per);
-    u64 local = 0;
-    for (int i = lo; i < hi; i++) local += smp_fixed(pr[i]);
-    u64 total;
-    const u64 excl = smp_scan(local, sh.warp, &total);
+    // ---- multinomial in index order (src/llama.cpp:288-307): first i with coin < cdf(i); indices are dealt round-robin,
+    // so the cdf is scanned round by round (thread order inside a round = index order)
     const u64 target = coin24 << 16;
+    u64 run = 0;
     if (threadIdx.x == 0) sh.idx = n - 1;
     __syncthreads();
-    if (local > 0 && excl <= target && target < excl + local) {
-      u64 run = excl;
-      for (int i = lo; i < hi; i++) { run += smp_fixed(pr[i]); if (target < run) { sh.idx = i; break; } }
+    for (int base = 0; base < n; base += SMP_THREADS) {
+      const int i = base + threadIdx.x;
+      const u64 mq = i < n ? smp_fixed(pr[i]) : 0ull;
+      u64 total;
+      const u64 excl = smp_scan(mq, sh.warp, &total);
+      if (run + total > target) {
+        if (mq > 0 && run + excl <= target && target < run + excl + mq) sh.idx = i;
+        break;                                   // block-uniform: run and total are the same in every thread
+      }
+      run += total;
     }
     __syncthreads();
     tok = sh.idx;

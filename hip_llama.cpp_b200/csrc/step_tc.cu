@@ -552,11 +552,7 @@ static int gemm_q8(cudaStream_t st, bool pdl, int n_mats, const int8_t* const* W
 // Development aid (THA_SKIP bit mask): leave a class of kernels out of the step to read its LIVE share of the step time off
 // the difference (results are garbage): 1 layer matmuls, 2 attention, 4 prep, 8 RoPE/scatter, 16 SwiGLU / quantise,
 // 32 classifier, 64 argmax.
-static int skip_mask() {
-  static int m = -1;
-  if (m < 0) { const char* v = getenv("THA_SKIP"); m = (v && *v) ? atoi(v) : 0; }
-  return m;
-}
+static int skip_mask() { return skip_mode(); }   // workspace.cu: THA_SKIP / tha_set_option("skip", mask)
 
 // What differs between a decode step and a prefill chunk.
 struct RowsIO {

@@ -51,6 +51,11 @@ int dual_min_rows() {
   return g_dual;
 }
 int* opt_dual() { return &g_dual; }
+static int g_skip = -1;
+int skip_mode() {   // development / measurement aid: leave a class of kernels out of the step (step_tc.cu); results are then garbage
+  if (g_skip < 0) { const char* v = getenv("THA_SKIP"); g_skip = (v && *v) ? atoi(v) : 0; }
+  return g_skip;
+}
 static int g_chain = -2;
 int chain_mode() {   // 1: matmul chains with fused epilogues (chain_tc.cu) where the shape allows; 0 (default): one launch per matmul
   // Off by default: measured on stories110M fp32 at 256 slots the chained step takes 1.29 ms against 0.99 ms -- a phase
@@ -208,6 +213,13 @@ extern "C" int tha_set_option(const char* name, int value) {
   if (!strcmp(name, "graph")) { *tha::opt_graph() = value != 0; return THA_STATUS_SUCCESS; }
   if (!strcmp(name, "tc")) { *tha::opt_tc() = value; return THA_STATUS_SUCCESS; }
   if (!strcmp(name, "dual")) { tha::dual_min_rows(); *tha::opt_dual() = value; return THA_STATUS_SUCCESS; }
+  if (!strcmp(name, "skip")) {   // cached graphs were captured with the old mask
+    tha::skip_mode();
+    tha::g_skip = value < 0 ? 0 : value;
+    std::lock_guard<std::mutex> lk(tha::g_mu);
+    for (auto& kv : tha::g_ws) tha::ws_drop_graphs(kv.second);
+    return THA_STATUS_SUCCESS;
+  }
   if (!strcmp(name, "chain")) { *tha::opt_chain() = value; return THA_STATUS_SUCCESS; }
   if (!strcmp(name, "mega")) { tha::mega_set_enabled(value); return THA_STATUS_SUCCESS; }
   return THA_STATUS_INVALID_ARG;
