@@ -44,6 +44,11 @@ class WeightsQ8(C.Structure):
                 [(n, QTensor) for n in ("wq", "wk", "wv", "wo", "w1", "w2", "w3", "wcls")] + [("group_size", C.c_int)])
 
 
+class WeightsBF16(C.Structure):
+    _fields_ = [(n, vp) for n in ("token_embedding_table", "rms_att_weight", "rms_ffn_weight", "rms_final_weight", "wq", "wk",
+                                  "wv", "wo", "w1", "w2", "w3", "wcls")]
+
+
 def declared_symbols(header: str = HEADER) -> list[str]:
     """Every function name include/tha_b200.h declares."""
     text = open(header).read()
@@ -93,6 +98,13 @@ class Lib:
             "tha_forward_batch_q8": [vp, I, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), vp, vp, vp],
             "tha_decode_step_q8": [vp, I, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), vp, vp, vp, vp],
             "tha_gemm_tf32x3": [vp, vp, C.c_longlong, vp, I, I, vp, I, C.c_longlong],
+            "tha_gemm_bf16": [vp, vp, C.c_longlong, vp, I, I, vp, I, C.c_longlong],
+            "tha_convert_bf16": [vp, vp, vp, C.c_size_t],
+            "tha_forward_batch_bf16": [vp, I, C.POINTER(Config), C.POINTER(WeightsBF16), C.POINTER(State), vp, vp, vp],
+            "tha_decode_step_bf16": [vp, I, C.POINTER(Config), C.POINTER(WeightsBF16), C.POINTER(State), vp, vp, vp, vp],
+            "tha_forward_greedy_bf16": [vp, I, C.POINTER(Config), C.POINTER(WeightsBF16), C.POINTER(State), vp, vp, vp],
+            "tha_forward_sample_bf16": [vp, I, C.POINTER(Config), C.POINTER(WeightsBF16), C.POINTER(State), vp, vp, vp, vp, F, F, vp],
+            "tha_prefill_bf16": [vp, C.POINTER(Config), C.POINTER(WeightsBF16), C.POINTER(State), I, vp, vp, vp, vp, vp, vp],
             "tha_forward_greedy_f32": [vp, I, C.POINTER(Config), C.POINTER(WeightsF32), C.POINTER(State), vp, vp, vp],
             "tha_forward_greedy_q8": [vp, I, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), vp, vp, vp],
             "tha_prefill_f32": [vp, C.POINTER(Config), C.POINTER(WeightsF32), C.POINTER(State), I, vp, vp, vp, vp, vp, vp],

@@ -96,6 +96,23 @@ def random_weights(c: Config, seed: int = 1337, std: float = 0.02, chunk: int = 
     return out
 
 
+def round_bf16(a: np.ndarray) -> np.ndarray:
+    """fp32 -> nearest bf16 (ties to even), returned as fp32 (what tha_convert_bf16 and torch's .to(bfloat16) produce)."""
+    u = np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+    r = ((u + np.uint32(0x7FFF) + ((u >> np.uint32(16)) & np.uint32(1))) & np.uint32(0xFFFF0000)).astype(np.uint32)
+    return r.view(np.float32).reshape(np.shape(a))
+
+
+def bf16_bits(a: np.ndarray) -> np.ndarray:
+    """The 16-bit patterns of round_bf16(a)."""
+    return (round_bf16(a).view(np.uint32) >> np.uint32(16)).astype(np.uint16)
+
+
+def bf16_weights(w: dict) -> dict:
+    """The checkpoint as the bf16 model path sees it: matrices and embedding rounded to bf16 (norm gains stay fp32)."""
+    return {k: (v if k.startswith("rms") else round_bf16(v)) for k, v in w.items()}
+
+
 def rope_tables(c: Config):
     """The two dead tables the v0 file still carries (train/model.py:40-47).  Readers skip
     them (src/utils.cpp:145-146); torch is used when present so the bytes equal the

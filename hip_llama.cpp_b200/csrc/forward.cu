@@ -408,6 +408,107 @@ int decode_step_q8(cudaStream_t st, int B, const tha_config_t* cfg, const tha_we
   return run_step(st, ws, &a, sizeof(a), [&]() { return issue_step_q8(st, ws, a, rc, rs); });
 }
 
+// ---------------------------------------------------------------------------- bf16 ----
+bool step_bf16_supported(const tha_config_t* c);
+int step_bf16_prepare(Workspace* ws, const tha_config_t* c, int B);
+int step_bf16_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& c, const tha_weights_bf16_t& w, const tha_state_t& s,
+                    const int* token_d, const int* pos_d, float* logits, int* next_d, const float* rc, const float* rs, bool pdl);
+int step_bf16_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_bf16_t& w, const tha_state_t& s,
+                      int n_seqs, const int* slot, const int* pos0, const int* len, const int* tokens, float* logits, int* next_d,
+                      const float* rc, const float* rs);
+int bf16_convert_launch(cudaStream_t st, const float* src, uint16_t* dst, size_t n);
+
+int embed_bf16_launch(cudaStream_t st, int B, float* x, const uint16_t* table, const int* token, const int* pos, int d, bool pdl);
+int gemv_bf16_launch(cudaStream_t stream, int mode, const GemvP& p, bool pdl);
+
+struct StepArgsBf16 {
+  int B; tha_config_t cfg; tha_weights_bf16_t w; tha_state_t s;
+  const int* token_d; const int* pos_d; float* logits_d; int* next_d; int pdl; int gemv;
+};
+
+// 1-8 slots: the five fused kernels per layer of issue_step_f32 over bf16 weights (gemv_bf16.cu)
+static int issue_step_bf16_gemv(cudaStream_t st, Workspace* ws, const StepArgsBf16& a, float* logits, const float* rc, const float* rs) {
+  const tha_config_t& c = a.cfg;
+  const int d = c.dim, hd = c.hidden_dim, hs = d / c.n_heads, kvd = hs * c.n_kv_heads;
+  const long long kv_bs = (long long)c.n_layers * c.seq_len * kvd;
+  const bool pdl = a.pdl != 0;
+  auto W = [](const uint16_t* p) { return reinterpret_cast<const float*>(p); };   // GemvP carries bf16 rows behind float pointers
+  THA_TRY(embed_bf16_launch(st, a.B, a.s.x, a.w.token_embedding_table, a.token_d, a.pos_d, d, pdl));
+  for (int l = 0; l < c.n_layers; l++) {
+    const int loff = l * c.seq_len * kvd;
+    GemvP p = {};
+    p.W0 = W(a.w.wq + (size_t)l * d * d); p.M0 = d;
+    p.W1 = W(a.w.wk + (size_t)l * d * kvd); p.M1 = kvd;
+    p.W2 = W(a.w.wv + (size_t)l * d * kvd); p.M2 = kvd;
+    p.K = d; p.B = a.B; p.X = a.s.x; p.x_stride = d;
+    p.rms_w = a.w.rms_att_weight + (size_t)l * d; p.pos = a.pos_d;
+    p.out = a.s.q; p.out_batch_stride = d;
+    p.kc = a.s.key_cache; p.vc = a.s.value_cache; p.kv_batch_stride = kv_bs; p.loff = loff;
+    p.kv_dim = kvd; p.head_size = hs; p.rope_cos = rc; p.rope_sin = rs;
+    THA_TRY(gemv_bf16_launch(st, GEMV_QKV, p, pdl));
+    THA_TRY(attn_fused_launch(st, ws, a.B, a.pos_d, c.n_heads, c.n_kv_heads, a.s.q, a.s.xb, a.s.key_cache + loff,
+                              a.s.value_cache + loff, kv_bs, hs, c.seq_len, pdl));
+    GemvP o = {};
+    o.W0 = W(a.w.wo + (size_t)l * d * d); o.M0 = d; o.K = d; o.B = a.B; o.X = a.s.xb; o.x_stride = d;
+    o.pos = a.pos_d; o.out = a.s.x; o.out_batch_stride = d;
+    THA_TRY(gemv_bf16_launch(st, GEMV_RESID, o, pdl));
+    GemvP f = {};
+    f.W0 = W(a.w.w1 + (size_t)l * d * hd); f.W1 = W(a.w.w3 + (size_t)l * d * hd); f.M0 = hd; f.M1 = hd;
+    f.K = d; f.B = a.B; f.X = a.s.x; f.x_stride = d; f.rms_w = a.w.rms_ffn_weight + (size_t)l * d;
+    f.pos = a.pos_d; f.out = a.s.hb; f.out_batch_stride = hd;
+    THA_TRY(gemv_bf16_launch(st, GEMV_SWIGLU, f, pdl));
+    GemvP g = {};
+    g.W0 = W(a.w.w2 + (size_t)l * d * hd); g.M0 = d; g.K = hd; g.B = a.B; g.X = a.s.hb; g.x_stride = hd;
+    g.pos = a.pos_d; g.out = a.s.x; g.out_batch_stride = d;
+    THA_TRY(gemv_bf16_launch(st, GEMV_RESID, g, pdl));
+  }
+  GemvP cl = {};
+  cl.W0 = W(a.w.wcls); cl.M0 = c.vocab_size; cl.K = d; cl.B = a.B; cl.X = a.s.x; cl.x_stride = d;
+  cl.rms_w = a.w.rms_final_weight; cl.pos = a.pos_d; cl.out = logits; cl.out_batch_stride = c.vocab_size;
+  THA_TRY(gemv_bf16_launch(st, GEMV_PLAIN, cl, pdl));
+  if (a.next_d) THA_TRY(argmax_launch(st, a.B, logits, c.vocab_size, a.next_d, pdl));
+  return THA_STATUS_SUCCESS;
+}
+
+static int check_bf16(const tha_config_t* cfg, const tha_weights_bf16_t* w, const tha_state_t* s) {
+  if (!cfg || !w || !s) return THA_STATUS_INVALID_ARG;
+  if (!w->token_embedding_table || !w->wq || !w->wk || !w->wv || !w->wo || !w->w1 || !w->w2 || !w->w3 || !w->wcls ||
+      !w->rms_att_weight || !w->rms_ffn_weight || !w->rms_final_weight)
+    return THA_STATUS_INVALID_ARG;
+  if (!s->x || !s->xb || !s->q || !s->key_cache || !s->value_cache) return THA_STATUS_INVALID_ARG;
+  if (!step_bf16_supported(cfg)) return THA_STATUS_NOT_SUPPORTED;
+  return THA_STATUS_SUCCESS;
+}
+
+int decode_step_bf16(cudaStream_t st, int B, const tha_config_t* cfg, const tha_weights_bf16_t* w, const tha_state_t* s,
+                     const int* token_d, const int* pos_d, float* logits_d, int* next_d) {
+  if (B <= 0 || !token_d || !pos_d) return THA_STATUS_INVALID_ARG;
+  THA_TRY(check_bf16(cfg, w, s));
+  float* lg = logits_d ? logits_d : s->logits;
+  if (!lg) return THA_STATUS_INVALID_ARG;
+  Workspace* ws = workspace();
+  if (!ws) return THA_STATUS_EXECUTION_FAILED;
+  const float *rc, *rs;
+  THA_TRY(ws_rope(ws, cfg->dim / cfg->n_heads, cfg->seq_len, &rc, &rs));
+  StepArgsBf16 a;
+  memset(&a, 0, sizeof(a));
+  a.B = B; a.cfg = *cfg; a.w = *w; a.s = *s; a.token_d = token_d; a.pos_d = pos_d; a.logits_d = logits_d; a.next_d = next_d;
+  a.pdl = pdl_enabled();
+  // 1-2 slots: the weights stream through the fused GEMV kernels (5 launches per layer); more: tensor cores (Llama-2-7B:
+  // 8 slots 12.4 ms per step on the GEMV path -- shared-memory-bound at 8 FMAs per weight -- against 4.0 ms at 64 slots on
+  // the tensor cores).  Option "tc" = 1 forces the tensor cores, 0 the GEMV path up to 8 slots.
+  a.gemv = (((B <= 2 && tc_mode() != 1) || (B <= 8 && tc_mode() == 0)) && s->hb) ? 1 : 0;
+  if (a.gemv) {
+    const int hs = cfg->dim / cfg->n_heads;
+    THA_TRY(attn_fused_prepare(ws, B, cfg->n_heads, cfg->n_kv_heads, hs, cfg->seq_len));
+    return run_step(st, ws, &a, sizeof(a), [&]() { return issue_step_bf16_gemv(st, ws, a, lg, rc, rs); });
+  }
+  THA_TRY(step_bf16_prepare(ws, cfg, B));
+  return run_step(st, ws, &a, sizeof(a), [&]() {
+    return step_bf16_issue(st, ws, B, *cfg, *w, *s, token_d, pos_d, lg, next_d, rc, rs, a.pdl != 0);
+  });
+}
+
 int last_step_launches_get() { return g_last_step_launches; }
 void last_step_launches_set(int v) { g_last_step_launches = v; }
 
@@ -568,6 +669,62 @@ extern "C" int tha_forward_sample_q8(void* stream, int n_batches, const tha_conf
                              next_host, [&](const int* tok_d, const int* pos_d, float* lg) {
                                return decode_step_q8(st, n_batches, cfg, w, s, tok_d, pos_d, lg, nullptr);
                              });
+}
+
+extern "C" int tha_convert_bf16(void* stream, const float* src_d, uint16_t* dst_d, size_t n) {
+  if (!src_d || !dst_d) return THA_STATUS_INVALID_ARG;
+  return bf16_convert_launch((cudaStream_t)stream, src_d, dst_d, n);
+}
+
+extern "C" int tha_decode_step_bf16(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_bf16_t* w,
+                                    const tha_state_t* s, const int* token_d, const int* pos_d, float* logits_d, int* next_d) {
+  return decode_step_bf16((cudaStream_t)stream, n_batches, cfg, w, s, token_d, pos_d, logits_d, next_d);
+}
+
+extern "C" int tha_forward_batch_bf16(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_bf16_t* w,
+                                      const tha_state_t* s, const int* token_host, const int* pos_host, float* logits_out) {
+  if (!cfg || !s) return THA_STATUS_INVALID_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  return forward_host(st, n_batches, cfg->vocab_size, cfg->seq_len, s->logits, token_host, pos_host, logits_out,
+                      [&](const int* tok_d, const int* pos_d, float* target) {
+                        return decode_step_bf16(st, n_batches, cfg, w, s, tok_d, pos_d, target, nullptr);
+                      });
+}
+
+extern "C" int tha_forward_greedy_bf16(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_bf16_t* w,
+                                       const tha_state_t* s, const int* token_host, const int* pos_host, int* next_host) {
+  cudaStream_t st = (cudaStream_t)stream;
+  return forward_host_greedy(st, n_batches, cfg, token_host, pos_host, next_host,
+                             [&](const int* tok_d, const int* pos_d, int* next_d) {
+                               return decode_step_bf16(st, n_batches, cfg, w, s, tok_d, pos_d, nullptr, next_d);
+                             });
+}
+
+extern "C" int tha_forward_sample_bf16(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_bf16_t* w,
+                                       const tha_state_t* s, const int* token_host, const int* pos_host, const int* force_host,
+                                       const unsigned long long* reseed_host, float temperature, float topp, int* next_host) {
+  if (!cfg || !s || !s->logits) return THA_STATUS_INVALID_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  return forward_host_sample(st, n_batches, cfg, s->logits, token_host, pos_host, force_host, reseed_host, temperature, topp,
+                             next_host, [&](const int* tok_d, const int* pos_d, float* lg) {
+                               return decode_step_bf16(st, n_batches, cfg, w, s, tok_d, pos_d, lg, nullptr);
+                             });
+}
+
+extern "C" int tha_prefill_bf16(void* stream, const tha_config_t* cfg, const tha_weights_bf16_t* w, const tha_state_t* s, int n_seqs,
+                                const int* slot_host, const int* pos0_host, const int* len_host, const int* tokens_host,
+                                float* logits_d, int* next_d) {
+  if (n_seqs < 1 || !slot_host || !pos0_host || !len_host || !tokens_host) return THA_STATUS_INVALID_ARG;
+  THA_TRY(check_bf16(cfg, w, s));
+  Workspace* ws = workspace();
+  if (!ws) return THA_STATUS_EXECUTION_FAILED;
+  const float *rc, *rs;
+  THA_TRY(ws_rope(ws, cfg->dim / cfg->n_heads, cfg->seq_len, &rc, &rs));
+  launches_reset();
+  const int rcode = step_bf16_prefill((cudaStream_t)stream, ws, *cfg, *w, *s, n_seqs, slot_host, pos0_host, len_host, tokens_host,
+                                      logits_d, next_d, rc, rs);
+  last_step_launches_set(launches_get());
+  return rcode;
 }
 
 extern "C" int tha_forward_greedy_f32(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_f32_t* w,

@@ -334,12 +334,15 @@ int tc_map(const void* ptr, long long rows, int K, long long ld, int box_rows, C
   auto it = g_maps.find(key);
   if (it != g_maps.end()) { *out = it->second; return THA_STATUS_SUCCESS; }
   CUtensorMap m;
-  // int8 rows are described as 32-bit words (same bytes, same swizzle): coordinates along K are then in words
-  const cuuint64_t dims[2] = {(cuuint64_t)(elem_bytes == 4 ? K : K / 4), (cuuint64_t)rows};
+  // int8 rows are described as 32-bit words (same bytes, same swizzle): coordinates along K are then in words;
+  // bf16 rows (elem_bytes = 2) as 64 elements per 128-byte box row
+  const cuuint64_t dims[2] = {(cuuint64_t)(elem_bytes == 1 ? K / 4 : K), (cuuint64_t)rows};
   const cuuint64_t strides[1] = {(cuuint64_t)ld * elem_bytes};
-  const cuuint32_t box[2] = {(cuuint32_t)32, (cuuint32_t)box_rows};
+  const cuuint32_t box[2] = {(cuuint32_t)(elem_bytes == 2 ? 64 : 32), (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
-  CUresult r = g_encode(&m, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT32, 2,
+  const CUtensorMapDataType dt = elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                 : (elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_UINT32);
+  CUresult r = g_encode(&m, dt, 2,
                         const_cast<void*>(ptr), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                         (CUtensorMapL2promotion)tc_env("THA_TC_PROMO", (int)CU_TENSOR_MAP_L2_PROMOTION_L2_256B),

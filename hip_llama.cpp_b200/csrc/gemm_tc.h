@@ -38,6 +38,18 @@ bool gemm_q8i_ok(const Q8iArgs& a);
 int gemm_q8i_pick_nt(int N, int gs);
 int gemm_q8i_launch(cudaStream_t st, const Q8iArgs& a, bool pdl);
 
+// bf16 weights x bf16 activations (gemm_bf16.cu): both operands straight from TMA-written shared memory
+struct BfArgs {
+  int n_mats; const uint16_t* W[3]; int M[3]; int out_off[3];
+  int K;
+  const uint16_t* X; int N; long long ldx;       // activations [N, ldx] bf16
+  float* out; long long ldo; long long zstride; int splits;
+  const float* colscale;
+};
+bool gemm_bf16_ok(const BfArgs& a);
+int gemm_bf16_pick_nt(int N);
+int gemm_bf16_launch(cudaStream_t st, const BfArgs& a, bool pdl);
+
 bool gemm_tc_ok(const TcArgs& a);
 int gemm_tc_pick_nt(int N);
 int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl);

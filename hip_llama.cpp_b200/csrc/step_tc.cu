@@ -185,6 +185,14 @@ __global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __res
   }
 }
 
+int rope_scatter_launch(cudaStream_t st, bool pdl, int R, const float* part, int nz, long long zstride, int ld, const int* pos, int d,
+                        int kvd, int hs, const float* rc, const float* rs, float* q, float* kc, float* vc, long long kv_bs, int loff,
+                        const int* slot) {
+  THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld / 2, 256), R), dim3(256), 0, st, pdl, part, nz, zstride, ld, pos, d, kvd, hs,
+                     rc, rs, q, kc, vc, kv_bs, loff, slot));
+  return THA_STATUS_SUCCESS;
+}
+
 // hb = silu(a) * c with a = w1.x, c = w3.x (sum of nz partials each), written as tf32 hi/lo.  grid (h / 256, B)
 __global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __restrict__ part, int nz, long long zstride,
                                                               int ld, const int* __restrict__ pos, int h,

@@ -100,6 +100,65 @@ class DeviceWeightsQ8:
         return n
 
 
+class DeviceWeightsBF16:
+    """bf16 weights: the fp32 checkpoint rounded to nearest-even bf16 on upload (matrices and embedding table; norm
+    gains stay fp32).  Layer-major contiguous like the fp32 tensors."""
+    MATS = ("tok_emb", "wq", "wk", "wv", "wo", "w1", "w2", "w3")
+
+    def __init__(self, cfg: Config, w: dict, device="cuda", shared_classifier=True):
+        self.cfg = cfg
+        self.t = {}
+        for n in ("rms_att", "rms_ffn", "rms_final"):
+            self.t[n] = torch.from_numpy(np.ascontiguousarray(w[n], dtype=np.float32)).to(device)
+        for n in self.MATS:
+            self.t[n] = torch.from_numpy(np.ascontiguousarray(w[n], dtype=np.float32)).to(device).to(torch.bfloat16)
+        if shared_classifier or "wcls" not in w or w["wcls"] is w["tok_emb"]:
+            self.t["wcls"] = self.t["tok_emb"]
+        else:
+            self.t["wcls"] = torch.from_numpy(np.ascontiguousarray(w["wcls"], dtype=np.float32)).to(device).to(torch.bfloat16)
+        self._bind()
+
+    def _bind(self):
+        t = self.t
+        self.c = cabi.WeightsBF16(_ptr(t["tok_emb"]), _ptr(t["rms_att"]), _ptr(t["rms_ffn"]), _ptr(t["rms_final"]), _ptr(t["wq"]),
+                                  _ptr(t["wk"]), _ptr(t["wv"]), _ptr(t["wo"]), _ptr(t["w1"]), _ptr(t["w2"]), _ptr(t["w3"]),
+                                  _ptr(t["wcls"]))
+
+    @classmethod
+    def random(cls, cfg: Config, seed: int = 1337, device="cuda", std: float = 0.02):
+        """Random-init N(0, std) generated on the device (Llama-2-7B: 13.5 GB), rounded to bf16."""
+        g = torch.Generator(device=device)
+        g.manual_seed(seed)
+        L, d, h, kvd, V = cfg.n_layers, cfg.dim, cfg.hidden_dim, cfg.kv_dim, cfg.vocab_size
+        shapes = {"tok_emb": (V, d), "wq": (L, d, d), "wk": (L, kvd, d), "wv": (L, kvd, d), "wo": (L, d, d),
+                  "w1": (L, h, d), "w2": (L, d, h), "w3": (L, h, d)}
+        w = cls.__new__(cls)
+        w.cfg = cfg
+        w.t = {"rms_att": torch.ones(L, d, device=device), "rms_ffn": torch.ones(L, d, device=device),
+               "rms_final": torch.ones(d, device=device)}
+        for n, sh in shapes.items():
+            t = torch.empty(sh, dtype=torch.bfloat16, device=device)
+            lead = sh[0] if len(sh) == 3 else 1
+            tv = t.view(lead, -1)
+            for l in range(lead):   # one layer at a time: bounded fp32 scratch
+                x = torch.empty(tv.shape[1], dtype=torch.float32, device=device)
+                x.normal_(0.0, std, generator=g)
+                tv[l] = x.to(torch.bfloat16)
+                del x
+            w.t[n] = t
+        w.t["wcls"] = w.t["tok_emb"]
+        w._bind()
+        return w
+
+    def nbytes(self) -> int:
+        seen, n = set(), 0
+        for t in self.t.values():
+            if t.data_ptr() not in seen:
+                seen.add(t.data_ptr())
+                n += t.numel() * t.element_size()
+        return n
+
+
 def device_random_weights(cfg: Config, q8: bool = False, seed: int = 1337, device="cuda", std: float = 0.02, gs: int = 64,
                           shapes: dict | None = None, shard_seed: int | None = None):
     """Random-init weights of the named architecture generated ON the device (benchmarks of models whose
@@ -192,10 +251,14 @@ class Engine:
         self.w = weights
         self.cfg = weights.cfg
         self.q8 = isinstance(weights, DeviceWeightsQ8)
+        self.bf16 = isinstance(weights, DeviceWeightsBF16)
         self.B = batch
         self.state = BatchState(self.cfg, batch, device, with_att)
         self.ccfg = c_config(self.cfg)
         self.device = device
+
+    def _fn(self, stem):
+        return getattr(self.lib.c, stem + ("_q8" if self.q8 else ("_bf16" if self.bf16 else "_f32")))
 
     def forward_batch(self, tokens, pos, logits_host=None, stream=None):
         """The reference call: HOST token/pos in, [B, vocab] logits out in pinned host memory."""
@@ -203,7 +266,7 @@ class Engine:
         ps = np.ascontiguousarray(pos, dtype=np.int32)
         if logits_host is None:
             logits_host = torch.empty(self.B, self.cfg.vocab_size, dtype=torch.float32).pin_memory()
-        fn = self.lib.c.tha_forward_batch_q8 if self.q8 else self.lib.c.tha_forward_batch_f32
+        fn = self._fn("tha_forward_batch")
         st = fn(_stream_ptr(stream), self.B, C.byref(self.ccfg), C.byref(self.w.c), C.byref(self.state.c),
                 tok.ctypes.data_as(C.c_void_p), ps.ctypes.data_as(C.c_void_p), C.c_void_p(logits_host.data_ptr()))
         self.lib.check(st, "tha_forward_batch")
@@ -216,7 +279,7 @@ class Engine:
         ps = np.ascontiguousarray(pos, dtype=np.int32)
         if next_host is None:
             next_host = np.zeros(self.B, np.int32)
-        fn = self.lib.c.tha_forward_greedy_q8 if self.q8 else self.lib.c.tha_forward_greedy_f32
+        fn = self._fn("tha_forward_greedy")
         st = fn(_stream_ptr(stream), self.B, C.byref(self.ccfg), C.byref(self.w.c), C.byref(self.state.c),
                 tok.ctypes.data_as(C.c_void_p), ps.ctypes.data_as(C.c_void_p), next_host.ctypes.data_as(C.c_void_p))
         self.lib.check(st, "tha_forward_greedy")
@@ -232,7 +295,7 @@ class Engine:
         rs = None if reseed is None else np.ascontiguousarray(reseed, dtype=np.uint64)
         if next_host is None:
             next_host = np.zeros(self.B, np.int32)
-        fn = self.lib.c.tha_forward_sample_q8 if self.q8 else self.lib.c.tha_forward_sample_f32
+        fn = self._fn("tha_forward_sample")
         vp = C.c_void_p
         st = fn(_stream_ptr(stream), self.B, C.byref(self.ccfg), C.byref(self.w.c), C.byref(self.state.c),
                 tok.ctypes.data_as(vp), ps.ctypes.data_as(vp), fc.ctypes.data_as(vp) if fc is not None else None,
@@ -243,7 +306,7 @@ class Engine:
 
     def decode_step(self, token_d, pos_d, logits_d=None, next_d=None, stream=None):
         """Resident step: device token/pos, optional device logits and greedy next tokens."""
-        fn = self.lib.c.tha_decode_step_q8 if self.q8 else self.lib.c.tha_decode_step_f32
+        fn = self._fn("tha_decode_step")
         st = fn(_stream_ptr(stream), self.B, C.byref(self.ccfg), C.byref(self.w.c), C.byref(self.state.c),
                 _ptr(token_d), _ptr(pos_d), _ptr(logits_d), _ptr(next_d))
         self.lib.check(st, "tha_decode_step")
@@ -251,7 +314,7 @@ class Engine:
     def decode_greedy(self, token_d, pos_d, next_d, logits_d=None, stream=None):
         """Resident greedy step: the step, the argmax and the slot bookkeeping (token = next,
         pos += 1) without leaving the device -- one launch where the persistent kernel applies."""
-        if self.q8:
+        if self.q8 or self.bf16:
             self.decode_step(token_d, pos_d, logits_d, next_d, stream)
             self.advance(token_d, pos_d, next_d, stream)
             return
@@ -270,7 +333,7 @@ class Engine:
         if slot.size and (slot.min() < 0 or slot.max() >= self.B):
             raise ValueError("slot out of range")
         vp = C.c_void_p
-        fn = self.lib.c.tha_prefill_q8 if self.q8 else self.lib.c.tha_prefill_f32
+        fn = self._fn("tha_prefill")
         st = fn(_stream_ptr(stream), C.byref(self.ccfg), C.byref(self.w.c), C.byref(self.state.c),
                                         len(seqs), slot.ctypes.data_as(vp), pos0.ctypes.data_as(vp), ln.ctypes.data_as(vp),
                                         toks.ctypes.data_as(vp), _ptr(logits_d), _ptr(next_d))

@@ -69,6 +69,16 @@ typedef struct {
   int group_size;
 } tha_weights_q8_t;
 
+/* bf16 weights (the reference declares 16-bit weight structs at include/models.hpp:77-117 and never fills them;
+ * BASELINE.json configs[3] "fp32/bf16"): the tensors of tha_weights_f32_t, matrices and embedding table as raw bf16 bit
+ * patterns (round-to-nearest-even of the fp32 checkpoint, tha_convert_bf16), norm gains fp32.  Residual stream, KV cache,
+ * attention and logits stay fp32; every vector entering a weight matmul is rounded to bf16. */
+typedef struct {
+  uint16_t* token_embedding_table;
+  float *rms_att_weight, *rms_ffn_weight, *rms_final_weight;
+  uint16_t *wq, *wk, *wv, *wo, *w1, *w2, *w3, *wcls;
+} tha_weights_bf16_t;
+
 /* ---- library ---------------------------------------------------------------- */
 int tha_version(void);
 const char* tha_last_error(void);       /* text of the last CUDA error seen by this library */
@@ -123,6 +133,11 @@ int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const float* W, int
                     long long ldx);
 /* 1 if a tensor-core matmul on the current device gave up on a pipeline barrier since the last call */
 int tha_gemm_check_error(void);
+/* bf16 weights x bf16 activations on the tensor cores (tcgen05.mma.kind::f16, fp32 accumulate), fp32 out:
+ * out[n*ldo + row] = sum_k W[row,k] X[n,k]; W [M,K], X [N,ldx] as raw bf16 bit patterns; K % 8 == 0, K >= 64.
+ * The matmul of the bf16 model path (tha_*_bf16 below). */
+int tha_gemm_bf16(void* stream, float* out, long long ldo, const uint16_t* W, int M, int K, const uint16_t* X, int N,
+                  long long ldx);
 /* runq.c:317-342 on the INT8 tensor cores: out[n*ldo + m] = sum_g (float)(sum_{k in g} Wq[m,k] Xq[n,k]) * Ws[m,g] * XsT[g*ldxs + n],
  * groups in ascending order, no FMA contraction -- bit-identical to the reference loop.  Xq int8 [N, K]; XsT the activation
  * group scales TRANSPOSED [K/gs, ldxs] with ldxs >= N rounded up to 16/32/64 (the column tile) and a multiple of 4.
@@ -224,6 +239,20 @@ int tha_forward_sample_f32(void* stream, int n_batches, const tha_config_t* cfg,
 int tha_forward_sample_q8(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_q8_t* w,
                           const tha_state_t* s, const int* token_host, const int* pos_host, const int* force_host,
                           const unsigned long long* reseed_host, float temperature, float topp, int* next_host);
+/* bf16 model path: same calls as the fp32 ones (thaDNN_s_forward_batch semantics, state as tha_state_t) */
+int tha_convert_bf16(void* stream, const float* src_d, uint16_t* dst_d, size_t n);   /* fp32 -> bf16, round to nearest even */
+int tha_forward_batch_bf16(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_bf16_t* w,
+                           const tha_state_t* s, const int* token_host, const int* pos_host, float* logits_out);
+int tha_decode_step_bf16(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_bf16_t* w,
+                         const tha_state_t* s, const int* token_d, const int* pos_d, float* logits_d, int* next_d);
+int tha_forward_greedy_bf16(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_bf16_t* w,
+                            const tha_state_t* s, const int* token_host, const int* pos_host, int* next_host);
+int tha_forward_sample_bf16(void* stream, int n_batches, const tha_config_t* cfg, const tha_weights_bf16_t* w,
+                            const tha_state_t* s, const int* token_host, const int* pos_host, const int* force_host,
+                            const unsigned long long* reseed_host, float temperature, float topp, int* next_host);
+int tha_prefill_bf16(void* stream, const tha_config_t* cfg, const tha_weights_bf16_t* w, const tha_state_t* s, int n_seqs,
+                     const int* slot_host, const int* pos0_host, const int* len_host, const int* tokens_host,
+                     float* logits_d, int* next_d);
 /* greedy sampler on the device: next[b] = first argmax of logits[b, :] */
 int tha_argmax_batch_f32(void* stream, int n_batches, const float* logits, int vocab, int* next_d);
 /* greedy bookkeeping of the batching driver (src/llama.cpp:1027-1050) kept on the device:

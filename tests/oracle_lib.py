@@ -48,6 +48,7 @@ class Oracle:
         lib.orc_open_v2.restype = C.c_void_p
         lib.orc_open_v2.argtypes = [C.c_char_p]
         lib.orc_close.argtypes = [C.c_void_p]
+        lib.orc_set_bf16_activations.argtypes = [C.c_void_p, C.c_int]
         lib.orc_get_config.argtypes = [C.c_void_p, i32p]
         lib.orc_seq_new.restype = C.c_void_p
         lib.orc_seq_new.argtypes = [C.c_void_p]
@@ -133,8 +134,13 @@ class Oracle:
         return o
 
     # ---- models ----
-    def open(self, path, quantized=False):
-        return OracleModel(self, path, quantized)
+    def open(self, path, quantized=False, bf16=False):
+        """bf16 = True: a v0 file whose weights were rounded to bf16 (checkpoint.round_bf16); matmul inputs are then rounded
+        to bf16 as the tensor cores consume them (oracle/llama2_oracle.c, orc_set_bf16_activations)."""
+        m = OracleModel(self, path, quantized)
+        if bf16:
+            self.lib.orc_set_bf16_activations(m.h, 1)
+        return m
 
 
 class OracleModel:

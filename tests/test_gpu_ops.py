@@ -340,3 +340,23 @@ def test_gemm_tf32x3_rejects_bad_shapes(L):
     W, X, O = tdev(np.zeros((8, 30), np.float32)), tdev(np.zeros((2, 30), np.float32)), tdev(np.zeros((2, 8), np.float32))
     assert L.c.tha_gemm_tf32x3(stream_ptr(), P(O), 8, P(W), 8, 30, P(X), 2, 30) == 7      # K % 4 != 0: NOT_SUPPORTED
     assert L.c.tha_gemm_tf32x3(stream_ptr(), P(O), 8, P(W), 0, 32, P(X), 2, 32) == 2      # M < 1: invalid argument
+
+
+@pytest.mark.parametrize("M,K,N", [(128, 64, 1), (300, 768, 5), (768, 2048, 16), (2304, 768, 40), (4096, 4096, 64),
+                                   (1000, 11008, 130), (4096, 4096, 300), (32000, 768, 256), (640, 4096, 2048)])
+def test_gemm_bf16_tensor_cores(M, K, N):
+    """tha_gemm_bf16 (tcgen05.mma.kind::f16, both operands from TMA-written shared memory, double-buffered TMEM
+    accumulator) against a float64 product of the same bf16 values: only fp32 accumulation order differs."""
+    import torch
+    lib = load_pkg("cabi").lib()
+    g = torch.Generator(device="cuda"); g.manual_seed(M + K + N)
+    W = (torch.randn(M, K, device="cuda", generator=g) * 0.05).to(torch.bfloat16)
+    X = torch.randn(N, K, device="cuda", generator=g).to(torch.bfloat16)
+    out = torch.zeros(N, M, device="cuda")
+    lib.check(lib.c.tha_gemm_bf16(stream_ptr(), P(out), M, P(W), M, K, P(X), N, K), "tha_gemm_bf16")
+    torch.cuda.synchronize()
+    assert lib.c.tha_gemm_check_error() == 0
+    want = (X.double() @ W.double().t())
+    err = (out.double() - want).abs().max().item()
+    scale = want.abs().max().item()
+    assert err <= 2e-5 * scale, f"max err {err:.3e} vs scale {scale:.3e}"   # fp32 accumulation in the tensor core over up to 11008 terms
