@@ -517,7 +517,20 @@ def extra_records(args, device, peak):
             dw.cfg = c
             out[f"7b_q8_B{B}"] = decode_record(c, dw, B, 4, 12, f"Llama-2-7B Q8_0 batched greedy decode, {B} slots, positions 4..15, "
                                                f"KV slab of {c.seq_len} positions")
-        del dw
+        # the same 64 slots with the full 2048-position context: only possible with the PAGED cache (dense fp32 KV would be
+        # 137 GB); pool = 8 blocks of 16 positions per slot
+        c = cfg
+        dw.cfg = c
+        paged = eng.PagedKV(c, 64, n_blocks=64 * 8)
+        tab = np.arange(64 * paged.nrow, dtype=np.int32).reshape(64, paged.nrow) % (64 * 8)
+        paged.set_table((tab * 37) % (64 * 8))          # scattered, collision-free for the first 8 blocks of every slot
+        e = eng.Engine(dw, 64, device=device, with_att=False, paged=paged)
+        v, ms = resident_tok_s(e, c, 64, 4, 12, device)
+        out["7b_q8_B64_paged_seq2048"] = {"workload": "Llama-2-7B Q8_0, 64 slots, context 2048, PAGED KV cache (512 blocks of 16 positions = 8.6 GB "
+                                                      "instead of a 137 GB slab), positions 4..15", "value": v, "unit": UNIT, "ms_per_step": ms}
+        del e
+        paged.close()
+        del paged, dw
         free()
     except Exception as ex:
         out["7b_q8"] = {"error": str(ex)}

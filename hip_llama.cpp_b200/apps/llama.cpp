@@ -7,7 +7,7 @@
 // Options (reference :1490-1510): -t temperature, -p top-p, -s seed, -n steps, -i prompt,
 // -z tokenizer path, -m mode (generate|test), -f/-o files, -b batch size.  Additions: -g <n>
 // number of GPUs, -k <file> write the generated token ids, -x 1 ignore stop tokens (timing), -r 0 prompt token by token,
-// -q 1 host-side sampler,
+// -q 1 host-side sampler, -c <blocks> paged KV cache,
 // and in test mode -t/-p/-s are honoured when given (-t 0 = greedy).  The checkpoint may be a
 // v0 fp32 file or a v2 Q8_0 file; the version is detected from the header.
 #include <stdio.h>
@@ -36,6 +36,7 @@ static void error_usage() {
   fprintf(stderr, "  -w <int>    tensor-parallel width: ONE replica split over this many ranks (rank r on GPU r %% n_gpus), greedy only (-t 0)\n");
   fprintf(stderr, "  -k <string> also write the generated token ids to this file\n");
   fprintf(stderr, "  -x <0|1>    ignore stop tokens (fixed-length timing runs)\n");
+  fprintf(stderr, "  -c <int>    paged KV cache: the slots of a GPU share this many blocks of 16 positions (-1: what fits; default 0: dense slabs)\n");
   fprintf(stderr, "  -q <0|1>    sampled runs: 1 = sample on the host from B*vocab logits as the reference does (default 0: sampler on the GPU)\n");
   fprintf(stderr, "  -r <0|1>    fp32 models: ingest prompts in one tensor-core pass (default 1); 0 = one decode step per prompt token\n");
   exit(EXIT_FAILURE);
@@ -46,7 +47,7 @@ int main(int argc, char* argv[]) {
   char* checkpoint_path = nullptr;
   const char* tokenizer_path = "./assets/tokenizer.bin";
   float temperature = 1.0f, topp = 0.9f;
-  int steps = 256, batch = 1, n_gpus = 0, ignore_stop = 0, prefill = 1, tp = 1, host_sampler = 0;
+  int steps = 256, batch = 1, n_gpus = 0, ignore_stop = 0, prefill = 1, tp = 1, host_sampler = 0, kv_blocks = 0;
   const char* prompt = nullptr;
   unsigned long long rng_seed = 0;
   const char* mode = "generate";
@@ -75,6 +76,7 @@ int main(int argc, char* argv[]) {
     else if (f == 'r') prefill = atoi(v);
     else if (f == 'w') tp = atoi(v);
     else if (f == 'q') host_sampler = atoi(v);
+    else if (f == 'c') kv_blocks = atoi(v);
     else error_usage();
   }
   if (rng_seed == 0) rng_seed = (unsigned int)time(nullptr);
@@ -98,6 +100,7 @@ int main(int argc, char* argv[]) {
   opt.ignore_stop = ignore_stop;
   opt.prefill = prefill;
   opt.host_sampler = host_sampler;
+  opt.kv_blocks = kv_blocks;
   opt.tp = tp < 1 ? 1 : tp;
   // ranks of one replica that share a GPU hand-shake between concurrent kernels: every rank's stream needs its own
   // hardware queue (set before the CUDA context exists)

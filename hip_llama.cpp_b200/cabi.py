@@ -112,6 +112,8 @@ class Lib:
             "tha_prefill_q8": [vp, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), I, vp, vp, vp, vp, vp, vp],
             "tha_matmul_q8_tc": [vp, vp, C.c_longlong, vp, vp, I, I, I, vp, vp, I, I],
             "tha_argmax_batch_f32": [vp, I, vp, I, vp],
+            "tha_kv_pool_register": [vp, vp, vp, I, I, I],
+            "tha_kv_pool_unregister": [vp],
             "tha_sample": [vp, I, vp, I, F, F, vp, vp, vp, vp, vp],
             "tha_forward_sample_f32": [vp, I, C.POINTER(Config), C.POINTER(WeightsF32), C.POINTER(State), vp, vp, vp, vp, F, F, vp],
             "tha_forward_sample_q8": [vp, I, C.POINTER(Config), C.POINTER(WeightsQ8), C.POINTER(State), vp, vp, vp, vp, F, F, vp],

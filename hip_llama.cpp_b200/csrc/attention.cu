@@ -88,6 +88,7 @@ struct AttnP {
   float4* part_acc; float2* part_ml; int* counters;
   float* out_hi; float* out_lo;             // nullable: the tf32 hi/lo split of `out` for the tensor-core wo matmul
   int8_t* out_q; float* out_sT; int ldxs, gs;   // nullable: `out` quantised per group (runq.c:145-171) for the int8 wo matmul
+  KvPaged pg;                                   // pg.table != nullptr: kc / vc are block pools (BatchManager), rows found through the table
 };
 
 __device__ __forceinline__ float attn_tf32(float v) { return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u); }
@@ -146,8 +147,8 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
 #pragma unroll
   for (int j = 0; j < J; j++) { m[j] = -INFINITY; l[j] = 0.0f; acc[j] = make_float4(0.f, 0.f, 0.f, 0.f); }
 
-  const float* kb = p.kc + (size_t)b * p.kv_batch_stride;
-  const float* vb = p.vc + (size_t)b * p.kv_batch_stride;
+  const float* kb = p.pg.table ? p.kc : p.kc + (size_t)b * p.kv_batch_stride;
+  const float* vb = p.pg.table ? p.vc : p.vc + (size_t)b * p.kv_batch_stride;
   // A warp takes rows t, t+8, .., t+8(RW-1) per iteration (RW x 2 x J independent 128-bit loads in flight per lane)
   // and folds them into the running softmax with ONE rescale: exp(m_old - m_new) once per RW rows.  Scores are scaled
   // by 1/sqrt(hs) (exact for head sizes 16 and 64; 1 ulp from the reference's division otherwise) and exponentials
@@ -158,16 +159,19 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   for (int t = t0 + warp; t < t1; t += 8 * RW) {
     float4 kr[RW][J], vr[RW][J];
     bool live[RW];
+    long long roff[RW];
 #pragma unroll
     for (int r = 0; r < RW; r++) {
       live[r] = (t + 8 * r) < t1;
-      const float* ka = kb + (size_t)(live[r] ? t + 8 * r : t) * p.kv_dim;
+      const int tr = live[r] ? t + 8 * r : t;
+      roff[r] = p.pg.table ? kv_paged_off(p.pg, b, tr, p.kv_dim) : (long long)tr * p.kv_dim;
+      const float* ka = kb + roff[r];
 #pragma unroll
       for (int j = 0; j < J; j++) kr[r][j] = ldg_stream(reinterpret_cast<const float4*>(ka + koff[j]));
     }
 #pragma unroll
     for (int r = 0; r < RW; r++) {
-      const float* va = vb + (size_t)(live[r] ? t + 8 * r : t) * p.kv_dim;
+      const float* va = vb + roff[r];
 #pragma unroll
       for (int j = 0; j < J; j++) vr[r][j] = ldg_stream(reinterpret_cast<const float4*>(va + koff[j]));
     }
@@ -320,13 +324,14 @@ int attn_fused_nsplit(int B, int nseg, int seq_len) {
 int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
                       int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo, int8_t* out_q, float* out_sT,
-                      int ldxs, int gs) {
+                      int ldxs, int gs, const KvPaged* pg) {
   const int dim = n_heads * head_size, kv_dim = n_kv_heads * head_size;
   const int J = fused_J(n_heads, head_size, dim, n_heads / n_kv_heads);
   if (!J || kv_dim % 4) return THA_STATUS_NOT_SUPPORTED;
   AttnP p;
   p.pos = pos_d; p.q = q; p.out = out; p.kc = kc; p.vc = vc; p.out_hi = out_hi; p.out_lo = out_lo;
   p.out_q = out_q; p.out_sT = out_sT; p.ldxs = ldxs; p.gs = gs;
+  if (pg) p.pg = *pg; else p.pg = KvPaged{};
   if (out_q && (gs < 32 || gs > 128 || (gs & (gs - 1)) || 128 % gs)) return THA_STATUS_NOT_SUPPORTED;
   p.kv_batch_stride = kv_batch_stride; p.kv_dim = kv_dim; p.head_size = head_size;
   p.kv_mul = n_heads / n_kv_heads; p.dim = dim;
@@ -421,5 +426,5 @@ extern "C" int tha_mha_fused_v1_f32(void* stream, int n_batches, const int* pos_
   if (!ws) return THA_STATUS_EXECUTION_FAILED;
   const int kv_dim = n_kv_heads * head_size;
   return attn_fused_launch((cudaStream_t)stream, ws, n_batches, pos_d, n_heads, n_kv_heads, q, xb, key_cache + loff,
-                           value_cache + loff, (long long)n_layers * seq_len * kv_dim, head_size, seq_len, false, nullptr, nullptr, nullptr, nullptr, 0, 0);
+                           value_cache + loff, (long long)n_layers * seq_len * kv_dim, head_size, seq_len, false, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr);
 }

@@ -20,6 +20,7 @@ struct AttnPrefillP {
   long long kv_batch_stride; int kv_dim, kv_mul, dim;
   const int* row_slot; const int* row_pos;                    // [rows]
   const int* tile_row0; const int* tile_n;                    // [tiles]: first row and row count (<= 64) of each query tile
+  KvPaged pg;                                                 // pg.table != nullptr: kc / vc are block pools, rows found through the table
 };
 
 constexpr int PF_TQ = 64, PF_TK = 64;
@@ -45,8 +46,8 @@ __global__ void __launch_bounds__(256) attn_prefill_kernel(const AttnPrefillP p)
   if (pos0 < 0 || n <= 0) return;
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int kh = h / p.kv_mul;
-  const float* kbase = p.kc + (size_t)slot * p.kv_batch_stride + kh * HS;
-  const float* vbase = p.vc + (size_t)slot * p.kv_batch_stride + kh * HS;
+  const float* kbase = (p.pg.table ? p.kc : p.kc + (size_t)slot * p.kv_batch_stride) + kh * HS;
+  const float* vbase = (p.pg.table ? p.vc : p.vc + (size_t)slot * p.kv_batch_stride) + kh * HS;
   const int kmax = pos0 + n - 1;   // last key any row of the tile may see
   const float sqrt_hs = sqrtf((float)HS);
 
@@ -79,8 +80,10 @@ __global__ void __launch_bounds__(256) attn_prefill_kernel(const AttnPrefillP p)
       const int r = tid & 63, c0 = tid >> 6;
       const int t = tk0 + r;
       const bool live = t <= kmax;
-      const float* krow = kbase + (size_t)(live ? t : kmax) * p.kv_dim;
-      const float* vrow = vbase + (size_t)(live ? t : kmax) * p.kv_dim;
+      const int tr = live ? t : kmax;
+      const long long roff = p.pg.table ? kv_paged_off(p.pg, slot, tr, p.kv_dim) : (long long)tr * p.kv_dim;
+      const float* krow = kbase + roff;
+      const float* vrow = vbase + roff;
       for (int c = c0; c < HS / 4; c += 4) {
         const float4 kv = *reinterpret_cast<const float4*>(krow + 4 * c);
         Kt[(4 * c + 0) * PF_TK + r] = kv.x; Kt[(4 * c + 1) * PF_TK + r] = kv.y;
@@ -193,10 +196,11 @@ bool attn_prefill_supported(int head_size, int kv_dim) {
 int attn_prefill_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_heads, int head_size, const float* q,
                         float* out, float* out_hi, float* out_lo, const float* kc, const float* vc,
                         long long kv_batch_stride, const int* row_slot, const int* row_pos, const int* tile_row0,
-                        const int* tile_n, bool pdl) {
+                        const int* tile_n, bool pdl, const KvPaged* pg) {
   if (!attn_prefill_supported(head_size, n_kv_heads * head_size)) return THA_STATUS_NOT_SUPPORTED;
   AttnPrefillP p;
   p.q = q; p.out = out; p.out_hi = out_hi; p.out_lo = out_lo; p.kc = kc; p.vc = vc;
+  if (pg) p.pg = *pg; else p.pg = KvPaged{};
   p.kv_batch_stride = kv_batch_stride; p.kv_dim = n_kv_heads * head_size; p.kv_mul = n_heads / n_kv_heads;
   p.dim = n_heads * head_size;
   p.row_slot = row_slot; p.row_pos = row_pos; p.tile_row0 = tile_row0; p.tile_n = tile_n;

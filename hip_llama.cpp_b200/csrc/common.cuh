@@ -62,6 +62,25 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
   return e;
 }
 
+// ---- paged KV cache (include/BatchManager.hpp) ---------------------------------------------
+// The cache rows of a slot either sit in the dense slab [slot][layer][seq_len][kv_dim] (table == nullptr; the layout of
+// src/models.cpp:176-177) or in BLOCKS of (1 << bs_shift) positions handed out by a BatchManager: pool
+// [block][layer][position in block][kv_dim], one table row of block ids per slot.
+struct KvPaged {
+  const int* table;
+  int stride;               // table row length (blocks per slot)
+  int bs_shift, bs_mask;
+  long long blk_stride;     // floats per block: n_layers * block_size * kv_dim
+  long long layer_off;      // floats: layer * block_size * kv_dim
+};
+#if defined(__CUDACC__)
+// offset of cache row (slot, t) from the pool base, layer included
+__device__ __forceinline__ long long kv_paged_off(const KvPaged& g, int slot, int t, int kvd) {
+  const int blk = __ldg(g.table + (size_t)slot * g.stride + (t >> g.bs_shift));
+  return (long long)blk * g.blk_stride + g.layer_off + (long long)(t & g.bs_mask) * kvd;
+}
+#endif
+
 // ---- device helpers ------------------------------------------------------------------
 #ifdef __CUDACC__
 

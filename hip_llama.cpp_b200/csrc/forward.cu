@@ -28,7 +28,7 @@ int attn_fused_prepare(Workspace* ws, int B, int n_heads, int n_kv_heads, int he
 int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
                       int head_size, int seq_len, bool pdl, float* out_hi = nullptr, float* out_lo = nullptr,
-                      int8_t* out_q = nullptr, float* out_sT = nullptr, int ldxs = 0, int gs = 0);
+                      int8_t* out_q = nullptr, float* out_sT = nullptr, int ldxs = 0, int gs = 0, const KvPaged* pg = nullptr);
 int launches_reset();
 int launches_get();
 // megastep.cu: the whole step as one persistent kernel (small models, B <= 8)
@@ -225,7 +225,10 @@ int decode_step_f32(cudaStream_t st, int B, const tha_config_t* cfg, const tha_w
   a.B = B; a.cfg = *cfg; a.w = *w; a.s = *s; a.token_d = token_d; a.pos_d = pos_d; a.logits_d = logits_d;
   a.next_d = next_d; a.pdl = pdl_enabled(); a.advance = advance;
   const int tcm = tc_mode();
-  const bool use_tc = tcm != 0 && (tcm == 1 || B > 8) && step_tc_supported(cfg, B);
+  // a paged KV cache (tha_kv_pool_register) is read and written by the row pipeline's kernels only
+  const bool paged = kv_pool_find(s->key_cache, nullptr);
+  if (paged && !step_tc_supported(cfg, B)) return THA_STATUS_NOT_SUPPORTED;
+  const bool use_tc = paged || (tcm != 0 && (tcm == 1 || B > 8) && step_tc_supported(cfg, B));
   a.mega = !use_tc && mega_enabled() && mega_supported(cfg, B);
   if (a.mega) {
     // scratch is grown outside any capture; the kernel writes logits only where the caller wants them
@@ -401,6 +404,7 @@ int decode_step_q8(cudaStream_t st, int B, const tha_config_t* cfg, const tha_we
       return (int)THA_STATUS_SUCCESS;
     });
   }
+  if (kv_pool_find(s->key_cache, nullptr)) return THA_STATUS_NOT_SUPPORTED;   // paged KV: tensor-core row pipeline only
   const bool fused = attn_fused_supported(cfg->n_heads, hs, cfg->dim, kvd);
   if (!fused && !s->att) return THA_STATUS_INVALID_ARG;
   if (fused) THA_TRY(attn_fused_prepare(ws, B, cfg->n_heads, cfg->n_kv_heads, hs, cfg->seq_len));
@@ -497,7 +501,7 @@ int decode_step_bf16(cudaStream_t st, int B, const tha_config_t* cfg, const tha_
   // 1-2 slots: the weights stream through the fused GEMV kernels (5 launches per layer); more: tensor cores (Llama-2-7B:
   // 8 slots 12.4 ms per step on the GEMV path -- shared-memory-bound at 8 FMAs per weight -- against 4.0 ms at 64 slots on
   // the tensor cores).  Option "tc" = 1 forces the tensor cores, 0 the GEMV path up to 8 slots.
-  a.gemv = (((B <= 2 && tc_mode() != 1) || (B <= 8 && tc_mode() == 0)) && s->hb) ? 1 : 0;
+  a.gemv = (((B <= 2 && tc_mode() != 1) || (B <= 8 && tc_mode() == 0)) && s->hb && !kv_pool_find(s->key_cache, nullptr)) ? 1 : 0;
   if (a.gemv) {
     const int hs = cfg->dim / cfg->n_heads;
     THA_TRY(attn_fused_prepare(ws, B, cfg->n_heads, cfg->n_kv_heads, hs, cfg->seq_len));

@@ -27,15 +27,15 @@ int attn_fused_prepare(Workspace* ws, int B, int n_heads, int n_kv_heads, int he
 int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
                       int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo, int8_t* out_q = nullptr,
-                      float* out_sT = nullptr, int ldxs = 0, int gs = 0);
+                      float* out_sT = nullptr, int ldxs = 0, int gs = 0, const KvPaged* pg = nullptr);
 bool attn_prefill_supported(int head_size, int kv_dim);
 int attn_prefill_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_heads, int head_size, const float* q,
                         float* out, float* out_hi, float* out_lo, const float* kc, const float* vc,
                         long long kv_batch_stride, const int* row_slot, const int* row_pos, const int* tile_row0,
-                        const int* tile_n, bool pdl);
+                        const int* tile_n, bool pdl, const KvPaged* pg = nullptr);
 int rope_scatter_launch(cudaStream_t st, bool pdl, int R, const float* part, int nz, long long zstride, int ld, const int* pos, int d,
                         int kvd, int hs, const float* rc, const float* rs, float* q, float* kc, float* vc, long long kv_bs, int loff,
-                        const int* slot);
+                        const int* slot, const KvPaged* pg = nullptr);
 
 __device__ __forceinline__ float bf16_to_f32(uint16_t v) { return __uint_as_float((uint32_t)v << 16); }
 // round to nearest even onto bf16 (finite inputs; NaN stays NaN)
@@ -286,8 +286,14 @@ static int bf_issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, 
   };
   int prev_z = 0;
   long long prev_zs = 0;
+  KvPool pool;
+  const bool paged = kv_pool_find(s.key_cache, &pool);
+  if (paged && s.value_cache != pool.v) return THA_STATUS_INVALID_ARG;
   for (int l = 0; l < L; l++) {
     const int loff = l * c.seq_len * kvd;
+    const KvPaged pg = paged ? kv_paged_of(pool, L, kvd, l) : KvPaged{};
+    const float* kcl = paged ? s.key_cache : s.key_cache + loff;
+    const float* vcl = paged ? s.value_cache : s.value_cache + loff;
     THA_TRY_RC(prep(R, prev_z, prev_zs, l == 0 ? w.token_embedding_table : (const uint16_t*)nullptr, w.rms_att_weight + (size_t)l * d, nogather));
     {
       const uint16_t* W[3] = {w.wq + (size_t)l * d * d, w.wk + (size_t)l * d * kvd, w.wv + (size_t)l * d * kvd};
@@ -295,14 +301,14 @@ static int bf_issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, 
       THA_TRY_RC(mm(3, W, M, off, d, sc.xb, R, sc.part, ld_qkv, (long long)R * ld_qkv, pl.z_qkv));
     }
     THA_TRY_RC(rope_scatter_launch(st, pdl, R, sc.part, pl.z_qkv, (long long)R * ld_qkv, ld_qkv, io.pos, d, kvd, hs, rc, rs, io.q,
-                                   s.key_cache, s.value_cache, kv_bs, loff, io.slot));
+                                   s.key_cache, s.value_cache, kv_bs, loff, io.slot, &pg));
     if (!io.logits && l == L - 1) return THA_STATUS_SUCCESS;   // cache-only ingestion: the last layer's K/V rows are in place
     if (io.n_tiles > 0)
-      THA_TRY_RC(attn_prefill_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, nullptr, nullptr, s.key_cache + loff,
-                                     s.value_cache + loff, kv_bs, io.slot, io.pos, io.tile_row0, io.tile_n, pdl));
+      THA_TRY_RC(attn_prefill_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, nullptr, nullptr, kcl,
+                                     vcl, kv_bs, io.slot, io.pos, io.tile_row0, io.tile_n, pdl, &pg));
     else
-      THA_TRY_RC(attn_fused_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, s.key_cache + loff, s.value_cache + loff,
-                                   kv_bs, hs, c.seq_len, pdl, nullptr, nullptr));
+      THA_TRY_RC(attn_fused_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, kcl, vcl,
+                                   kv_bs, hs, c.seq_len, pdl, nullptr, nullptr, nullptr, nullptr, 0, 0, &pg));
     THA_CUDA_OK(launch(bf_round_kernel, dim3(ceil_div(d / 4, 256), R), dim3(256), 0, st, pdl, (const float*)io.xb, (long long)d, 0, 0LL, 0,
                        io.pos, d, sc.xb));
     {

@@ -38,13 +38,13 @@ int attn_fused_prepare(Workspace* ws, int B, int n_heads, int n_kv_heads, int he
 int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
                       int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo, int8_t* out_q = nullptr,
-                      float* out_sT = nullptr, int ldxs = 0, int gs = 0);
+                      float* out_sT = nullptr, int ldxs = 0, int gs = 0, const KvPaged* pg = nullptr);
 
 bool attn_prefill_supported(int head_size, int kv_dim);
 int attn_prefill_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_heads, int head_size, const float* q,
                         float* out, float* out_hi, float* out_lo, const float* kc, const float* vc,
                         long long kv_batch_stride, const int* row_slot, const int* row_pos, const int* tile_row0,
-                        const int* tile_n, bool pdl);
+                        const int* tile_n, bool pdl, const KvPaged* pg = nullptr);
 
 __device__ __forceinline__ float st_tf32(float v) { return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u); }
 
@@ -158,12 +158,14 @@ __global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __res
                                                               const float* __restrict__ rc, const float* __restrict__ rs,
                                                               float* __restrict__ q, float* __restrict__ kc,
                                                               float* __restrict__ vc, long long kv_bs, int loff,
-                                                              const int* __restrict__ slot) {
+                                                              const int* __restrict__ slot, const KvPaged pg) {
   pdl_wait();
   pdl_trigger();
   const int b = blockIdx.y, pb = pos[b];
   if (pb < 0) return;
   const int sb = slot ? slot[b] : b;   // cache slab of this row
+  // where the row of position pb lives: the slot's dense slab, or a block of the pool (BatchManager)
+  const long long rowoff = pg.table ? kv_paged_off(pg, sb, pb, kvd) : (long long)sb * kv_bs + loff + (long long)pb * kvd;
   const int pair = blockIdx.x * blockDim.x + threadIdx.x;
   const int i = pair * 2;
   if (i >= d + 2 * kvd) return;
@@ -179,17 +181,17 @@ __global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __res
     const float c = rc[(size_t)pb * (hs >> 1) + j], s = rs[(size_t)pb * (hs >> 1) + j];
     const float r0 = v.x * c - v.y * s, r1 = v.x * s + v.y * c;
     if (i < d) *reinterpret_cast<float2*>(q + (size_t)b * d + li) = make_float2(r0, r1);
-    else *reinterpret_cast<float2*>(kc + (size_t)sb * kv_bs + loff + (size_t)pb * kvd + li) = make_float2(r0, r1);
+    else *reinterpret_cast<float2*>(kc + rowoff + li) = make_float2(r0, r1);
   } else {
-    *reinterpret_cast<float2*>(vc + (size_t)sb * kv_bs + loff + (size_t)pb * kvd + (i - d - kvd)) = v;
+    *reinterpret_cast<float2*>(vc + rowoff + (i - d - kvd)) = v;
   }
 }
 
 int rope_scatter_launch(cudaStream_t st, bool pdl, int R, const float* part, int nz, long long zstride, int ld, const int* pos, int d,
                         int kvd, int hs, const float* rc, const float* rs, float* q, float* kc, float* vc, long long kv_bs, int loff,
-                        const int* slot) {
+                        const int* slot, const KvPaged* pg) {
   THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld / 2, 256), R), dim3(256), 0, st, pdl, part, nz, zstride, ld, pos, d, kvd, hs,
-                     rc, rs, q, kc, vc, kv_bs, loff, slot));
+                     rc, rs, q, kc, vc, kv_bs, loff, slot, pg ? *pg : KvPaged{}));
   return THA_STATUS_SUCCESS;
 }
 
@@ -708,7 +710,8 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
   }
   const int R = io.R;
   const bool q8 = wq != nullptr;
-  if (!q8 && !tp && io.n_tiles == 0 && !io.out_rows && io.n_out == R && io.logits && sc.ctr && chain_supported(c, R, sc, w, s))
+  if (!q8 && !tp && io.n_tiles == 0 && !io.out_rows && io.n_out == R && io.logits && sc.ctr && chain_supported(c, R, sc, w, s) &&
+      !kv_pool_find(s.key_cache, nullptr))
     return issue_rows_chain(st, ws, c, w, s, sc, io, rc, rs, pdl);
   const int gs = wq ? wq->group_size : 0;
   const Dims dm = dims_of(c, tp);
@@ -733,6 +736,9 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
     if (need > tp->xchg_floats || !tp->connected || tp->hidden_of[tp->rank] != hd) return THA_STATUS_INVALID_ARG;
   }
   const int skip = skip_mask();
+  KvPool pool;
+  const bool paged = kv_pool_find(s.key_cache, &pool);
+  if (paged && (tp || s.value_cache != pool.v)) return THA_STATUS_INVALID_ARG;
   int xk = 0;   // exchanges issued so far in this step
   auto peers_of = [&](int which, bool w2) -> TpPeers {
     TpPeers t = {};
@@ -792,10 +798,13 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
       const int M[3] = {da, kvd, kvd}, off[3] = {0, da, da + kvd};
       THA_TRY_RC(mm(3, W, Q, l, M, off, d, sc.xh, sc.xl, R, sc.part, ld_qkv, (long long)R * ld_qkv, pl.z_qkv, sc.scale));
     }
+    const KvPaged pg = paged ? kv_paged_of(pool, L, kvd, l) : KvPaged{};
+    const float* kcl = paged ? s.key_cache : s.key_cache + loff;      // layer's cache rows: pool base, or slab + layer offset
+    const float* vcl = paged ? s.value_cache : s.value_cache + loff;
     if (!(skip & 8))
     THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld_qkv / 2, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part,
                        pl.z_qkv, (long long)R * ld_qkv, ld_qkv, io.pos, da, kvd, hs, rc, rs, io.q, s.key_cache, s.value_cache,
-                       kv_bs, loff, io.slot));
+                       kv_bs, loff, io.slot, pg));
     if (!io.logits && l == L - 1) {   // cache-only ingestion: the last layer's K/V rows are in place
       if (tpx) THA_CUDA_OK(launch(tp_epoch_kernel, dim3(1), dim3(32), 0, st, pdl, tp->epoch()));
       return THA_STATUS_SUCCESS;
@@ -803,13 +812,13 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
     if (skip & 2) {
     } else if (io.n_tiles > 0) {
       THA_TRY_RC(attn_prefill_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, wq ? nullptr : sc.xh,
-                                     wq ? nullptr : sc.xl, s.key_cache + loff, s.value_cache + loff, kv_bs, io.slot, io.pos,
-                                     io.tile_row0, io.tile_n, pdl));
+                                     wq ? nullptr : sc.xl, kcl, vcl, kv_bs, io.slot, io.pos,
+                                     io.tile_row0, io.tile_n, pdl, &pg));
     } else {
       // Q8_0: the quantiser of the attention output (runq.c:437) runs in the attention kernel's final store
-      THA_TRY_RC(attn_fused_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, s.key_cache + loff,
-                                   s.value_cache + loff, kv_bs, hs, c.seq_len, pdl, wq ? nullptr : sc.xh, wq ? nullptr : sc.xl,
-                                   wq ? sc.xq : nullptr, wq ? sc.xsT : nullptr, ldxs, gs));
+      THA_TRY_RC(attn_fused_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, kcl,
+                                   vcl, kv_bs, hs, c.seq_len, pdl, wq ? nullptr : sc.xh, wq ? nullptr : sc.xl,
+                                   wq ? sc.xq : nullptr, wq ? sc.xsT : nullptr, ldxs, gs, &pg));
     }
     if ((skip & 16) || (wq && io.n_tiles == 0 && !(skip & 2))) {
     } else if (wq)   // prompt rows: runq.c:437 as its own launch

@@ -82,6 +82,25 @@ void trace_launch(const void* fn, cudaStream_t st) {
   g_trace_ev.emplace_back(fn, ev);
 }
 
+static std::map<const float*, KvPool> g_kv_pools;
+bool kv_pool_find(const float* key_cache, KvPool* out) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto it = g_kv_pools.find(key_cache);
+  if (it == g_kv_pools.end()) return false;
+  if (out) *out = it->second;
+  return true;
+}
+KvPaged kv_paged_of(const KvPool& pool, int n_layers, int kv_dim, int layer) {
+  KvPaged g;
+  g.table = pool.table; g.stride = pool.stride;
+  int sh = 0;
+  while ((1 << sh) < pool.block_size) sh++;
+  g.bs_shift = sh; g.bs_mask = pool.block_size - 1;
+  g.blk_stride = (long long)n_layers * pool.block_size * kv_dim;
+  g.layer_off = (long long)layer * pool.block_size * kv_dim;
+  return g;
+}
+
 Workspace* workspace() {
   int dev = -1;
   if (cudaGetDevice(&dev) != cudaSuccess) { set_last_error("cudaGetDevice", cudaGetLastError()); return nullptr; }
@@ -206,6 +225,27 @@ int* opt_graph() { return &g_graph; }
 }  // namespace tha
 
 extern "C" int tha_version(void) { return 100; }
+
+// Paged KV cache.  key_pool / value_pool: [n_blocks][n_layers][block_size][kv_dim] fp32 on the device (the caller allocates
+// them; a tha_state_t is paged when its key_cache == key_pool and value_cache == value_pool); block_table_d: [slots][stride]
+// block ids on the device, row s listing the blocks that hold positions 0.., block_size positions each (a power of two).
+// The kernels read the table at run time: update it (stream-ordered) before a step that needs a new block.
+extern "C" int tha_kv_pool_register(float* key_pool, float* value_pool, const int* block_table_d, int table_stride, int block_size,
+                                    int n_blocks) {
+  if (!key_pool || !value_pool || !block_table_d || table_stride < 1 || block_size < 1 || (block_size & (block_size - 1)) || n_blocks < 1)
+    return THA_STATUS_INVALID_ARG;
+  std::lock_guard<std::mutex> lk(tha::g_mu);
+  tha::KvPool p = {key_pool, value_pool, block_table_d, table_stride, block_size, n_blocks};
+  tha::g_kv_pools[key_pool] = p;
+  for (auto& kv : tha::g_ws) tha::ws_drop_graphs(kv.second);   // a graph may have captured this address as a dense slab
+  return THA_STATUS_SUCCESS;
+}
+extern "C" int tha_kv_pool_unregister(float* key_pool) {
+  std::lock_guard<std::mutex> lk(tha::g_mu);
+  tha::g_kv_pools.erase(key_pool);
+  for (auto& kv : tha::g_ws) tha::ws_drop_graphs(kv.second);
+  return THA_STATUS_SUCCESS;
+}
 extern "C" const char* tha_last_error(void) { return tha::last_error_text(); }
 extern "C" int tha_set_option(const char* name, int value) {
   if (!name) return THA_STATUS_INVALID_ARG;

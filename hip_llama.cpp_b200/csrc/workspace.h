@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "common.cuh"
+
 #include <map>
 #include <tuple>
 #include <vector>
@@ -43,6 +45,11 @@ struct Workspace {
   cudaStream_t side_stream = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
+
+// Registered block pools (tha_kv_pool_register): a tha_state_t whose key_cache is a registered pool is PAGED
+struct KvPool { const float* k; const float* v; const int* table; int stride; int block_size; int n_blocks; };
+bool kv_pool_find(const float* key_cache, KvPool* out);
+KvPaged kv_paged_of(const KvPool& pool, int n_layers, int kv_dim, int layer);
 
 Workspace* workspace();   // for the current device (thread-safe)
 int ws_ensure_attn(Workspace* ws, size_t part_slots, int n_counters);

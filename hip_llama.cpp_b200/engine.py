@@ -226,18 +226,61 @@ def device_random_weights(cfg: Config, q8: bool = False, seed: int = 1337, devic
     return w
 
 
-class BatchState:
-    """Batched RunState: every buffer x B (src/models.cpp:155-179); KV [B][L][S][kv_dim] fp32."""
+class PagedKV:
+    """A block pool for the KV cache of `batch` slots (what BatchManager::create_pool builds in the C++ layer): K and V pools
+    [n_blocks][L][block_size][kv_dim] and a device table [batch][blocks per slot] of block ids, registered with the library
+    (tha_kv_pool_register).  The caller decides which block holds which positions of which slot (set_table)."""
 
-    def __init__(self, cfg: Config, batch: int, device="cuda", with_att=True):
+    def __init__(self, cfg: Config, batch: int, n_blocks: int, block_size: int = 16, device="cuda"):
+        self.cfg, self.B, self.n_blocks, self.block_size = cfg, batch, n_blocks, block_size
+        self.nrow = (cfg.seq_len + block_size - 1) // block_size
+        self.k = torch.zeros(n_blocks, cfg.n_layers, block_size, cfg.kv_dim, dtype=torch.float32, device=device)
+        self.v = torch.zeros_like(self.k)
+        self.table = torch.zeros(batch, self.nrow, dtype=torch.int32, device=device)
+        self.lib = cabi.lib()
+        self.lib.check(self.lib.c.tha_kv_pool_register(_ptr(self.k), _ptr(self.v), _ptr(self.table), self.nrow, block_size, n_blocks),
+                       "tha_kv_pool_register")
+
+    def set_table(self, rows):
+        self.table.copy_(torch.from_numpy(np.ascontiguousarray(rows, dtype=np.int32)).to(self.table.device))
+
+    def rows(self, which: str, slot: int, n: int) -> np.ndarray:
+        """Cache rows 0..n-1 of a slot, every layer, gathered through the table: [L, n, kv_dim]."""
+        pool = (self.k if which == "key_cache" else self.v).cpu().numpy()
+        tab = self.table[slot].cpu().numpy()
+        out = np.empty((self.cfg.n_layers, n, self.cfg.kv_dim), np.float32)
+        for t in range(n):
+            out[:, t] = pool[tab[t // self.block_size], :, t % self.block_size]
+        return out
+
+    def close(self):
+        if self.k is not None:
+            self.lib.c.tha_kv_pool_unregister(_ptr(self.k))
+            self.k = self.v = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class BatchState:
+    """Batched RunState: every buffer x B (src/models.cpp:155-179); KV [B][L][S][kv_dim] fp32, or a PagedKV pool."""
+
+    def __init__(self, cfg: Config, batch: int, device="cuda", with_att=True, paged: "PagedKV | None" = None):
         self.cfg, self.B = cfg, batch
         z = lambda *shape: torch.zeros(*shape, dtype=torch.float32, device=device)
         self.x, self.xb, self.xb2, self.q = z(batch, cfg.dim), z(batch, cfg.dim), z(batch, cfg.dim), z(batch, cfg.dim)
         self.hb, self.hb2 = z(batch, cfg.hidden_dim), z(batch, cfg.hidden_dim)
         self.att = z(batch, cfg.n_heads, cfg.seq_len) if with_att else None
         self.logits = z(batch, cfg.vocab_size)
-        self.key_cache = z(batch, cfg.n_layers, cfg.seq_len, cfg.kv_dim)
-        self.value_cache = z(batch, cfg.n_layers, cfg.seq_len, cfg.kv_dim)
+        self.paged = paged
+        if paged is not None:
+            self.key_cache, self.value_cache = paged.k, paged.v
+        else:
+            self.key_cache = z(batch, cfg.n_layers, cfg.seq_len, cfg.kv_dim)
+            self.value_cache = z(batch, cfg.n_layers, cfg.seq_len, cfg.kv_dim)
         self.c = cabi.State(_ptr(self.x), _ptr(self.xb), _ptr(self.xb2), _ptr(self.hb), _ptr(self.hb2), _ptr(self.q),
                             None, None, _ptr(self.att), _ptr(self.logits), _ptr(self.key_cache),
                             _ptr(self.value_cache), None, None, None, None)
@@ -246,14 +289,14 @@ class BatchState:
 class Engine:
     """One model replica on one GPU, B slots."""
 
-    def __init__(self, weights, batch: int, device="cuda", with_att=True):
+    def __init__(self, weights, batch: int, device="cuda", with_att=True, paged: "PagedKV | None" = None):
         self.lib = cabi.lib()
         self.w = weights
         self.cfg = weights.cfg
         self.q8 = isinstance(weights, DeviceWeightsQ8)
         self.bf16 = isinstance(weights, DeviceWeightsBF16)
         self.B = batch
-        self.state = BatchState(self.cfg, batch, device, with_att)
+        self.state = BatchState(self.cfg, batch, device, with_att, paged)
         self.ccfg = c_config(self.cfg)
         self.device = device
 

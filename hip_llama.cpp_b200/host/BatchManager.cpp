@@ -17,7 +17,82 @@ BatchManager::BatchManager(int batch_size_, int seq_len_, int n_layers_, int kv_
   mask_physical_KV_block.assign(batch_size, std::vector<bool>(nrow_blocks, false));
 }
 
-BatchManager::~BatchManager() {}
+BatchManager::~BatchManager() { destroy_pool(); }
+
+// ---- paged mode ---------------------------------------------------------------------------------
+bool BatchManager::create_pool(size_t n_blocks) {
+  destroy_pool();
+  const size_t blk_floats = (size_t)n_layers * block_size * kv_dim;
+  if (n_blocks < 1) return false;
+  if (tha_malloc((void**)&pool_k_, n_blocks * blk_floats * sizeof(float)) != 0) { pool_k_ = nullptr; return false; }
+  if (tha_malloc((void**)&pool_v_, n_blocks * blk_floats * sizeof(float)) != 0) { tha_free(pool_k_); pool_k_ = pool_v_ = nullptr; return false; }
+  if (tha_malloc((void**)&table_d_, (size_t)batch_size * nrow_blocks * sizeof(int)) != 0) {
+    tha_free(pool_k_); tha_free(pool_v_); pool_k_ = pool_v_ = nullptr; table_d_ = nullptr;
+    return false;
+  }
+  tha_memset(pool_k_, 0, n_blocks * blk_floats * sizeof(float));
+  tha_memset(pool_v_, 0, n_blocks * blk_floats * sizeof(float));
+  tha_memset(table_d_, 0, (size_t)batch_size * nrow_blocks * sizeof(int));
+  pool_blocks_ = n_blocks;
+  num_physical_blocks = n_blocks;
+  cur_physical_blocks = 0;
+  table_h_.assign((size_t)batch_size * nrow_blocks, 0);
+  dirty_.assign(batch_size, 0);
+  free_list_.clear();
+  for (size_t b = n_blocks; b-- > 0;) free_list_.push_back((int)b);   // block 0 is handed out first
+  for (auto& m : mask_physical_KV_block) std::fill(m.begin(), m.end(), false);
+  std::fill(n_block_table_filled.begin(), n_block_table_filled.end(), 0);
+  logicId_physicAddr_mapper.clear();
+  gpu_physical_KV_blocks = pool_k_;
+  gpu_physical_V_blocks = pool_v_;
+  if (tha_kv_pool_register(pool_k_, pool_v_, table_d_, nrow_blocks, block_size, (int)n_blocks) != 0) { destroy_pool(); return false; }
+  return true;
+}
+
+void BatchManager::destroy_pool() {
+  if (!pool_blocks_) return;
+  tha_kv_pool_unregister(pool_k_);
+  if (bound_ && bound_->key_cache == pool_k_) { bound_->key_cache = nullptr; bound_->value_cache = nullptr; }
+  tha_free(pool_k_); tha_free(pool_v_); tha_free(table_d_);
+  pool_k_ = pool_v_ = nullptr; table_d_ = nullptr;
+  pool_blocks_ = 0;
+  free_list_.clear();
+}
+
+void BatchManager::bind_paged(RunState* s_d) {
+  bound_ = s_d;
+  if (s_d) { s_d->key_cache = pool_k_; s_d->value_cache = pool_v_; }
+}
+
+bool BatchManager::ensure_position(int seq_id, int pos) {
+  if (!paged()) { return true; }
+  const int need = pos / block_size;
+  for (int rb = 0; rb <= need && rb < nrow_blocks; rb++) {
+    if (mask_physical_KV_block[seq_id][rb]) continue;
+    if (free_list_.empty()) return false;
+    const int id = free_list_.back();
+    free_list_.pop_back();
+    mask_physical_KV_block[seq_id][rb] = true;
+    n_block_table_filled[seq_id]++;
+    cur_physical_blocks++;
+    table_h_[(size_t)seq_id * nrow_blocks + rb] = id;
+    dirty_[seq_id] = 1;
+    KVBlock blk;
+    blk.addr = pool_k_ + (size_t)id * n_layers * block_size * kv_dim;
+    blk.occupied = 1;
+    logicId_physicAddr_mapper[(size_t)id] = blk;
+  }
+  return true;
+}
+
+void BatchManager::sync_table(void* stream) {
+  if (!paged()) return;
+  for (int s = 0; s < batch_size; s++)
+    if (dirty_[s]) {
+      tha_memcpy_async(table_d_ + (size_t)s * nrow_blocks, table_h_.data() + (size_t)s * nrow_blocks, (size_t)nrow_blocks * sizeof(int), stream);
+      dirty_[s] = 0;
+    }
+}
 
 size_t BatchManager::block_bytes() const {
   return (size_t)2 * n_layers * block_size * kv_dim * sizeof(float);  // K and V rows of every layer
@@ -69,6 +144,7 @@ int BatchManager::active_slots() const {
 // block id = slot * nrow_blocks + row block: the slab is batch-major, so a slot's blocks are
 // its own rows; "allocation" is bookkeeping that bounds the live footprint.
 void BatchManager::get_KV_Block(int seq_id) {
+  if (paged()) { ensure_position(seq_id, logical_KV_table[seq_id].second); return; }
   const int filled = logical_KV_table[seq_id].second;
   const int rb = filled / block_size;
   if (rb < nrow_blocks && !mask_physical_KV_block[seq_id][rb]) {
@@ -135,6 +211,18 @@ void BatchManager::push_kv_data_to_kv_cache(thablasHandle_t* handle, std::vector
 }
 
 void BatchManager::dealloc_gpu_block(int seq_id) {
+  if (paged()) {   // the slot's blocks go back to the free list (the table row keeps its stale ids: nothing reads past pos)
+    for (int rb = 0; rb < nrow_blocks; rb++)
+      if (mask_physical_KV_block[seq_id][rb]) {
+        mask_physical_KV_block[seq_id][rb] = false;
+        const int id = table_h_[(size_t)seq_id * nrow_blocks + rb];
+        free_list_.push_back(id);
+        logicId_physicAddr_mapper.erase((size_t)id);
+        cur_physical_blocks--;
+      }
+    n_block_table_filled[seq_id] = 0;
+    return;
+  }
   for (int rb = 0; rb < nrow_blocks; rb++)
     if (mask_physical_KV_block[seq_id][rb]) {
       mask_physical_KV_block[seq_id][rb] = false;

@@ -110,8 +110,28 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
     load_s = (time_in_ms() - t_load0) / 1000.0;
     fprintf(stdout, "\nLoad model time thread %d: %f\n", gid, load_s);
 
+    const int kvd = cfg.dim * cfg.n_kv_heads / cfg.n_heads;
+    BatchManager bm(B, cfg.seq_len, cfg.n_layers, kvd);
     RunState* s_d = nullptr;
-    alloc_state_to_device_batch_cfg(&cfg, s_d, B, tha_step_needs_att_scratch((const tha_config_t*)&cfg));
+    // opt.kv_blocks != 0: PAGED KV cache -- the slots share a pool of blocks of 16 positions (K and V rows of all layers)
+    // handed out as sequences grow and returned when a request finishes, instead of B slabs of seq_len positions each
+    const bool paged = opt.kv_blocks != 0;
+    if (paged) {
+      alloc_state_to_device_batch_paged(&cfg, s_d, B, 0);
+      size_t n_blocks = opt.kv_blocks > 0 ? (size_t)opt.kv_blocks : (size_t)B * bm.nrow_blocks;
+      if (opt.kv_blocks < 0) {   // auto: what fits in 80 % of the free memory, at most one full context per slot
+        const size_t fit = (size_t)(0.8 * (double)bm.get_gpu_memory(gid)) / bm.block_bytes();
+        if (fit < n_blocks) n_blocks = fit;
+      }
+      if (!bm.create_pool(n_blocks)) { fprintf(stderr, "cannot allocate a KV pool of %zu blocks: %s\n", n_blocks, tha_last_error()); exit(EXIT_FAILURE); }
+      bm.bind_paged(s_d);
+      fprintf(stdout, "paged KV cache: %zu blocks of %d positions (%.1f MB) for %d slots\n", n_blocks, bm.block_size,
+              n_blocks * bm.block_bytes() / 1e6, B);
+    } else {
+      alloc_state_to_device_batch_cfg(&cfg, s_d, B, tha_step_needs_att_scratch((const tha_config_t*)&cfg));
+      bm.bind(s_d);
+    }
+    int pending_req = -1;   // paged: a request that did not fit the pool yet
     // temperature != 0: softmax / top-p / coin run on the device (tha_forward_sample_*, csrc/sampler.cu), one xorshift*
     // stream per request as in the reference (src/llama.cpp:895-900); opt.host_sampler = 1 keeps the reference's scheme
     // (B * vocab logits to pinned host memory, sample() on the host cores)
@@ -121,9 +141,6 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
     std::vector<int> force(B, -1);
     std::vector<unsigned long long> reseed(B, 0ull);
 
-    const int kvd = cfg.dim * cfg.n_kv_heads / cfg.n_heads;
-    BatchManager bm(B, cfg.seq_len, cfg.n_layers, kvd);
-    bm.bind(s_d);
     std::vector<Slot> slots(B);
     std::vector<int> token(B, 0), pos(B, -1), next(B, 0);
     Config cfg_local = cfg;
@@ -138,16 +155,31 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
       pf_slot.clear(); pf_pos0.clear(); pf_len.clear(); pf_tokens.clear();
       for (int s = 0; s < B && !queue_empty; s++) {
         if (bm.request_of(s) >= 0) continue;
-        const int req = next_idx.fetch_add(opt.device_stride);
+        const int req = pending_req >= 0 ? pending_req : next_idx.fetch_add(opt.device_stride);
+        pending_req = -1;
         if (req >= requests->num_reqs) { queue_empty = true; break; }
+        const std::string& prompt = requests->str_reqs[req];
+        std::vector<int> ptoks(prompt.size() + 3, 0);
+        int n_prompt = 0;
+        encode(&tok, prompt.c_str(), 1, 0, ptoks.data(), &n_prompt);
+        if (n_prompt < 1) { fprintf(stderr, "something is wrong, expected at least 1 prompt token\n"); exit(EXIT_FAILURE); }
+        if (paged) {
+          // admission control: a request enters only if the pool can still hold every admitted request grown to its
+          // position limit -- a running sequence then never finds the pool empty
+          int limit = requests->max_seq_len;
+          if (opt.max_new_positions > 0 && opt.max_new_positions < limit) limit = opt.max_new_positions;
+          size_t reserved = 0;
+          for (int t = 0; t < B; t++)
+            if (bm.request_of(t) >= 0) reserved += bm.blocks_for(slots[t].steps) - (size_t)bm.n_block_table_filled[t];
+          if (bm.free_blocks() < reserved + bm.blocks_for(limit)) {
+            if (bm.active_slots() == 0) { fprintf(stderr, "KV pool too small for one request of %d positions\n", limit); exit(EXIT_FAILURE); }
+            pending_req = req;   // wait for a finishing request
+            break;
+          }
+        }
         const int got = bm.acquire_slot(req);   // lowest free slot == s
         Slot& sl = slots[got];
-        const std::string& prompt = requests->str_reqs[req];
-        sl.prompt.assign(prompt.size() + 3, 0);
-        int n_prompt = 0;
-        encode(&tok, prompt.c_str(), 1, 0, sl.prompt.data(), &n_prompt);
-        if (n_prompt < 1) { fprintf(stderr, "something is wrong, expected at least 1 prompt token\n"); exit(EXIT_FAILURE); }
-        sl.prompt.resize(n_prompt);
+        sl.prompt.assign(ptoks.begin(), ptoks.begin() + n_prompt);
         sl.text.clear();
         sl.ids.assign(1, sl.prompt[0]);
         sl.steps = requests->max_seq_len;
@@ -161,6 +193,7 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
         int m = use_prefill ? n_prompt - 1 : 0;
         if (m > sl.steps - 1) m = sl.steps - 1;
         if (m >= 1) {
+          if (!bm.ensure_position(got, m - 1)) { fprintf(stderr, "KV pool exhausted\n"); exit(EXIT_FAILURE); }
           pf_slot.push_back(got); pf_pos0.push_back(0); pf_len.push_back(m);
           pf_tokens.insert(pf_tokens.end(), sl.prompt.begin(), sl.prompt.begin() + m);
           for (int j = 1; j <= m; j++) {
@@ -173,7 +206,18 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
         }
         if (opt.verbose) fprintf(stderr, "\nDevice %d - seq id %d in batch, Request %d\n", gid, got, req);
       }
-      if (bm.active_slots() == 0) break;
+      if (bm.active_slots() == 0) {
+        if (pending_req >= 0) continue;   // cannot happen (checked above), kept for clarity
+        break;
+      }
+      if (paged) {   // the block that receives this step's K/V row of every active slot exists before the step runs
+        for (int s = 0; s < B; s++)
+          if (bm.request_of(s) >= 0 && !bm.ensure_position(s, pos[s])) {
+            fprintf(stderr, "KV pool exhausted (%zu blocks): raise -c or lower -b\n", bm.num_physical_blocks);
+            exit(EXIT_FAILURE);
+          }
+        bm.sync_table((void*)handle.calc_stream);
+      }
       if (!pf_slot.empty()) {
         if (t32)
           CHECK_THA(tha_prefill_f32((void*)handle.calc_stream, (const tha_config_t*)&cfg_local, (const tha_weights_f32_t*)w_d,
@@ -246,6 +290,7 @@ int run_data_parallel(Transformer* t32, TransformerQ8* tq8, const char* tokenize
     loop_s = (time_in_ms() - t_loop0) / 1000.0;
 
     if (logits_host) tha_host_free(logits_host);
+    bm.destroy_pool();   // paged: the pools are the BatchManager's (s_d's cache pointers are cleared with them)
     free_state_on_device(s_d);
     if (w_d) free_weight_on_device(w_d, w_d->wcls == w_d->token_embedding_table);
     if (wq_d) free_weight_on_device_q8(wq_d, 1);

@@ -77,6 +77,20 @@ void alloc_state_to_device_batch_cfg(const Config* p, RunState*& s, int batch_si
   CHECK_THA(tha_memset(s->value_cache, 0, B * L * S * kvd * sizeof(float)));
 }
 
+// State for a PAGED KV cache: every activation buffer, no K/V slabs (BatchManager::create_pool + bind_paged supply them).
+void alloc_state_to_device_batch_paged(const Config* p, RunState*& s, int batch_size, int with_att) {
+  const size_t B = batch_size, dim = p->dim, vocab = p->vocab_size, hid = p->hidden_dim, S = p->seq_len, H = p->n_heads;
+  s = (RunState*)calloc(1, sizeof(RunState));
+  s->x = dalloc(B * dim);
+  s->xb = dalloc(B * dim);
+  s->xb2 = dalloc(B * dim);
+  s->hb = dalloc(B * hid);
+  s->hb2 = dalloc(B * hid);
+  s->q = dalloc(B * dim);
+  s->att = with_att ? dalloc(B * H * S) : nullptr;
+  s->logits = dalloc(B * vocab);
+}
+
 void alloc_state_to_device_batch(Transformer* t_h, RunState*& s_d_batch, int batch_size) {
   alloc_state_to_device_batch_cfg(&t_h->config, s_d_batch, batch_size, 1);
 }

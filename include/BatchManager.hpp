@@ -11,6 +11,12 @@
 //     live KV footprint and admission control can refuse a request that would not fit;
 //   * the slot table (which request sits in which slot, at which position) is the state the
 //     driver loop of src/llama.cpp:968-1073 keeps in local arrays.
+// PAGED mode (create_pool): the blocks are real.  K and V live in two device pools
+// [n_blocks][n_layers][block_size][kv_dim]; a slot's positions are found through a row of block ids in a
+// device-resident table that the attention / RoPE-scatter kernels read (tha_kv_pool_register); a block is taken
+// from the free list when a sequence reaches it and returned when its request finishes, so B slots share a pool
+// sized for the positions actually in flight instead of B x seq_len (Llama-2-7B fp32 KV: 2.1 GB per 2048
+// positions).
 #pragma once
 #include <stddef.h>
 
@@ -65,6 +71,24 @@ class BatchManager {
   void push_kv_data_to_kv_cache(thablasHandle_t* handle, std::vector<size_t> kv_cache_block_ids, float* data);
   void dealloc_gpu_block(int seq_id);
 
+  // ---- paged mode ------------------------------------------------------------------------------
+  bool create_pool(size_t n_blocks);              // allocate the pools and the device table (current device); false: no memory
+  void destroy_pool();
+  void bind_paged(RunState* s_d);                 // point s_d->key_cache / value_cache at the pools (the state must not own slabs)
+  bool paged() const { return pool_blocks_ > 0; }
+  size_t free_blocks() const { return free_list_.size(); }
+  size_t blocks_for(int positions) const { return ((size_t)positions + block_size - 1) / block_size; }
+  bool ensure_position(int seq_id, int pos);      // the blocks covering positions 0..pos exist (false: pool exhausted)
+  void sync_table(void* stream);                  // upload table rows that changed since the last call (stream-ordered)
+  const int* host_table() const { return table_h_.data(); }
+
  private:
   RunState* bound_;
+  size_t pool_blocks_ = 0;
+  float* pool_k_ = nullptr;
+  float* pool_v_ = nullptr;
+  int* table_d_ = nullptr;
+  std::vector<int> table_h_;                      // [batch_size][nrow_blocks]
+  std::vector<int> free_list_;
+  std::vector<char> dirty_;                       // per slot
 };

@@ -76,6 +76,8 @@ struct DriverOptions {
                                // one forced-prompt decode step per token (src/llama.cpp:1029-1030); 0 = the reference's scheme
   int tp = 1;                  // > 1: ONE replica split tensor-parallel over `tp` ranks (app flag -w); rank r runs on device r % n_devices,
                                // all ranks are driven by one host thread; greedy decode only (temperature 0), prompts fed token by token
+  int kv_blocks = 0;           // 0: dense KV slabs [B][L][seq_len][kv_dim] as the reference; > 0: PAGED cache, the B slots share this many
+                               // blocks of 16 positions (BatchManager::create_pool); -1: as many as fit in 80 % of the free memory
   int host_sampler = 0;        // temperature != 0: 1 = the reference's scheme (B * vocab logits to the host, sample() on the host cores);
                                // 0 = softmax / top-p / coin on the device (tha_forward_sample_*), B token ids back per step
   int verbose = 0;

@@ -112,6 +112,8 @@ void alloc_state_to_device_batch_noatt(Transformer* t_h, RunState*& s_d_batch, i
 void copy_weight_to_device_q8(TransformerQ8* t_h, TransformerWeightsQ8*& w_d);
 void free_weight_on_device_q8(TransformerWeightsQ8* w_d, int shared_classifier);
 void alloc_state_to_device_batch_cfg(const Config* cfg, RunState*& s_d_batch, int batch_size, int with_att);
+// activation buffers only: the K/V rows live in a BatchManager block pool (BatchManager::create_pool / bind_paged)
+void alloc_state_to_device_batch_paged(const Config* cfg, RunState*& s_d_batch, int batch_size, int with_att);
 // Tensor-parallel shards (B200 addition): rows of wq/wk/wv/w1/w3, columns of wo/w2, everything
 // else replicated.  Hidden units are dealt in whole groups of `unit` (the Q8_0 group size; 64 for fp32 models).
 int tp_split_hidden(int hidden, int tp, int unit, int* hidden_of_rank);

@@ -253,6 +253,17 @@ int tha_forward_sample_bf16(void* stream, int n_batches, const tha_config_t* cfg
 int tha_prefill_bf16(void* stream, const tha_config_t* cfg, const tha_weights_bf16_t* w, const tha_state_t* s, int n_seqs,
                      const int* slot_host, const int* pos0_host, const int* len_host, const int* tokens_host,
                      float* logits_d, int* next_d);
+/* Paged KV cache (fills in include/BatchManager.hpp:11-52 of the reference, whose alloc_new_block /
+ * convert_block_ids_to_block_addrs / push_kv_data_to_kv_cache are stubs).  key_pool / value_pool: device arrays
+ * [n_blocks][n_layers][block_size][kv_dim] fp32 owned by the caller; block_table_d: device array [slots][table_stride] of
+ * block ids, row s listing in order the blocks that hold slot s's positions (block_size, a power of two, positions each).
+ * After registration a tha_state_t whose key_cache == key_pool and value_cache == value_pool is PAGED: the attention,
+ * prefill-attention and RoPE/scatter kernels find every cache row through the table (read at run time: update it,
+ * stream-ordered, before the step that first touches a new block).  Paged states run the tensor-core row pipeline at
+ * every batch size (fp32, Q8_0, bf16; decode and prefill). */
+int tha_kv_pool_register(float* key_pool, float* value_pool, const int* block_table_d, int table_stride, int block_size,
+                         int n_blocks);
+int tha_kv_pool_unregister(float* key_pool);
 /* greedy sampler on the device: next[b] = first argmax of logits[b, :] */
 int tha_argmax_batch_f32(void* stream, int n_batches, const float* logits, int vocab, int* next_d);
 /* greedy bookkeeping of the batching driver (src/llama.cpp:1027-1050) kept on the device:
