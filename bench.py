@@ -522,8 +522,9 @@ def extra_records(args, device, peak):
         c = cfg
         dw.cfg = c
         paged = eng.PagedKV(c, 64, n_blocks=64 * 8)
-        tab = np.arange(64 * paged.nrow, dtype=np.int32).reshape(64, paged.nrow) % (64 * 8)
-        paged.set_table((tab * 37) % (64 * 8))          # scattered, collision-free for the first 8 blocks of every slot
+        tab = np.zeros((64, paged.nrow), np.int32)
+        tab[:, :8] = ((np.arange(64)[:, None] * 8 + np.arange(8)[None, :]) * 37) % (64 * 8)   # scattered over the pool, one owner per block
+        paged.set_table(tab)
         e = eng.Engine(dw, 64, device=device, with_att=False, paged=paged)
         v, ms = resident_tok_s(e, c, 64, 4, 12, device)
         out["7b_q8_B64_paged_seq2048"] = {"workload": "Llama-2-7B Q8_0, 64 slots, context 2048, PAGED KV cache (512 blocks of 16 positions = 8.6 GB "
