@@ -575,6 +575,52 @@ def extra_records(args, device, peak):
         free()
     except Exception as ex:
         out["prefill_7b_f32_2048"] = {"error": str(ex)}
+    try:   # configs[3], bf16: prompt of 2048 positions (tensor-core matmuls AND attention), decode at 1 and 64 slots
+        cfg = dataclasses.replace(ck.LLAMA2_7B, seq_len=2304)
+        dw = eng.DeviceWeightsBF16.random(cfg, seed=1337, device=device)
+        e = eng.Engine(dw, 1, device=device, with_att=False)
+        rng = np.random.default_rng(0)
+        T = 2048
+        seqs = [(0, 0, rng.integers(3, cfg.vocab_size, size=T).astype(np.int32))]
+        st = torch.cuda.Stream()
+        logits = torch.zeros(1, cfg.vocab_size, device=device)
+        nxt = torch.zeros(1, dtype=torch.int32, device=device)
+        with torch.cuda.stream(st):
+            e.prefill(seqs, logits, nxt, stream=st)
+            st.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            reps = 3
+            for _ in range(reps):
+                e.prefill(seqs, logits, nxt, stream=st)
+            e1.record(st)
+            st.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        d, h, L, kvd = cfg.dim, cfg.hidden_dim, cfg.n_layers, cfg.kv_dim
+        flops = 2.0 * T * L * (2 * d * d + 2 * d * kvd + 3 * d * h) + 2.0 * L * T * T * d + 2.0 * cfg.vocab_size * d
+        try:
+            tf_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"])
+        except Exception:
+            tf_peak = 1381.0
+        out["prefill_7b_bf16_2048"] = {"workload": "Llama-2-7B bf16, one prompt of 2048 positions through tha_prefill_bf16 (tcgen05 kind::f16 matmuls "
+                                                   "and prompt attention)", "ms": ms, "prompt_tok_per_s": T / ms * 1e3,
+                                       "useful_tflops": flops / ms / 1e9, "tensor_frac_of_sustained_bf16": flops / ms / 1e9 / tf_peak}
+        v, msd = resident_tok_s(e, cfg, 1, 2, 8, device, pos0=T)
+        nb = step_bytes(cfg, dw.nbytes(), T + 5, 1, elem_bytes_emb=2)
+        out["decode_7b_bf16_B1_after_prefill"] = {"workload": "Llama-2-7B bf16 greedy decode, 1 slot, positions 2050..2057", "value": v, "unit": UNIT,
+                                                  "ms_per_step": msd, "achieved_gbs": nb / msd / 1e6, "hbm_frac": nb / msd / 1e6 / peak}
+        del e
+        c64 = dataclasses.replace(ck.LLAMA2_7B, seq_len=512)
+        dw.cfg = c64
+        e = eng.Engine(dw, 64, device=device, with_att=False)
+        v, msd = resident_tok_s(e, c64, 64, 4, 12, device)
+        nb = sum(step_bytes(c64, dw.nbytes(), p_, 64, elem_bytes_emb=2) for p_ in range(4, 16)) / 12
+        out["7b_bf16_B64"] = {"workload": "Llama-2-7B bf16 batched greedy decode, 64 slots, positions 4..15, KV slab of 512 positions", "value": v,
+                              "unit": UNIT, "ms_per_step": msd, "achieved_gbs": nb / msd / 1e6, "hbm_frac": nb / msd / 1e6 / peak}
+        del e, dw
+        free()
+    except Exception as ex:
+        out["prefill_7b_bf16_2048"] = {"error": str(ex)}
     return out
 
 

@@ -10,6 +10,8 @@
 //   prep  x += partials | embedding row; RMSNorm in the reference's order g * (ss * x); round -> bf16 row
 //   gemm  wq|wk|wv -> partials;  rope_scatter (step_tc.cu);  attention (fp32);  round -> bf16
 //   gemm  wo -> partials;  prep(ffn);  gemm w1|w3;  SwiGLU + round;  gemm w2 -> partials;  ... prep(final); gemm wcls
+#include <stdlib.h>
+
 #include <map>
 #include <mutex>
 #include <vector>
@@ -33,6 +35,10 @@ int attn_prefill_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_
                         float* out, float* out_hi, float* out_lo, const float* kc, const float* vc,
                         long long kv_batch_stride, const int* row_slot, const int* row_pos, const int* tile_row0,
                         const int* tile_n, bool pdl, const KvPaged* pg = nullptr);
+bool attn_prefill_tc_supported(int head_size, int kv_dim);
+int attn_prefill_tc_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_heads, int head_size, const float* q, float* out,
+                           uint16_t* out_b16, const float* kc, const float* vc, long long kv_batch_stride, const int* row_slot,
+                           const int* row_pos, const int* tile_row0, const int* tile_n, bool pdl, const KvPaged* pg);
 int rope_scatter_launch(cudaStream_t st, bool pdl, int R, const float* part, int nz, long long zstride, int ld, const int* pos, int d,
                         int kvd, int hs, const float* rc, const float* rs, float* q, float* kc, float* vc, long long kv_bs, int loff,
                         const int* slot, const KvPaged* pg = nullptr);
@@ -116,28 +122,33 @@ __global__ void __launch_bounds__(256) bf_round_kernel(const float* __restrict__
   pdl_wait();
   pdl_trigger();
   const int b = blockIdx.y;
-  const int i4 = blockIdx.x * blockDim.x + threadIdx.x;
-  if (4 * i4 >= K) return;
-  float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (pos[b] >= 0) {
-    if (h > 0) {
-      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), c = a;
+  const bool idle = pos[b] < 0;
+  // two float4 per thread, a block-width apart: both (pairs of) loads are in flight before the first exponential
+#pragma unroll
+  for (int u = 0; u < 2; u++) {
+    const int i4 = (blockIdx.x * 2 + u) * blockDim.x + threadIdx.x;
+    if (4 * i4 >= K) continue;
+    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!idle) {
+      if (h > 0) {
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), c = a;
 #pragma unroll 8
-      for (int z = 0; z < nz; z++) {
-        const float4 pa = *reinterpret_cast<const float4*>(src + (size_t)z * zstride + (size_t)b * ld + 4 * i4);
-        const float4 pc = *reinterpret_cast<const float4*>(src + (size_t)z * zstride + (size_t)b * ld + h + 4 * i4);
-        a.x += pa.x; a.y += pa.y; a.z += pa.z; a.w += pa.w;
-        c.x += pc.x; c.y += pc.y; c.z += pc.z; c.w += pc.w;
+        for (int z = 0; z < nz; z++) {
+          const float4 pa = *reinterpret_cast<const float4*>(src + (size_t)z * zstride + (size_t)b * ld + 4 * i4);
+          const float4 pc = *reinterpret_cast<const float4*>(src + (size_t)z * zstride + (size_t)b * ld + h + 4 * i4);
+          a.x += pa.x; a.y += pa.y; a.z += pa.z; a.w += pa.w;
+          c.x += pc.x; c.y += pc.y; c.z += pc.z; c.w += pc.w;
+        }
+        r.x = a.x * (1.0f / (1.0f + expf(-a.x))); r.x *= c.x;
+        r.y = a.y * (1.0f / (1.0f + expf(-a.y))); r.y *= c.y;
+        r.z = a.z * (1.0f / (1.0f + expf(-a.z))); r.z *= c.z;
+        r.w = a.w * (1.0f / (1.0f + expf(-a.w))); r.w *= c.w;
+      } else {
+        r = *reinterpret_cast<const float4*>(src + (size_t)b * ld + 4 * i4);
       }
-      r.x = a.x * (1.0f / (1.0f + expf(-a.x))); r.x *= c.x;
-      r.y = a.y * (1.0f / (1.0f + expf(-a.y))); r.y *= c.y;
-      r.z = a.z * (1.0f / (1.0f + expf(-a.z))); r.z *= c.z;
-      r.w = a.w * (1.0f / (1.0f + expf(-a.w))); r.w *= c.w;
-    } else {
-      r = *reinterpret_cast<const float4*>(src + (size_t)b * ld + 4 * i4);
     }
+    reinterpret_cast<uint2*>(out + (size_t)b * K)[i4] = pack4_bf16(r);
   }
-  reinterpret_cast<uint2*>(out + (size_t)b * K)[i4] = pack4_bf16(r);
 }
 
 // x[b] = embedding row of token[b] (bf16 table -> fp32 residual stream); idle slots untouched.  grid (B), the GEMV step's first kernel
@@ -251,10 +262,12 @@ struct BfRows {
   int R;
   float *x, *q, *xb;
   const int *token, *pos, *slot;
-  int n_tiles; const int *tile_row0, *tile_n;
+  int n_tiles; const int *tile_row0, *tile_n; int tile_rows;   // prefill attention tiles (rows per tile: 64 CUDA cores, 128 tensor cores)
   int n_out; const int* out_rows;
   float* logits; int* next;
 };
+
+static int bf_attn_tc = -1;   // THA_ATTN_TC=0: keep the CUDA-core prefill attention (development aid)
 
 static int bf_issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_bf16_t& w, const tha_state_t& s,
                          const BfRows& io, const float* rc, const float* rs, bool pdl) {
@@ -270,6 +283,9 @@ static int bf_issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, 
   int prep_threads = ceil_div(d / 4, 32) * 32;
   if (prep_threads > 1024) prep_threads = 1024;
   if (prep_threads < 128) prep_threads = 128;
+  // many rows (prompt ingestion): 256 threads with up to four float4 each -- eight CTAs per SM and four independent loads per
+  // thread hide the L2 latency that a 1024-thread CTA per row (lowest latency for a handful of decode rows) leaves exposed
+  if (R >= 512 && d / 4 <= 256 * BPREP_MAX_V && prep_threads > 256) prep_threads = 256;
   const int* nogather = nullptr;
   auto prep = [&](int rows, int nz, long long zs, const uint16_t* emb, const float* gain, const int* gather) -> int {
     THA_CUDA_OK(launch(bf_prep_kernel, dim3(rows), dim3(prep_threads), 0, st, pdl, io.x, (const float*)sc.part, nz, zs, emb, io.token,
@@ -303,14 +319,21 @@ static int bf_issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, 
     THA_TRY_RC(rope_scatter_launch(st, pdl, R, sc.part, pl.z_qkv, (long long)R * ld_qkv, ld_qkv, io.pos, d, kvd, hs, rc, rs, io.q,
                                    s.key_cache, s.value_cache, kv_bs, loff, io.slot, &pg));
     if (!io.logits && l == L - 1) return THA_STATUS_SUCCESS;   // cache-only ingestion: the last layer's K/V rows are in place
-    if (io.n_tiles > 0)
+    bool rounded = false;   // the attention kernel already left its output as bf16 rows in sc.xb
+    if (io.n_tiles > 0 && io.tile_rows == 128) {
+      // prompt rows, head size 64 / 128: Q K^T and P V on the tensor cores (attn_prefill_tc.cu)
+      THA_TRY_RC(attn_prefill_tc_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, sc.xb, kcl, vcl, kv_bs, io.slot, io.pos,
+                                        io.tile_row0, io.tile_n, pdl, &pg));
+      rounded = true;
+    } else if (io.n_tiles > 0)
       THA_TRY_RC(attn_prefill_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, nullptr, nullptr, kcl,
                                      vcl, kv_bs, io.slot, io.pos, io.tile_row0, io.tile_n, pdl, &pg));
     else
       THA_TRY_RC(attn_fused_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, kcl, vcl,
                                    kv_bs, hs, c.seq_len, pdl, nullptr, nullptr, nullptr, nullptr, 0, 0, &pg));
-    THA_CUDA_OK(launch(bf_round_kernel, dim3(ceil_div(d / 4, 256), R), dim3(256), 0, st, pdl, (const float*)io.xb, (long long)d, 0, 0LL, 0,
-                       io.pos, d, sc.xb));
+    if (!rounded)
+      THA_CUDA_OK(launch(bf_round_kernel, dim3(ceil_div(d / 4, 512), R), dim3(256), 0, st, pdl, (const float*)io.xb, (long long)d, 0, 0LL, 0,
+                         io.pos, d, sc.xb));
     {
       const uint16_t* W[1] = {w.wo + (size_t)l * d * d};
       const int M[1] = {d}, off[1] = {0};
@@ -322,7 +345,7 @@ static int bf_issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, 
       const int M[2] = {hd, hd}, off[2] = {0, hd};
       THA_TRY_RC(mm(2, W, M, off, d, sc.xb, R, sc.part, ld_h, (long long)R * ld_h, pl.z_w13));
     }
-    THA_CUDA_OK(launch(bf_round_kernel, dim3(ceil_div(hd / 4, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part, (long long)ld_h, pl.z_w13,
+    THA_CUDA_OK(launch(bf_round_kernel, dim3(ceil_div(hd / 4, 512), R), dim3(256), 0, st, pdl, (const float*)sc.part, (long long)ld_h, pl.z_w13,
                        (long long)R * ld_h, hd, io.pos, hd, sc.hb));
     {
       const uint16_t* W[1] = {w.w2 + (size_t)l * d * hd};
@@ -355,18 +378,20 @@ int step_bf16_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
                       const float* rc, const float* rs) {
   const int hs = c.dim / c.n_heads;
   if (!step_bf16_supported(&c) || !attn_prefill_supported(hs, hs * c.n_kv_heads)) return THA_STATUS_NOT_SUPPORTED;
+  if (bf_attn_tc < 0) { const char* v = getenv("THA_ATTN_TC"); bf_attn_tc = (v && *v) ? atoi(v) : 1; }
+  const int TQ = (bf_attn_tc && attn_prefill_tc_supported(hs, hs * c.n_kv_heads)) ? 128 : 64;   // query rows per attention tile
   long long R = 0, T = 0;
   for (int i = 0; i < n_seqs; i++) {
     if (len[i] < 1 || pos0[i] < 0 || slot[i] < 0 || (long long)pos0[i] + len[i] > c.seq_len) return THA_STATUS_INVALID_ARG;
     R += len[i];
-    T += ceil_div(len[i], 64);
+    T += ceil_div(len[i], TQ);
   }
   if (R < 1 || R > (1 << 20)) return THA_STATUS_INVALID_ARG;
   std::vector<int> tab((size_t)3 * R + 2 * T + n_seqs);
   int *h_slot = tab.data(), *h_pos = h_slot + R, *h_tok = h_pos + R, *h_t0 = h_tok + R, *h_tn = h_t0 + T, *h_last = h_tn + T;
   int r = 0, t = 0;
   for (int i = 0; i < n_seqs; i++) {
-    for (int j = 0; j < len[i]; j += 64) { h_t0[t] = r + j; h_tn[t] = (len[i] - j < 64) ? len[i] - j : 64; t++; }
+    for (int j = 0; j < len[i]; j += TQ) { h_t0[t] = r + j; h_tn[t] = (len[i] - j < TQ) ? len[i] - j : TQ; t++; }
     for (int j = 0; j < len[i]; j++, r++) {
       h_slot[r] = slot[i]; h_pos[r] = pos0[i] + j; h_tok[r] = tokens[r];
       if (tokens[r] < 0 || tokens[r] >= c.vocab_size) return THA_STATUS_INVALID_ARG;
@@ -383,7 +408,7 @@ int step_bf16_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
   BfRows io = {};
   io.R = (int)R; io.x = sc.xr; io.q = sc.qr; io.xb = sc.xbr;
   io.slot = sc.tab; io.pos = sc.tab + R; io.token = sc.tab + 2 * R;
-  io.n_tiles = (int)T; io.tile_row0 = sc.tab + 3 * R; io.tile_n = sc.tab + 3 * R + T;
+  io.n_tiles = (int)T; io.tile_row0 = sc.tab + 3 * R; io.tile_n = sc.tab + 3 * R + T; io.tile_rows = TQ;
   io.n_out = n_seqs; io.out_rows = sc.tab + 3 * R + 2 * T; io.logits = logits; io.next = logits ? next_d : nullptr;
   return bf_issue_rows(st, ws, c, w, s, io, rc, rs, pdl_enabled() != 0);
 }

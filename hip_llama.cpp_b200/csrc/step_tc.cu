@@ -152,7 +152,8 @@ __global__ void __launch_bounds__(1024) tc_prep_kernel(float* __restrict__ x, co
 }
 
 // q|k|v rows of every slot (sum of nz partials): RoPE on q and k pairs (run.cc:271-286 with the host-built
-// cos/sin tables), q -> state, k/v -> the cache row of pos[b].  grid (pairs / 256, B).
+// cos/sin tables), q -> state, k/v -> the cache row of pos[b].  A thread takes TWO pairs a block-width apart (two
+// independent chains of loads).  grid (pairs / 512, B).
 __global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __restrict__ part, int nz, long long zstride,
                                                               int ld, const int* __restrict__ pos, int d, int kvd, int hs,
                                                               const float* __restrict__ rc, const float* __restrict__ rs,
@@ -166,31 +167,42 @@ __global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __res
   const int sb = slot ? slot[b] : b;   // cache slab of this row
   // where the row of position pb lives: the slot's dense slab, or a block of the pool (BatchManager)
   const long long rowoff = pg.table ? kv_paged_off(pg, sb, pb, kvd) : (long long)sb * kv_bs + loff + (long long)pb * kvd;
-  const int pair = blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = pair * 2;
-  if (i >= d + 2 * kvd) return;
-  float2 v = make_float2(0.f, 0.f);
+  float2 v[2];
+  int idx[2];
+#pragma unroll
+  for (int u = 0; u < 2; u++) {
+    const int pair = (blockIdx.x * 2 + u) * blockDim.x + threadIdx.x;
+    idx[u] = pair * 2;
+    v[u] = make_float2(0.f, 0.f);
+    if (idx[u] < d + 2 * kvd) {
 #pragma unroll 4
-  for (int z = 0; z < nz; z++) {
-    const float2 pz = *reinterpret_cast<const float2*>(part + (size_t)z * zstride + (size_t)b * ld + i);
-    v.x += pz.x; v.y += pz.y;
+      for (int z = 0; z < nz; z++) {
+        const float2 pz = *reinterpret_cast<const float2*>(part + (size_t)z * zstride + (size_t)b * ld + idx[u]);
+        v[u].x += pz.x; v[u].y += pz.y;
+      }
+    }
   }
-  if (i < d + kvd) {
-    const int li = (i < d) ? i : i - d;
-    const int j = (li % hs) >> 1;
-    const float c = rc[(size_t)pb * (hs >> 1) + j], s = rs[(size_t)pb * (hs >> 1) + j];
-    const float r0 = v.x * c - v.y * s, r1 = v.x * s + v.y * c;
-    if (i < d) *reinterpret_cast<float2*>(q + (size_t)b * d + li) = make_float2(r0, r1);
-    else *reinterpret_cast<float2*>(kc + rowoff + li) = make_float2(r0, r1);
-  } else {
-    *reinterpret_cast<float2*>(vc + rowoff + (i - d - kvd)) = v;
+#pragma unroll
+  for (int u = 0; u < 2; u++) {
+    const int i = idx[u];
+    if (i >= d + 2 * kvd) continue;
+    if (i < d + kvd) {
+      const int li = (i < d) ? i : i - d;
+      const int j = (li % hs) >> 1;
+      const float c = rc[(size_t)pb * (hs >> 1) + j], s = rs[(size_t)pb * (hs >> 1) + j];
+      const float r0 = v[u].x * c - v[u].y * s, r1 = v[u].x * s + v[u].y * c;
+      if (i < d) *reinterpret_cast<float2*>(q + (size_t)b * d + li) = make_float2(r0, r1);
+      else *reinterpret_cast<float2*>(kc + rowoff + li) = make_float2(r0, r1);
+    } else {
+      *reinterpret_cast<float2*>(vc + rowoff + (i - d - kvd)) = v[u];
+    }
   }
 }
 
 int rope_scatter_launch(cudaStream_t st, bool pdl, int R, const float* part, int nz, long long zstride, int ld, const int* pos, int d,
                         int kvd, int hs, const float* rc, const float* rs, float* q, float* kc, float* vc, long long kv_bs, int loff,
                         const int* slot, const KvPaged* pg) {
-  THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld / 2, 256), R), dim3(256), 0, st, pdl, part, nz, zstride, ld, pos, d, kvd, hs,
+  THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld / 2, 512), R), dim3(256), 0, st, pdl, part, nz, zstride, ld, pos, d, kvd, hs,
                      rc, rs, q, kc, vc, kv_bs, loff, slot, pg ? *pg : KvPaged{}));
   return THA_STATUS_SUCCESS;
 }
@@ -802,7 +814,7 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
     const float* kcl = paged ? s.key_cache : s.key_cache + loff;      // layer's cache rows: pool base, or slab + layer offset
     const float* vcl = paged ? s.value_cache : s.value_cache + loff;
     if (!(skip & 8))
-    THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld_qkv / 2, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part,
+    THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld_qkv / 2, 512), R), dim3(256), 0, st, pdl, (const float*)sc.part,
                        pl.z_qkv, (long long)R * ld_qkv, ld_qkv, io.pos, da, kvd, hs, rc, rs, io.q, s.key_cache, s.value_cache,
                        kv_bs, loff, io.slot, pg));
     if (!io.logits && l == L - 1) {   // cache-only ingestion: the last layer's K/V rows are in place

@@ -49,6 +49,7 @@ class Oracle:
         lib.orc_open_v2.argtypes = [C.c_char_p]
         lib.orc_close.argtypes = [C.c_void_p]
         lib.orc_set_bf16_activations.argtypes = [C.c_void_p, C.c_int]
+        lib.orc_set_bf16_attention.argtypes = [C.c_void_p, C.c_int]
         lib.orc_get_config.argtypes = [C.c_void_p, i32p]
         lib.orc_seq_new.restype = C.c_void_p
         lib.orc_seq_new.argtypes = [C.c_void_p]
@@ -157,6 +158,11 @@ class OracleModel:
 
     def new_seq(self):
         return OracleSeq(self)
+
+    def set_bf16_attention(self, on):
+        """Prompt positions of the bf16 path with head size 64 / 128: the tensor-core attention rule (q, k, v, p rounded to
+        bf16, keys in tiles of 128); decode positions keep run.cc's fp32 attention."""
+        self.lib.orc_set_bf16_attention(self.h, 1 if on else 0)
 
     def forward_many(self, seqs, tokens, pos, n_threads=1):
         n = len(seqs)

@@ -81,6 +81,7 @@ MODELS = {
     "fusedA": dict(dim=256, hidden_dim=704, n_layers=3, n_heads=8, n_kv_heads=8, vocab_size=512, seq_len=48),
     "fusedGQA": dict(dim=256, hidden_dim=704, n_layers=2, n_heads=8, n_kv_heads=2, vocab_size=320, seq_len=40),
     "hs64": dict(dim=256, hidden_dim=512, n_layers=2, n_heads=4, n_kv_heads=2, vocab_size=300, seq_len=200),
+    "hs128": dict(dim=512, hidden_dim=1024, n_layers=2, n_heads=4, n_kv_heads=2, vocab_size=300, seq_len=420),
 }
 
 
@@ -118,16 +119,20 @@ def test_bf16_one_layer_agrees_to_fp32_noise(oracle, tmp_path, B):
     check_ratios(r, fl, f"bf16 one layer B={B}", min_tight=0.6)
 
 
-@pytest.mark.parametrize("name", ["fusedA", "hs64"])
+@pytest.mark.parametrize("name", ["fusedA", "hs64", "hs128"])
 def test_bf16_prefill_vs_oracle(oracle, tmp_path, name):
+    """Head sizes 64 and 128 take the tensor-core prompt attention (attn_prefill_tc.cu: q, k, v, p rounded to bf16, keys in
+    tiles of 128 -- the oracle restates that rule for the prompt positions); head size 32 the CUDA-core kernel."""
     import torch
     eng = load_pkg("engine")
     cfg, wb, path = bf16_model(tmp_path, name, MODELS[name])
     m = oracle.open(path, bf16=True)
+    tc_attention = cfg.head_size in (64, 128)
+    m.set_bf16_attention(tc_attention)
     B = 4
     e = eng.Engine(eng.DeviceWeightsBF16(cfg, wb), B)
     rng = np.random.default_rng(3)
-    lens = [1, 9, min(cfg.seq_len - 6, 70), min(cfg.seq_len - 6, 130)]
+    lens = [1, 9, min(cfg.seq_len - 6, 70), min(cfg.seq_len - 6, 130 if name != "hs128" else 400)]
     prompts = [rng.integers(0, cfg.vocab_size, size=n).astype(np.int32) for n in lens]
     seqs = [m.new_seq() for _ in range(B)]
     want_last = []
@@ -150,6 +155,7 @@ def test_bf16_prefill_vs_oracle(oracle, tmp_path, name):
             have = getattr(e.state, cache)[b].cpu().numpy()[:, :n]
             want = seqs[b].buf(cache).reshape(m.n_layers, m.seq_len, m.kv_dim)[:, :n]
             assert_close_scaled(have, want, BF16_EPS, f"{cache} slot {b}")
+    m.set_bf16_attention(False)   # decode positions: run.cc's fp32 attention
     for step in range(3):   # decode continues from the prefilled cache
         tok = rng.integers(0, cfg.vocab_size, size=B).astype(np.int32)
         pos = np.array([lens[b] + step for b in range(B)], np.int32)
