@@ -276,7 +276,7 @@ int attn_fused_nsplit(int B, int nseg, int seq_len);
 // Returns J (0 = shape not supported by the fused kernel).  The NARROWEST segment wins: J = 1 needs 48 registers per
 // thread (five CTAs per SM whose load and math phases interleave) where J = 6 needs 188 (one CTA per SM, its 8 warps in
 // lock step): measured on stories110M at 256 slots, position 128: 140 k -> 172 k tok/s; 64 slots: 63 k -> 79 k;
-// Llama-2-7B Q8_0 at 64 slots, position 256: 5.0 k (J = 8) -> 6.4 k tok/s (tools/attn_sweep.sh).  A warp still reads
+// Llama-2-7B Q8_0 at 64 slots, position 256: 5.0 k (J = 8) -> 6.4 k tok/s (tools/r01/attn_sweep.sh).  A warp still reads
 // 512 contiguous bytes of each K / V row.  THA_ATTN_J forces a width (development aid).
 // Grouped-query models: a segment covers whole groups of query heads that share a K/V head where one fits (each K/V
 // row is then read by one CTA, not by kv_mul of them).

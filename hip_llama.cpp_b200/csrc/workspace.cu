@@ -45,7 +45,7 @@ int tc_mode() {
 int* opt_tc() { return &g_tc; }
 static int g_dual = -2;
 int dual_min_rows() {
-  // off by default: measured slower (tools/dual_sweep.sh) -- the matmuls are persistent full-GPU kernels, two branches
+  // off by default: measured slower (tools/r01/dual_sweep.sh) -- the matmuls are persistent full-GPU kernels, two branches
   // only serialise smaller ones
   if (g_dual == -2) { const char* v = getenv("THA_DUAL"); g_dual = (v && *v) ? atoi(v) : 0; }
   return g_dual;
