@@ -90,6 +90,7 @@ class Lib:
             "tha_mha_scores_v2_f32": [vp, I, vp, I, vp, vp, vp, I, I, I, I, I],
             "tha_mha_weighted_v2_f32": [vp, I, vp, I, vp, vp, vp, I, I, I, I, I],
             "tha_mha_fused_v1_f32": [vp, I, vp, I, I, I, vp, vp, vp, vp, I, I, I],
+            "tha_mha_fused_v1_f32_static": [vp, I, vp, I, I, I, vp, vp, vp, vp, I, I, I],
             "tha_quantize_q8": [vp, vp, vp, vp, I, I],
             "tha_matmul_batch_q8": [vp, I, vp, I, vp, vp, vp, vp, I, I, I],
             "tha_forward_batch_f32": [vp, I, C.POINTER(Config), C.POINTER(WeightsF32), C.POINTER(State), vp, vp, vp],

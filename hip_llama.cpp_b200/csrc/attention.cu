@@ -9,7 +9,10 @@
 //     still fills the GPU; the last CTA of a (slot, segment) merges the splits.
 //     K/V rows are read once, fully coalesced (a warp reads whole contiguous row
 //     segments with 128-bit loads); scores never touch HBM.
+#include <stdio.h>
 #include <stdlib.h>
+
+#include <mutex>
 
 #include "common.cuh"
 #include "workspace.h"
@@ -427,4 +430,97 @@ extern "C" int tha_mha_fused_v1_f32(void* stream, int n_batches, const int* pos_
   const int kv_dim = n_kv_heads * head_size;
   return attn_fused_launch((cudaStream_t)stream, ws, n_batches, pos_d, n_heads, n_kv_heads, q, xb, key_cache + loff,
                            value_cache + loff, (long long)n_layers * seq_len * kv_dim, head_size, seq_len, false, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr);
+}
+
+// ------------------------------------------------------------------ no-allocation variant -------
+// tha_mha_fused_v1_f32_static: the fused attention above for callers that may not allocate (CUDA graph capture, serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The split scratch (per-split accumulators, maxima / sums, arrival counters) lives in ONE file-scope device array of a fixed
+// size instead of the Workspace's growable buffers.  Every GPU that loads the library holds the array until exit; every
+// call on a device shares it, so two calls that overlap on that GPU (different streams) race -- serialise them.
+namespace tha {
+
+constexpr int ATTN_STATIC_SLOTS = 32768;      // float4 + float2 per slot; a launch needs B * nseg * nsplit * 32 J slots
+constexpr int ATTN_STATIC_COUNTERS = 256;     // one per (slot, segment) of a split launch (B * nseg <= 148 when nsplit > 1)
+constexpr size_t ATTN_STATIC_ACC_OFF = 0;
+constexpr size_t ATTN_STATIC_ML_OFF = ATTN_STATIC_ACC_OFF + (size_t)ATTN_STATIC_SLOTS * sizeof(float4);
+constexpr size_t ATTN_STATIC_CNT_OFF = ATTN_STATIC_ML_OFF + (size_t)ATTN_STATIC_SLOTS * sizeof(float2);
+constexpr size_t ATTN_STATIC_BYTES = ATTN_STATIC_CNT_OFF + (size_t)ATTN_STATIC_COUNTERS * sizeof(int);   // 787,456 bytes
+
+static __device__ __align__(256) unsigned char attn_static_scratch[ATTN_STATIC_BYTES];
+
+constexpr int ATTN_STATIC_MAX_DEV = 64;
+static unsigned char* attn_static_ptr[ATTN_STATIC_MAX_DEV];   // device address of the array, per device (nullptr: not resolved yet)
+static std::mutex attn_static_mu;
+
+// The array's name is only a host-side handle here: its device address is asked for once per device, with that device current.
+static int attn_static_base(unsigned char** base) {
+  int dev = -1;
+  THA_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= ATTN_STATIC_MAX_DEV) return THA_STATUS_NOT_SUPPORTED;
+  std::lock_guard<std::mutex> g(attn_static_mu);
+  if (!attn_static_ptr[dev]) {
+    void* ptr = nullptr;
+    THA_CUDA_OK(cudaGetSymbolAddress(&ptr, attn_static_scratch));
+    attn_static_ptr[dev] = static_cast<unsigned char*>(ptr);
+  }
+  *base = attn_static_ptr[dev];
+  return THA_STATUS_SUCCESS;
+}
+
+}  // namespace tha
+
+extern "C" int tha_mha_fused_v1_f32_static(void* stream, int n_batches, const int* pos_d, int n_heads, int n_kv_heads,
+                                           int n_layers, const float* q, float* xb, const float* key_cache,
+                                           const float* value_cache, int head_size, int seq_len, int loff) {
+  if (n_batches <= 0 || !pos_d || !q || !xb || !key_cache || !value_cache || n_kv_heads <= 0 || n_heads <= 0 ||
+      n_heads % n_kv_heads || seq_len <= 0)
+    return THA_STATUS_INVALID_ARG;
+  const int dim = n_heads * head_size, kv_dim = n_kv_heads * head_size;
+  const int J = fused_J(n_heads, head_size, dim, n_heads / n_kv_heads);
+  if (!J || kv_dim % 4) return THA_STATUS_NOT_SUPPORTED;
+  AttnP p;
+  p.pos = pos_d; p.q = q; p.out = xb; p.kc = key_cache + loff; p.vc = value_cache + loff;
+  p.out_hi = nullptr; p.out_lo = nullptr; p.out_q = nullptr; p.out_sT = nullptr; p.ldxs = 0; p.gs = 0;
+  p.pg = KvPaged{};
+  p.kv_batch_stride = (long long)n_layers * seq_len * kv_dim; p.kv_dim = kv_dim; p.head_size = head_size;
+  p.kv_mul = n_heads / n_kv_heads; p.dim = dim;
+  p.nseg = dim / (128 * J);
+  p.nsplit = attn_fused_nsplit(n_batches, p.nseg, seq_len);
+  const int F = 32 * J;
+  cudaStream_t st = (cudaStream_t)stream;
+  p.part_acc = nullptr; p.part_ml = nullptr; p.counters = nullptr;
+  if (p.nsplit > 1) {
+    const size_t slots = (size_t)n_batches * p.nseg * p.nsplit * F;
+    const int counters = n_batches * p.nseg;
+    if (slots > (size_t)ATTN_STATIC_SLOTS || counters > ATTN_STATIC_COUNTERS) {
+      char msg[256];
+      snprintf(msg, sizeof(msg),
+               "tha_mha_fused_v1_f32_static: launch needs %zu scratch slots and %d counters, the static scratch holds %d and %d "
+               "(use tha_mha_fused_v1_f32)", slots, counters, ATTN_STATIC_SLOTS, ATTN_STATIC_COUNTERS);
+      set_last_error(msg, cudaErrorInvalidValue);
+      return THA_STATUS_INVALID_ARG;
+    }
+    unsigned char* base = nullptr;
+    const int rc = attn_static_base(&base);
+    if (rc) return rc;
+    p.part_acc = reinterpret_cast<float4*>(base + ATTN_STATIC_ACC_OFF);
+    p.part_ml = reinterpret_cast<float2*>(base + ATTN_STATIC_ML_OFF);
+    p.counters = reinterpret_cast<int*>(base + ATTN_STATIC_CNT_OFF);
+    // the arrival counters must start at zero: the kernel resets them when it finishes, but the array outlives every
+    // call (an aborted launch, or a larger launch before this one) -- so clear the ones this launch reads, on its stream
+    THA_CUDA_OK(cudaMemsetAsync(p.counters, 0, (size_t)counters * sizeof(int), st));
+  }
+  dim3 grid(n_batches, p.nseg, p.nsplit), block(256);
+  const size_t smem = (size_t)8 * F * (sizeof(float4) + sizeof(float2));
+  void (*k)(const AttnP) = nullptr;
+  switch (J) {
+    case 1: k = attn_fused_kernel<1>; break; case 2: k = attn_fused_kernel<2>; break;
+    case 3: k = attn_fused_kernel<3>; break; case 4: k = attn_fused_kernel<4>; break;
+    case 5: k = attn_fused_kernel<5>; break; case 6: k = attn_fused_kernel<6>; break;
+    case 7: k = attn_fused_kernel<7>; break; case 8: k = attn_fused_kernel<8>; break;
+  }
+  if (smem > 40 * 1024) THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  THA_CUDA_OK(launch(k, grid, block, smem, st, false, p));
+  return THA_STATUS_SUCCESS;
 }

@@ -177,6 +177,18 @@ int tha_mha_weighted_v2_f32(void* stream, int n_batches, const int* pos_d, int n
 int tha_mha_fused_v1_f32(void* stream, int n_batches, const int* pos_d, int n_heads, int n_kv_heads,
                          int n_layers, const float* q, float* xb, const float* key_cache,
                          const float* value_cache, int head_size, int seq_len, int loff);
+/* The same kernel and arguments for callers that may not allocate.  No counterpart in the reference: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid
+ * cudaMalloc.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine): the split
+ * scratch is a file-scope device array of 787,456 bytes (32768 partial slots of 24 bytes + 256 arrival counters)
+ * that every GPU loading the library holds until exit.  A launch whose time split needs more
+ * (n_batches * segments * splits * 32 J > 32768 slots, or n_batches * segments > 256 with a split) returns
+ * THA_STATUS_INVALID_ARG and tha_last_error() names the sizes; use tha_mha_fused_v1_f32 then.  All calls on a device
+ * share the array: the counters a launch uses are cleared on its stream first, and calls that overlap on the GPU
+ * (two streams) race -- serialise them.  Results are bit-identical to tha_mha_fused_v1_f32. */
+int tha_mha_fused_v1_f32_static(void* stream, int n_batches, const int* pos_d, int n_heads, int n_kv_heads,
+                                int n_layers, const float* q, float* xb, const float* key_cache,
+                                const float* value_cache, int head_size, int seq_len, int loff);
 
 /* ---- Q8_0 (runq.c) ---------------------------------------------------------------- */
 /* quantize, runq.c:145-171, bit-exact: n = rows*cols values, groups of `gs` */
