@@ -16,6 +16,7 @@
 
 #include "common.cuh"
 #include "workspace.h"
+#include "ktrace.cuh"
 
 namespace tha {
 
@@ -118,8 +119,10 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   float2* sm_ml = reinterpret_cast<float2*>(sm_acc + 8 * F);  // [8][F]
   __shared__ int is_last;
 
+  const int kt = threadIdx.x == 0 ? kt_begin(KT_ATTN) : -1;
   pdl_wait();
   pdl_trigger();
+  kt_stamp(kt, 1);
   const int b = blockIdx.x, seg = blockIdx.y, split = blockIdx.z;
   const int pb = p.pos[b];
   if (pb < 0) {   // idle slot: the int8 matmul that follows gets zeros (as the stand-alone quantiser gave it)
@@ -233,6 +236,7 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   float* outp = p.out + (size_t)b * p.dim + seg * (128 * J) + 4 * f;
   if (p.nsplit == 1) {
     if (f < F) attn_store(p, outp, make_float4(A.x / L, A.y / L, A.z / L, A.w / L), b);
+    kt_stamp(kt, 6);
     return;
   }
 

@@ -71,13 +71,21 @@ static thread_local int g_last_step_launches = 0;
 // griddepcontrol.wait -> load -> compute -> flush), 9-10 kernels per layer; two independent chains overlap each other's
 // latency and the attention kernel of one (HBM-bound) runs under the matmuls of the other.  The weights are read by
 // both branches; they run a layer apart at most, so the second read is an L2 hit (28 MB per layer of stories110M).
-struct DualPlan { bool on; int B0, B1; Workspace* ws2; cudaStream_t st2; };
+struct DualPlan { bool on; int B0, B1; Workspace* ws2; cudaStream_t st2; int sms; };
+// The two branches must RUN side by side, not one after the other: every matmul launch of a branch is planned for, and
+// limited to, half of the SMs (THA_DUAL_SMS overrides) -- a persistent matmul that takes all 148 SMs leaves nothing for its twin.
+static int dual_sms() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("THA_DUAL_SMS"); v = (e && *e) ? atoi(e) : 74; }
+  return v;
+}
+struct SmBudgetScope { explicit SmBudgetScope(int n) { set_sm_budget(n); } ~SmBudgetScope() { set_sm_budget(0); } };
 static int dual_plan(Workspace* ws, int B, DualPlan* d) {
-  d->on = false; d->B0 = B; d->B1 = 0; d->ws2 = nullptr; d->st2 = nullptr;
+  d->on = false; d->B0 = B; d->B1 = 0; d->ws2 = nullptr; d->st2 = nullptr; d->sms = 0;
   const int m = dual_min_rows();
   if (m <= 0 || B < m || B < 2) return THA_STATUS_SUCCESS;
   THA_TRY_RC2(ws_ensure_dual(ws));
-  d->on = true; d->B0 = (B + 1) / 2; d->B1 = B - d->B0; d->ws2 = ws->sibling; d->st2 = ws->side_stream;
+  d->on = true; d->sms = dual_sms(); d->B0 = (B + 1) / 2; d->B1 = B - d->B0; d->ws2 = ws->sibling; d->st2 = ws->side_stream;
   return THA_STATUS_SUCCESS;
 }
 static tha_state_t state_rows(const tha_state_t& s, const tha_config_t& c, int row0) {
@@ -242,6 +250,7 @@ int decode_step_f32(cudaStream_t st, int B, const tha_config_t* cfg, const tha_w
   if (use_tc) {
     DualPlan dp;
     THA_TRY(dual_plan(ws, B, &dp));
+    SmBudgetScope budget(dp.sms);
     THA_TRY(step_tc_prepare(ws, cfg, dp.B0));
     if (dp.on) THA_TRY(step_tc_prepare(dp.ws2, cfg, dp.B1));
     a.mega = dp.on ? 3 : 2;   // part of the graph key
@@ -384,6 +393,7 @@ int decode_step_q8(cudaStream_t st, int B, const tha_config_t* cfg, const tha_we
   if (tcm != 0 && step_tc_q8_supported(cfg, B, gs)) {
     DualPlan dp;
     THA_TRY(dual_plan(ws, B, &dp));
+    SmBudgetScope budget(dp.sms);
     THA_TRY(step_tc_q8_prepare(ws, cfg, dp.B0, gs));
     if (dp.on) THA_TRY(step_tc_q8_prepare(dp.ws2, cfg, dp.B1, gs));
     a.tc = dp.on ? 2 : 1;   // part of the graph key

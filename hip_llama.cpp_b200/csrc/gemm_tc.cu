@@ -40,6 +40,8 @@
 #include "common.cuh"
 #include "gemm_tc.h"
 #include "tc_common.cuh"
+#include "ktrace.cuh"
+#include "workspace.h"
 
 namespace tha {
 
@@ -64,6 +66,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
   uint64_t* accfree = accum + 1;              // ... and read out by the 12 epilogue warps: the next item may overwrite it
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accfree + 1);
   int* abort_flag = reinterpret_cast<int*>(tmem_slot + 1);
+  __shared__ int kt_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles01 = p.tiles[0] + p.tiles[1];
@@ -90,6 +93,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
     tc_mbar_init(accum, 1);
     tc_mbar_init(accfree, 4 * TC_CGROUPS);
     *abort_flag = 0;
+    kt_s = kt_begin((unsigned long long)KT_GEMM | ((unsigned long long)p.splits << 16) | ((unsigned long long)p.n_items << 32));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -113,6 +117,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
   const uint32_t tmem_d = tmem_base;                               // main accumulator (hi.hi terms)
   const uint32_t tmem_dl = tmem_base + (S::SPLIT_ACC ? NT : 0);    // lo-term accumulator
   const uint32_t tmem_a = tmem_base + S::ACC_COLS;                 // W operand ring
+  const int kt = kt_s;
 
   if (warp == 0) {
     // ===== W producer: weights never depend on the previous kernel, so no programmatic-dependency wait here --
@@ -141,6 +146,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
     // ===== X producer (activations: written by the previous kernel)
     if (lane == 0) {
       pdl_wait();
+      kt_stamp(kt, 1);
       int gb = 0;
       bool ok = true;
       for (int it = blockIdx.x; it < p.n_items && ok; it += gridDim.x) {
@@ -177,6 +183,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
           TC_TRACE(8, i);
           if (!tc_mbar_wait(&ready[sa], (g / S::SA) & 1u, abort_flag)) { ok = false; break; }
           TC_TRACE(9, i);
+          if (n_it == 0 && i == 0) kt_stamp(kt, 2);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           TC_TRACE(5, i);
           const int nk = (w.nkb - i * S::KG) < S::KG ? (w.nkb - i * S::KG) : S::KG;
@@ -202,6 +209,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
           TC_TRACE(7, i);
         }
         if (ok) tc_commit(accum);
+        if (n_it == 0) kt_stamp(kt, 3);
         gb += w.nst;
       }
     }
@@ -255,30 +263,65 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
         pdl_wait();   // returns at once (the X producer already waited); makes the predecessor's writes visible to these threads
       }
       if (ok) ok = tc_mbar_wait(accum, n_it & 1u, abort_flag);
+      if (n_it == 0 && threadIdx.x == 128) kt_stamp(kt, 4);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const int row = w.row0 + r;
       const bool row_ok = row < p.M[w.mat];
       float* outz = p.out + (size_t)(it % p.splits) * p.zstride + p.out_off[w.mat] + row;
       if (ok) {
+        // Whole tile inside the output (every tile of the model shapes): no per-element bounds checks, the 16 column
+        // scales as four 128-bit read-only loads, the store address advanced by one 64-bit add per column.  (The
+        // checked form below costs ~25 instructions per element -- 64-bit multiplies, two predicates, a branch -- and made
+        // this read-out issue-bound: ~1 us per 16 columns with 12 warps on 4 schedulers.)
+        const bool full = row_ok && (w.n0 + NT <= p.N);
+        const bool cs_vec = p.colscale && ((reinterpret_cast<uintptr_t>(p.colscale) & 15) == 0);
 #pragma unroll 1
         for (int c = 16 * grp; c < NT; c += 16 * TC_CGROUPS) {
           uint32_t v[16], w2[16];
           const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c;
           tc_tmem_ld16(taddr, v);
           if (S::SPLIT_ACC) tc_tmem_ld16(taddr + NT, w2);
-          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          float sc[16];
+          if (full && p.colscale) {
+            if (cs_vec) {
 #pragma unroll
-          for (int j = 0; j < 16; j++) {
-            const int n = w.n0 + c + j;
-            if (n < p.N && row_ok) {
-              float x = __uint_as_float(v[j]);
-              if (S::SPLIT_ACC) x += __uint_as_float(w2[j]);
-              if (p.colscale) x *= p.colscale[n];
-              outz[(size_t)n * p.ldo] = x;
+              for (int j4 = 0; j4 < 4; j4++) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(p.colscale + w.n0 + c) + j4);
+                sc[4 * j4] = t.x; sc[4 * j4 + 1] = t.y; sc[4 * j4 + 2] = t.z; sc[4 * j4 + 3] = t.w;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; j++) sc[j] = __ldg(p.colscale + w.n0 + c + j);
             }
           }
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          if (n_it == 0 && threadIdx.x == 128) kt_stamp(kt, 7 + 2 * (c / (16 * TC_CGROUPS)));
+          if (full) {
+            float* o = outz + (size_t)(w.n0 + c) * p.ldo;
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+              float x = __uint_as_float(v[j]);
+              if (S::SPLIT_ACC) x += __uint_as_float(w2[j]);
+              if (p.colscale) x *= sc[j];
+              *o = x;
+              o += p.ldo;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+              const int n = w.n0 + c + j;
+              if (n < p.N && row_ok) {
+                float x = __uint_as_float(v[j]);
+                if (S::SPLIT_ACC) x += __uint_as_float(w2[j]);
+                if (p.colscale) x *= p.colscale[n];
+                outz[(size_t)n * p.ldo] = x;
+              }
+            }
+          }
+          if (n_it == 0 && threadIdx.x == 128) kt_stamp(kt, 8 + 2 * (c / (16 * TC_CGROUPS)));
         }
       }
+      if (n_it == 0 && threadIdx.x == 128) kt_stamp(kt, 5);
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
       if (lane == 0) tc_mbar_arrive(accfree);
@@ -286,6 +329,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constan
     }
   }
   __syncthreads();
+  if (threadIdx.x == 0) kt_stamp(kt, 6);
   if (warp == 2) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(S::TMEM_COLS));
@@ -380,12 +424,6 @@ bool gemm_tc_ok(const TcArgs& a) {
 
 int gemm_tc_pick_nt(int N) { return N <= 16 ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128)); }   // wider N: more column tiles
 
-static int tc_sm_count() {
-  int dev = 0, sms = 148;
-  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  return sms;
-}
-
 template <int NT>
 static int tc_launch_nt(cudaStream_t st, const CUtensorMap* mw, const CUtensorMap& mxh, const CUtensorMap& mxl, const TcP& p, dim3 grid, bool pdl) {
   using S = TcSmem<NT>;
@@ -423,7 +461,7 @@ int gemm_tc_launch(cudaStream_t st, const TcArgs& a, bool pdl) {
   p.ny = ceil_div(a.N, NT);
   p.splits = splits;
   p.n_items = tiles * p.ny * splits;
-  const int sms = tc_sm_count();
+  const int sms = sm_budget();
   dim3 grid(p.n_items < sms ? p.n_items : sms, 1, 1);
   switch (NT) {
     case 16: return tc_launch_nt<16>(st, mw, mxh, mxl, p, grid, pdl);
@@ -825,11 +863,7 @@ int gemm_q8i_launch(cudaStream_t st, const Q8iArgs& a, bool pdl) {
   p.ny = ceil_div(a.N, NT);
   p.splits = splits;
   p.n_items = tiles * p.ny * splits;
-  int sms = 148;
-  {
-    int dev = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  }
+  const int sms = sm_budget();
   dim3 grid(p.n_items < sms ? p.n_items : sms, 1, 1);
   switch (NT) {
     case 16: return q8i_launch_nt<16>(st, mw, mx, p, grid, pdl);

@@ -29,6 +29,7 @@
 #include "gemm_tc.h"
 #include "tp.h"
 #include "workspace.h"
+#include "ktrace.cuh"
 
 namespace tha {
 
@@ -105,8 +106,10 @@ __global__ void __launch_bounds__(1024) tc_prep_kernel(float* __restrict__ x, co
                                                       float* __restrict__ xl, float* __restrict__ scale,
                                                       const int* __restrict__ gather, const TpPeers tp) {
   __shared__ float red[33];
+  const int kt = threadIdx.x == 0 ? kt_begin(KT_PREP) : -1;
   pdl_wait();
   pdl_trigger();
+  kt_stamp(kt, 1);
   if (tp.n && !emb) tp_wait_peers(tp);
   const int ob = blockIdx.x;
   const int b = gather ? gather[ob] : ob;
@@ -148,6 +151,7 @@ __global__ void __launch_bounds__(1024) tc_prep_kernel(float* __restrict__ x, co
     float m = tot / d;
     m += 1e-5f;
     scale[ob] = 1.0f / sqrtf(m);
+    kt_stamp(kt, 6);
   }
 }
 
@@ -160,8 +164,10 @@ __global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __res
                                                               float* __restrict__ q, float* __restrict__ kc,
                                                               float* __restrict__ vc, long long kv_bs, int loff,
                                                               const int* __restrict__ slot, const KvPaged pg) {
+  const int kt = threadIdx.x == 0 ? kt_begin(KT_ROPE) : -1;
   pdl_wait();
   pdl_trigger();
+  kt_stamp(kt, 1);
   const int b = blockIdx.y, pb = pos[b];
   if (pb < 0) return;
   const int sb = slot ? slot[b] : b;   // cache slab of this row
@@ -197,6 +203,7 @@ __global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __res
       *reinterpret_cast<float2*>(vc + rowoff + (i - d - kvd)) = v[u];
     }
   }
+  kt_stamp(kt, 6);
 }
 
 int rope_scatter_launch(cudaStream_t st, bool pdl, int R, const float* part, int nz, long long zstride, int ld, const int* pos, int d,
@@ -211,8 +218,10 @@ int rope_scatter_launch(cudaStream_t st, bool pdl, int R, const float* part, int
 __global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __restrict__ part, int nz, long long zstride,
                                                               int ld, const int* __restrict__ pos, int h,
                                                               float* __restrict__ hh, float* __restrict__ hl) {
+  const int kt = threadIdx.x == 0 ? kt_begin(KT_SWIGLU) : -1;
   pdl_wait();
   pdl_trigger();
+  kt_stamp(kt, 1);
   const int b = blockIdx.y;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= h) return;
@@ -231,6 +240,7 @@ __global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __res
   const float hi = st_tf32(r);
   hh[(size_t)b * h + i] = hi;
   hl[(size_t)b * h + i] = r - hi;
+  kt_stamp(kt, 6);
 }
 
 
@@ -391,7 +401,8 @@ static int pick_splits(int tiles, int K, int N, int align) {
     const int per = ceil_div(ceil_div(kb, z), align) * align;   // Q8_0: a split starts on a 4-k-block ring slot
     if (ceil_div(kb, per) != z) continue;                        // the kernel needs every split non-empty
     const int ctas = tiles * z;
-    const float eff = (float)ctas / (float)(ceil_div(ctas, 148) * 148);
+    const int sms = sm_budget();
+    const float eff = (float)ctas / (float)(ceil_div(ctas, sms) * sms);
     const float score = eff - charge * (z - 1);
     if (score > best_score) { best_score = score; best = z; }
   }
@@ -410,7 +421,7 @@ static int pick_splits_q8(int tiles, int K, int N, int gs) {
     if (ceil_div(slots, per) != z) continue;
     const int per_pad = ceil_div(per, sb) * sb;
     const int items = tiles * ny * z;
-    const float cost = (float)ceil_div(items, 148) * (per_pad + 3.0f) + 0.5f * (z - 1);
+    const float cost = (float)ceil_div(items, sm_budget()) * (per_pad + 3.0f) + 0.5f * (z - 1);
     if (cost < best_cost) { best_cost = cost; best = z; }
   }
   return best;

@@ -9,6 +9,7 @@
 
 #include "common.cuh"
 #include "workspace.h"
+#include "ktrace.cuh"
 
 namespace tha {
 
@@ -51,6 +52,13 @@ int dual_min_rows() {
   return g_dual;
 }
 int* opt_dual() { return &g_dual; }
+static thread_local int g_sm_budget = 0;
+int sm_budget() {
+  static int sms = 0;
+  if (!sms) { int dev = 0, n = 148; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); sms = n; }
+  return (g_sm_budget > 0 && g_sm_budget < sms) ? g_sm_budget : sms;
+}
+void set_sm_budget(int n) { g_sm_budget = n; }
 static int g_skip = -1;
 int skip_mode() {   // development / measurement aid: leave a class of kernels out of the step (step_tc.cu); results are then garbage
   if (g_skip < 0) { const char* v = getenv("THA_SKIP"); g_skip = (v && *v) ? atoi(v) : 0; }
@@ -225,6 +233,40 @@ int* opt_graph() { return &g_graph; }
 }  // namespace tha
 
 extern "C" int tha_version(void) { return 100; }
+
+// ---- ktrace.cuh: device-side step timeline (development aid) ----
+namespace tha {
+static std::vector<int (*)(const KtSlots&)>& kt_setters() { static std::vector<int (*)(const KtSlots&)> v; return v; }
+void kt_register(int (*setter)(const KtSlots&)) { kt_setters().push_back(setter); }
+static KtSlots g_kt = {nullptr, nullptr};
+}  // namespace tha
+// enable = 1: arm (records start at 0).  enable = 0: copy up to max_records records of KT_STAMPS u64 into out_host, disarm;
+// returns the record count through *n_out.
+extern "C" int tha_ktrace(unsigned long long* out_host, int max_records, int enable, int* n_out) {
+  using namespace tha;
+  if (enable) {
+    if (!g_kt.buf) {
+      THA_CUDA_OK(cudaMalloc(&g_kt.buf, (size_t)KT_MAX * KT_STAMPS * sizeof(unsigned long long)));
+      THA_CUDA_OK(cudaMalloc(&g_kt.ctr, sizeof(unsigned int)));
+    }
+    THA_CUDA_OK(cudaMemset(g_kt.buf, 0, (size_t)KT_MAX * KT_STAMPS * sizeof(unsigned long long)));
+    THA_CUDA_OK(cudaMemset(g_kt.ctr, 0, sizeof(unsigned int)));
+    for (auto f : kt_setters()) if (f(g_kt)) return THA_STATUS_EXECUTION_FAILED;
+    return THA_STATUS_SUCCESS;
+  }
+  if (!g_kt.buf) return THA_STATUS_INVALID_ARG;
+  THA_CUDA_OK(cudaDeviceSynchronize());
+  unsigned int n = 0;
+  THA_CUDA_OK(cudaMemcpy(&n, g_kt.ctr, sizeof(n), cudaMemcpyDeviceToHost));
+  if (n > (unsigned)KT_MAX) n = KT_MAX;
+  if ((int)n > max_records) n = max_records > 0 ? max_records : 0;
+  if (out_host && n) THA_CUDA_OK(cudaMemcpy(out_host, g_kt.buf, (size_t)n * KT_STAMPS * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  if (n_out) *n_out = (int)n;
+  const KtSlots off = {nullptr, nullptr};
+  for (auto f : kt_setters()) f(off);
+  cudaFree(g_kt.buf); cudaFree(g_kt.ctr); g_kt = off;
+  return THA_STATUS_SUCCESS;
+}
 
 // Paged KV cache.  key_pool / value_pool: [n_blocks][n_layers][block_size][kv_dim] fp32 on the device (the caller allocates
 // them; a tha_state_t is paged when its key_cache == key_pool and value_cache == value_pool); block_table_d: [slots][stride]

@@ -68,6 +68,8 @@ void step_tc_release(Workspace* ws);   // ... and the row pipeline's scratch key
 int skip_mode();       // bit mask of kernel classes left out of the row pipeline (live-share measurements): 1 layer matmuls, 2 attention,
                        // 4 prep, 8 RoPE / scatter, 16 SwiGLU / quantise, 32 classifier, 64 argmax
 int chain_mode();      // 1: matmul chains with fused epilogues (chain_tc.cu), 0: one launch per matmul (the round-1 pipeline)
+int sm_budget();            // SMs one matmul launch may occupy: all of them, or a branch's share while a dual step is planned / issued
+void set_sm_budget(int n);  // 0 = all
 int dual_min_rows();   // rows from which a step is issued as two concurrent half-batches (0 = never)
 int ws_rope(Workspace* ws, int head_size, int seq_len, const float** cos_d, const float** sin_d);
 
