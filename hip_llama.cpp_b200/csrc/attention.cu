@@ -115,8 +115,8 @@ __device__ __forceinline__ void attn_store(const AttnP& p, float* outp, float4 r
 template <int J>
 __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   constexpr int F = 32 * J;  // slots per segment
-  extern __shared__ float4 sm_acc[];                 // [8][F]
-  float2* sm_ml = reinterpret_cast<float2*>(sm_acc + 8 * F);  // [8][F]
+  extern __shared__ float4 sm_acc[];                 // [warps][F]
+  float2* sm_ml = reinterpret_cast<float2*>(sm_acc + (blockDim.x >> 5) * F);  // [warps][F]
   __shared__ int is_last;
 
   const int kt = threadIdx.x == 0 ? kt_begin(KT_ATTN) : -1;
@@ -162,14 +162,15 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   // previous form (this kernel was issue- as well as latency-limited: sm__throughput 50 % at 4.3 TB/s).
   constexpr int RW = (J <= 2) ? 4 : 2;
   const float inv_sqrt_hs = 1.0f / sqrt_hs;
-  for (int t = t0 + warp; t < t1; t += 8 * RW) {
+  const int nw = blockDim.x >> 5;   // warps of this CTA: 8, or fewer when the grid would not fit one wave (attn_pick_warps)
+  for (int t = t0 + warp; t < t1; t += nw * RW) {
     float4 kr[RW][J], vr[RW][J];
     bool live[RW];
     long long roff[RW];
 #pragma unroll
     for (int r = 0; r < RW; r++) {
-      live[r] = (t + 8 * r) < t1;
-      const int tr = live[r] ? t + 8 * r : t;
+      live[r] = (t + nw * r) < t1;
+      const int tr = live[r] ? t + nw * r : t;
       roff[r] = p.pg.table ? kv_paged_off(p.pg, b, tr, p.kv_dim) : (long long)tr * p.kv_dim;
       const float* ka = kb + roff[r];
 #pragma unroll
@@ -210,7 +211,7 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
     }
   }
 
-  // ---- merge the 8 warps of this CTA ----
+  // ---- merge the warps of this CTA ----
 #pragma unroll
   for (int j = 0; j < J; j++) {
     const int f = lane + 32 * j;
@@ -222,10 +223,8 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   float M = -INFINITY, L = 0.0f;
   float4 A = make_float4(0.f, 0.f, 0.f, 0.f);
   if (f < F) {
-#pragma unroll
-    for (int w = 0; w < 8; w++) M = fmaxf(M, sm_ml[w * F + f].x);
-#pragma unroll
-    for (int w = 0; w < 8; w++) {
+    for (int w = 0; w < nw; w++) M = fmaxf(M, sm_ml[w * F + f].x);
+    for (int w = 0; w < nw; w++) {
       const float2 ml = sm_ml[w * F + f];
       const float e = (ml.x == -INFINITY) ? 0.0f : expf(ml.x - M);
       const float4 a = sm_acc[w * F + f];
@@ -327,6 +326,28 @@ int attn_fused_nsplit(int B, int nseg, int seq_len) {
   return target;
 }
 
+// Warps per CTA.  Eight, unless the grid (one CTA per slot and segment, unsplit) would then need more than one wave of
+// the machine: 256 slots x 6 segments of stories110M are 1536 CTAs against 740 resident ones (five per SM at 48 registers), i.e.
+// three rounds of a latency-bound kernel (12 us per layer at position 10).  Warps per SM are what the register file allows either
+// way, so narrower CTAs cost no bandwidth at long contexts; they put every (slot, segment) on the machine at once.
+// A CTA needs one thread per float4 of its segment for the merge: warps >= J.
+static int attn_pick_warps(void (*k)(const AttnP), int J, long long ctas) {
+  static int sms = 0;
+  if (!sms) { int dev = 0; sms = 148; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+  static int forced = -1;
+  if (forced < 0) { const char* v = getenv("THA_ATTN_WARPS"); forced = (v && *v) ? atoi(v) : 0; }
+  if (forced >= J && forced <= 8 && forced > 0) return forced;
+  int smallest = 8;
+  for (int nw = 8; nw >= 2 && nw >= J; nw >>= 1) {
+    smallest = nw;
+    int per_sm = 0;
+    const size_t smem = (size_t)nw * 32 * J * (sizeof(float4) + sizeof(float2));
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, nw * 32, smem) != cudaSuccess) { cudaGetLastError(); return 8; }
+    if (ctas <= (long long)per_sm * sms) return nw;
+  }
+  return smallest;   // more than one wave whatever the shape: the most even distribution
+}
+
 // kc / vc are the caches already offset to the layer (base + loff).
 int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
                       const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
@@ -350,8 +371,6 @@ int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_
     if (st) return st;
   }
   p.part_acc = ws->part_acc; p.part_ml = ws->part_ml; p.counters = ws->counters;
-  dim3 grid(B, p.nseg, p.nsplit), block(256);
-  const size_t smem = (size_t)8 * F * (sizeof(float4) + sizeof(float2));
   void (*k)(const AttnP) = nullptr;
   switch (J) {
     case 1: k = attn_fused_kernel<1>; break; case 2: k = attn_fused_kernel<2>; break;
@@ -359,6 +378,9 @@ int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_
     case 5: k = attn_fused_kernel<5>; break; case 6: k = attn_fused_kernel<6>; break;
     case 7: k = attn_fused_kernel<7>; break; case 8: k = attn_fused_kernel<8>; break;
   }
+  const int nw = attn_pick_warps(k, J, (long long)B * p.nseg * p.nsplit);
+  dim3 grid(B, p.nseg, p.nsplit), block(32 * nw);
+  const size_t smem = (size_t)nw * F * (sizeof(float4) + sizeof(float2));
   if (smem > 40 * 1024) THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   THA_CUDA_OK(launch(k, grid, block, smem, stream, pdl, p));
   return THA_STATUS_SUCCESS;
@@ -515,8 +537,6 @@ extern "C" int tha_mha_fused_v1_f32_static(void* stream, int n_batches, const in
     // call (an aborted launch, or a larger launch before this one) -- so clear the ones this launch reads, on its stream
     THA_CUDA_OK(cudaMemsetAsync(p.counters, 0, (size_t)counters * sizeof(int), st));
   }
-  dim3 grid(n_batches, p.nseg, p.nsplit), block(256);
-  const size_t smem = (size_t)8 * F * (sizeof(float4) + sizeof(float2));
   void (*k)(const AttnP) = nullptr;
   switch (J) {
     case 1: k = attn_fused_kernel<1>; break; case 2: k = attn_fused_kernel<2>; break;
@@ -524,6 +544,9 @@ extern "C" int tha_mha_fused_v1_f32_static(void* stream, int n_batches, const in
     case 5: k = attn_fused_kernel<5>; break; case 6: k = attn_fused_kernel<6>; break;
     case 7: k = attn_fused_kernel<7>; break; case 8: k = attn_fused_kernel<8>; break;
   }
+  const int nw = attn_pick_warps(k, J, (long long)n_batches * p.nseg * p.nsplit);   // as attn_fused_launch: bit-identical results
+  dim3 grid(n_batches, p.nseg, p.nsplit), block(32 * nw);
+  const size_t smem = (size_t)nw * F * (sizeof(float4) + sizeof(float2));
   if (smem > 40 * 1024) THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   THA_CUDA_OK(launch(k, grid, block, smem, st, false, p));
   return THA_STATUS_SUCCESS;

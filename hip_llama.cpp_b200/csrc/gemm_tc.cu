@@ -589,6 +589,7 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
   constexpr int LG = 128 / NT;                   // groups per TMEM read (128 columns)
   const int sb = LG / gps;                       // slots per TMEM read batch (NT <= gs: at least 1)
   const int tiles01 = p.tiles[0] + p.tiles[1];
+  __shared__ int kt_q8_s;
 
   // work item -> (matrix, row0, n0, first slot, real slots, padded slots, real groups)
   struct Item { int mat, row0, n0, slot0, nslots, npad, ng; };
@@ -616,6 +617,7 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
     for (int b = 0; b < S::NMD; b++) tc_mbar_init(&mdone[b], 1);
     for (int b = 0; b < S::NACC_MAX; b++) tc_mbar_init(&aempty[b], 4);
     *abort_flag = 0;
+    kt_q8_s = kt_begin((unsigned long long)KT_GEMM_Q8 | ((unsigned long long)p.splits << 16) | ((unsigned long long)p.n_items << 32));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -633,6 +635,7 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
+  const int kt = kt_q8_s;
 
   if (warp == 0) {
     // ===== TMA producer
@@ -651,6 +654,7 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
           const int pre = w.npad < nring ? w.npad : nring;
           for (; j < pre; j++) tc_tma_2d_hint(smem + j * S::SLOT, mw, (w.slot0 + j) * 32, w.row0, &full[j], pol_w);
           pdl_wait();
+          kt_stamp(kt, 1);
           for (j = 0; j < pre; j++) {
             tc_mbar_expect_tx(&full[j], S::SLOT);
             tc_tma_2d(smem + j * S::SLOT + S::W_BYTES, &mx, (w.slot0 + j) * 32, w.n0, &full[j]);
@@ -685,6 +689,7 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
             if (!tc_mbar_wait(&aempty[jg & nacc_mask], ((jg >> nacc_sh) & 1u) ^ 1u, abort_flag)) { ok = false; break; }
           }
           if (!tc_mbar_wait(&full[s], (jg / nring) & 1u, abort_flag)) { ok = false; break; }
+          if (jg == 0) kt_stamp(kt, 2);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint64_t adesc = tc_smem_desc(tc_smem_u32(smem + s * S::SLOT));
           const uint64_t bdesc = tc_smem_desc(tc_smem_u32(smem + s * S::SLOT + S::W_BYTES));
@@ -695,6 +700,7 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
                     (uint32_t)((sub & (mpg - 1)) != 0));
           tc_commit(&mdone[jg % S::NMD]);
         }
+        if (jb == 0 && warp == 1) kt_stamp(kt, 3);
         jb += w.npad;
       }
     }
@@ -754,6 +760,7 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
         }
         ok = __shfl_sync(THA_FULL_MASK, wok, 0) != 0;
         if (!ok) break;
+        if (jb == 0 && bi == 0 && threadIdx.x == 128) kt_stamp(kt, 4);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t ta = tq + (uint32_t)(((s_first & (nacc - 1)) << gps_sh) * NT);
         tc_tmem_ld64(ta, v);
@@ -793,11 +800,13 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
           if (n < p.N) outz[(size_t)n * p.ldo] = acc[c];
         }
       }
+      if (jb == 0 && threadIdx.x == 128) kt_stamp(kt, 5);
       jb += w.npad;
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }
   __syncthreads();
+  if (threadIdx.x == 0) kt_stamp(kt, 6);
   if (warp == 2) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(S::TMEM_COLS));

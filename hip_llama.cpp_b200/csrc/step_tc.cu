@@ -214,7 +214,8 @@ int rope_scatter_launch(cudaStream_t st, bool pdl, int R, const float* part, int
   return THA_STATUS_SUCCESS;
 }
 
-// hb = silu(a) * c with a = w1.x, c = w3.x (sum of nz partials each), written as tf32 hi/lo.  grid (h / 256, B)
+// hb = silu(a) * c with a = w1.x, c = w3.x (sum of nz partials each), written as tf32 hi/lo.  Two consecutive values per
+// thread (64-bit loads / stores; h even): 256 slots x 2048 values are then 1024 blocks = one wave, not two.  grid (h / 512, B)
 __global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __restrict__ part, int nz, long long zstride,
                                                               int ld, const int* __restrict__ pos, int h,
                                                               float* __restrict__ hh, float* __restrict__ hl) {
@@ -223,23 +224,25 @@ __global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __res
   pdl_trigger();
   kt_stamp(kt, 1);
   const int b = blockIdx.y;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
   if (i >= h) return;
-  float r = 0.0f;
+  float2 r = make_float2(0.f, 0.f);
   if (pos[b] >= 0) {
-    float a = 0.0f, c = 0.0f;
+    float2 a = make_float2(0.f, 0.f), c = a;
 #pragma unroll 4
     for (int z = 0; z < nz; z++) {
-      a += part[(size_t)z * zstride + (size_t)b * ld + i];
-      c += part[(size_t)z * zstride + (size_t)b * ld + h + i];
+      const float2 az = *reinterpret_cast<const float2*>(part + (size_t)z * zstride + (size_t)b * ld + i);
+      const float2 cz = *reinterpret_cast<const float2*>(part + (size_t)z * zstride + (size_t)b * ld + h + i);
+      a.x += az.x; a.y += az.y; c.x += cz.x; c.y += cz.y;
     }
     r = a;
-    r *= (1.0f / (1.0f + expf(-r)));   // run.cc:344-347 operation order
-    r *= c;
+    r.x *= (1.0f / (1.0f + expf(-r.x)));   // run.cc:344-347 operation order
+    r.y *= (1.0f / (1.0f + expf(-r.y)));
+    r.x *= c.x; r.y *= c.y;
   }
-  const float hi = st_tf32(r);
-  hh[(size_t)b * h + i] = hi;
-  hl[(size_t)b * h + i] = r - hi;
+  const float2 hi = make_float2(st_tf32(r.x), st_tf32(r.y));
+  *reinterpret_cast<float2*>(hh + (size_t)b * h + i) = hi;
+  *reinterpret_cast<float2*>(hl + (size_t)b * h + i) = make_float2(r.x - hi.x, r.y - hi.y);
   kt_stamp(kt, 6);
 }
 
@@ -261,8 +264,10 @@ __global__ void __launch_bounds__(1024) tc_prep_q8_kernel(float* __restrict__ x,
                                                           int8_t* __restrict__ xq, float* __restrict__ xsT, int ldxs,
                                                           const int* __restrict__ gather, const TpPeers tp) {
   __shared__ float red[33];
+  const int kt = threadIdx.x == 0 ? kt_begin(KT_PREP) : -1;
   pdl_wait();
   pdl_trigger();
+  kt_stamp(kt, 1);
   if (tp.n && !emb) tp_wait_peers(tp);
   const int ob = blockIdx.x;
   const int b = gather ? gather[ob] : ob;
@@ -314,6 +319,7 @@ __global__ void __launch_bounds__(1024) tc_prep_q8_kernel(float* __restrict__ x,
       q8_quant4(t, gs, i, qr, xsT, ldxs, ob, in);
     }
   }
+  kt_stamp(kt, 6);
 }
 
 // One float4 per thread: src row (attention output), or with h > 0 the SwiGLU of the w1|w3 partials (run.cc:344-347
@@ -321,8 +327,10 @@ __global__ void __launch_bounds__(1024) tc_prep_q8_kernel(float* __restrict__ x,
 __global__ void __launch_bounds__(256) tc_quant_split_kernel(const float* __restrict__ src, long long ld, int nz,
                                                              long long zstride, int h, const int* __restrict__ pos, int K,
                                                              int gs, int8_t* __restrict__ oq, float* __restrict__ osT, int ldxs) {
+  const int kt = threadIdx.x == 0 ? kt_begin(KT_SWIGLU) : -1;
   pdl_wait();
   pdl_trigger();
+  kt_stamp(kt, 1);
   const int b = blockIdx.y;
   const int i4 = blockIdx.x * blockDim.x + threadIdx.x;
   const bool in = 4 * i4 < K;   // K % gs == 0: a group is never cut, but a warp may be
@@ -346,6 +354,7 @@ __global__ void __launch_bounds__(256) tc_quant_split_kernel(const float* __rest
     }
   }
   q8_quant4(r, gs, i4, oq + (size_t)b * K, osT, ldxs, b, in);
+  kt_stamp(kt, 6);
 }
 
 // ---- scratch ----------------------------------------------------------------------------
@@ -865,7 +874,7 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
       THA_CUDA_OK(launch(tc_quant_split_kernel, dim3(ceil_div(hd / 4, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part,
                          (long long)ld_h, pl.z_w13, (long long)R * ld_h, hd, io.pos, hd, gs, sc.hq, sc.hsT, ldxs));
     else
-      THA_CUDA_OK(launch(tc_swiglu_split_kernel, dim3(ceil_div(hd, 256), R), dim3(256), 0, st, pdl, (const float*)sc.part, pl.z_w13,
+      THA_CUDA_OK(launch(tc_swiglu_split_kernel, dim3(ceil_div(hd, 512), R), dim3(256), 0, st, pdl, (const float*)sc.part, pl.z_w13,
                          (long long)R * ld_h, ld_h, io.pos, hd, sc.hh, sc.hl));
     {
       const float* W[1] = {wq ? nullptr : w.w2 + (size_t)l * d * hd};

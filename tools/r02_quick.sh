@@ -7,3 +7,6 @@ python tools/step_timeline.py --batch 256 --pos 10 --show 12 > gpurun_out/timeli
 timeout 300 python bench.py --no-cpu-baseline --no-e2e --no-extra --steps 20 --warmup 5 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['value'],1), 'tok/s', round(d['ms_per_step'],4), 'ms', 'frac', round(d['roofline']['frac'],3)); print(d['roofline'].get('live_shares_us'))"
+THA_DUAL=16 timeout 300 python bench.py --no-cpu-baseline --no-e2e --no-extra --no-shares --steps 20 --warmup 5 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('dual', round(d['value'],1), 'tok/s', round(d['ms_per_step'],4), 'ms')"

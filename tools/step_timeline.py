@@ -12,10 +12,16 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--batch", type=int, default=256)
 ap.add_argument("--pos", type=int, default=10)
 ap.add_argument("--show", type=int, default=24, help="kernels to print (from the second layer on)")
+ap.add_argument("--model", default="s110m", choices=["s110m", "7b"])
+ap.add_argument("--quant", default="f32", choices=["f32", "q8"])
+ap.add_argument("--seq-len", type=int, default=0)
 a = ap.parse_args()
 ck, eng = load_pkg("checkpoint"), load_pkg("engine")
-cfg = ck.STORIES110M
-dw = eng.device_random_weights(cfg, q8=False, seed=1)
+import dataclasses
+cfg = ck.STORIES110M if a.model == "s110m" else ck.LLAMA2_7B
+if a.seq_len:
+    cfg = dataclasses.replace(cfg, seq_len=a.seq_len)
+dw = eng.device_random_weights(cfg, q8=(a.quant == "q8"), seed=1)
 e = eng.Engine(dw, a.batch, with_att=False)
 B = a.batch
 tok = torch.randint(3, cfg.vocab_size, (B,), dtype=torch.int32, device="cuda")
