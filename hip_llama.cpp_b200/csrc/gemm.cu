@@ -1,9 +1,11 @@
 // thaBLAS_s_matmul (src/thaBLAS.cpp:134-170): C[M,N] = A[M,K] . B[K,N], row-major fp32.
-// Exact-fp32 shared-memory tiled kernel (64x64 tile, 4x4 micro-tile per thread) for
-// arbitrary shapes.  The tensor-core (tcgen05) path for prefill lives in gemm_tc.cu.
+// Shapes of at least 32 x 64 x 64 with K % 4 == 0 run on the tensor cores (matmul_tc_route, gemm_tc.cu: tcgen05 3xTF32, fp32
+// accuracy); everything else on this exact-fp32 shared-memory tiled kernel (64x64 tile, 4x4 micro-tile per thread).
 #include "common.cuh"
 
 namespace tha {
+
+int matmul_tc_route(cudaStream_t st, int m, int n, int k, const float* A, const float* B, float* C);   // gemm_tc.cu
 
 constexpr int TM = 64, TN = 64, TK = 16;
 
@@ -56,6 +58,10 @@ extern "C" int tha_matmul_f32(void* stream, int m, int n, int k, const float* A,
     printf("THABLAS ERROR: INVALID ARGUMENT\n");
     fflush(stdout);
     return THA_STATUS_INVALID_ARG;
+  }
+  {  // shapes worth a tensor-core launch go to the tcgen05 3xTF32 kernel (gemm_tc.cu); the rest stay on CUDA cores
+    const int st = matmul_tc_route((cudaStream_t)stream, m, n, k, A, B, C);
+    if (st != THA_STATUS_NOT_SUPPORTED) return st;
   }
   dim3 grid(ceil_div(n, TN), ceil_div(m, TM));
   sgemm_tiled_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(m, n, k, A, B, C);

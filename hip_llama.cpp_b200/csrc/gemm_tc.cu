@@ -881,6 +881,8 @@ int gemm_q8i_launch(cudaStream_t st, const Q8iArgs& a, bool pdl) {
   }
 }
 
+static std::map<int, std::pair<float*, size_t>> g_split_scratch;   // per device: scratch of the C-ABI matmuls ([hi | lo], [Bt | hi | lo])
+
 // Forget tensor maps (call when buffers they describe are freed and their addresses may be reused
 // with another shape -- the key includes the shape, so reuse with the same shape stays valid).
 void gemm_tc_forget() {
@@ -893,7 +895,6 @@ void gemm_tc_forget() {
 using namespace tha;
 
 // C-ABI: out[n*ldo + row] = sum_k W[row,k] X[n,k]   (N rows of activations against one weight matrix)
-static std::map<int, std::pair<float*, size_t>> g_split_scratch;   // per device: [hi | lo]
 
 extern "C" int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const float* W, int M, int K, const float* X, int N,
                                long long ldx) {
@@ -925,6 +926,61 @@ extern "C" int tha_gemm_tf32x3(void* stream, float* out, long long ldo, const fl
   if (!gemm_tc_ok(a)) return THA_STATUS_NOT_SUPPORTED;
   return gemm_tc_launch(st, a, false);
 }
+// thaBLAS_s_matmul (src/thaBLAS.cpp:134-170: C[m, n] = A[m, k] . B[k, n], all row-major fp32) on the tensor cores.
+// The tcgen05 kernel wants both operands K-major: A already is (it plays the activations: one output row per A row), B is
+// transposed once into scratch and plays the weights, so out[i * n + j] = sum_k Bt[j, k] A[i, k] = C[i, j] lands in place.
+// Returns NOT_SUPPORTED for shapes the caller should leave to the CUDA-core kernel (tiny, or K not a multiple of 4).
+namespace tha {
+__global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict__ in, float* __restrict__ out, int rows, int cols) {
+  __shared__ float t[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int r = r0 + ty + i, c = c0 + tx;
+    t[ty + i][tx] = (r < rows && c < cols) ? in[(size_t)r * cols + c] : 0.0f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int c = c0 + ty + i, r = r0 + tx;                 // out[c][r]
+    if (c < cols && r < rows) out[(size_t)c * rows + r] = t[tx][ty + i];
+  }
+}
+
+int matmul_tc_route(cudaStream_t st, int m, int n, int k, const float* A, const float* B, float* C) {
+  if (m < 32 || n < 64 || k < 64 || (k & 3) || (long long)m * n * k < (1ll << 21)) return THA_STATUS_NOT_SUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(A) & 15u) || (reinterpret_cast<uintptr_t>(C) & 3u)) return THA_STATUS_NOT_SUPPORTED;
+  int dev = 0;
+  THA_CUDA_OK(cudaGetDevice(&dev));
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_tc_mu);
+    auto& e = g_split_scratch[dev];
+    const size_t need = (size_t)n * k + (size_t)2 * m * k;
+    if (need > e.second) {
+      if (e.first) THA_CUDA_OK(cudaFree(e.first));
+      THA_CUDA_OK(cudaMalloc(&e.first, need * sizeof(float)));
+      e.second = need;
+    }
+    scratch = e.first;
+  }
+  float* bt = scratch;
+  float* hi = scratch + (size_t)n * k;
+  float* lo = hi + (size_t)m * k;
+  transpose_kernel<<<dim3(ceil_div(n, 32), ceil_div(k, 32)), 256, 0, st>>>(B, bt, k, n);
+  count_launch();
+  split_hilo_kernel<<<dim3(ceil_div(k, 256) < 8 ? ceil_div(k, 256) : 8, m), 256, 0, st>>>(A, k, hi, lo, k);
+  count_launch();
+  THA_LAUNCH_OK();
+  TcArgs a = {};
+  a.n_mats = 1; a.W[0] = bt; a.M[0] = n; a.out_off[0] = 0; a.K = k; a.Xhi = hi; a.Xlo = lo; a.N = m; a.ldx = k;
+  a.out = C; a.ldo = n; a.zstride = 0; a.splits = 1; a.colscale = nullptr;
+  if (!gemm_tc_ok(a)) return THA_STATUS_NOT_SUPPORTED;
+  return gemm_tc_launch(st, a, false);
+}
+}  // namespace tha
+
 extern "C" int tha_matmul_q8_tc(void* stream, float* out, long long ldo, const int8_t* Wq, const float* Ws, int gs, int M, int K,
                                 const int8_t* Xq, const float* XsT, int ldxs, int N) {
   if (!out || !Wq || !Ws || !Xq || !XsT || M < 1 || N < 1 || K < 1 || gs < 1) return THA_STATUS_INVALID_ARG;

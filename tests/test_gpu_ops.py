@@ -111,6 +111,23 @@ def test_matmul(L, m, n, k):
     assert L.c.tha_matmul_f32(stream_ptr(), 0, n, k, P(A), P(B), P(Cc)) == 2
 
 
+# thaBLAS_s_matmul at shapes that take the tcgen05 route (gemm_tc.cu matmul_tc_route: B transposed once, A split hi / lo,
+# 3xTF32): fp32-level accuracy (norm-wise 2e-5 as test_gemm_tf32x3), ragged tiles in every dimension
+@pytest.mark.parametrize("m,n,k", [(1000, 1000, 1000), (256, 4096, 768), (33, 65, 68), (2048, 2048, 2048), (130, 11008, 4096)])
+def test_matmul_tensor_cores(L, m, n, k):
+    rng = np.random.default_rng(m + n + k)
+    a = rng.standard_normal((m, k)).astype(np.float32)
+    b = rng.standard_normal((k, n)).astype(np.float32)
+    A, B, Cc = tdev(a), tdev(b), tdev(np.full((m, n), 3.0, np.float32))
+    for _ in range(2):   # twice: the scratch and the tensor maps are reused
+        L.check(L.c.tha_matmul_f32(stream_ptr(), m, n, k, P(A), P(B), P(Cc)))
+    sync()
+    assert L.c.tha_gemm_check_error() == 0
+    import torch
+    want = (torch.from_numpy(a).double() @ torch.from_numpy(b).double()).numpy()
+    assert_close_scaled(Cc.cpu().numpy(), want, 2e-5, f"matmul {m}x{n}x{k} on the tensor cores")
+
+
 # the weight matmul: stories110M and 7B shapes, odd shapes through the scalar path
 @pytest.mark.parametrize("M,K", [(768, 768), (2048, 768), (768, 2048), (32000, 768), (4096, 11008), (100, 100), (3, 3), (31, 20)])
 @pytest.mark.parametrize("B", [1, 3, 8, 13])
