@@ -120,8 +120,8 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   __shared__ int is_last;
 
   const int kt = threadIdx.x == 0 ? kt_begin(KT_ATTN) : -1;
+  pdl_trigger();   // the next kernel may start its launch (it waits for this grid to complete before touching memory)
   pdl_wait();
-  pdl_trigger();
   kt_stamp(kt, 1);
   const int b = blockIdx.x, seg = blockIdx.y, split = blockIdx.z;
   const int pb = p.pos[b];
@@ -136,7 +136,14 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   const float sqrt_hs = sqrtf((float)hs);
 
   const int n = pb + 1;
-  const int chunk = (n + p.nsplit - 1) / p.nsplit;
+  // Splits in use: the launch provides p.nsplit CTAs per (slot, segment) for the longest context, but a split is only worth
+  // its merge (partials through L2, a fence, an atomic, a second round of loads: ~5 us) when it has a full iteration of rows
+  // to itself.  Short contexts use fewer splits -- one below 33 positions, which then stores its result directly; the
+  // surplus CTAs leave at once.  Every CTA of the (slot, segment) derives the same count from pos[b].
+  int nsp = (n + 31) >> 5;
+  if (nsp > p.nsplit) nsp = p.nsplit;
+  if (split >= nsp) return;
+  const int chunk = (n + nsp - 1) / nsp;
   const int t0 = split * chunk;
   const int t1 = (t0 + chunk < n) ? (t0 + chunk) : n;
 
@@ -233,14 +240,14 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
     }
   }
   float* outp = p.out + (size_t)b * p.dim + seg * (128 * J) + 4 * f;
-  if (p.nsplit == 1) {
+  if (nsp == 1) {
     if (f < F) attn_store(p, outp, make_float4(A.x / L, A.y / L, A.z / L, A.w / L), b);
     kt_stamp(kt, 6);
     return;
   }
 
   // ---- publish this split's partial; the last CTA of (slot, segment) merges all ----
-  const size_t pbase = ((size_t)(b * p.nseg + seg) * p.nsplit) * F;
+  const size_t pbase = ((size_t)(b * p.nseg + seg) * p.nsplit) * F;   // stride of the launch's split count: the scratch was sized by it
   if (f < F) {
     p.part_acc[pbase + (size_t)split * F + f] = A;
     p.part_ml[pbase + (size_t)split * F + f] = make_float2(M, L);
@@ -249,17 +256,17 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   __syncthreads();
   if (threadIdx.x == 0) {
     const int old = atomicAdd(&p.counters[b * p.nseg + seg], 1);
-    is_last = (old == p.nsplit - 1);
+    is_last = (old == nsp - 1);
   }
   __syncthreads();
   if (!is_last) return;
   __threadfence();
   if (f < F) {
     float GM = -INFINITY;
-    for (int s = 0; s < p.nsplit; s++) GM = fmaxf(GM, __ldcg(&p.part_ml[pbase + (size_t)s * F + f]).x);
+    for (int s = 0; s < nsp; s++) GM = fmaxf(GM, __ldcg(&p.part_ml[pbase + (size_t)s * F + f]).x);
     float GL = 0.0f;
     float4 GA = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int s = 0; s < p.nsplit; s++) {   // fixed order: result independent of arrival order
+    for (int s = 0; s < nsp; s++) {   // fixed order: result independent of arrival order
       const float2 ml = __ldcg(&p.part_ml[pbase + (size_t)s * F + f]);
       const float e = (ml.x == -INFINITY) ? 0.0f : expf(ml.x - GM);
       const float4 a = __ldcg(&p.part_acc[pbase + (size_t)s * F + f]);

@@ -39,6 +39,10 @@ void count_launch(int n = 1);
 // Development aid (THA_TRACE=1, graphs off): an event after every launch; tha_trace_dump() prints the time between
 // consecutive events per kernel (= its live duration including the gap before it).
 void trace_launch(const void* fn, cudaStream_t st);
+// THA_CARVEOUT=1 (experiment, off by default): every kernel of a step asks for the maximum shared-memory carve-out, so an SM
+// that alternates between the ~200 KB tensor-core matmuls and small-footprint glue kernels never reconfigures its L1 / shared
+// split.  Measured slower (0.883 -> 0.928 ms/step at 256 slots): the glue kernels lose their L1.
+void prefer_max_smem(const void* fn);
 
 // Launch with optional programmatic-dependent-launch attribute.  Kernels launched
 // this way call pdl_wait() before touching anything a previous kernel wrote and
@@ -57,6 +61,7 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
   count_launch();
+  prefer_max_smem(reinterpret_cast<const void*>(kernel));
   const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
   trace_launch(reinterpret_cast<const void*>(kernel), stream);
   return e;

@@ -83,8 +83,8 @@ __global__ void softmax_kernel(float* x, int size) {
 // x[b,:] = table[token[b],:]  (src/thaDNN.cpp:31-36, B blocking D2D copies there).
 __global__ void embed_kernel(float* __restrict__ x, const float* __restrict__ table,
                              const int* __restrict__ token, const int* __restrict__ pos, int dim) {
+  pdl_trigger();   // the next kernel may start its launch (it waits for this grid to complete before touching memory)
   pdl_wait();
-  pdl_trigger();
   int b = blockIdx.x;
   if (pos[b] < 0) return;
   const float4* src = reinterpret_cast<const float4*>(table + (size_t)token[b] * dim);
@@ -94,8 +94,8 @@ __global__ void embed_kernel(float* __restrict__ x, const float* __restrict__ ta
 
 // Greedy sampler: first maximum wins (strict >, src/llama.cpp:275-286).  One block per row.
 __global__ void argmax_kernel(const float* __restrict__ logits, int vocab, int* __restrict__ next) {
+  pdl_trigger();   // the next kernel may start its launch (it waits for this grid to complete before touching memory)
   pdl_wait();
-  pdl_trigger();
   __shared__ float sv[32];
   __shared__ int si[32];
   const float* p = logits + (size_t)blockIdx.x * vocab;
@@ -153,8 +153,8 @@ __global__ void quantize_q8_kernel(int8_t* __restrict__ q, float* __restrict__ s
 // src/llama.cpp:1027-1050): token[b] = next[b]; pos[b] += 1 for active slots.
 __global__ void advance_slots_kernel(int B, int* __restrict__ token, int* __restrict__ pos,
                                      const int* __restrict__ next, int seq_len) {
+  pdl_trigger();   // the next kernel may start its launch (it waits for this grid to complete before touching memory)
   pdl_wait();
-  pdl_trigger();
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   int p = pos[b];

@@ -115,6 +115,14 @@ static unsigned long long fnv1a(const void* data, size_t n, unsigned long long h
 // CUDA graph and replay it.  `key`/`key_len`: every value the launches depend on.
 template <typename IssueFn>
 static int run_step(cudaStream_t st, Workspace* ws, const void* key_data, size_t key_len, IssueFn issue, bool do_launch = true) {
+  std::lock_guard<std::mutex> guard(ws->mu);
+  if (!ws->step_done) THA_CUDA_OK(cudaEventCreateWithFlags(&ws->step_done, cudaEventDisableTiming));
+  else if (ws->last_stream != st) THA_CUDA_OK(cudaStreamWaitEvent(st, ws->step_done, 0));   // the previous step (another stream) still owns the scratch
+  ws->last_stream = st;
+  struct StepDone {   // recorded behind whatever this call put on the stream
+    Workspace* ws; cudaStream_t st; bool armed;
+    ~StepDone() { if (armed) cudaEventRecord(ws->step_done, st); }
+  } step_done_guard{ws, st, do_launch};
   launches_reset();
   const bool use_graph = graph_enabled() && st != nullptr && st != cudaStreamLegacy;
   if (!use_graph) {
@@ -123,10 +131,24 @@ static int run_step(cudaStream_t st, Workspace* ws, const void* key_data, size_t
     g_last_step_launches = launches_get();
     return rc2;
   }
+  // The cache is keyed by a hash of the argument bytes; a hit is only trusted after comparing the bytes themselves (the
+  // argument structs of the step variants differ in size, and the size is compared first): a colliding entry is recaptured.
   const unsigned long long key = fnv1a(key_data, key_len);
   auto it = ws->graphs.find(key);
+  if (it != ws->graphs.end() && (it->second.key.size() != key_len || memcmp(it->second.key.data(), key_data, key_len) != 0)) {
+    if (it->second.exec) cudaGraphExecDestroy(it->second.exec);
+    ws->graphs.erase(it);
+    it = ws->graphs.end();
+  }
   const bool fresh = it == ws->graphs.end();
   if (fresh) {
+    if (ws->graphs.size() >= WS_MAX_GRAPHS) {   // bounded: drop the least recently replayed graph
+      auto victim = ws->graphs.begin();
+      for (auto g = ws->graphs.begin(); g != ws->graphs.end(); ++g)
+        if (g->second.last_use < victim->second.last_use) victim = g;
+      if (victim->second.exec) cudaGraphExecDestroy(victim->second.exec);
+      ws->graphs.erase(victim);
+    }
     cudaGraph_t graph = nullptr;
     THA_CUDA_OK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
     int rc2 = issue();
@@ -135,11 +157,13 @@ static int run_step(cudaStream_t st, Workspace* ws, const void* key_data, size_t
     if (e != cudaSuccess) { set_last_error("cudaStreamEndCapture", e); return THA_STATUS_EXECUTION_FAILED; }
     StepGraph sg;
     sg.launches = launches_get();
+    sg.key.assign(static_cast<const unsigned char*>(key_data), static_cast<const unsigned char*>(key_data) + key_len);
     e = cudaGraphInstantiate(&sg.exec, graph, 0);
     cudaGraphDestroy(graph);
     if (e != cudaSuccess) { set_last_error("cudaGraphInstantiate", e); return THA_STATUS_EXECUTION_FAILED; }
     it = ws->graphs.emplace(key, sg).first;
   }
+  it->second.last_use = ++ws->graph_clock;
   if (do_launch) THA_CUDA_OK(cudaGraphLaunch(it->second.exec, st));
   else if (fresh) THA_CUDA_OK(cudaGraphUpload(it->second.exec, st));   // prepare only: the executable graph is resident, nothing runs
   g_last_step_launches = it->second.launches;

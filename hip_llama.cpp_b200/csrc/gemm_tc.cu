@@ -505,7 +505,12 @@ int gemm_tc_check_error() {
 // Every tcgen05 instruction costs its issuing thread a few hundred cycles whatever its size (measured: ~300 per
 // kind::i8 MMA, ~200 per tcgen05.ld, ~450 per wait::ld), so the epilogue reads 128 accumulator columns -- 128/NT
 // consecutive groups, laid out back to back in TMEM -- per round trip.
-constexpr int Q8I_THREADS = 256;
+// Epilogue warps: four (one per 32-lane TMEM quarter) for narrow column tiles; EIGHT for NT >= 32 -- two per quarter, each with
+// half of the tile's columns.  At NT = 64 a slot of 16 KB of weights leaves 64 KB of int32 group sums in TMEM (read at 64 B per
+// cycle: ~1000 cycles) and costs 640 scaling instructions per row; with one warp per quarter the two are strictly serial
+// (~1650 cycles per slot, 2.0 TB/s of weights); with two, one warp's TMEM read runs under the other's arithmetic.
+__host__ __device__ constexpr int q8i_epi_warps(int nt) { return nt >= 32 ? 8 : 4; }
+__host__ __device__ constexpr int q8i_threads(int nt) { return 128 + 32 * q8i_epi_warps(nt); }
 
 struct Q8iP {
   int M[3]; int tiles[3]; int out_off[3];
@@ -566,7 +571,7 @@ __device__ __forceinline__ void tc_tmem_ld64(uint32_t taddr, uint32_t* v) {
 // number of TMEM read batches with slots past the end of K: TMA zero-fills them, their integer sums are 0 and the
 // epilogue skips their groups.
 template <int NT>
-__global__ void __launch_bounds__(Q8I_THREADS, 1)
+__global__ void __launch_bounds__(q8i_threads(NT), 1)
 gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__ CUtensorMap mw1,
                 const __grid_constant__ CUtensorMap mw2, const __grid_constant__ CUtensorMap mx, const Q8iP p) {
   using S = Q8iSmem<NT>;
@@ -615,7 +620,7 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
   if (threadIdx.x == 0) {
     for (int s = 0; s < S::NSLOT; s++) tc_mbar_init(&full[s], 1);
     for (int b = 0; b < S::NMD; b++) tc_mbar_init(&mdone[b], 1);
-    for (int b = 0; b < S::NACC_MAX; b++) tc_mbar_init(&aempty[b], 4);
+    for (int b = 0; b < S::NACC_MAX; b++) tc_mbar_init(&aempty[b], q8i_epi_warps(NT));
     *abort_flag = 0;
     kt_q8_s = kt_begin((unsigned long long)KT_GEMM_Q8 | ((unsigned long long)p.splits << 16) | ((unsigned long long)p.n_items << 32));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -705,8 +710,10 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
       }
     }
   } else if (warp >= 4) {
-    // ===== epilogue: thread = weight row (TMEM lane), all NT columns
+    // ===== epilogue: thread = weight row (TMEM lane) x CH columns (all NT, or one half of them: q8i_epi_warps)
+    constexpr int EW = q8i_epi_warps(NT), ET = 32 * EW, CH = NT * 4 / EW;
     const int q = warp & 3;
+    const int c0 = ((warp - 4) >> 2) * CH;       // first column of this warp's share
     const int r = q * 32 + lane;
     const uint32_t tq = tmem_base + ((uint32_t)(q * 32) << 16);
     const int gps_sh = 31 - __clz(gps);
@@ -714,7 +721,7 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
     pdl_wait();                                     // the activation scales come from the previous kernel
     int jb = 0;
     bool ok = true;
-    uint32_t v[128];
+    uint32_t v[LG * CH];
     for (int it = blockIdx.x; it < p.n_items && ok; it += gridDim.x) {
       const Item w = item_of(it);
       const int ng = w.ng;
@@ -722,9 +729,9 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
       const bool row_ok = row < p.M[w.mat];
       const int g0 = w.slot0 * gps;
       const float* srow = p.S[w.mat] + (size_t)(row_ok ? row : p.M[w.mat] - 1) * p.ngrp + g0;
-      float acc[NT];
+      float acc[CH];
 #pragma unroll
-      for (int c = 0; c < NT; c++) acc[c] = 0.0f;
+      for (int c = 0; c < CH; c++) acc[c] = 0.0f;
       // Weight scales: this thread's row, four groups per 128-bit load, requested two to three chunks (8-12 groups,
       // well over a thousand cycles) before their use -- with ~200 KB of the SM's memory carved out as shared, L1
       // keeps next to nothing and every one of these loads is an L2 round trip.
@@ -741,14 +748,14 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
       };
       float4 ws_cur = load_ws4(0), ws_n1 = load_ws4(1), ws_n2 = load_ws4(2);
       {  // the activation scales of this item's K range -> shared memory (NT floats per group)
-        asm volatile("bar.sync 1, 128;" ::: "memory");   // the 4 epilogue warps: everybody is done with the previous item's
+        asm volatile("bar.sync 1, %0;" ::"n"(ET) : "memory");   // the epilogue warps: everybody is done with the previous item's
         const float* src = p.xsT + (size_t)g0 * p.ldxs + w.n0;
-        const int t = threadIdx.x - 128;            // 0..127
-        for (int i = t; i < ng * (NT / 4); i += 128) {
+        const int t = threadIdx.x - 128;            // 0..ET-1
+        for (int i = t; i < ng * (NT / 4); i += ET) {
           const int g = i / (NT / 4), c4 = i - g * (NT / 4);
           reinterpret_cast<float4*>(xs_sm)[i] = __ldg(reinterpret_cast<const float4*>(src + (size_t)g * p.ldxs) + c4);
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(ET) : "memory");
       }
       for (int bi = 0; bi * sb < w.npad && ok; bi++) {
         // the batch's slots: the last slot of each issuer covers the earlier ones (an issuer's commits complete in order)
@@ -763,8 +770,16 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
         if (jb == 0 && bi == 0 && threadIdx.x == 128) kt_stamp(kt, 4);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t ta = tq + (uint32_t)(((s_first & (nacc - 1)) << gps_sh) * NT);
-        tc_tmem_ld64(ta, v);
-        tc_tmem_ld64(ta + 64, v + 64);
+        if (EW == 4) {
+          tc_tmem_ld64(ta, v);
+          tc_tmem_ld64(ta + 64, v + 64);
+        } else {   // this warp's CH columns of each of the LG groups, 16 at a time
+#pragma unroll
+          for (int b = 0; b < LG; b++)
+#pragma unroll
+            for (int c = 0; c < CH; c += 16)
+              tc_tmem_ld16(ta + (uint32_t)(b * NT + c0 + c), *reinterpret_cast<uint32_t(*)[16]>(v + b * CH + c));
+        }
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncwarp();
@@ -778,14 +793,14 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
             const int wi = gi & 3;
             const float ws = wi == 0 ? ws_cur.x : (wi == 1 ? ws_cur.y : (wi == 2 ? ws_cur.z : ws_cur.w));
 #pragma unroll
-            for (int c = 0; c < NT; c += 4) {
-              const float4 t = *reinterpret_cast<const float4*>(xs_sm + gi * NT + c);   // same address in every lane: a broadcast
+            for (int c = 0; c < CH; c += 4) {
+              const float4 t = *reinterpret_cast<const float4*>(xs_sm + gi * NT + c0 + c);   // same address in every lane: a broadcast
               const float xs[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
               for (int e = 0; e < 4; e++) {
                 // |group sum| <= 128 * 127 * 127 < 2^22: 1.5 * 2^23 + i is exact in fp32, so this IS (float)i -- two
                 // full-rate instructions instead of a quarter-rate I2F
-                const float f = __int_as_float(0x4B400000 + (int)v[b * NT + c + e]) - 12582912.0f;
+                const float f = __int_as_float(0x4B400000 + (int)v[b * CH + c + e]) - 12582912.0f;
                 acc[c + e] = __fadd_rn(acc[c + e], __fmul_rn(__fmul_rn(f, ws), xs[e]));   // runq.c:334, no contraction
               }
             }
@@ -795,8 +810,8 @@ gemm_q8i_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__
       float* outz = p.out + (size_t)(it % p.splits) * p.zstride + p.out_off[w.mat] + row;
       if (ok && row_ok) {
 #pragma unroll
-        for (int c = 0; c < NT; c++) {
-          const int n = w.n0 + c;
+        for (int c = 0; c < CH; c++) {
+          const int n = w.n0 + c0 + c;
           if (n < p.N) outz[(size_t)n * p.ldo] = acc[c];
         }
       }
@@ -833,7 +848,7 @@ static int q8i_launch_nt(cudaStream_t st, const CUtensorMap* mw, const CUtensorM
   using S = Q8iSmem<NT>;
   auto k = gemm_q8i_kernel<NT>;
   THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
-  THA_CUDA_OK(launch(k, grid, dim3(Q8I_THREADS), (size_t)S::TOTAL, st, pdl, mw[0], mw[1], mw[2], mx, p));
+  THA_CUDA_OK(launch(k, grid, dim3(q8i_threads(NT)), (size_t)S::TOTAL, st, pdl, mw[0], mw[1], mw[2], mx, p));
   return THA_STATUS_SUCCESS;
 }
 

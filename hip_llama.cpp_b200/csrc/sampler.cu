@@ -209,8 +209,8 @@ __device__ bool smp_select(const float* pr, int n, float cutoff, u64 target, Smp
 
 __global__ void __launch_bounds__(SMP_THREADS, 2) sample_kernel(const SampleP P) {
   __shared__ SmpShared sh;
+  pdl_trigger();   // the next kernel may start its launch (it waits for this grid to complete before touching memory)
   pdl_wait();
-  pdl_trigger();
   const int b = blockIdx.x, n = P.vocab;
   if (P.pos[b] < 0) {
     if (threadIdx.x == 0) { P.next[b] = 0; if (P.reseed && P.reseed[b]) P.rng[b] = P.reseed[b]; }

@@ -91,8 +91,8 @@ __device__ __forceinline__ void tp_add_partials(float4& v, const TpPeers& t, lon
   }
 }
 __global__ void tp_epoch_kernel(unsigned* epoch) {
+  pdl_trigger();   // the next kernel may start its launch (it waits for this grid to complete before touching memory)
   pdl_wait();
-  pdl_trigger();
   if (threadIdx.x == 0) *epoch += 1u;
 }
 
@@ -107,8 +107,8 @@ __global__ void __launch_bounds__(1024) tc_prep_kernel(float* __restrict__ x, co
                                                       const int* __restrict__ gather, const TpPeers tp) {
   __shared__ float red[33];
   const int kt = threadIdx.x == 0 ? kt_begin(KT_PREP) : -1;
+  pdl_trigger();   // the next kernel may start its launch (it waits for this grid to complete before touching memory)
   pdl_wait();
-  pdl_trigger();
   kt_stamp(kt, 1);
   if (tp.n && !emb) tp_wait_peers(tp);
   const int ob = blockIdx.x;
@@ -131,10 +131,17 @@ __global__ void __launch_bounds__(1024) tc_prep_kernel(float* __restrict__ x, co
       v = xr[i];
       if (tp.n) tp_add_partials(v, tp, zstride, (size_t)b * d + 4 * i);
       else {
-#pragma unroll 4
-        for (int z = 0; z < nz; z++) {   // fixed order; unrolled so the loads of several partials are in flight together
-          const float4 pz = *reinterpret_cast<const float4*>(part + (size_t)z * zstride + (size_t)b * d + 4 * i);
-          v.x += pz.x; v.y += pz.y; v.z += pz.z; v.w += pz.w;
+        // eight partials of this element are requested before the first one is added (one L2 round trip per eight splits,
+        // not per four -- the block may have 1024 threads: 64 registers each); the sum keeps the fixed order z = 0, 1, ...
+        const float* pp = part + (size_t)b * d + 4 * i;
+        for (int z0 = 0; z0 < nz; z0 += 8) {
+          float4 pz[8];
+#pragma unroll
+          for (int u = 0; u < 8; u++)
+            if (z0 + u < nz) pz[u] = ldg_stream(reinterpret_cast<const float4*>(pp + (size_t)(z0 + u) * zstride));
+#pragma unroll
+          for (int u = 0; u < 8; u++)
+            if (z0 + u < nz) { v.x += pz[u].x; v.y += pz[u].y; v.z += pz[u].z; v.w += pz[u].w; }
         }
       }
     }
@@ -165,8 +172,8 @@ __global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __res
                                                               float* __restrict__ vc, long long kv_bs, int loff,
                                                               const int* __restrict__ slot, const KvPaged pg) {
   const int kt = threadIdx.x == 0 ? kt_begin(KT_ROPE) : -1;
+  pdl_trigger();   // the next kernel may start its launch (it waits for this grid to complete before touching memory)
   pdl_wait();
-  pdl_trigger();
   kt_stamp(kt, 1);
   const int b = blockIdx.y, pb = pos[b];
   if (pb < 0) return;
@@ -220,8 +227,8 @@ __global__ void __launch_bounds__(256) tc_swiglu_split_kernel(const float* __res
                                                               int ld, const int* __restrict__ pos, int h,
                                                               float* __restrict__ hh, float* __restrict__ hl) {
   const int kt = threadIdx.x == 0 ? kt_begin(KT_SWIGLU) : -1;
+  pdl_trigger();   // the next kernel may start its launch (it waits for this grid to complete before touching memory)
   pdl_wait();
-  pdl_trigger();
   kt_stamp(kt, 1);
   const int b = blockIdx.y;
   const int i = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
@@ -265,8 +272,8 @@ __global__ void __launch_bounds__(1024) tc_prep_q8_kernel(float* __restrict__ x,
                                                           const int* __restrict__ gather, const TpPeers tp) {
   __shared__ float red[33];
   const int kt = threadIdx.x == 0 ? kt_begin(KT_PREP) : -1;
+  pdl_trigger();   // the next kernel may start its launch (it waits for this grid to complete before touching memory)
   pdl_wait();
-  pdl_trigger();
   kt_stamp(kt, 1);
   if (tp.n && !emb) tp_wait_peers(tp);
   const int ob = blockIdx.x;
@@ -328,8 +335,8 @@ __global__ void __launch_bounds__(256) tc_quant_split_kernel(const float* __rest
                                                              long long zstride, int h, const int* __restrict__ pos, int K,
                                                              int gs, int8_t* __restrict__ oq, float* __restrict__ osT, int ldxs) {
   const int kt = threadIdx.x == 0 ? kt_begin(KT_SWIGLU) : -1;
+  pdl_trigger();   // the next kernel may start its launch (it waits for this grid to complete before touching memory)
   pdl_wait();
-  pdl_trigger();
   kt_stamp(kt, 1);
   const int b = blockIdx.y;
   const int i4 = blockIdx.x * blockDim.x + threadIdx.x;

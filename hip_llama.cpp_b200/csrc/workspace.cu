@@ -3,6 +3,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -26,6 +27,21 @@ void set_last_error(const char* where, cudaError_t e) {
   cudaGetLastError();  // clear the sticky-free error so later calls are not poisoned
 }
 
+static int env_flag(const char* name, int dflt);
+void prefer_max_smem(const void* fn) {
+  static int on = -1;
+  if (on < 0) on = env_flag("THA_CARVEOUT", 0);   // measured: 0.883 -> 0.928 ms/step with it on (the glue kernels lose their L1)
+  if (!on) return;
+  static std::mutex mu;
+  static std::map<std::pair<int, const void*>, bool> done;   // per (device, kernel)
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return;
+  std::lock_guard<std::mutex> lk(mu);
+  bool& d = done[std::make_pair(dev, fn)];
+  if (d) return;
+  d = true;
+  if (cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared) != cudaSuccess) cudaGetLastError();
+}
 static int env_flag(const char* name, int dflt) {
   const char* v = getenv(name);
   if (!v || !*v) return dflt;

@@ -8,6 +8,7 @@
 #include "common.cuh"
 
 #include <map>
+#include <mutex>
 #include <tuple>
 #include <vector>
 
@@ -18,7 +19,10 @@ struct RopeTable { float* cos_d = nullptr; float* sin_d = nullptr; };
 struct StepGraph {
   cudaGraphExec_t exec = nullptr;
   int launches = 0;
+  std::vector<unsigned char> key;        // the argument bytes the graph was captured for (the map key is only their hash)
+  unsigned long long last_use = 0;       // for eviction: ws->graph_clock at the last replay
 };
+constexpr size_t WS_MAX_GRAPHS = 64;     // cached executable graphs per workspace; the least recently used one goes first
 
 struct Workspace {
   int device = -1;
@@ -38,6 +42,14 @@ struct Workspace {
   std::map<std::pair<int, int>, RopeTable> rope;
   // cached graphs of the decode step keyed by a hash of every launch argument
   std::map<unsigned long long, StepGraph> graphs;
+  unsigned long long graph_clock = 0;
+  // One step at a time: the scratch buffers, the attention split counters and the graph cache are shared by every stream and
+  // host thread that uses this device.  run_step() serialises host threads on `mu`, records `step_done` behind every step and,
+  // when the stream differs from the previous step's, makes the new stream wait for that event first -- two streams never have
+  // steps in flight over the same scratch.  (last_stream is only compared, never dereferenced: it may have been destroyed.)
+  std::mutex mu;
+  cudaStream_t last_stream = nullptr;
+  cudaEvent_t step_done = nullptr;
   // two half-batches of a step as two concurrent branches of the graph (forward.cu, "dual"): the second branch's
   // scratch owner, its stream and the fork / join events
   Workspace* sibling = nullptr;
