@@ -61,9 +61,9 @@ for r in recs:
     launches.append((kind, last, r))
 for kind, last, r in launches:
     extra = ""
-    if kind == 1:
+    if kind in (1, 7):
         extra = f" z={(int(r[15]) >> 16) & 0xFFFF} items={int(r[15]) >> 32}"
-    print(f"{KIND.get(kind, '?'):7s} {'last ' if last else 'first'} enter={fmt(r, 0)} dep={fmt(r, 1)} s2={fmt(r, 2)} s3={fmt(r, 3)} s4={fmt(r, 4)} s5={fmt(r, 5)} done={fmt(r, 6)}{extra}" + (" epi: " + " ".join(fmt(r, k) for k in range(7, 13)) if kind == 1 else ""))
+    print(f"{KIND.get(kind, '?'):7s} {'last ' if last else 'first'} enter={fmt(r, 0)} dep={fmt(r, 1)} s2={fmt(r, 2)} s3={fmt(r, 3)} s4={fmt(r, 4)} s5={fmt(r, 5)} done={fmt(r, 6)}{extra}" + (" epi: " + " ".join(fmt(r, k) for k in range(7, 15)) if kind in (1, 7) else ""))
     shown += 1
     if shown >= a.show * 2 + 2 * skip:
         break
