@@ -10,10 +10,15 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--model", default="7b"); ap.add_argument("--seqs", type=int, default=1)
 ap.add_argument("--len", type=int, default=2048); ap.add_argument("--reps", type=int, default=3)
 ap.add_argument("--logits", type=int, default=1)
+ap.add_argument("--bf16", type=int, default=0, help="1: the bf16 weight path (tha_prefill_bf16)")
 a = ap.parse_args()
 eng = load_pkg("engine")
 args = argparse.Namespace(model=a.model, quant="f32", seq_len=0)
-cfg, dw, _ = bench.build_weights(args, "cuda")
+if a.bf16:
+    cfg, _ck = bench.model_config(a.model)
+    dw = eng.DeviceWeightsBF16.random(cfg, seed=1337, device="cuda")
+else:
+    cfg, dw, _ = bench.build_weights(args, "cuda")
 e = eng.Engine(dw, a.seqs, device="cuda", with_att=False)
 rng = np.random.default_rng(0)
 seqs = [(i, 0, rng.integers(3, cfg.vocab_size, size=a.len).astype(np.int32)) for i in range(a.seqs)]
@@ -32,4 +37,4 @@ T = a.seqs * a.len
 d, h, L, kvd = cfg.dim, cfg.hidden_dim, cfg.n_layers, cfg.dim // cfg.n_heads * cfg.n_kv_heads
 pmm = L * (d * d * 2 + 2 * d * kvd + 3 * d * h)
 flops = 2 * T * pmm + 2 * L * a.seqs * a.len * a.len * d + 2 * a.seqs * cfg.vocab_size * d
-print(f"{a.model} prefill {a.seqs} x {a.len}: {ms:.2f} ms  {T / ms * 1e3:.0f} prompt tok/s  {flops / ms / 1e9:.1f} useful TFLOP/s  launches {e.last_step_launches()} abort={err}")
+print(f"{a.model} {'bf16' if a.bf16 else 'f32'} prefill {a.seqs} x {a.len}: {ms:.2f} ms  {T / ms * 1e3:.0f} prompt tok/s  {flops / ms / 1e9:.1f} useful TFLOP/s  launches {e.last_step_launches()} abort={err}")
