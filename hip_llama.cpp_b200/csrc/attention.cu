@@ -84,6 +84,16 @@ __global__ void mha_weighted_kernel(const int* __restrict__ pos, float* __restri
 }
 
 // ------------------------------------------------------------------ fused ----------
+// RoPE + KV scatter inside the attention kernel (one launch and one dependency less per layer).  The wq|wk|wv matmul leaves
+// nz split-K partials of the row [q | k | v]; a CTA sums its own slice of them: q (rotated, run.cc:271-286 with the host-built
+// tables) for its segment, and -- in the CTA that owns the end of the context -- the new position's k (rotated) and v for
+// the same columns, which it writes to the cache row of pos[b] and folds into the softmax from registers.  The cache rows
+// 0 .. pos-1 are read as before.  q_out (nullable) keeps RunState.q as the reference leaves it.
+struct AttnRope {
+  const float* part; int nz; long long zstride; int ld;     // partials: part[z * zstride + b * ld + column]
+  const float* rc; const float* rs;                         // cos / sin tables [seq_len][head_size / 2]
+  float* q_out; float* kc_w; float* vc_w;                   // kc_w / vc_w: the same rows as AttnP.kc / vc, writable
+};
 struct AttnP {
   const int* pos; const float* q; float* out;
   const float* kc; const float* vc;         // already offset by loff
@@ -93,6 +103,7 @@ struct AttnP {
   float* out_hi; float* out_lo;             // nullable: the tf32 hi/lo split of `out` for the tensor-core wo matmul
   int8_t* out_q; float* out_sT; int ldxs, gs;   // nullable: `out` quantised per group (runq.c:145-171) for the int8 wo matmul
   KvPaged pg;                                   // pg.table != nullptr: kc / vc are block pools (BatchManager), rows found through the table
+  AttnRope rp;                                  // rp.part != nullptr (ROPE kernels): q / k / v of the new position come from the matmul's partials
 };
 
 __device__ __forceinline__ float attn_tf32(float v) { return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u); }
@@ -112,7 +123,7 @@ __device__ __forceinline__ void attn_store(const AttnP& p, float* outp, float4 r
 }
 
 // J = float4 slots per lane; a CTA covers a segment of 128*J query floats (whole heads).
-template <int J>
+template <int J, bool ROPE = false>
 __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   constexpr int F = 32 * J;  // slots per segment
   extern __shared__ float4 sm_acc[];                 // [warps][F]
@@ -145,15 +156,47 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   if (split >= nsp) return;
   const int chunk = (n + nsp - 1) / nsp;
   const int t0 = split * chunk;
-  const int t1 = (t0 + chunk < n) ? (t0 + chunk) : n;
+  const int t1f = (t0 + chunk < n) ? (t0 + chunk) : n;
+  // ROPE: the row of position pb is not in the cache yet -- the cache rows end at pb, the new row is folded in afterwards by
+  // warp 0 of the CTA whose range reaches the end
+  const bool own_new = ROPE && t1f == n && warp == 0;
+  const int t1 = (ROPE && t1f == n) ? n - 1 : t1f;
 
   float4 qv[J];
   int koff[J];
+  float4 knew[ROPE ? J : 1], vnew[ROPE ? J : 1];
 #pragma unroll
   for (int j = 0; j < J; j++) {
     const int qo = seg * (128 * J) + 4 * (lane + 32 * j);
-    qv[j] = *reinterpret_cast<const float4*>(p.q + (size_t)b * p.dim + qo);
     koff[j] = ((qo / hs) / p.kv_mul) * hs + (qo % hs);
+    if (!ROPE) {
+      qv[j] = *reinterpret_cast<const float4*>(p.q + (size_t)b * p.dim + qo);
+    } else {
+      const float* pr = p.rp.part + (size_t)b * p.rp.ld;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), kk = a, vv = a;
+      for (int z = 0; z < p.rp.nz; z++) {   // fixed order, as tc_rope_scatter_kernel sums them
+        const float4 t = *reinterpret_cast<const float4*>(pr + (size_t)z * p.rp.zstride + qo);
+        a.x += t.x; a.y += t.y; a.z += t.z; a.w += t.w;
+        if (own_new) {
+          const float4 tk = *reinterpret_cast<const float4*>(pr + (size_t)z * p.rp.zstride + p.dim + koff[j]);
+          const float4 tv = *reinterpret_cast<const float4*>(pr + (size_t)z * p.rp.zstride + p.dim + p.kv_dim + koff[j]);
+          kk.x += tk.x; kk.y += tk.y; kk.z += tk.z; kk.w += tk.w;
+          vv.x += tv.x; vv.y += tv.y; vv.z += tv.z; vv.w += tv.w;
+        }
+      }
+      const int jj = (qo % hs) >> 1;         // the float4 holds the pairs jj and jj + 1 of its head (q and k alike)
+      const float2 c2 = *reinterpret_cast<const float2*>(p.rp.rc + (size_t)pb * (hs >> 1) + jj);
+      const float2 s2 = *reinterpret_cast<const float2*>(p.rp.rs + (size_t)pb * (hs >> 1) + jj);
+      qv[j] = make_float4(a.x * c2.x - a.y * s2.x, a.x * s2.x + a.y * c2.x, a.z * c2.y - a.w * s2.y, a.z * s2.y + a.w * c2.y);
+      if (p.rp.q_out && split == 0 && warp == 0) *reinterpret_cast<float4*>(p.rp.q_out + (size_t)b * p.dim + qo) = qv[j];
+      if (own_new) {
+        knew[j] = make_float4(kk.x * c2.x - kk.y * s2.x, kk.x * s2.x + kk.y * c2.x, kk.z * c2.y - kk.w * s2.y, kk.z * s2.y + kk.w * c2.y);
+        vnew[j] = vv;
+        const long long ro = p.pg.table ? kv_paged_off(p.pg, b, pb, p.kv_dim) : (long long)b * p.kv_batch_stride + (long long)pb * p.kv_dim;
+        *reinterpret_cast<float4*>(p.rp.kc_w + ro + koff[j]) = knew[j];
+        *reinterpret_cast<float4*>(p.rp.vc_w + ro + koff[j]) = vnew[j];
+      }
+    }
   }
   float m[J], l[J];
   float4 acc[J];
@@ -215,6 +258,22 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
         a.z = fmaf(pr, vr[r][j].z, a.z); a.w = fmaf(pr, vr[r][j].w, a.w);
       }
       l[j] = ls; acc[j] = a; m[j] = mn;
+    }
+  }
+
+  if (ROPE && own_new) {   // ---- the new position, from registers
+#pragma unroll
+    for (int j = 0; j < J; j++) {
+      float sc = dot4(qv[j], knew[j], 0.0f);
+      for (int o = LH >> 1; o > 0; o >>= 1) sc += __shfl_xor_sync(THA_FULL_MASK, sc, o);
+      sc *= inv_sqrt_hs;
+      const float mn = fmaxf(m[j], sc);
+      const float corr = __expf(m[j] - mn);   // exp(-inf) = 0 when this is the only row
+      const float pr = __expf(sc - mn);
+      l[j] = l[j] * corr + pr;
+      acc[j] = make_float4(fmaf(pr, vnew[j].x, acc[j].x * corr), fmaf(pr, vnew[j].y, acc[j].y * corr),
+                           fmaf(pr, vnew[j].z, acc[j].z * corr), fmaf(pr, vnew[j].w, acc[j].w * corr));
+      m[j] = mn;
     }
   }
 
@@ -356,10 +415,10 @@ static int attn_pick_warps(void (*k)(const AttnP), int J, long long ctas) {
 }
 
 // kc / vc are the caches already offset to the layer (base + loff).
-int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
-                      const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
-                      int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo, int8_t* out_q, float* out_sT,
-                      int ldxs, int gs, const KvPaged* pg) {
+static int attn_fused_launch_impl(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
+                                  const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
+                                  int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo, int8_t* out_q, float* out_sT,
+                                  int ldxs, int gs, const KvPaged* pg, const AttnRope* rp) {
   const int dim = n_heads * head_size, kv_dim = n_kv_heads * head_size;
   const int J = fused_J(n_heads, head_size, dim, n_heads / n_kv_heads);
   if (!J || kv_dim % 4) return THA_STATUS_NOT_SUPPORTED;
@@ -367,6 +426,9 @@ int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_
   p.pos = pos_d; p.q = q; p.out = out; p.kc = kc; p.vc = vc; p.out_hi = out_hi; p.out_lo = out_lo;
   p.out_q = out_q; p.out_sT = out_sT; p.ldxs = ldxs; p.gs = gs;
   if (pg) p.pg = *pg; else p.pg = KvPaged{};
+  p.rp = rp ? *rp : AttnRope{};
+  if (rp && (J > 2 || !rp->part || !rp->rc || !rp->rs || !rp->kc_w || !rp->vc_w || (rp->ld & 3) || (rp->zstride & 3) || (head_size & 3)))
+    return THA_STATUS_NOT_SUPPORTED;
   if (out_q && (gs < 32 || gs > 128 || (gs & (gs - 1)) || 128 % gs)) return THA_STATUS_NOT_SUPPORTED;
   p.kv_batch_stride = kv_batch_stride; p.kv_dim = kv_dim; p.head_size = head_size;
   p.kv_mul = n_heads / n_kv_heads; p.dim = dim;
@@ -380,7 +442,8 @@ int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_
   p.part_acc = ws->part_acc; p.part_ml = ws->part_ml; p.counters = ws->counters;
   void (*k)(const AttnP) = nullptr;
   switch (J) {
-    case 1: k = attn_fused_kernel<1>; break; case 2: k = attn_fused_kernel<2>; break;
+    case 1: k = rp ? attn_fused_kernel<1, true> : attn_fused_kernel<1>; break;
+    case 2: k = rp ? attn_fused_kernel<2, true> : attn_fused_kernel<2>; break;
     case 3: k = attn_fused_kernel<3>; break; case 4: k = attn_fused_kernel<4>; break;
     case 5: k = attn_fused_kernel<5>; break; case 6: k = attn_fused_kernel<6>; break;
     case 7: k = attn_fused_kernel<7>; break; case 8: k = attn_fused_kernel<8>; break;
@@ -391,6 +454,30 @@ int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_
   if (smem > 40 * 1024) THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   THA_CUDA_OK(launch(k, grid, block, smem, stream, pdl, p));
   return THA_STATUS_SUCCESS;
+}
+
+int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads,
+                      const float* q, float* out, const float* kc, const float* vc, long long kv_batch_stride,
+                      int head_size, int seq_len, bool pdl, float* out_hi, float* out_lo, int8_t* out_q, float* out_sT,
+                      int ldxs, int gs, const KvPaged* pg) {
+  return attn_fused_launch_impl(stream, ws, B, pos_d, n_heads, n_kv_heads, q, out, kc, vc, kv_batch_stride, head_size, seq_len, pdl,
+                                out_hi, out_lo, out_q, out_sT, ldxs, gs, pg, nullptr);
+}
+// Segments of at most two float4 per lane (every multi-head model; wide grouped-query segments keep the separate kernel: the
+// new row's k / v would cost them 16 registers per float4)
+bool attn_fused_rope_supported(int n_heads, int n_kv_heads, int head_size) {
+  const int J = fused_J(n_heads, head_size, n_heads * head_size, n_heads / n_kv_heads);
+  return J == 1 || J == 2;
+}
+// The same with RoPE + KV scatter of the new position inside the kernel: part / nz / zstride / ld describe the wq|wk|wv
+// partials, q_out (nullable) receives the rotated queries, the new k / v rows are written through kc / vc.
+int attn_fused_rope_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads, float* q_out,
+                           float* out, float* kc, float* vc, long long kv_batch_stride, int head_size, int seq_len, bool pdl,
+                           float* out_hi, float* out_lo, int8_t* out_q, float* out_sT, int ldxs, int gs, const KvPaged* pg,
+                           const float* part, int nz, long long zstride, int ld, const float* rc, const float* rs) {
+  AttnRope rp = {part, nz, zstride, ld, rc, rs, q_out, kc, vc};
+  return attn_fused_launch_impl(stream, ws, B, pos_d, n_heads, n_kv_heads, q_out, out, kc, vc, kv_batch_stride, head_size, seq_len, pdl,
+                                out_hi, out_lo, out_q, out_sT, ldxs, gs, pg, &rp);
 }
 
 }  // namespace tha
@@ -516,6 +603,7 @@ extern "C" int tha_mha_fused_v1_f32_static(void* stream, int n_batches, const in
   p.pos = pos_d; p.q = q; p.out = xb; p.kc = key_cache + loff; p.vc = value_cache + loff;
   p.out_hi = nullptr; p.out_lo = nullptr; p.out_q = nullptr; p.out_sT = nullptr; p.ldxs = 0; p.gs = 0;
   p.pg = KvPaged{};
+  p.rp = AttnRope{};
   p.kv_batch_stride = (long long)n_layers * seq_len * kv_dim; p.kv_dim = kv_dim; p.head_size = head_size;
   p.kv_mul = n_heads / n_kv_heads; p.dim = dim;
   p.nseg = dim / (128 * J);

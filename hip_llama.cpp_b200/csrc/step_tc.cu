@@ -42,6 +42,11 @@ int attn_fused_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_
                       float* out_sT = nullptr, int ldxs = 0, int gs = 0, const KvPaged* pg = nullptr);
 
 bool attn_prefill_supported(int head_size, int kv_dim);
+bool attn_fused_rope_supported(int n_heads, int n_kv_heads, int head_size);
+int attn_fused_rope_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads, float* q_out,
+                           float* out, float* kc, float* vc, long long kv_batch_stride, int head_size, int seq_len, bool pdl,
+                           float* out_hi, float* out_lo, int8_t* out_q, float* out_sT, int ldxs, int gs, const KvPaged* pg,
+                           const float* part, int nz, long long zstride, int ld, const float* rc, const float* rs);
 int attn_prefill_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_heads, int head_size, const float* q,
                         float* out, float* out_hi, float* out_lo, const float* kc, const float* vc,
                         long long kv_batch_stride, const int* row_slot, const int* row_pos, const int* tile_row0,
@@ -840,7 +845,10 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
     const KvPaged pg = paged ? kv_paged_of(pool, L, kvd, l) : KvPaged{};
     const float* kcl = paged ? s.key_cache : s.key_cache + loff;      // layer's cache rows: pool base, or slab + layer offset
     const float* vcl = paged ? s.value_cache : s.value_cache + loff;
-    if (!(skip & 8))
+    // decode rows: RoPE + KV scatter ride in the attention kernel (one launch and one dependency less per layer)
+    const bool rope_in_attn = io.n_tiles == 0 && !(!io.logits && l == L - 1) && !(skip & 2) && rope_fuse_mode() &&
+                              attn_fused_rope_supported(c.n_heads, c.n_kv_heads, hs);
+    if (!(skip & 8) && !rope_in_attn)
     THA_CUDA_OK(launch(tc_rope_scatter_kernel, dim3(ceil_div(ld_qkv / 2, 512), R), dim3(256), 0, st, pdl, (const float*)sc.part,
                        pl.z_qkv, (long long)R * ld_qkv, ld_qkv, io.pos, da, kvd, hs, rc, rs, io.q, s.key_cache, s.value_cache,
                        kv_bs, loff, io.slot, pg));
@@ -853,6 +861,11 @@ static int issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
       THA_TRY_RC(attn_prefill_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, wq ? nullptr : sc.xh,
                                      wq ? nullptr : sc.xl, kcl, vcl, kv_bs, io.slot, io.pos,
                                      io.tile_row0, io.tile_n, pdl, &pg));
+    } else if (rope_in_attn) {
+      THA_TRY_RC(attn_fused_rope_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, const_cast<float*>(kcl),
+                                        const_cast<float*>(vcl), kv_bs, hs, c.seq_len, pdl, wq ? nullptr : sc.xh, wq ? nullptr : sc.xl,
+                                        wq ? sc.xq : nullptr, wq ? sc.xsT : nullptr, ldxs, gs, &pg, sc.part, pl.z_qkv,
+                                        (long long)R * ld_qkv, ld_qkv, rc, rs));
     } else {
       // Q8_0: the quantiser of the attention output (runq.c:437) runs in the attention kernel's final store
       THA_TRY_RC(attn_fused_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, kcl,

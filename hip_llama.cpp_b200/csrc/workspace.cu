@@ -88,6 +88,12 @@ int chain_mode() {   // 1: matmul chains with fused epilogues (chain_tc.cu) wher
   return g_chain;
 }
 int* opt_chain() { chain_mode(); return &g_chain; }
+static int g_rope_fuse = -2;
+int rope_fuse_mode() {   // 1 (default): RoPE + KV scatter of a decode step inside the attention kernel; 0: tc_rope_scatter_kernel
+  if (g_rope_fuse == -2) { const char* v = getenv("THA_ROPE_FUSE"); g_rope_fuse = (v && *v) ? atoi(v) : 1; }
+  return g_rope_fuse;
+}
+int* opt_rope_fuse() { rope_fuse_mode(); return &g_rope_fuse; }
 void count_launch(int n) { g_launches += n; }
 int launches_reset() { int v = g_launches; g_launches = 0; return v; }
 int launches_get() { return g_launches; }
@@ -319,6 +325,12 @@ extern "C" int tha_set_option(const char* name, int value) {
     return THA_STATUS_SUCCESS;
   }
   if (!strcmp(name, "chain")) { *tha::opt_chain() = value; return THA_STATUS_SUCCESS; }
+  if (!strcmp(name, "ropefuse")) {   // cached graphs were captured with the other kernel sequence
+    *tha::opt_rope_fuse() = value != 0;
+    std::lock_guard<std::mutex> lk(tha::g_mu);
+    for (auto& kv : tha::g_ws) tha::ws_drop_graphs(kv.second);
+    return THA_STATUS_SUCCESS;
+  }
   if (!strcmp(name, "mega")) { tha::mega_set_enabled(value); return THA_STATUS_SUCCESS; }
   return THA_STATUS_INVALID_ARG;
 }
