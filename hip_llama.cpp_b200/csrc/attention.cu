@@ -93,6 +93,7 @@ struct AttnRope {
   const float* part; int nz; long long zstride; int ld;     // partials: part[z * zstride + b * ld + column]
   const float* rc; const float* rs;                         // cos / sin tables [seq_len][head_size / 2]
   float* q_out; float* kc_w; float* vc_w;                   // kc_w / vc_w: the same rows as AttnP.kc / vc, writable
+  uint16_t* out_b16;                                        // nullable (bf16 model path): the output row rounded to bf16 (nearest even) as well
 };
 struct AttnP {
   const int* pos; const float* q; float* out;
@@ -113,6 +114,14 @@ __device__ __forceinline__ void attn_store(const AttnP& p, float* outp, float4 r
   if (p.out_q) {
     const int i4 = (int)((outp - p.out) - (size_t)b * p.dim) >> 2;
     q8_quant4(r, p.gs, i4, p.out_q + (size_t)b * p.dim, p.out_sT, p.ldxs, b, true);
+  }
+  if (p.rp.out_b16) {   // the rounding of step_bf16.cu's bf_round_kernel (nearest even; NaN stays NaN)
+    auto b16 = [](float f) -> uint32_t {
+      const uint32_t u = __float_as_uint(f);
+      if ((u & 0x7FFFFFFFu) > 0x7F800000u) return (u >> 16) | 0x40u;
+      return (u + 0x7FFFu + ((u >> 16) & 1u)) >> 16;
+    };
+    *reinterpret_cast<uint2*>(p.rp.out_b16 + (outp - p.out)) = make_uint2(b16(r.x) | (b16(r.y) << 16), b16(r.z) | (b16(r.w) << 16));
   }
   if (p.out_hi) {
     const size_t off = outp - p.out;
@@ -137,6 +146,8 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
   const int b = blockIdx.x, seg = blockIdx.y, split = blockIdx.z;
   const int pb = p.pos[b];
   if (pb < 0) {   // idle slot: the int8 matmul that follows gets zeros (as the stand-alone quantiser gave it)
+    if (p.rp.out_b16 && split == 0 && threadIdx.x < F)   // bf16 path: zeros into the wo matmul, as bf_round_kernel wrote
+      *reinterpret_cast<uint2*>(p.rp.out_b16 + (size_t)b * p.dim + seg * (128 * J) + 4 * threadIdx.x) = make_uint2(0u, 0u);
     if (p.out_q && split == 0 && threadIdx.x < F)
       q8_quant4(make_float4(0.f, 0.f, 0.f, 0.f), p.gs, (seg * (128 * J) >> 2) + threadIdx.x, p.out_q + (size_t)b * p.dim, p.out_sT,
                 p.ldxs, b, true);
@@ -474,8 +485,8 @@ bool attn_fused_rope_supported(int n_heads, int n_kv_heads, int head_size) {
 int attn_fused_rope_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads, float* q_out,
                            float* out, float* kc, float* vc, long long kv_batch_stride, int head_size, int seq_len, bool pdl,
                            float* out_hi, float* out_lo, int8_t* out_q, float* out_sT, int ldxs, int gs, const KvPaged* pg,
-                           const float* part, int nz, long long zstride, int ld, const float* rc, const float* rs) {
-  AttnRope rp = {part, nz, zstride, ld, rc, rs, q_out, kc, vc};
+                           const float* part, int nz, long long zstride, int ld, const float* rc, const float* rs, uint16_t* out_b16) {
+  AttnRope rp = {part, nz, zstride, ld, rc, rs, q_out, kc, vc, out_b16};
   return attn_fused_launch_impl(stream, ws, B, pos_d, n_heads, n_kv_heads, q_out, out, kc, vc, kv_batch_stride, head_size, seq_len, pdl,
                                 out_hi, out_lo, out_q, out_sT, ldxs, gs, pg, &rp);
 }

@@ -35,6 +35,12 @@ int attn_prefill_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_
                         float* out, float* out_hi, float* out_lo, const float* kc, const float* vc,
                         long long kv_batch_stride, const int* row_slot, const int* row_pos, const int* tile_row0,
                         const int* tile_n, bool pdl, const KvPaged* pg = nullptr);
+bool attn_fused_rope_supported(int n_heads, int n_kv_heads, int head_size);
+int attn_fused_rope_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads, float* q_out,
+                           float* out, float* kc, float* vc, long long kv_batch_stride, int head_size, int seq_len, bool pdl,
+                           float* out_hi, float* out_lo, int8_t* out_q, float* out_sT, int ldxs, int gs, const KvPaged* pg,
+                           const float* part, int nz, long long zstride, int ld, const float* rc, const float* rs,
+                           uint16_t* out_b16 = nullptr);
 bool attn_prefill_tc_supported(int head_size, int kv_dim);
 int attn_prefill_tc_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_heads, int head_size, const float* q, float* out,
                            uint16_t* out_b16, const float* kc, const float* vc, long long kv_batch_stride, const int* row_slot,
@@ -316,6 +322,10 @@ static int bf_issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, 
       const int M[3] = {d, kvd, kvd}, off[3] = {0, d, d + kvd};
       THA_TRY_RC(mm(3, W, M, off, d, sc.xb, R, sc.part, ld_qkv, (long long)R * ld_qkv, pl.z_qkv));
     }
+    // decode rows: RoPE + KV scatter and the bf16 rounding of the output ride in the attention kernel (7 launches per layer, not 10)
+    const bool rope_in_attn = io.n_tiles == 0 && !(!io.logits && l == L - 1) && rope_fuse_mode() &&
+                              attn_fused_rope_supported(c.n_heads, c.n_kv_heads, hs);
+    if (!rope_in_attn)
     THA_TRY_RC(rope_scatter_launch(st, pdl, R, sc.part, pl.z_qkv, (long long)R * ld_qkv, ld_qkv, io.pos, d, kvd, hs, rc, rs, io.q,
                                    s.key_cache, s.value_cache, kv_bs, loff, io.slot, &pg));
     if (!io.logits && l == L - 1) return THA_STATUS_SUCCESS;   // cache-only ingestion: the last layer's K/V rows are in place
@@ -328,7 +338,12 @@ static int bf_issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, 
     } else if (io.n_tiles > 0)
       THA_TRY_RC(attn_prefill_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, nullptr, nullptr, kcl,
                                      vcl, kv_bs, io.slot, io.pos, io.tile_row0, io.tile_n, pdl, &pg));
-    else
+    else if (rope_in_attn) {
+      THA_TRY_RC(attn_fused_rope_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, const_cast<float*>(kcl),
+                                        const_cast<float*>(vcl), kv_bs, hs, c.seq_len, pdl, nullptr, nullptr, nullptr, nullptr, 0, 0, &pg,
+                                        sc.part, pl.z_qkv, (long long)R * ld_qkv, ld_qkv, rc, rs, sc.xb));
+      rounded = true;
+    } else
       THA_TRY_RC(attn_fused_launch(st, ws, R, io.pos, c.n_heads, c.n_kv_heads, io.q, io.xb, kcl, vcl,
                                    kv_bs, hs, c.seq_len, pdl, nullptr, nullptr, nullptr, nullptr, 0, 0, &pg));
     if (!rounded)

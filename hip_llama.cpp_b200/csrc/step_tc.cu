@@ -46,7 +46,8 @@ bool attn_fused_rope_supported(int n_heads, int n_kv_heads, int head_size);
 int attn_fused_rope_launch(cudaStream_t stream, Workspace* ws, int B, const int* pos_d, int n_heads, int n_kv_heads, float* q_out,
                            float* out, float* kc, float* vc, long long kv_batch_stride, int head_size, int seq_len, bool pdl,
                            float* out_hi, float* out_lo, int8_t* out_q, float* out_sT, int ldxs, int gs, const KvPaged* pg,
-                           const float* part, int nz, long long zstride, int ld, const float* rc, const float* rs);
+                           const float* part, int nz, long long zstride, int ld, const float* rc, const float* rs,
+                           uint16_t* out_b16 = nullptr);
 int attn_prefill_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_heads, int head_size, const float* q,
                         float* out, float* out_hi, float* out_lo, const float* kc, const float* vc,
                         long long kv_batch_stride, const int* row_slot, const int* row_pos, const int* tile_row0,
