@@ -58,7 +58,11 @@ int step_tc_q8_issue(cudaStream_t st, Workspace* ws, int B, const tha_config_t& 
                      const float* rc, const float* rs, bool pdl, const TpCtx* tp = nullptr);
 TpCtx* tp_ctx(tha_tp_t* t);
 int gemm_tc_check_error();
-int tc_mode();   // -1 auto (B > 8), 0 never, 1 whenever the shape allows
+int tc_mode();   // -1 auto (more than TC_MIN_SLOTS slots), 0 never, 1 whenever the shape allows
+// From five slots on the tensor-core row pipeline wins over both small-batch paths (measured after the round-2 read-out fixes):
+// stories110M fp32 at 5 / 8 slots 0.476 / 0.485 ms per step against the persistent step kernel's 0.537 / 0.559; Llama-2-7B fp32 at
+// 8 slots 6.83 ms against the fused GEMV step's 10.71 (0.60 vs 0.38 of HBM); at 4 slots the two are level, below the GEMV / mega paths win.
+constexpr int TC_MIN_SLOTS = 4;
 int advance_launch(cudaStream_t st, int B, int* token, int* pos, const int* next, int seq_len, bool pdl);
 int sample_launch(cudaStream_t st, int B, float* logits, int vocab, float temperature, float topp, unsigned long long* rng,
                   const unsigned long long* reseed, const int* force, const int* pos, int* next, bool pdl);
@@ -260,7 +264,7 @@ int decode_step_f32(cudaStream_t st, int B, const tha_config_t* cfg, const tha_w
   // a paged KV cache (tha_kv_pool_register) is read and written by the row pipeline's kernels only
   const bool paged = kv_pool_find(s->key_cache, nullptr);
   if (paged && !step_tc_supported(cfg, B)) return THA_STATUS_NOT_SUPPORTED;
-  const bool use_tc = paged || (tcm != 0 && (tcm == 1 || B > 8) && step_tc_supported(cfg, B));
+  const bool use_tc = paged || (tcm != 0 && (tcm == 1 || B > TC_MIN_SLOTS) && step_tc_supported(cfg, B));
   a.mega = !use_tc && mega_enabled() && mega_supported(cfg, B);
   if (a.mega) {
     // scratch is grown outside any capture; the kernel writes logits only where the caller wants them

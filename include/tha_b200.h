@@ -83,7 +83,7 @@ typedef struct {
 int tha_version(void);
 const char* tha_last_error(void);       /* text of the last CUDA error seen by this library */
 int tha_set_option(const char* name, int value); /* "pdl", "graph", "mega" (0/1); "tc": -1 auto (tensor-core
-                                                    matmuls for more than 8 slots), 0 never, 1 whenever supported */
+                                                    matmuls for more than 4 slots), 0 never, 1 whenever supported */
 
 /* ---- runtime shim: the only way the C++ host layer touches the CUDA runtime ---------
  * (reference: hipSetDevice / hipMalloc / hipMemcpy / hipHostMalloc / hipStreamCreate /
