@@ -198,10 +198,17 @@ __global__ void __launch_bounds__(256) attn_fused_kernel(const AttnP p) {
       const int jj = (qo % hs) >> 1;         // the float4 holds the pairs jj and jj + 1 of its head (q and k alike)
       const float2 c2 = *reinterpret_cast<const float2*>(p.rp.rc + (size_t)pb * (hs >> 1) + jj);
       const float2 s2 = *reinterpret_cast<const float2*>(p.rp.rs + (size_t)pb * (hs >> 1) + jj);
-      qv[j] = make_float4(a.x * c2.x - a.y * s2.x, a.x * s2.x + a.y * c2.x, a.z * c2.y - a.w * s2.y, a.z * s2.y + a.w * c2.y);
+      // (x, y) -> (x c - y s, x s + y c), written as in tc_rope_scatter_kernel: one product rounded, the other fused
+      auto rot = [](float x, float y, float c, float sn, float& o0, float& o1) {
+        o0 = fmaf(x, c, -__fmul_rn(y, sn));
+        o1 = fmaf(x, sn, __fmul_rn(y, c));
+      };
+      rot(a.x, a.y, c2.x, s2.x, qv[j].x, qv[j].y);
+      rot(a.z, a.w, c2.y, s2.y, qv[j].z, qv[j].w);
       if (p.rp.q_out && split == 0 && warp == 0) *reinterpret_cast<float4*>(p.rp.q_out + (size_t)b * p.dim + qo) = qv[j];
       if (own_new) {
-        knew[j] = make_float4(kk.x * c2.x - kk.y * s2.x, kk.x * s2.x + kk.y * c2.x, kk.z * c2.y - kk.w * s2.y, kk.z * s2.y + kk.w * c2.y);
+        rot(kk.x, kk.y, c2.x, s2.x, knew[j].x, knew[j].y);
+        rot(kk.z, kk.w, c2.y, s2.y, knew[j].z, knew[j].w);
         vnew[j] = vv;
         const long long ro = p.pg.table ? kv_paged_off(p.pg, b, pb, p.kv_dim) : (long long)b * p.kv_batch_stride + (long long)pb * p.kv_dim;
         *reinterpret_cast<float4*>(p.rp.kc_w + ro + koff[j]) = knew[j];

@@ -527,8 +527,7 @@ int sample_launch(cudaStream_t st, int B, float* logits, int vocab, float temper
   p.logits = logits; p.vocab = vocab; p.temperature = temperature; p.topp = topp; p.rng = rng; p.reseed = reseed;
   p.force = force; p.pos = pos; p.next = next;
   // the row in shared memory when it fits beside the histograms (vocab <= ~48 k); THA_SAMPLE_RESIDENT=0 keeps it in HBM / L2
-  static int resident = -1;
-  if (resident < 0) { const char* v = getenv("THA_SAMPLE_RESIDENT"); resident = (v && *v) ? atoi(v) : 1; }
+  const int resident = sample_resident_mode();
   const size_t row = (size_t)((vocab + 3) & ~3) * sizeof(float) + (size_t)16 * SMP_THREADS * sizeof(u64);   // the row + the private counters
   if (resident && temperature != 0.0f && row + sizeof(SmpShared) + 1024 <= (size_t)227 * 1024) {
     THA_CUDA_OK(cudaFuncSetAttribute(sample_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row));

@@ -209,7 +209,9 @@ __global__ void __launch_bounds__(256) tc_rope_scatter_kernel(const float* __res
       const int li = (i < d) ? i : i - d;
       const int j = (li % hs) >> 1;
       const float c = rc[(size_t)pb * (hs >> 1) + j], s = rs[(size_t)pb * (hs >> 1) + j];
-      const float r0 = v[u].x * c - v[u].y * s, r1 = v[u].x * s + v[u].y * c;
+      // one product rounded, the other fused: the SAME expression as the attention kernel's in-kernel RoPE (attention.cu), so the
+      // two forms of the step leave identical bits in the cache
+      const float r0 = fmaf(v[u].x, c, -__fmul_rn(v[u].y, s)), r1 = fmaf(v[u].x, s, __fmul_rn(v[u].y, c));
       if (i < d) *reinterpret_cast<float2*>(q + (size_t)b * d + li) = make_float2(r0, r1);
       else *reinterpret_cast<float2*>(kc + rowoff + li) = make_float2(r0, r1);
     } else {

@@ -94,6 +94,12 @@ int rope_fuse_mode() {   // 1 (default): RoPE + KV scatter of a decode step insi
   return g_rope_fuse;
 }
 int* opt_rope_fuse() { rope_fuse_mode(); return &g_rope_fuse; }
+static int g_sample_resident = -2;
+int sample_resident_mode() {   // 1 (default): the sampler keeps a slot's row in shared memory; 0: every pass over HBM / L2 (the first form)
+  if (g_sample_resident == -2) { const char* v = getenv("THA_SAMPLE_RESIDENT"); g_sample_resident = (v && *v) ? atoi(v) : 1; }
+  return g_sample_resident;
+}
+int* opt_sample_resident() { sample_resident_mode(); return &g_sample_resident; }
 void count_launch(int n) { g_launches += n; }
 int launches_reset() { int v = g_launches; g_launches = 0; return v; }
 int launches_get() { return g_launches; }
@@ -325,6 +331,12 @@ extern "C" int tha_set_option(const char* name, int value) {
     return THA_STATUS_SUCCESS;
   }
   if (!strcmp(name, "chain")) { *tha::opt_chain() = value; return THA_STATUS_SUCCESS; }
+  if (!strcmp(name, "sample_resident")) {   // graphs that contain the sampler were captured with the other kernel
+    *tha::opt_sample_resident() = value != 0;
+    std::lock_guard<std::mutex> lk(tha::g_mu);
+    for (auto& kv : tha::g_ws) tha::ws_drop_graphs(kv.second);
+    return THA_STATUS_SUCCESS;
+  }
   if (!strcmp(name, "ropefuse")) {   // cached graphs were captured with the other kernel sequence
     *tha::opt_rope_fuse() = value != 0;
     std::lock_guard<std::mutex> lk(tha::g_mu);

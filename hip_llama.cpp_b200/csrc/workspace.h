@@ -79,6 +79,7 @@ void ws_release(Workspace* ws);        // free everything a (tensor-parallel ran
 void step_tc_release(Workspace* ws);   // ... and the row pipeline's scratch keyed by it
 int skip_mode();       // bit mask of kernel classes left out of the row pipeline (live-share measurements): 1 layer matmuls, 2 attention,
                        // 4 prep, 8 RoPE / scatter, 16 SwiGLU / quantise, 32 classifier, 64 argmax
+int sample_resident_mode();   // 1: the device sampler keeps a slot's row in shared memory
 int rope_fuse_mode();  // 1: a decode step's RoPE + KV scatter run inside the attention kernel
 int chain_mode();      // 1: matmul chains with fused epilogues (chain_tc.cu), 0: one launch per matmul (the round-1 pipeline)
 int sm_budget();            // SMs one matmul launch may occupy: all of them, or a branch's share while a dual step is planned / issued

@@ -127,6 +127,44 @@ def test_fp32_tensor_core_step_vs_oracle(oracle, tmp_path, name, B):
     assert flips == 0
 
 
+@pytest.mark.parametrize("name,B,quant", [("fusedA", 16, False), ("fusedGQA", 33, False), ("fusedA", 12, True)])
+def test_rope_inside_attention_equals_separate_kernel(tmp_path, name, B, quant):
+    """tha_set_option("ropefuse", 1) (default): RoPE + KV scatter of a decode step run inside the attention kernel.  The rotated
+    queries and the cache rows it writes must be the SAME BITS as tc_rope_scatter_kernel's (same sums, same formula); the
+    logits agree to fp32 noise (the new position enters the softmax last instead of in its warp's turn)."""
+    lib = load_pkg("cabi").lib()
+    cfg, w, v0, v2 = small_model_files(str(tmp_path), name, MODELS[name])
+    rng = np.random.default_rng(5)
+    steps = 9
+    toks = rng.integers(0, cfg.vocab_size, size=(steps, B)).astype(np.int32)
+    out = {}
+    try:
+        for fuse in (1, 0):
+            lib.check(lib.c.tha_set_option(b"ropefuse", fuse))
+            e = engine_from_v2(v2, B) if quant else engine_from_v0(v0, B)
+            lg = []
+            for t in range(steps):
+                pos = np.where(np.arange(B) % 3 == 2, t - 2, t).astype(np.int32)   # a third of the slots join two steps late
+                lg.append(e.forward_batch(toks[t], pos).numpy())
+            assert e.last_step_launches() > 1
+            out[fuse] = (np.stack(lg), e.state.key_cache.cpu().numpy(), e.state.value_cache.cpu().numpy(), e.state.q.cpu().numpy(),
+                         e.last_step_launches())
+    finally:
+        lib.check(lib.c.tha_set_option(b"ropefuse", 1))
+    assert out[1][4] == out[0][4] - cfg.n_layers, "one launch less per layer"
+    # layer 0 sees identical inputs: identical bits.  Deeper layers inherit the fp32 noise of the attention outputs (and under
+    # Q8_0 a 1-ulp change can flip a rounding of the next quantiser).
+    if not quant:
+        assert np.array_equal(out[1][1][:, 0], out[0][1][:, 0]) and np.array_equal(out[1][2][:, 0], out[0][2][:, 0]), "layer-0 cache rows differ"
+        assert_close(out[1][1], out[0][1], 2e-5, "key cache, fused vs separate RoPE")
+        assert_close(out[1][2], out[0][2], 2e-5, "value cache, fused vs separate RoPE")
+        assert_close(out[1][3], out[0][3], 2e-5, "rotated queries of the last layer")
+        assert_close(out[1][0], out[0][0], 2e-5, "logits, fused vs separate RoPE")
+    else:
+        assert np.array_equal(out[1][1][:, 0], out[0][1][:, 0]) and np.array_equal(out[1][2][:, 0], out[0][2][:, 0]), "layer-0 cache rows differ"
+        assert_close_scaled(out[1][0], out[0][0], Q8_E2E_EPS, "logits, fused vs separate RoPE (Q8_0)")
+
+
 @pytest.mark.parametrize("name,B", [("fusedA", 16), ("fusedGQA", 70), ("fusedA", 130)])
 def test_fp32_chained_matmuls_vs_oracle(oracle, tmp_path, name, B):
     """tha_set_option("chain", 1): wo -> w1|w3 -> w2 -> next wq|wk|wv as ONE persistent launch per layer with residual /

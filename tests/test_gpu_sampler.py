@@ -176,3 +176,41 @@ def test_forward_sample_equals_forward_then_sample(tmp_path):
         torch.cuda.synchronize()
         assert nx.tolist() == nxt.cpu().numpy().tolist(), f"step {step}"
         tok = nx.astype(np.int32)
+
+
+def test_sampler_resident_and_streaming_forms_pick_the_same_tokens():
+    """The two forms of the kernel (row resident in shared memory: integer keys, four key bits per level, no atomics; row in
+    HBM / L2: three histogram levels of shared atomics) accumulate the same integer masses over the same candidates, so
+    they must agree on EVERY token and leave the same probabilities and stream states -- whatever the distribution."""
+    import torch
+    lib = load_pkg("cabi").lib()
+    rng = np.random.default_rng(77)
+    B, V = 48, 32000
+    cases = [(rng.standard_normal((B, V)) * 2.0, 1.0, 0.9), (rng.standard_normal((B, V)) * 0.02, 1.0, 0.9),
+             (rng.standard_normal((B, V)) * 6.0, 0.7, 0.5), (rng.standard_normal((B, 5000)) * 3.0, 1.3, 0.95),
+             (rng.standard_normal((B, V)) * 2.0, 1.0, 1.0)]           # the last: multinomial over the whole row
+    seeds = np.arange(1, B + 1, dtype=np.uint64) * np.uint64(2654435761)
+    try:
+        for logits, temperature, topp in cases:
+            logits = logits.astype(np.float32)
+            logits[3, 100:200] = logits[3, 100]                        # a run of equal probabilities: index order decides
+            got = {}
+            for resident in (1, 0):
+                lib.check(lib.c.tha_set_option(b"sample_resident", resident))
+                toks, state = run_device(logits, temperature, topp, seeds, draws=4)
+                got[resident] = (toks, state)
+            assert np.array_equal(got[1][0], got[0][0]), f"tokens differ (temperature {temperature}, top-p {topp}, vocab {logits.shape[1]})"
+            assert np.array_equal(got[1][1], got[0][1]), "stream states differ"
+        # the probabilities the kernel leaves in the logits buffer are the same bits in both forms
+        lg = {}
+        for resident in (1, 0):
+            lib.check(lib.c.tha_set_option(b"sample_resident", resident))
+            t = tdev(cases[0][0].astype(np.float32))
+            st = tdev(seeds.view(np.int64)); nxt = torch.zeros(B, dtype=torch.int32, device="cuda")
+            pos = torch.zeros(B, dtype=torch.int32, device="cuda")
+            lib.check(lib.c.tha_sample(stream_ptr(), B, P(t), V, C.c_float(1.0), C.c_float(0.9), P(st), None, None, P(pos), P(nxt)))
+            torch.cuda.synchronize()
+            lg[resident] = t.cpu().numpy()
+        assert np.array_equal(lg[1], lg[0]), "probabilities differ between the two forms"
+    finally:
+        lib.check(lib.c.tha_set_option(b"sample_resident", 1))
