@@ -17,6 +17,8 @@
 //   of S (two passes: maximum, then exponentials), writes its row of P (bf16) into shared memory;  hs/... 8 MMAs: P V into
 //   TMEM;  every thread folds its row of P V into its register accumulator (rescaled by exp(m_old - m_new)).
 // Nothing overlaps inside a CTA; there are tiles x heads CTAs (512 per 7B layer at 2048 positions) to fill the machine.
+#include <string.h>
+
 #include "common.cuh"
 #include "gemm_tc.h"
 #include "tc_common.cuh"
@@ -32,6 +34,9 @@ struct AttnPfTcP {
   const int* tile_row0; const int* tile_n;                    // [tiles]: first row and row count (<= 128)
   KvPaged pg;
   int* error_flag;
+  int staged_rows;     // STAGED kernels: rows of the bf16 staging buffers (K row-major, V transposed) the tensor maps describe
+  const int* row_stage; // STAGED: staging row of every row of the call (a sequence starts at a multiple of 64: TMA wants the
+                        // inner coordinate of the transposed V tile 16-byte aligned)
 };
 
 constexpr int PTC_TQ = 128, PTC_TK = 128;
@@ -73,8 +78,15 @@ __device__ __forceinline__ void ptc_mma(uint32_t tmem_d, uint64_t adesc, uint64_
 // byte offset of element (row r, column c) of a K-major bf16 tile whose rows are 128 bytes (64 values), SWIZZLE_128B
 __device__ __forceinline__ int ptc_off(int r, int c) { return r * 128 + ((((c >> 3) ^ (r & 7))) << 4) + ((c & 7) << 1); }
 
-template <int HS>
-__global__ void __launch_bounds__(256, PTC_CTAS_PER_SM) attn_prefill_tc_kernel(const AttnPfTcP p) {
+// STAGED: the prompt's K rows (bf16, row-major) and V rows (bf16, TRANSPOSED: [kv column][prompt row]) were written once per
+// layer by bf_kv_stage_kernel (step_bf16.cu); a key tile then is two TMA loads (mk: [128 keys x HS], mv: [HS x 128 keys]) into
+// the swizzled layout the MMAs read, double-buffered so that the next tile lands while this one is multiplied and soft-maxed.
+// (Unstaged, every CTA re-reads the fp32 cache rows, converts them and transposes V with 2-byte shared-memory stores: at 2048
+// positions that was 363 us per 7B layer with the tensor pipe 4.6 % busy.)  Staged keys are addressed by prompt row: the
+// sequence's row of position 0 is row_stage[row0] - pos0, so every sequence of the call must start at position 0.
+template <int HS, bool STAGED>
+__global__ void __launch_bounds__(256, PTC_CTAS_PER_SM)
+attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap mk, const __grid_constant__ CUtensorMap mv, const AttnPfTcP p) {
   constexpr int KBH = HS / 64;                       // 64-value k-blocks along the head dimension
   constexpr int Q_BYTES = KBH * PTC_TQ * 128;        // Q tile  [128 rows][HS]
   constexpr int K_BYTES = KBH * PTC_TK * 128;        // K tile  [128 keys][HS]
@@ -89,11 +101,14 @@ __global__ void __launch_bounds__(256, PTC_CTAS_PER_SM) attn_prefill_tc_kernel(c
   // share one region (96 KB per CTA at head size 128)
   constexpr int KP_BYTES = K_BYTES > P_BYTES ? K_BYTES : P_BYTES;
   unsigned char* Qs = smem;
-  unsigned char* Ks = Qs + Q_BYTES;
+  unsigned char* Ks = Qs + Q_BYTES;                  // STAGED: two K buffers, then two V^T buffers
   unsigned char* Ps = Ks;
-  unsigned char* Vt = Ks + KP_BYTES;
-  uint64_t* bar = reinterpret_cast<uint64_t*>(Vt + V_BYTES);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+  unsigned char* Vt = Ks + (STAGED ? 2 : 1) * KP_BYTES;
+  unsigned char* const K0 = Ks;
+  unsigned char* const V0 = Vt;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(Vt + (STAGED ? 2 : 1) * V_BYTES);
+  uint64_t* full = bar + 1;                          // STAGED: tile landed in buffer 0 / 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 3);
   int* abort_flag = reinterpret_cast<int*>(tmem_slot + 1);
 
   // 8 warps: warp w serves TMEM lanes 32 (w & 3) .. (query rows) and column half w >> 2 -- two threads per query row, each
@@ -104,8 +119,14 @@ __global__ void __launch_bounds__(256, PTC_CTAS_PER_SM) attn_prefill_tc_kernel(c
   const int tile = blockIdx.x, h = blockIdx.y;
   if (tid == 0) {
     tc_mbar_init(bar, 1);
+    tc_mbar_init(&full[0], 1); tc_mbar_init(&full[1], 1);
     *abort_flag = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (STAGED) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mk) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mv) : "memory");
+    }
   }
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem_u32(tmem_slot)), "r"(TMEM_COLS));
@@ -154,8 +175,25 @@ __global__ void __launch_bounds__(256, PTC_CTAS_PER_SM) attn_prefill_tc_kernel(c
   unsigned phase = 0;
   bool ok = true;
 
-  for (int t0 = 0; live_tile && t0 <= kmax; t0 += PTC_TK) {
+  // STAGED: a tile = KBH boxes of K [128 keys x 64 values] + two boxes of V^T [HS x 64 keys], by prompt row
+  const int key_row0 = STAGED ? p.row_stage[row0] - pos0 : 0;
+  auto stage_tile = [&](int t0, int buf) {
+    tc_mbar_expect_tx(&full[buf], K_BYTES + V_BYTES);
+#pragma unroll
+    for (int kb = 0; kb < KBH; kb++) tc_tma_2d(K0 + buf * KP_BYTES + kb * (PTC_TK * 128), &mk, kh * HS + kb * 64, key_row0 + t0, &full[buf]);
+#pragma unroll
+    for (int j = 0; j < 2; j++) tc_tma_2d(V0 + buf * V_BYTES + j * (HS * 128), &mv, key_row0 + t0 + 64 * j, kh * HS, &full[buf]);
+  };
+  if (STAGED && live_tile && tid == 0) stage_tile(0, 0);
+  int it = 0;
+  for (int t0 = 0; live_tile && t0 <= kmax; t0 += PTC_TK, it++) {
     __syncthreads();     // the previous tile's K / V^T / P are no longer read by an MMA (its completion was waited for)
+    if (STAGED) {
+      const int buf = it & 1;
+      if (tid == 0 && t0 + PTC_TK <= kmax) stage_tile(t0 + PTC_TK, buf ^ 1);   // its buffer: the tile before this one, finished
+      Ks = K0 + buf * KP_BYTES; Ps = Ks; Vt = V0 + buf * V_BYTES;
+      if (ok) ok = tc_mbar_wait(&full[buf], (unsigned)(it >> 1) & 1u, abort_flag);
+    } else {
     // ---- K tile (rows = keys): warp w takes rows w, w+8, ..; eight rows' loads are issued before the first is converted
 #pragma unroll 1
     for (int rb = 0; rb < PTC_TK / 8; rb += 8) {
@@ -219,6 +257,7 @@ __global__ void __launch_bounds__(256, PTC_CTAS_PER_SM) attn_prefill_tc_kernel(c
       }
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> visible to the tensor core's reads
+    }
     __syncthreads();
     // ---- S = Q K^T
     if (tid == 0) {
@@ -333,11 +372,15 @@ __global__ void __launch_bounds__(256, PTC_CTAS_PER_SM) attn_prefill_tc_kernel(c
 bool attn_prefill_tc_supported(int head_size, int kv_dim) { return (head_size == 64 || head_size == 128) && kv_dim % 4 == 0; }
 
 // tiles of up to 128 query rows (tile_row0 / tile_n), never across sequences
+// k16 / vt16 (nullable): the staged bf16 copies of this call's K rows [staged_rows][kv_dim] and V rows, transposed
+// [kv_dim][staged_ld] (every sequence of the call starts at position 0; step_bf16.cu decides)
 int attn_prefill_tc_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_heads, int head_size, const float* q, float* out,
                            uint16_t* out_b16, const float* kc, const float* vc, long long kv_batch_stride, const int* row_slot,
-                           const int* row_pos, const int* tile_row0, const int* tile_n, bool pdl, const KvPaged* pg) {
+                           const int* row_pos, const int* tile_row0, const int* tile_n, bool pdl, const KvPaged* pg,
+                           const uint16_t* k16, const uint16_t* vt16, int staged_rows, int staged_ld, const int* row_stage) {
   if (!attn_prefill_tc_supported(head_size, n_kv_heads * head_size)) return THA_STATUS_NOT_SUPPORTED;
   AttnPfTcP p;
+  p.staged_rows = staged_rows; p.row_stage = row_stage;
   p.q = q; p.out = out; p.out_b16 = out_b16; p.kc = kc; p.vc = vc;
   if (pg) p.pg = *pg; else p.pg = KvPaged{};
   p.kv_batch_stride = kv_batch_stride; p.kv_dim = n_kv_heads * head_size; p.kv_mul = n_heads / n_kv_heads;
@@ -346,10 +389,22 @@ int attn_prefill_tc_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_
   THA_TRY_RC(gemm_tc_init(&p.error_flag));
   const int kbh = head_size / 64;
   const size_t kp = (size_t)kbh * 128 * 128 > (size_t)2 * 128 * 128 ? (size_t)kbh * 128 * 128 : (size_t)2 * 128 * 128;
-  const size_t smem = (size_t)kbh * 128 * 128 + kp + (size_t)2 * head_size * 128 + 1024 + 64;
-  void (*k)(const AttnPfTcP) = head_size == 64 ? attn_prefill_tc_kernel<64> : attn_prefill_tc_kernel<128>;
+  const bool staged = k16 && vt16 && staged_rows > 0 && row_stage;
+  const int nb = staged ? 2 : 1;
+  const size_t smem = (size_t)kbh * 128 * 128 + nb * kp + (size_t)nb * 2 * head_size * 128 + 1024 + 64;
+  CUtensorMap mk, mv;
+  if (staged) {
+    const int kvd = n_kv_heads * head_size;
+    THA_TRY_RC(tc_map(k16, staged_rows, kvd, kvd, 128, &mk, 2));
+    THA_TRY_RC(tc_map(vt16, kvd, staged_ld, staged_ld, head_size, &mv, 2));
+  } else {
+    memset(&mk, 0, sizeof(mk)); memset(&mv, 0, sizeof(mv));
+  }
+  void (*k)(const CUtensorMap, const CUtensorMap, const AttnPfTcP) =
+      staged ? (head_size == 64 ? attn_prefill_tc_kernel<64, true> : attn_prefill_tc_kernel<128, true>)
+             : (head_size == 64 ? attn_prefill_tc_kernel<64, false> : attn_prefill_tc_kernel<128, false>);
   THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  THA_CUDA_OK(launch(k, dim3(n_tiles, n_heads), dim3(256), smem, stream, pdl, p));
+  THA_CUDA_OK(launch(k, dim3(n_tiles, n_heads), dim3(256), smem, stream, pdl, mk, mv, p));
   return THA_STATUS_SUCCESS;
 }
 

@@ -44,7 +44,8 @@ int attn_fused_rope_launch(cudaStream_t stream, Workspace* ws, int B, const int*
 bool attn_prefill_tc_supported(int head_size, int kv_dim);
 int attn_prefill_tc_launch(cudaStream_t stream, int n_tiles, int n_heads, int n_kv_heads, int head_size, const float* q, float* out,
                            uint16_t* out_b16, const float* kc, const float* vc, long long kv_batch_stride, const int* row_slot,
-                           const int* row_pos, const int* tile_row0, const int* tile_n, bool pdl, const KvPaged* pg);
+                           const int* row_pos, const int* tile_row0, const int* tile_n, bool pdl, const KvPaged* pg,
+                           const uint16_t* k16, const uint16_t* vt16, int staged_rows, int staged_ld, const int* row_stage);
 int rope_scatter_launch(cudaStream_t st, bool pdl, int R, const float* part, int nz, long long zstride, int ld, const int* pos, int d,
                         int kvd, int hs, const float* rc, const float* rs, float* q, float* kc, float* vc, long long kv_bs, int loff,
                         const int* slot, const KvPaged* pg = nullptr);
@@ -181,12 +182,45 @@ __global__ void bf_convert_kernel(const float* __restrict__ src, uint16_t* __res
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = f32_to_bf16(src[i]);
 }
 
+// K rows and V rows of the prompt positions just written to the cache -> bf16 (nearest even): k16[srow[r]][c] row-major and
+// vt16[c][srow[r]] TRANSPOSED, r = row of the call, srow[r] = its staging row (a sequence starts at a multiple of 64), c = kv column.  32 x 32 tiles through shared memory: both sides coalesced.
+// grid (kvd / 32, R / 32), 256 threads (32 x 8)
+__global__ void __launch_bounds__(256) bf_kv_stage_kernel(const float* __restrict__ kc, const float* __restrict__ vc, long long kv_bs,
+                                                          const int* __restrict__ slot, const int* __restrict__ pos, const KvPaged pg,
+                                                          const int* __restrict__ srow, int R, int kvd, int ld,
+                                                          uint16_t* __restrict__ k16, uint16_t* __restrict__ vt16) {
+  __shared__ uint16_t t[32][34];
+  pdl_wait();
+  pdl_trigger();
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int r = r0 + ty + i, c = c0 + tx;
+    uint16_t kb = 0, vb = 0;
+    if (r < R && c < kvd && pos[r] >= 0) {
+      const long long ro = pg.table ? kv_paged_off(pg, slot[r], pos[r], kvd) : (long long)slot[r] * kv_bs + (long long)pos[r] * kvd;
+      kb = f32_to_bf16(kc[ro + c]);
+      vb = f32_to_bf16(vc[ro + c]);
+    }
+    if (r < R && c < kvd) k16[(size_t)srow[r] * kvd + c] = kb;
+    t[ty + i][tx] = vb;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int c = c0 + ty + i, r = r0 + tx;
+    if (c < kvd && r < R) vt16[(size_t)c * ld + srow[r]] = t[tx][ty + i];
+  }
+}
+
 // ---- scratch (per workspace) ---------------------------------------------------------------------------------------
 struct BfScratch {
   uint16_t *xb = nullptr, *hb = nullptr;             // matmul inputs [R, d], [R, hidden]
   float* part = nullptr;                             // split-K partials
   float *xr = nullptr, *qr = nullptr, *xbr = nullptr; int* tab = nullptr;   // prefill rows
-  size_t n_xb = 0, n_hb = 0, n_part = 0, n_xr = 0, n_qr = 0, n_xbr = 0, n_tab = 0;
+  uint16_t *k16 = nullptr, *vt16 = nullptr;          // prompt attention on the tensor cores: this layer's K rows [R, kvd] and V rows TRANSPOSED [kvd, ld] in bf16
+  size_t n_xb = 0, n_hb = 0, n_part = 0, n_xr = 0, n_qr = 0, n_xbr = 0, n_tab = 0, n_k16 = 0, n_vt16 = 0;
 };
 static std::map<Workspace*, BfScratch> g_bf_scratch;
 static std::mutex g_bf_mu;
@@ -244,7 +278,7 @@ bool step_bf16_supported(const tha_config_t* c) {
   return attn_fused_supported(c->n_heads, hs, d, kvd);
 }
 
-static int bf_prepare(Workspace* ws, const tha_config_t& c, int R, bool prefill, int n_tab) {
+static int bf_prepare(Workspace* ws, const tha_config_t& c, int R, bool prefill, int n_tab, int Rs = 0) {
   THA_TRY_RC(gemm_tc_init(nullptr));
   std::lock_guard<std::mutex> lk(g_bf_mu);
   BfScratch& s = g_bf_scratch[ws];
@@ -257,6 +291,14 @@ static int bf_prepare(Workspace* ws, const tha_config_t& c, int R, bool prefill,
     THA_TRY_RC(bf_grow(&s.qr, &s.n_qr, (size_t)R * c.dim, ws));
     THA_TRY_RC(bf_grow(&s.xbr, &s.n_xbr, (size_t)R * c.dim, ws));
     THA_TRY_RC(bf_grow(&s.tab, &s.n_tab, (size_t)n_tab, ws));
+    const int kvd_ = c.dim / c.n_heads * c.n_kv_heads;
+    const size_t before = s.n_k16 + s.n_vt16;
+    THA_TRY_RC(bf_grow(&s.k16, &s.n_k16, (size_t)Rs * kvd_, ws));
+    THA_TRY_RC(bf_grow(&s.vt16, &s.n_vt16, (size_t)kvd_ * Rs, ws));
+    if (s.n_k16 + s.n_vt16 != before) {   // the padding columns of V^T are read (and masked): they must hold finite values
+      THA_CUDA_OK(cudaMemset(s.k16, 0, s.n_k16 * sizeof(uint16_t)));
+      THA_CUDA_OK(cudaMemset(s.vt16, 0, s.n_vt16 * sizeof(uint16_t)));
+    }
     return THA_STATUS_SUCCESS;
   }
   const int hs = c.dim / c.n_heads;
@@ -269,11 +311,18 @@ struct BfRows {
   float *x, *q, *xb;
   const int *token, *pos, *slot;
   int n_tiles; const int *tile_row0, *tile_n; int tile_rows;   // prefill attention tiles (rows per tile: 64 CUDA cores, 128 tensor cores)
+  bool staged;                                                 // every sequence starts at position 0: K / V^T staged in bf16 for the tensor-core attention
+  const int* srow; int Rs;                                     // staging row of every row, staging rows in all
   int n_out; const int* out_rows;
   float* logits; int* next;
 };
 
 static int bf_attn_tc = -1;   // THA_ATTN_TC=0: keep the CUDA-core prefill attention (development aid)
+static int bf_stage_mode() {   // THA_ATTN_STAGE=0: the tensor-core attention converts the fp32 cache rows itself (the first form)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("THA_ATTN_STAGE"); v = (e && *e) ? atoi(e) : 1; }
+  return v;
+}
 
 static int bf_issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, const tha_weights_bf16_t& w, const tha_state_t& s,
                          const BfRows& io, const float* rc, const float* rs, bool pdl) {
@@ -332,8 +381,13 @@ static int bf_issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, 
     bool rounded = false;   // the attention kernel already left its output as bf16 rows in sc.xb
     if (io.n_tiles > 0 && io.tile_rows == 128) {
       // prompt rows, head size 64 / 128: Q K^T and P V on the tensor cores (attn_prefill_tc.cu)
+      if (io.staged) {   // this layer's K rows and V rows (transposed) in bf16: the attention tiles load them with TMA
+        THA_CUDA_OK(launch(bf_kv_stage_kernel, dim3(ceil_div(kvd, 32), ceil_div(R, 32)), dim3(256), 0, st, pdl, kcl, vcl, kv_bs, io.slot,
+                           io.pos, pg, io.srow, R, kvd, io.Rs, sc.k16, sc.vt16));
+      }
       THA_TRY_RC(attn_prefill_tc_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, sc.xb, kcl, vcl, kv_bs, io.slot, io.pos,
-                                        io.tile_row0, io.tile_n, pdl, &pg));
+                                        io.tile_row0, io.tile_n, pdl, &pg, io.staged ? sc.k16 : nullptr, io.staged ? sc.vt16 : nullptr,
+                                        io.Rs, io.Rs, io.srow));
       rounded = true;
     } else if (io.n_tiles > 0)
       THA_TRY_RC(attn_prefill_launch(st, io.n_tiles, c.n_heads, c.n_kv_heads, hs, io.q, io.xb, nullptr, nullptr, kcl,
@@ -402,10 +456,13 @@ int step_bf16_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
     T += ceil_div(len[i], TQ);
   }
   if (R < 1 || R > (1 << 20)) return THA_STATUS_INVALID_ARG;
-  std::vector<int> tab((size_t)3 * R + 2 * T + n_seqs);
+  std::vector<int> tab((size_t)3 * R + 2 * T + n_seqs + R);
   int *h_slot = tab.data(), *h_pos = h_slot + R, *h_tok = h_pos + R, *h_t0 = h_tok + R, *h_tn = h_t0 + T, *h_last = h_tn + T;
-  int r = 0, t = 0;
+  int* h_srow = h_last + n_seqs;   // staging row of every row: sequences start at multiples of 64
+  int r = 0, t = 0, Rs = 0;
   for (int i = 0; i < n_seqs; i++) {
+    for (int j = 0; j < len[i]; j++) h_srow[r + j] = Rs + j;
+    Rs += ceil_div(len[i], 64) * 64;
     for (int j = 0; j < len[i]; j += TQ) { h_t0[t] = r + j; h_tn[t] = (len[i] - j < TQ) ? len[i] - j : TQ; t++; }
     for (int j = 0; j < len[i]; j++, r++) {
       h_slot[r] = slot[i]; h_pos[r] = pos0[i] + j; h_tok[r] = tokens[r];
@@ -413,7 +470,7 @@ int step_bf16_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
     }
     h_last[i] = r - 1;
   }
-  THA_TRY_RC(bf_prepare(ws, c, (int)R, true, (int)tab.size()));
+  THA_TRY_RC(bf_prepare(ws, c, (int)R, true, (int)tab.size(), Rs));
   BfScratch sc;
   {
     std::lock_guard<std::mutex> lk(g_bf_mu);
@@ -424,6 +481,9 @@ int step_bf16_prefill(cudaStream_t st, Workspace* ws, const tha_config_t& c, con
   io.R = (int)R; io.x = sc.xr; io.q = sc.qr; io.xb = sc.xbr;
   io.slot = sc.tab; io.pos = sc.tab + R; io.token = sc.tab + 2 * R;
   io.n_tiles = (int)T; io.tile_row0 = sc.tab + 3 * R; io.tile_n = sc.tab + 3 * R + T; io.tile_rows = TQ;
+  io.staged = TQ == 128 && bf_attn_tc >= 1 && bf_stage_mode();
+  for (int i = 0; i < n_seqs; i++) io.staged = io.staged && pos0[i] == 0;   // staged keys are addressed by prompt row
+  io.srow = sc.tab + 3 * R + 2 * T + n_seqs; io.Rs = Rs;
   io.n_out = n_seqs; io.out_rows = sc.tab + 3 * R + 2 * T; io.logits = logits; io.next = logits ? next_d : nullptr;
   return bf_issue_rows(st, ws, c, w, s, io, rc, rs, pdl_enabled() != 0);
 }
