@@ -5,6 +5,8 @@ peers' exchange blocks, so on a single-GPU box the same code runs with all ranks
 kernels of different ranks overlap and hand-shake through the same flags).  PDL is switched off for that layout: an
 early-launched persistent matmul of one rank would otherwise hold every SM's shared memory while it waits for a peer
 that needs an SM to make progress.  Multi-GPU runs (tools/tp_check.py under torchrun, bench.py --tp) keep PDL on."""
+import os
+
 import numpy as np
 import pytest
 
@@ -181,3 +183,19 @@ def test_tp_prefill_then_decode(oracle, tmp_path, no_pdl, q8):
     finally:
         for r in ranks:
             r.close()
+
+
+def test_tp_on_two_real_devices():
+    """The same parity check with one PROCESS PER GPU (tools/tp_check.py under torchrun: IPC-mapped exchange blocks, PDL on,
+    ranks on different devices), fp32 and Q8_0, 3 and 20 slots, against the oracle of the unsplit model; every rank must
+    also agree with rank 0 bit for bit.  Needs two devices: skipped on a one-GPU box."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29533", os.path.join(root, "tools", "tp_check.py")]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0 and "TP_CHECK PASS" in r.stdout, r.stdout[-3000:]
