@@ -87,19 +87,12 @@ __device__ __forceinline__ float4 ld_peer4(const float* p) {
   return r;
 }
 // x += every rank's partials, ranks in ascending order, splits in ascending order (identical on every rank)
-// Eight loads are requested before the first is added (a peer's HBM is ~2 us away: one round trip per eight partials, not
-// per four); the order of the sum is unchanged.
 __device__ __forceinline__ void tp_add_partials(float4& v, const TpPeers& t, long long zstride, size_t off) {
   for (int r = 0; r < t.n; r++) {
-    const float* pp = t.part[r] + off;
-    for (int z0 = 0; z0 < t.nz[r]; z0 += 8) {
-      float4 pz[8];
-#pragma unroll
-      for (int u = 0; u < 8; u++)
-        if (z0 + u < t.nz[r]) pz[u] = ld_peer4(pp + (size_t)(z0 + u) * zstride);
-#pragma unroll
-      for (int u = 0; u < 8; u++)
-        if (z0 + u < t.nz[r]) { v.x += pz[u].x; v.y += pz[u].y; v.z += pz[u].z; v.w += pz[u].w; }
+#pragma unroll 4
+    for (int z = 0; z < t.nz[r]; z++) {
+      const float4 pz = ld_peer4(t.part[r] + (size_t)z * zstride + off);
+      v.x += pz.x; v.y += pz.y; v.z += pz.z; v.w += pz.w;
     }
   }
 }
