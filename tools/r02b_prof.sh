@@ -8,7 +8,7 @@ B="--no-cpu-baseline --no-e2e --no-extra --no-shares"
 CMD="python bench.py --steps 20 --warmup 5 $B"
 timeout 300 $CMD > gpurun_out/r02b_plain.json 2> gpurun_out/r02b_plain.err || { tail -5 gpurun_out/r02b_plain.err; exit 1; }
 timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none \
-  -k regex:"$K" -s $((5 * 113)) -c $((20 * 113)) --csv --log-file gpurun_out/r02b_launches_s110m_f32_B256_pos5-24.csv $CMD > gpurun_out/r02b_ll.log 2>&1
+  -k regex:"$K" -s $((5 * 101)) -c $((20 * 101)) --csv --log-file gpurun_out/r02b_launches_s110m_f32_B256_pos5-24.csv $CMD > gpurun_out/r02b_ll.log 2>&1
 tail -1 gpurun_out/r02b_ll.log | cut -c1-200
 S="python bench.py --steps 4 --warmup 3 $B"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:"gemm_tf32x3|attn_fused" -s 200 -c 6 -o gpurun_out/r02b_step_s110m_f32_B256 -f $S > gpurun_out/r02b_full1.log 2>&1; tail -1 gpurun_out/r02b_full1.log | cut -c1-160
