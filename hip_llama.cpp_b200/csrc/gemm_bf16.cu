@@ -37,12 +37,18 @@ struct BfP {
   int splits, n_items;
 };
 
-template <int NT>
+// MT = weight tiles of 128 rows per work item.  MT = 2 (prompt-sized N only): a CTA multiplies 256 weight rows by the
+// same 256 activation columns -- per 64-value k-block it pulls 32 + 32 KB through L2 for twice the flops of the 16 + 32 KB
+// of a 128-row tile.  With 128 x 256 tiles the prompt matmuls were bound by L2 -> shared-memory traffic (768 MB per
+// 4096 x 4096 x 2048 matmul, ~48 % of the sustained tensor peak); the two accumulators then fill all 512 TMEM columns, so
+// the read-out of an item is no longer hidden behind the next item's MMAs (eight warps keep it at a few per cent).
+template <int NT, int MT = 1>
 struct BfSmem {
-  static constexpr int W_BYTES = TC_BM * 128, X_BYTES = NT * 128, STAGE = W_BYTES + X_BYTES;
+  static constexpr int W_BYTES = MT * TC_BM * 128, X_BYTES = NT * 128, STAGE = W_BYTES + X_BYTES;
   static constexpr int NST_RAW = (TC_SMEM_LIMIT - 2048) / STAGE;
   static constexpr int NST = NST_RAW > 8 ? 8 : NST_RAW;
-  static constexpr int TMEM_COLS = 2 * NT < 32 ? 32 : 2 * NT;        // powers of two: NT in {16, 32, 64, 128, 256}
+  static constexpr int NBUF = (2 * MT * NT <= 512) ? 2 : 1;           // accumulator buffers of MT x NT columns
+  static constexpr int TMEM_COLS = NBUF * MT * NT < 32 ? 32 : NBUF * MT * NT;   // powers of two: NT in {16, 32, 64, 128, 256}
   static constexpr int TOTAL = NST * STAGE + 1024 + (2 * NST + 4) * 8 + 64;
   static_assert(NST >= 3, "ring too short");
   static_assert(TOTAL <= TC_SMEM_LIMIT, "shared memory overflow");
@@ -60,11 +66,12 @@ __device__ __forceinline__ void bf_mma(uint32_t tmem_d, uint64_t adesc, uint64_t
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 
-template <int NT>
-__global__ void __launch_bounds__(BF_THREADS, 1)
+template <int NT, int MT = 1>
+__global__ void __launch_bounds__(128 + 128 * MT, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__ CUtensorMap mw1,
                  const __grid_constant__ CUtensorMap mw2, const __grid_constant__ CUtensorMap mx, const BfP p) {
-  using S = BfSmem<NT>;
+  using S = BfSmem<NT, MT>;
+  constexpr int NBUF = S::NBUF;
   extern __shared__ unsigned char tc_smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::NST * S::STAGE);
@@ -86,7 +93,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant_
     w.n0 = (t - tile * p.ny) * NT;
     w.mat = 0;
     if (tile >= p.tiles[0]) { w.mat = 1; if (tile >= tiles01) { w.mat = 2; tile -= tiles01; } else tile -= p.tiles[0]; }
-    w.row0 = tile * TC_BM;
+    w.row0 = tile * (TC_BM * MT);
     w.kb0 = z * p.kblocks_per_split;
     w.nkb = p.kblocks_total - w.kb0;
     if (w.nkb > p.kblocks_per_split) w.nkb = p.kblocks_per_split;
@@ -95,7 +102,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant_
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S::NST; s++) { tc_mbar_init(&full[s], 1); tc_mbar_init(&empty[s], 1); }
-    for (int b = 0; b < 2; b++) { tc_mbar_init(&accum[b], 1); tc_mbar_init(&accfree[b], 4); }
+    for (int b = 0; b < 2; b++) { tc_mbar_init(&accum[b], 1); tc_mbar_init(&accfree[b], 4 * MT); }
     *abort_flag = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -161,12 +168,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant_
       bool ok = true;
       for (int it = blockIdx.x; it < p.n_items && ok; it += gridDim.x, n_it++) {
         const Item w = item_of(it);
-        const int buf = n_it & 1;
-        if (n_it >= 2) {                           // the buffer's previous accumulator must have been read out
-          if (!tc_mbar_wait(&accfree[buf], ((n_it >> 1) & 1u) ^ 1u, abort_flag)) break;
+        const int buf = n_it % NBUF, use = n_it / NBUF;   // use-th time this buffer is filled
+        if (use >= 1) {                            // the buffer's previous accumulator must have been read out
+          if (!tc_mbar_wait(&accfree[buf], (unsigned)(use & 1) ^ 1u, abort_flag)) break;
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         }
-        const uint32_t d = tmem_base + (uint32_t)(buf * NT);
+        const uint32_t d = tmem_base + (uint32_t)(buf * MT * NT);
         for (int i = 0; i < w.nkb; i++) {
           const int g = gb + i, s = g % S::NST;
           if (!tc_mbar_wait(&full[s], (g / S::NST) & 1u, abort_flag)) { ok = false; break; }
@@ -175,7 +182,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant_
           const uint64_t bdesc = tc_smem_desc(tc_smem_u32(smem + s * S::STAGE + S::W_BYTES));
 #pragma unroll
           for (int k = 0; k < BF_BK / 16; k++)     // UMMA K = 16 bf16 = 32 bytes = 2 descriptor units
-            bf_mma(d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (uint32_t)((i | k) != 0));
+#pragma unroll
+            for (int m = 0; m < MT; m++)           // the m-th 128 rows of the W stage: 16 KB = 1024 descriptor units further
+              bf_mma(d + (uint32_t)(m * NT), adesc + (uint64_t)(1024 * m + 2 * k), bdesc + (uint64_t)(2 * k), idesc, (uint32_t)((i | k) != 0));
           tc_commit(&empty[s]);
         }
         if (ok) tc_commit(&accum[buf]);
@@ -183,8 +192,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant_
       }
     }
   } else if (warp >= 4) {
-    // ===== epilogue: thread = weight row of the tile (TMEM lane)
-    const int q = warp & 3;
+    // ===== epilogue: thread = weight row of the tile (TMEM lane); warps 4-7 read the first 128 rows, 8-11 the second (MT = 2)
+    const int q = warp & 3, mt = (warp - 4) >> 2;
     const int r = q * 32 + lane;
     pdl_trigger();
     pdl_wait();                                    // the column scales come from the previous kernel
@@ -192,35 +201,53 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant_
     bool ok = true;
     for (int it = blockIdx.x; it < p.n_items; it += gridDim.x, n_it++) {
       const Item w = item_of(it);
-      const int buf = n_it & 1;
-      if (ok) ok = tc_mbar_wait(&accum[buf], (n_it >> 1) & 1u, abort_flag);
+      const int buf = n_it % NBUF, use = n_it / NBUF;
+      if (ok) ok = tc_mbar_wait(&accum[buf], (unsigned)(use & 1), abort_flag);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const int row = w.row0 + r;
+      const int row = w.row0 + mt * TC_BM + r;
       const bool row_ok = row < p.M[w.mat];
       float* outz = p.out + (size_t)(it % p.splits) * p.zstride + p.out_off[w.mat] + row;
-      const uint32_t tq = tmem_base + (uint32_t)(buf * NT) + ((uint32_t)(q * 32) << 16);
+      const uint32_t tq = tmem_base + (uint32_t)(buf * MT * NT + mt * NT) + ((uint32_t)(q * 32) << 16);
+      // whole tile inside the output: no per-element bounds checks, the store address advanced by one add per column
+      // (the checked form costs ~25 instructions per element: gemm_tc.cu has the measurement)
+      const bool full = row_ok && (w.n0 + NT <= p.N);
+      const bool cs_vec = p.colscale && ((reinterpret_cast<uintptr_t>(p.colscale) & 15) == 0);
       if (ok) {
 #pragma unroll 1
         for (int c = 0; c < NT; c += 32) {          // two 16-column loads in flight
-          uint32_t v0[16], v1[16];
-          tc_tmem_ld16(tq + (uint32_t)c, v0);
-          if (NT > 16) tc_tmem_ld16(tq + (uint32_t)(c + 16), v1);
-          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          uint32_t v[32];
+          tc_tmem_ld16(tq + (uint32_t)c, *reinterpret_cast<uint32_t(*)[16]>(v));
+          if (NT > 16) tc_tmem_ld16(tq + (uint32_t)(c + 16), *reinterpret_cast<uint32_t(*)[16]>(v + 16));
+          constexpr int NC = NT > 16 ? 32 : 16;
+          float sc[NC];
+          if (full && p.colscale) {
 #pragma unroll
-          for (int j = 0; j < 16; j++) {
-            const int n = w.n0 + c + j;
-            if (n < p.N && row_ok) {
-              float x = __uint_as_float(v0[j]);
-              if (p.colscale) x *= p.colscale[n];
-              outz[(size_t)n * p.ldo] = x;
+            for (int j = 0; j < NC; j += 4) {
+              if (cs_vec) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(p.colscale + w.n0 + c + j));
+                sc[j] = t.x; sc[j + 1] = t.y; sc[j + 2] = t.z; sc[j + 3] = t.w;
+              } else {
+#pragma unroll
+                for (int e = 0; e < 4; e++) sc[j + e] = __ldg(p.colscale + w.n0 + c + j + e);
+              }
             }
           }
-          if (NT > 16) {
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          if (full) {
+            float* o = outz + (size_t)(w.n0 + c) * p.ldo;
 #pragma unroll
-            for (int j = 0; j < 16; j++) {
-              const int n = w.n0 + c + 16 + j;
+            for (int j = 0; j < NC; j++) {
+              float x = __uint_as_float(v[j]);
+              if (p.colscale) x *= sc[j];
+              *o = x;
+              o += p.ldo;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < NC; j++) {
+              const int n = w.n0 + c + j;
               if (n < p.N && row_ok) {
-                float x = __uint_as_float(v1[j]);
+                float x = __uint_as_float(v[j]);
                 if (p.colscale) x *= p.colscale[n];
                 outz[(size_t)n * p.ldo] = x;
               }
@@ -252,25 +279,33 @@ bool gemm_bf16_ok(const BfArgs& a) {
 
 int gemm_bf16_pick_nt(int N) { return N <= 16 ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : (N <= 128 ? 128 : 256))); }
 
-template <int NT>
+template <int NT, int MT = 1>
 static int bf_launch_nt(cudaStream_t st, const CUtensorMap* mw, const CUtensorMap& mx, const BfP& p, dim3 grid, bool pdl) {
-  using S = BfSmem<NT>;
-  auto k = gemm_bf16_kernel<NT>;
+  using S = BfSmem<NT, MT>;
+  auto k = gemm_bf16_kernel<NT, MT>;
   THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
-  THA_CUDA_OK(launch(k, grid, dim3(BF_THREADS), (size_t)S::TOTAL, st, pdl, mw[0], mw[1], mw[2], mx, p));
+  THA_CUDA_OK(launch(k, grid, dim3(128 + 128 * MT), (size_t)S::TOTAL, st, pdl, mw[0], mw[1], mw[2], mx, p));
   return THA_STATUS_SUCCESS;
+}
+// 256-row work items for prompt-sized N (THA_BF16_MT=1 keeps 128-row items)
+static int bf_mt(int NT, int N) {
+  static int forced = -1;
+  if (forced < 0) { const char* v = getenv("THA_BF16_MT"); forced = (v && *v) ? atoi(v) : 0; }
+  if (forced == 1 || forced == 2) return NT == 256 ? forced : 1;
+  return (NT == 256 && N >= 512) ? 2 : 1;
 }
 
 int gemm_bf16_launch(cudaStream_t st, const BfArgs& a, bool pdl) {
   if (!gemm_bf16_ok(a)) return THA_STATUS_INVALID_ARG;
   const int NT = gemm_bf16_pick_nt(a.N);
+  const int MT = bf_mt(NT, a.N);
   CUtensorMap mw[3], mx;
   BfP p = {};
   int tiles = 0;
   for (int i = 0; i < 3; i++) {
     if (i < a.n_mats) {
-      THA_TRY_RC(tc_map(a.W[i], a.M[i], a.K, a.K, TC_BM, &mw[i], 2));
-      p.M[i] = a.M[i]; p.tiles[i] = ceil_div(a.M[i], TC_BM); p.out_off[i] = a.out_off[i];
+      THA_TRY_RC(tc_map(a.W[i], a.M[i], a.K, a.K, TC_BM * MT, &mw[i], 2));
+      p.M[i] = a.M[i]; p.tiles[i] = ceil_div(a.M[i], TC_BM * MT); p.out_off[i] = a.out_off[i];
     } else {
       mw[i] = mw[0];
     }
@@ -295,7 +330,7 @@ int gemm_bf16_launch(cudaStream_t st, const BfArgs& a, bool pdl) {
     case 32: return bf_launch_nt<32>(st, mw, mx, p, grid, pdl);
     case 64: return bf_launch_nt<64>(st, mw, mx, p, grid, pdl);
     case 128: return bf_launch_nt<128>(st, mw, mx, p, grid, pdl);
-    default: return bf_launch_nt<256>(st, mw, mx, p, grid, pdl);
+    default: return MT == 2 ? bf_launch_nt<256, 2>(st, mw, mx, p, grid, pdl) : bf_launch_nt<256>(st, mw, mx, p, grid, pdl);
   }
 }
 

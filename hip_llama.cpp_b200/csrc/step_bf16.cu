@@ -237,13 +237,17 @@ static int bf_grow(T** p, size_t* cap, size_t need, Workspace* ws) {
 }
 
 // Split-K factor of one matmul: whole waves of the 148 persistent CTAs, at least two 64-value k-blocks per split, a
-// charge per split for the partials its consumer sums (as step_tc.cu's planner).
+// charge per split for the partials its consumer sums (as step_tc.cu's planner).  Prompt-sized row counts (>= 512: 256-row
+// work items, gemm_bf16.cu bf_mt) are compute-bound, and there a split is expensive: it writes and re-reads R x M fp32
+// partials, 4 F / (K BW) of the matmul's own time (F ~ 1.3 PFLOP/s, BW ~ 6.5 TB/s: 0.2 at K = 4096) -- at 2048 rows the old
+// charge picked three splits for wq|wk|wv and the RoPE kernel read 303 MB per layer.
 static int bf_splits(int tiles, int K, int R) {
   const int kb = ceil_div(K, 64);
-  const int items1 = tiles * ceil_div(R, gemm_bf16_pick_nt(R));
+  const bool big = R >= 512;
+  const int items1 = (big ? ceil_div(tiles, 2) : tiles) * ceil_div(R, gemm_bf16_pick_nt(R));
   int best = 1;
   float best_score = -1.0f;
-  const float charge = 0.012f + 0.25f * (float)R / (float)K / 16.0f;
+  const float charge = big ? 800.0f / (float)K : 0.012f + 0.25f * (float)R / (float)K / 16.0f;
   for (int z = 1; z <= 16; z++) {
     if (z > 1 && kb / z < 2) break;
     if (ceil_div(kb, ceil_div(kb, z)) != z) continue;

@@ -360,7 +360,8 @@ def test_gemm_tf32x3_rejects_bad_shapes(L):
 
 
 @pytest.mark.parametrize("M,K,N", [(128, 64, 1), (300, 768, 5), (768, 2048, 16), (2304, 768, 40), (4096, 4096, 64),
-                                   (1000, 11008, 130), (4096, 4096, 300), (32000, 768, 256), (640, 4096, 2048)])
+                                   (1000, 11008, 130), (4096, 4096, 300), (32000, 768, 256), (640, 4096, 2048), (1100, 768, 600),
+                                   (4096, 4096, 1027)])   # the last three: 256-row work items (N >= 512), ragged in rows and columns
 def test_gemm_bf16_tensor_cores(M, K, N):
     """tha_gemm_bf16 (tcgen05.mma.kind::f16, both operands from TMA-written shared memory, double-buffered TMEM
     accumulator) against a float64 product of the same bf16 values: only fp32 accumulation order differs."""
