@@ -35,6 +35,7 @@ struct BfP {
   const float* colscale;
   int* error_flag;
   int splits, n_items;
+  uint16_t* swiglu_out; long long ld_swiglu;   // SWIGLU kernels
 };
 
 // MT = weight tiles of 128 rows per work item.  MT = 2 (prompt-sized N only): a CTA multiplies 256 weight rows by the
@@ -66,7 +67,9 @@ __device__ __forceinline__ void bf_mma(uint32_t tmem_d, uint64_t adesc, uint64_t
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 
-template <int NT, int MT = 1>
+// SWIGLU (MT = 2): the two 128-row halves of a work item are the SAME rows of two matrices (mw0 = w1, mw1 = w3); the read-out
+// combines the two accumulators of a row into silu(a) * c (run.cc:344-347 order) and stores it as bf16.
+template <int NT, int MT = 1, bool SWIGLU = false>
 __global__ void __launch_bounds__(128 + 128 * MT, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant__ CUtensorMap mw1,
                  const __grid_constant__ CUtensorMap mw2, const __grid_constant__ CUtensorMap mx, const BfP p) {
@@ -93,7 +96,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant_
     w.n0 = (t - tile * p.ny) * NT;
     w.mat = 0;
     if (tile >= p.tiles[0]) { w.mat = 1; if (tile >= tiles01) { w.mat = 2; tile -= tiles01; } else tile -= p.tiles[0]; }
-    w.row0 = tile * (TC_BM * MT);
+    w.row0 = tile * (SWIGLU ? TC_BM : TC_BM * MT);
     w.kb0 = z * p.kblocks_per_split;
     w.nkb = p.kblocks_total - w.kb0;
     if (w.nkb > p.kblocks_per_split) w.nkb = p.kblocks_per_split;
@@ -130,6 +133,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant_
       const bool stream_w = p.ny == 1;            // every weight tile is read once: do not let it displace the activations in L2
       int gb = 0;
       bool ok = true, first = true;
+      auto load_w = [&](unsigned char* dst, const CUtensorMap* mw, int kcol, int row0, uint64_t* bar) {
+        if (SWIGLU) {   // 128 rows of w1, then the same 128 rows of w3
+          tc_tma_2d(dst, &mw0, kcol, row0, bar);
+          tc_tma_2d(dst + TC_BM * 128, &mw1, kcol, row0, bar);
+        } else if (stream_w) tc_tma_2d_hint(dst, mw, kcol, row0, bar, pol_w);
+        else tc_tma_2d(dst, mw, kcol, row0, bar);
+      };
       for (int it = blockIdx.x; it < p.n_items && ok; it += gridDim.x) {
         const Item w = item_of(it);
         const CUtensorMap* mw = (w.mat == 0) ? &mw0 : (w.mat == 1 ? &mw1 : &mw2);
@@ -138,10 +148,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant_
           // weights never depend on the previous kernel: the first ring goes out before the dependency wait (the bytes may
           // land before the matching expect_tx -- the phase cannot complete until that arrival)
           const int pre = w.nkb < S::NST ? w.nkb : S::NST;
-          for (; i < pre; i++) {
-            if (stream_w) tc_tma_2d_hint(smem + i * S::STAGE, mw, (w.kb0 + i) * BF_BK, w.row0, &full[i], pol_w);
-            else tc_tma_2d(smem + i * S::STAGE, mw, (w.kb0 + i) * BF_BK, w.row0, &full[i]);
-          }
+          for (; i < pre; i++) load_w(smem + i * S::STAGE, mw, (w.kb0 + i) * BF_BK, w.row0, &full[i]);
           pdl_wait();
           for (int j = 0; j < pre; j++) {
             tc_mbar_expect_tx(&full[j], S::STAGE);
@@ -153,8 +160,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant_
           const int g = gb + i, s = g % S::NST;
           if (g >= S::NST && !tc_mbar_wait(&empty[s], ((g / S::NST) & 1u) ^ 1u, abort_flag)) { ok = false; break; }
           tc_mbar_expect_tx(&full[s], S::STAGE);
-          if (stream_w) tc_tma_2d_hint(smem + s * S::STAGE, mw, (w.kb0 + i) * BF_BK, w.row0, &full[s], pol_w);
-          else tc_tma_2d(smem + s * S::STAGE, mw, (w.kb0 + i) * BF_BK, w.row0, &full[s]);
+          load_w(smem + s * S::STAGE, mw, (w.kb0 + i) * BF_BK, w.row0, &full[s]);
           tc_tma_2d(smem + s * S::STAGE + S::W_BYTES, &mx, (w.kb0 + i) * BF_BK, w.n0, &full[s]);
         }
         gb += w.nkb;
@@ -204,6 +210,36 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mw0, const __grid_constant_
       const int buf = n_it % NBUF, use = n_it / NBUF;
       if (ok) ok = tc_mbar_wait(&accum[buf], (unsigned)(use & 1), abort_flag);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (SWIGLU) {
+        // both accumulators of this thread's row; warps 4-7 take the first half of the columns, 8-11 the second
+        const int srow = w.row0 + r;
+        const uint32_t ta = tmem_base + (uint32_t)(buf * MT * NT) + ((uint32_t)(q * 32) << 16);
+        if (ok && srow < p.M[0]) {
+          uint16_t* o = p.swiglu_out + (size_t)(w.n0 + mt * (NT / 2)) * p.ld_swiglu + srow;
+#pragma unroll 1
+          for (int c = mt * (NT / 2); c < (mt + 1) * (NT / 2); c += 16) {
+            uint32_t va[16], vc[16];
+            tc_tmem_ld16(ta + (uint32_t)c, va);
+            tc_tmem_ld16(ta + (uint32_t)(NT + c), vc);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+              if (w.n0 + c + j < p.N) {
+                float h = __uint_as_float(va[j]);
+                h *= (1.0f / (1.0f + expf(-h)));
+                h *= __uint_as_float(vc[j]);
+                const uint32_t u = __float_as_uint(h);   // round to nearest even, NaN stays NaN (step_bf16.cu f32_to_bf16)
+                *o = ((u & 0x7FFFFFFFu) > 0x7F800000u) ? (uint16_t)((u >> 16) | 0x40u) : (uint16_t)((u + 0x7FFFu + ((u >> 16) & 1u)) >> 16);
+              }
+              o += p.ld_swiglu;
+            }
+          }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) tc_mbar_arrive(&accfree[buf]);
+        continue;
+      }
       const int row = w.row0 + mt * TC_BM + r;
       const bool row_ok = row < p.M[w.mat];
       float* outz = p.out + (size_t)(it % p.splits) * p.zstride + p.out_off[w.mat] + row;
@@ -279,10 +315,10 @@ bool gemm_bf16_ok(const BfArgs& a) {
 
 int gemm_bf16_pick_nt(int N) { return N <= 16 ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : (N <= 128 ? 128 : 256))); }
 
-template <int NT, int MT = 1>
+template <int NT, int MT = 1, bool SWIGLU = false>
 static int bf_launch_nt(cudaStream_t st, const CUtensorMap* mw, const CUtensorMap& mx, const BfP& p, dim3 grid, bool pdl) {
   using S = BfSmem<NT, MT>;
-  auto k = gemm_bf16_kernel<NT, MT>;
+  auto k = gemm_bf16_kernel<NT, MT, SWIGLU>;
   THA_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
   THA_CUDA_OK(launch(k, grid, dim3(128 + 128 * MT), (size_t)S::TOTAL, st, pdl, mw[0], mw[1], mw[2], mx, p));
   return THA_STATUS_SUCCESS;
@@ -295,10 +331,18 @@ static int bf_mt(int NT, int N) {
   return (NT == 256 && N >= 512) ? 2 : 1;
 }
 
+bool gemm_bf16_swiglu_ok(const BfArgs& a) {
+  const int NT = gemm_bf16_pick_nt(a.N);
+  return a.swiglu_out && a.n_mats == 2 && a.M[0] == a.M[1] && a.splits <= 1 && NT == 256 && bf_mt(NT, a.N) == 2 && !a.colscale &&
+         (a.ld_swiglu % 1) == 0;
+}
+
 int gemm_bf16_launch(cudaStream_t st, const BfArgs& a, bool pdl) {
   if (!gemm_bf16_ok(a)) return THA_STATUS_INVALID_ARG;
   const int NT = gemm_bf16_pick_nt(a.N);
-  const int MT = bf_mt(NT, a.N);
+  const bool swiglu = a.swiglu_out != nullptr;
+  if (swiglu && !gemm_bf16_swiglu_ok(a)) return THA_STATUS_NOT_SUPPORTED;
+  const int MT = swiglu ? 1 : bf_mt(NT, a.N);   // SwiGLU: 128-row boxes of each of the two matrices (the kernel itself runs MT = 2)
   CUtensorMap mw[3], mx;
   BfP p = {};
   int tiles = 0;
@@ -311,6 +355,7 @@ int gemm_bf16_launch(cudaStream_t st, const BfArgs& a, bool pdl) {
     }
     tiles += p.tiles[i];
   }
+  if (swiglu) { tiles = p.tiles[0]; p.tiles[1] = 0; p.swiglu_out = a.swiglu_out; p.ld_swiglu = a.ld_swiglu; }   // an item = a pair of tiles
   THA_TRY_RC(tc_map(a.X, a.N, a.K, a.ldx, NT, &mx, 2));
   p.K = a.K; p.N = a.N;
   p.kblocks_total = ceil_div(a.K, BF_BK);
@@ -330,7 +375,8 @@ int gemm_bf16_launch(cudaStream_t st, const BfArgs& a, bool pdl) {
     case 32: return bf_launch_nt<32>(st, mw, mx, p, grid, pdl);
     case 64: return bf_launch_nt<64>(st, mw, mx, p, grid, pdl);
     case 128: return bf_launch_nt<128>(st, mw, mx, p, grid, pdl);
-    default: return MT == 2 ? bf_launch_nt<256, 2>(st, mw, mx, p, grid, pdl) : bf_launch_nt<256>(st, mw, mx, p, grid, pdl);
+    default: return swiglu ? bf_launch_nt<256, 2, true>(st, mw, mx, p, grid, pdl)
+                           : (MT == 2 ? bf_launch_nt<256, 2>(st, mw, mx, p, grid, pdl) : bf_launch_nt<256>(st, mw, mx, p, grid, pdl));
   }
 }
 

@@ -45,7 +45,12 @@ struct BfArgs {
   const uint16_t* X; int N; long long ldx;       // activations [N, ldx] bf16
   float* out; long long ldo; long long zstride; int splits;
   const float* colscale;
+  // SwiGLU in the read-out (prompt-sized N, two matrices w1 | w3 of equal height, no split-K): a work item multiplies 128 rows
+  // of w1 AND the same 128 rows of w3; its read-out writes silu(w1 x) * (w3 x), rounded to bf16, to swiglu_out[n * ld_swiglu + row]
+  // (the input of the w2 matmul) and `out` is not written at all.
+  uint16_t* swiglu_out; long long ld_swiglu;
 };
+bool gemm_bf16_swiglu_ok(const BfArgs& a);   // the launch can take the SwiGLU read-out
 bool gemm_bf16_ok(const BfArgs& a);
 int gemm_bf16_pick_nt(int N);
 int gemm_bf16_launch(cudaStream_t st, const BfArgs& a, bool pdl);

@@ -322,6 +322,11 @@ struct BfRows {
 };
 
 static int bf_attn_tc = -1;   // THA_ATTN_TC=0: keep the CUDA-core prefill attention (development aid)
+static int bf_swiglu_mode() {   // THA_BF16_SWIGLU=0: SwiGLU stays its own kernel behind the w1|w3 matmul
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("THA_BF16_SWIGLU"); v = (e && *e) ? atoi(e) : 1; }
+  return v;
+}
 static int bf_stage_mode() {   // THA_ATTN_STAGE=0: the tensor-core attention converts the fp32 cache rows itself (the first form)
   static int v = -1;
   if (v < 0) { const char* e = getenv("THA_ATTN_STAGE"); v = (e && *e) ? atoi(e) : 1; }
@@ -413,11 +418,21 @@ static int bf_issue_rows(cudaStream_t st, Workspace* ws, const tha_config_t& c, 
       THA_TRY_RC(mm(1, W, M, off, d, sc.xb, R, sc.part, d, (long long)R * d, pl.z_wo));
     }
     THA_TRY_RC(prep(R, pl.z_wo, (long long)R * d, nullptr, w.rms_ffn_weight + (size_t)l * d, nogather));
+    bool swiglu_fused = false;
     {
       const uint16_t* W[2] = {w.w1 + (size_t)l * d * hd, w.w3 + (size_t)l * d * hd};
       const int M[2] = {hd, hd}, off[2] = {0, hd};
-      THA_TRY_RC(mm(2, W, M, off, d, sc.xb, R, sc.part, ld_h, (long long)R * ld_h, pl.z_w13));
+      // prompt-sized row counts without split-K: SwiGLU in the matmul's read-out -- the fp32 w1|w3 outputs (180 MB per 7B layer at
+      // 2048 rows) are never written, the bf16 input of w2 comes straight out of TMEM
+      BfArgs a = {};
+      a.n_mats = 2; a.W[0] = W[0]; a.W[1] = W[1]; a.M[0] = hd; a.M[1] = hd; a.out_off[0] = 0; a.out_off[1] = hd;
+      a.K = d; a.X = sc.xb; a.N = R; a.ldx = d; a.out = sc.part; a.ldo = ld_h; a.zstride = (long long)R * ld_h; a.splits = pl.z_w13;
+      a.swiglu_out = sc.hb; a.ld_swiglu = hd;
+      swiglu_fused = bf_swiglu_mode() && gemm_bf16_swiglu_ok(a);
+      if (swiglu_fused) THA_TRY_RC(gemm_bf16_launch(st, a, pdl));
+      else THA_TRY_RC(mm(2, W, M, off, d, sc.xb, R, sc.part, ld_h, (long long)R * ld_h, pl.z_w13));
     }
+    if (!swiglu_fused)
     THA_CUDA_OK(launch(bf_round_kernel, dim3(ceil_div(hd / 4, 512), R), dim3(256), 0, st, pdl, (const float*)sc.part, (long long)ld_h, pl.z_w13,
                        (long long)R * ld_h, hd, io.pos, hd, sc.hb));
     {
