@@ -804,7 +804,7 @@ def main():
                 if args.model == "7b":
                     raise RuntimeError("7B CPU sample skipped (26 GB checkpoint on tmpfs)")
                 nth = 1 if args.quant == "f32" else host_cores()
-                v, done, kind, used, fast = cpu_reference(args, cfg, r["host_w"], 1, nth, 64, 1, args.cpu_seconds)
+                v, done, kind, used, fast = cpu_reference(args, cfg, r["host_w"], 1, nth, 256, 1, args.cpu_seconds)
                 line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": used, "kind": kind,
                                         "sample": f"1 sequence x {done} greedy decode positions from pos 0, oracle/_ref "
                                                   f"({'runq.c' if args.quant == 'q8' else 'run.cc'} unmodified, "
