@@ -539,7 +539,10 @@ int decode_step_bf16(cudaStream_t st, int B, const tha_config_t* cfg, const tha_
   // 1-2 slots: the weights stream through the fused GEMV kernels (5 launches per layer); more: tensor cores (Llama-2-7B:
   // 8 slots 12.4 ms per step on the GEMV path -- shared-memory-bound at 8 FMAs per weight -- against 4.0 ms at 64 slots on
   // the tensor cores).  Option "tc" = 1 forces the tensor cores, 0 the GEMV path up to 8 slots.
-  a.gemv = (((B <= 2 && tc_mode() != 1) || (B <= 8 && tc_mode() == 0)) && s->hb && !kv_pool_find(s->key_cache, nullptr)) ? 1 : 0;
+  // The tensor-core row pipeline at every slot count (7 launches per layer since RoPE and the output rounding moved into the
+  // attention kernel): Llama-2-7B at 1 / 2 slots 2.96 / 2.98 ms per step against the fused GEMV step's 3.53 / 4.08
+  // (tools/bf16_small.py); the GEMV step remains behind tha_set_option("tc", 0).
+  a.gemv = (B <= 8 && tc_mode() == 0 && s->hb && !kv_pool_find(s->key_cache, nullptr)) ? 1 : 0;
   if (a.gemv) {
     const int hs = cfg->dim / cfg->n_heads;
     THA_TRY(attn_fused_prepare(ws, B, cfg->n_heads, cfg->n_kv_heads, hs, cfg->seq_len));

@@ -108,6 +108,25 @@ def test_bf16_batched_ragged_vs_oracle(oracle, tmp_path, name, B):
     check_ratios(r, fl, f"bf16 {name} B={B}")
 
 
+@pytest.mark.parametrize("B", [1, 2, 7])
+def test_bf16_gemv_step_vs_oracle(oracle, tmp_path, B):
+    """tha_set_option("tc", 0): the fused GEMV step over bf16 rows (gemv_bf16.cu), no longer the default at any slot count."""
+    eng = load_pkg("engine")
+    lib = load_pkg("cabi").lib()
+    cfg, wb, path = bf16_model(tmp_path, "fusedA", MODELS["fusedA"])
+    m = oracle.open(path, bf16=True)
+    fm = floor_model(oracle, tmp_path, cfg, wb, "fusedA")
+    try:
+        lib.check(lib.c.tha_set_option(b"tc", 0))
+        e = eng.Engine(eng.DeviceWeightsBF16(cfg, wb), B)
+        r, _, fl = ragged_ratios(e, m, min(cfg.seq_len, 8), B, np.random.default_rng(B), floor=fm, sample=list(range(B)))
+        launches = e.last_step_launches()
+    finally:
+        lib.check(lib.c.tha_set_option(b"tc", -1))
+    assert launches == 5 * cfg.n_layers + 2, launches   # embed + 5 fused kernels per layer + classifier (final norm folded in)
+    check_ratios(r, fl, f"bf16 GEMV step B={B}")
+
+
 @pytest.mark.parametrize("B", [1, 40])
 def test_bf16_one_layer_agrees_to_fp32_noise(oracle, tmp_path, B):
     """One layer: five vectors are rounded per token, so a flipped rounding is rare and most rows must match to ~1e-7."""
