@@ -84,10 +84,11 @@ static int dual_sms() {
   return v;
 }
 struct SmBudgetScope { explicit SmBudgetScope(int n) { set_sm_budget(n); } ~SmBudgetScope() { set_sm_budget(0); } };
-static int dual_plan(Workspace* ws, int B, DualPlan* d) {
+// Not for paged states (the second branch addresses its slots through the same block table rows) and not with chained matmuls.
+static int dual_plan(Workspace* ws, int B, DualPlan* d, bool paged) {
   d->on = false; d->B0 = B; d->B1 = 0; d->ws2 = nullptr; d->st2 = nullptr; d->sms = 0;
   const int m = dual_min_rows();
-  if (m <= 0 || B < m || B < 2) return THA_STATUS_SUCCESS;
+  if (m <= 0 || B < m || B < 2 || paged || chain_mode()) return THA_STATUS_SUCCESS;
   THA_TRY_RC2(ws_ensure_dual(ws));
   d->on = true; d->sms = dual_sms(); d->B0 = (B + 1) / 2; d->B1 = B - d->B0; d->ws2 = ws->sibling; d->st2 = ws->side_stream;
   return THA_STATUS_SUCCESS;
@@ -277,7 +278,7 @@ int decode_step_f32(cudaStream_t st, int B, const tha_config_t* cfg, const tha_w
   }
   if (use_tc) {
     DualPlan dp;
-    THA_TRY(dual_plan(ws, B, &dp));
+    THA_TRY(dual_plan(ws, B, &dp, paged));
     SmBudgetScope budget(dp.sms);
     THA_TRY(step_tc_prepare(ws, cfg, dp.B0));
     if (dp.on) THA_TRY(step_tc_prepare(dp.ws2, cfg, dp.B1));
@@ -420,7 +421,7 @@ int decode_step_q8(cudaStream_t st, int B, const tha_config_t* cfg, const tha_we
   const int tcm = tc_mode();
   if (tcm != 0 && step_tc_q8_supported(cfg, B, gs)) {
     DualPlan dp;
-    THA_TRY(dual_plan(ws, B, &dp));
+    THA_TRY(dual_plan(ws, B, &dp, kv_pool_find(s->key_cache, nullptr)));
     SmBudgetScope budget(dp.sms);
     THA_TRY(step_tc_q8_prepare(ws, cfg, dp.B0, gs));
     if (dp.on) THA_TRY(step_tc_q8_prepare(dp.ws2, cfg, dp.B1, gs));

@@ -62,9 +62,11 @@ int tc_mode() {
 int* opt_tc() { return &g_tc; }
 static int g_dual = -2;
 int dual_min_rows() {
-  // off by default: measured slower (tools/r01/dual_sweep.sh) -- the matmuls are persistent full-GPU kernels, two branches
-  // only serialise smaller ones
-  if (g_dual == -2) { const char* v = getenv("THA_DUAL"); g_dual = (v && *v) ? atoi(v) : 0; }
+  // From 256 rows on a step is issued as two concurrent half-batch branches, each branch's matmuls planned for and limited to
+  // half of the SMs (forward.cu dual_plan): the two dependency chains overlap each other's latency.  Measured after the
+  // round-2 fixes: stories110M fp32 at 256 slots 0.811 -> 0.793 ms per step; at 128 / 64 slots it loses (0.645 -> 0.670,
+  // 0.541 -> 0.578: a chain of half the slots is barely shorter), hence the threshold.  THA_DUAL=0 / option "dual" 0: never.
+  if (g_dual == -2) { const char* v = getenv("THA_DUAL"); g_dual = (v && *v) ? atoi(v) : 256; }
   return g_dual;
 }
 int* opt_dual() { return &g_dual; }
