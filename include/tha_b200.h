@@ -83,7 +83,11 @@ typedef struct {
 int tha_version(void);
 const char* tha_last_error(void);       /* text of the last CUDA error seen by this library */
 int tha_set_option(const char* name, int value); /* "pdl", "graph", "mega" (0/1); "tc": -1 auto (tensor-core
-                                                    matmuls for more than 4 slots), 0 never, 1 whenever supported */
+                                                    matmuls for more than 4 slots), 0 never, 1 whenever supported;
+                                                    "dual": slots from which a step runs as two concurrent half-batch
+                                                    branches (default 256, 0 never); "ropefuse" (RoPE + KV write inside
+                                                    the attention kernel), "sample_resident", "chain", "skip": A/B and
+                                                    diagnostic switches, see DESIGN.md section 4 */
 
 /* ---- runtime shim: the only way the C++ host layer touches the CUDA runtime ---------
  * (reference: hipSetDevice / hipMalloc / hipMemcpy / hipHostMalloc / hipStreamCreate /
