@@ -127,6 +127,24 @@ def test_fp32_tensor_core_step_vs_oracle(oracle, tmp_path, name, B):
     assert flips == 0
 
 
+# the attention shape of Llama-2-70B (the reference's 70B drivers stream layers because the model does not fit
+# its GPUs; on a B200 a 70B Q8_0 / bf16 model is resident and only the grouped-query attention differs from 7B): 8 query heads
+# of 128 on one K/V head -- a CTA covers the whole group (J = 8), RoPE stays its own kernel
+GQA70 = dict(dim=1024, hidden_dim=2816, n_layers=2, n_heads=8, n_kv_heads=1, vocab_size=512, seq_len=72)
+
+
+@pytest.mark.parametrize("B,quant", [(3, False), (20, False), (20, True)])
+def test_llama2_70b_attention_shape_vs_oracle(oracle, tmp_path, B, quant):
+    cfg, w, v0, v2 = small_model_files(str(tmp_path), "gqa70", GQA70, std=0.04)
+    if quant:
+        e, m = engine_from_v2(v2, B), oracle.open(v2, quantized=True)
+        run_ragged(e, m, 24, B, np.random.default_rng(B), Q8_E2E_EPS, q8=True, stagger=5)
+    else:
+        e, m = engine_from_v0(v0, B), oracle.open(v0)
+        assert run_ragged(e, m, 40, B, np.random.default_rng(B), FP32_EPS, stagger=7 if B > 8 else 0) == 0
+    assert load_pkg("cabi").lib().c.tha_gemm_check_error() == 0
+
+
 @pytest.mark.parametrize("name,B,quant", [("fusedA", 16, False), ("fusedGQA", 33, False), ("fusedA", 12, True)])
 def test_rope_inside_attention_equals_separate_kernel(tmp_path, name, B, quant):
     """tha_set_option("ropefuse", 1) (default): RoPE + KV scatter of a decode step run inside the attention kernel.  The rotated
