@@ -575,6 +575,13 @@ def extra_records(args, device, peak):
         nb = step_bytes(cfg, dw.nbytes(), T + 5, 1)
         out["decode_7b_f32_B1_after_prefill"] = {"workload": "Llama-2-7B fp32 greedy decode, 1 slot, positions 2050..2057", "value": v, "unit": UNIT,
                                                  "ms_per_step": msd, "achieved_gbs": nb / msd / 1e6, "hbm_frac": nb / msd / 1e6 / peak}
+        del e
+        free()
+        e = eng.Engine(dw, 8, device=device, with_att=False)   # 8 slots x 2304 positions of fp32 KV: 19 GB
+        v, msd = resident_tok_s(e, cfg, 8, 2, 8, device, pos0=5)
+        nb = step_bytes(cfg, dw.nbytes(), 10, 8)
+        out["7b_f32_B8"] = {"workload": "Llama-2-7B fp32 greedy decode, 8 slots, positions 7..14 (tensor-core row pipeline from five slots on)",
+                            "value": v, "unit": UNIT, "ms_per_step": msd, "achieved_gbs": nb / msd / 1e6, "hbm_frac": nb / msd / 1e6 / peak}
         del e, dw
         free()
     except Exception as ex:
